@@ -1,0 +1,174 @@
+// ecoz2_cli.cpp -- `ecoz2 vq learn|quantize` command line on top of the C ABI.
+//
+// The reference's CLI is the Rust binary (src/main.rs:95-97 -> src/vq/mod.rs); there
+// is no Rust toolchain in this environment, so this C++ driver keeps the same
+// sub-commands, option names, defaults and file-resolution rules
+// (src/vq/mod.rs:39-96,151-216; src/utl/mod.rs:66-260) and calls the very same
+// three C entry points the Rust FFI shim binds (src/ecoz2_lib/mod.rs:96-122).
+#include <dirent.h>
+#include <sys/stat.h>
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <fstream>
+#include <sstream>
+#include <string>
+#include <vector>
+
+#include "ecoz2_vq_b200.h"
+
+namespace {
+
+bool ends_with(const std::string &s, const std::string &suf) {
+    return s.size() >= suf.size() && s.compare(s.size() - suf.size(), suf.size(), suf) == 0;
+}
+bool is_dir(const std::string &p) {
+    struct stat st;
+    return stat(p.c_str(), &st) == 0 && S_ISDIR(st.st_mode);
+}
+bool is_file(const std::string &p) {
+    struct stat st;
+    return stat(p.c_str(), &st) == 0 && S_ISREG(st.st_mode);
+}
+// src/utl/mod.rs:246-260 (WalkDir)
+void walk(const std::string &dir, const std::string &ext, std::vector<std::string> &out) {
+    DIR *d = opendir(dir.c_str());
+    if (!d) return;
+    while (dirent *e = readdir(d)) {
+        const std::string name = e->d_name;
+        if (name == "." || name == "..") continue;
+        const std::string path = dir + "/" + name;
+        if (is_dir(path)) walk(path, ext, out);
+        else if (is_file(path) && ends_with(path, ext)) out.push_back(path);
+    }
+    closedir(d);
+}
+// src/utl/mod.rs:146-196: rows `tt,class,selection`, '#' comments, header line
+bool files_from_csv(const std::string &csv, const std::string &tt, const std::string &cls,
+                    const std::string &subdir, const std::string &ext, const std::string *templ,
+                    std::vector<std::string> &out) {
+    std::ifstream in(csv);
+    if (!in) return false;
+    std::string line;
+    bool header = true;
+    while (std::getline(in, line)) {
+        if (line.empty() || line[0] == '#') continue;
+        if (header) { header = false; continue; }
+        std::stringstream ss(line);
+        std::string r_tt, r_class, r_sel;
+        std::getline(ss, r_tt, ',');
+        std::getline(ss, r_class, ',');
+        std::getline(ss, r_sel, ',');
+        while (!r_sel.empty() && (r_sel.back() == '\r' || r_sel.back() == ' ')) r_sel.pop_back();
+        if (tt != r_tt) continue;
+        if (!cls.empty() && cls != r_class) continue;
+        std::string f;
+        if (templ) {
+            f = *templ;
+            for (size_t p; (p = f.find("{class}")) != std::string::npos;) f.replace(p, 7, r_class);
+            for (size_t p; (p = f.find("{selection}")) != std::string::npos;) f.replace(p, 11, r_sel);
+        } else {
+            f = "data/" + subdir + "/" + r_class + "/" + r_sel + ext;
+        }
+        out.push_back(f);
+    }
+    return !out.empty();
+}
+// src/utl/mod.rs:66-83,201-243
+bool resolve(const std::vector<std::string> &given, const std::string &tt, const std::string &cls,
+             const std::string &subdir, const std::string &ext, const std::string *templ,
+             std::vector<std::string> &out) {
+    if (given.size() == 1 && ends_with(given[0], ".csv"))
+        return files_from_csv(given[0], tt, cls, subdir, ext, templ, out);
+    for (const std::string &g : given) {
+        if (is_dir(g)) walk(g, ext, out);
+        else if (is_file(g) && ends_with(g, ext)) out.push_back(g);
+    }
+    std::sort(out.begin(), out.end());
+    return !out.empty();
+}
+
+void step(void *, int M, double avg, double sigma, double inertia) {
+    // src/ecoz2_lib/mod.rs:59-63
+    printf("   Ecoz2ObserverRef.step: M=%d avg_distortion=%g sigma=%g inertia=%g\n", M, avg, sigma,
+           inertia);
+}
+
+int usage() {
+    fprintf(stderr,
+            "usage:\n"
+            "  ecoz2 vq learn [-B <codebook> | -P <P>] [-e <eps>=0.05] [--class-name <class>]\n"
+            "                 --predictors <files|dirs|one.csv>...\n"
+            "  ecoz2 vq quantize --codebook <cb> --predictors <files|dirs|one.csv>...\n"
+            "                 [--predictors-dir-template <t>] [--tt TRAIN|TEST] [--class-name <c>] [-s]\n"
+            "environment: ECOZ2_VQ_GPUS=all|0,1,..  ECOZ2_VQ_MAX_M=<stop size>  ECOZ2_VQ_MIN_DISTS=0|1\n");
+    return 2;
+}
+
+}  // namespace
+
+int main(int argc, char **argv) {
+    if (argc < 3 || strcmp(argv[1], "vq") != 0) return usage();
+    const std::string cmd = argv[2];
+    std::string base_cb, class_name, codebook, tt, templ = "data/predictors";
+    bool have_class = false, show = false, have_templ = false;
+    int P = -1;
+    double eps = 0.05;
+    std::vector<std::string> predictors;
+    for (int i = 3; i < argc; i++) {
+        const std::string a = argv[i];
+        auto next = [&](std::string &dst) { if (i + 1 < argc) dst = argv[++i]; };
+        std::string v;
+        if (a == "-B" || a == "--base-codebook") next(base_cb);
+        else if (a == "-P" || a == "--prediction-order") { next(v); P = atoi(v.c_str()); }
+        else if (a == "-e" || a == "--epsilon") { next(v); eps = atof(v.c_str()); }
+        else if (a == "--class-name") { next(class_name); have_class = true; }
+        else if (a == "--codebook") next(codebook);
+        else if (a == "--tt") next(tt);
+        else if (a == "--predictors-dir-template") { next(templ); have_templ = true; }
+        else if (a == "-s" || a == "--show-filenames") show = true;
+        else if (a == "--exp-key") next(v);  // comet logging is out of scope (needs network)
+        else if (a == "--predictors") {
+            while (i + 1 < argc && argv[i + 1][0] != '-') predictors.push_back(argv[++i]);
+        } else return usage();
+    }
+    (void) have_templ;
+    std::vector<std::string> files;
+    if (cmd == "learn") {
+        if (!base_cb.empty() && P >= 0) {
+            printf("Only one of base codebook or prediction order expected\n");
+            return 1;
+        }
+        if (base_cb.empty() && P < 0) return usage();
+        if (!resolve(predictors, "TRAIN", have_class ? class_name : "", "predictors", ".prd", nullptr,
+                     files)) {
+            printf("No predictors given\n");
+            return 1;
+        }
+        const std::string cls = have_class ? class_name : "_";
+        printf("vq_learn: base_codebook_opt=%s prediction_order=%d, epsilon=%g codebook_class_name=%s "
+               "predictor_filenames: %zu\n",
+               base_cb.empty() ? "None" : base_cb.c_str(), P, eps, cls.c_str(), files.size());
+        std::vector<const char *> ptrs;
+        for (auto &f : files) ptrs.push_back(f.c_str());
+        if (!base_cb.empty())
+            return ecoz2_vq_learn_using_base_codebook(&base_cb[0], eps, ptrs.data(), (int) ptrs.size(),
+                                                      nullptr, step);
+        return ecoz2_vq_learn(P, eps, cls.c_str(), ptrs.data(), (int) ptrs.size(), nullptr, step);
+    }
+    if (cmd == "quantize") {
+        if (codebook.empty() || predictors.empty()) return usage();
+        if (!resolve(predictors, tt, have_class ? class_name : "", "", ".prd", &templ, files)) {
+            printf("No predictors given\n");
+            return 1;
+        }
+        printf("number of predictor files: %zu\n", files.size());
+        printf("nom_raas = %s\n", codebook.c_str());
+        std::vector<const char *> ptrs;
+        for (auto &f : files) ptrs.push_back(f.c_str());
+        return ecoz2_vq_quantize(codebook.c_str(), ptrs.data(), (int) ptrs.size(), show ? 1 : 0);
+    }
+    return usage();
+}

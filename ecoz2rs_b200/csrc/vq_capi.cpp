@@ -1,0 +1,461 @@
+// vq_capi.cpp -- the extern "C" surface declared in include/ecoz2_vq_b200.h.
+//
+// PART 1: drop-in `ecoz2_vq_learn`, `ecoz2_vq_learn_using_base_codebook`,
+//         `ecoz2_vq_quantize` (reference ecoz2/src/ecoz2/ecoz2.c:109-164 ->
+//         ecoz2/src/vq/vq_learn.c, vq_learn.i:161-247, vq_quantize.c:13-111).
+// PART 2: thin forwards to vqb200::Engine.
+#include <cfloat>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "vq_engine.h"
+#include "vq_io.h"
+#include "vq_nccl.h"
+
+using vqb200::Engine;
+
+struct ecoz2b200_engine {
+    Engine impl;
+    ecoz2b200_engine(const int *d, int n, int P, int M) : impl(d, n, P, M) {}
+};
+
+namespace {
+
+double wall_s() {
+    using namespace std::chrono;
+    return duration<double>(steady_clock::now().time_since_epoch()).count();
+}
+
+// ECOZ2_VQ_GPUS: unset/"" -> device 0; "all" -> every visible device; else "0,2,3"
+std::vector<int> devices_from_env() {
+    std::vector<int> devs;
+    const char *env = getenv("ECOZ2_VQ_GPUS");
+    int visible = ecoz2b200_device_count();
+    if (!env || !*env) {
+        devs.push_back(0);
+    } else if (strcmp(env, "all") == 0) {
+        for (int i = 0; i < visible; i++) devs.push_back(i);
+    } else {
+        std::string s(env);
+        size_t pos = 0;
+        while (pos < s.size()) {
+            size_t comma = s.find(',', pos);
+            if (comma == std::string::npos) comma = s.size();
+            if (comma > pos) devs.push_back(atoi(s.substr(pos, comma - pos).c_str()));
+            pos = comma + 1;
+        }
+    }
+    if (devs.empty()) devs.push_back(0);
+    return devs;
+}
+
+int env_int(const char *name, int dflt) {
+    const char *v = getenv(name);
+    return (v && *v) ? atoi(v) : dflt;
+}
+
+struct LearnCtx {
+    Engine *eng;
+    std::string class_name, prefix, cb_filename;
+    vqb200::Report *report;
+    void *target;
+    vq_learn_callback_t callback;
+    double DDprv = DBL_MAX;
+    long tot_vecs;
+    bool min_dists;
+    double t_stage;
+    int P;
+    int rc = 0;
+};
+
+void on_pass(void *c, int M, int pass, double DD, double secs, int empty_cells) {
+    LearnCtx *ctx = (LearnCtx *) c;
+    // same progress lines as the reference (vq_learn_par.c:44,114-123)
+    printf("(%d)", pass);
+    printf("\n      (pass=%d) min processing took %.2fs\n", pass, secs);
+    printf("\tDP=%g\tDDprv=%g\tDD=%g\t(DDprv-DD)/DD=%g\r", DD / ctx->tot_vecs, ctx->DDprv, DD,
+           (ctx->DDprv - DD) / DD);
+    fflush(stdout);
+    if (empty_cells > 0)  // review_cells, vq_learn.i:108-119
+        printf("\nWARN: review_cells: %d empty cell(s) for codebook size %d)\n", empty_cells, M);
+    ctx->DDprv = DD;
+}
+
+void on_stage(void *c, const ecoz2b200_stage_info *info) {
+    LearnCtx *ctx = (LearnCtx *) c;
+    printf("\n      (%d-cbook) processing took %.2fs\n", info->M, wall_s() - ctx->t_stage);
+    // codebook saved with reflections (vq_learn_par.c:133)
+    if (vqb200::cbook_save(ctx->cb_filename.c_str(), ctx->class_name.c_str(), info->reflections,
+                           info->M, ctx->P))
+        fprintf(stderr, "error saving codebook %s\n", ctx->cb_filename.c_str());
+    if (ctx->callback)
+        ctx->callback(ctx->target, info->M, info->avgDistortion, info->sigma, info->inertia);
+    std::vector<int32_t> cw;
+    std::vector<double> md;
+    if (ctx->min_dists) {
+        cw.resize((size_t) ctx->tot_vecs);
+        md.resize((size_t) ctx->tot_vecs);
+        if (ctx->eng->last_assignment(cw.data(), md.data())) ctx->rc = ECOZ2B200_ERR_CUDA;
+    }
+    ctx->report->cbook(ctx->cb_filename, info->passes, info->avgDistortion, info->sigma,
+                       info->inertia, info->M, info->cardd, info->discel,
+                       ctx->min_dists ? cw.data() : nullptr, ctx->min_dists ? md.data() : nullptr);
+    printf("\n");
+    // name of the next size (vq_learn_par.c:152-154)
+    char buf[64];
+    snprintf(buf, sizeof buf, "_M_%04d.cbook", info->M * 2);
+    ctx->cb_filename = ctx->prefix + buf;
+    ctx->t_stage = wall_s();
+}
+
+// vq_learn_ (vq_learn.i:161-247)
+int learn_files(const double *base_refl, int base_K, int P, double eps, const char *class_name,
+                const char *files[], int num_files, void *target, vq_learn_callback_t callback) {
+    const std::string class_dir = std::string("data/codebooks/") + class_name;
+    vqb200::mk_dirs(class_dir);
+    char epsbuf[64];
+    snprintf(epsbuf, sizeof epsbuf, "%g", eps);
+    const std::string prefix = class_dir + "/eps_" + epsbuf;
+
+    // predictor headers first: total size fixes the GPU shard boundaries
+    std::vector<int> Ts(num_files);
+    long tot_vecs = 0;
+    for (int i = 0; i < num_files; i++) {
+        int p = 0, t = 0;
+        if (vqb200::prd_info(files[i], &p, &t, nullptr) || p != P) {
+            fprintf(stderr, "error loading predictor %s\n", files[i]);
+            return 2;
+        }
+        Ts[i] = t;
+        tot_vecs += t;
+    }
+    const int stop_M = env_int("ECOZ2_VQ_MAX_M", 4096);
+    std::vector<int> devs = devices_from_env();
+    std::unique_ptr<ecoz2b200_engine> h(
+        new ecoz2b200_engine(devs.data(), (int) devs.size(), P, stop_M < 2 ? 2 : stop_M));
+    Engine &eng = h->impl;
+    if (!eng.ok()) return ECOZ2B200_ERR_CUDA;
+    if (getenv("ECOZ2_VQ_MODE") && strcmp(getenv("ECOZ2_VQ_MODE"), "fp64") == 0)
+        eng.set_mode(ECOZ2B200_MODE_FP64);
+    int rc = eng.frames_reserve(tot_vecs);
+    if (rc) return ECOZ2B200_ERR_CUDA;
+    {
+        std::vector<double> buf;
+        for (int i = 0; i < num_files; i++) {
+            const size_t vals = (size_t) Ts[i] * (P + 1);
+            if (buf.size() < vals) buf.resize(vals);
+            if (vqb200::prd_read(files[i], buf.data(), (long) vals)) {
+                fprintf(stderr, "error loading predictor %s\n", files[i]);
+                return 2;
+            }
+            rc = eng.frames_append_host(buf.data(), Ts[i]);
+            if (rc) return ECOZ2B200_ERR_CUDA;
+            // the staging vector is reused: the (pageable) copy above is complete on return
+            if (eng.frames_count() < 0) return 1;
+        }
+    }
+    rc = eng.frames_commit();
+    if (rc) return ECOZ2B200_ERR_CUDA;
+    printf("%ld training vectors (ε=%g)\n", tot_vecs, eps);
+
+    if (base_refl) {  // initial_codebook_from_base, vq_learn.i:75-82
+        if (2 * base_K > (stop_M < 2 ? 2 : stop_M)) {
+            fprintf(stderr, "ERROR: maximum codebook size reached: %d", stop_M);
+            return 1;
+        }
+        rc = eng.codebook_set_reflections(base_refl, base_K);
+        if (!rc) rc = eng.codebook_grow();
+    } else {
+        rc = eng.codebook_initial();
+    }
+    if (rc) return rc == ECOZ2B200_ERR_ARG ? 1 : ECOZ2B200_ERR_CUDA;
+
+    vqb200::Report report;
+    report.prepare(prefix + ".rpt", tot_vecs, eps);
+
+    LearnCtx ctx;
+    ctx.eng = &eng;
+    ctx.class_name = class_name;
+    ctx.prefix = prefix;
+    ctx.report = &report;
+    ctx.target = target;
+    ctx.callback = callback;
+    ctx.tot_vecs = tot_vecs;
+    ctx.min_dists = env_int("ECOZ2_VQ_MIN_DISTS", 1) != 0;
+    ctx.P = P;
+    char buf[64];
+    snprintf(buf, sizeof buf, "_M_%04d.cbook", eng.codebook_size());
+    ctx.cb_filename = prefix + buf;
+    printf("%s\n", ctx.cb_filename.c_str());
+    printf("\n(devices=%d, B200 CUDA path)\n", (int) devs.size());
+    const double t0 = wall_s();
+    ctx.t_stage = t0;
+    rc = eng.learn(eps, stop_M, on_stage, on_pass, &ctx);
+    printf("\nprocessing took %.2fs\n", wall_s() - t0);
+    report.close();
+    if (rc) return ECOZ2B200_ERR_CUDA;
+    return ctx.rc;
+}
+
+}  // namespace
+
+// ============================================================================ PART 1
+extern "C" {
+
+int ecoz2_vq_learn(int prediction_order, double epsilon, const char *codebook_class_name,
+                   const char *predictor_filenames[], int num_predictors, void *callback_target,
+                   vq_learn_callback_t callback) {
+    // vq_learn.c:17-19
+    printf("\nCodebook generation:\n\n");
+    printf("prediction_order=%d class='%s'  epsilon=%g\n\n", prediction_order, codebook_class_name,
+           epsilon);
+    return learn_files(nullptr, 0, prediction_order, epsilon, codebook_class_name,
+                       predictor_filenames, num_predictors, callback_target, callback);
+}
+
+int ecoz2_vq_learn_using_base_codebook(char *base_codebook, double epsilon,
+                                       const char *predictor_filenames[], int num_predictors,
+                                       void *callback_target, vq_learn_callback_t callback) {
+    // vq_learn.c:44-60
+    int P = 0, M = 0;
+    char cls[vqb200::kMaxClassNameLen];
+    if (vqb200::cbook_info(base_codebook, &P, &M, cls)) {
+        fprintf(stderr, "error loading base codebook %s.\n", base_codebook);
+        return 2;
+    }
+    std::vector<double> refl((size_t) M * (P + 1));
+    if (vqb200::cbook_read(base_codebook, refl.data(), (long) refl.size())) {
+        fprintf(stderr, "error loading base codebook %s.\n", base_codebook);
+        return 2;
+    }
+    printf("\nCodebook generation:\n\n");
+    printf("base_codebook: %s  num_vecs=%d prediction_order=%d class='%s'  epsilon=%g\n\n",
+           base_codebook, M, P, cls, epsilon);
+    return learn_files(refl.data(), M, P, epsilon, cls, predictor_filenames, num_predictors,
+                       callback_target, callback);
+}
+
+int ecoz2_vq_quantize(const char *nom_raas, const char *predictor_filenames[], int num_predictors,
+                      int show_filenames) {
+    // vq_quantize.c:13-111
+    int P = 0, M = 0;
+    char cb_class[vqb200::kMaxClassNameLen];
+    if (vqb200::cbook_info(nom_raas, &P, &M, cb_class)) {
+        printf("error loading codebook (%d).\n", vqb200::cb_errnum_last);
+        return 1;
+    }
+    std::vector<double> refl((size_t) M * (P + 1));
+    if (vqb200::cbook_read(nom_raas, refl.data(), (long) refl.size())) {
+        printf("error loading codebook (%d).\n", vqb200::cb_errnum_last);
+        return 1;
+    }
+    std::vector<int> devs = devices_from_env();
+    std::unique_ptr<ecoz2b200_engine> h(
+        new ecoz2b200_engine(devs.data(), (int) devs.size(), P, M < 2 ? 2 : M));
+    Engine &eng = h->impl;
+    if (!eng.ok()) return ECOZ2B200_ERR_CUDA;
+    if (eng.codebook_set_reflections(refl.data(), M)) return ECOZ2B200_ERR_CUDA;
+    printf("%s: %d symbols\n", nom_raas, M);
+
+    int num_seqs = 0;
+    double ddprm_total = 0;
+    std::vector<double> buf;
+    std::vector<uint16_t> seq;
+    for (int i = 0; i < num_predictors; i++) {
+        const char *prd_filename = predictor_filenames[i];
+        int p = 0, T = 0;
+        if (vqb200::prd_info(prd_filename, &p, &T, nullptr) || p != P) {
+            fprintf(stderr, "%s: error loading predictor.\n", prd_filename);
+            return 2;
+        }
+        const size_t vals = (size_t) T * (P + 1);
+        if (buf.size() < vals) buf.resize(vals);
+        if (vqb200::prd_read(prd_filename, buf.data(), (long) vals)) {
+            fprintf(stderr, "%s: error loading predictor.\n", prd_filename);
+            return 2;
+        }
+        if (seq.size() < (size_t) T) seq.resize((size_t) T);
+        double ddprm = 0;
+        if (eng.quantize_host(buf.data(), T, seq.data(), &ddprm)) return ECOZ2B200_ERR_CUDA;
+        ddprm_total += ddprm;
+        num_seqs++;
+
+        const std::string className = vqb200::get_class_name(prd_filename);
+        const char *base_dir = "sequences";
+        if (strstr(prd_filename, "TRAIN/")) base_dir = "sequences/TRAIN";
+        else if (strstr(prd_filename, "TEST/")) base_dir = "sequences/TEST";
+        const std::string base_dir_with_m = std::string(base_dir) + "/M" + std::to_string(M);
+        const std::string seq_filename =
+            vqb200::get_output_filename(prd_filename, base_dir_with_m, ".seq");
+        if (vqb200::seq_save(seq_filename.c_str(), className.c_str(), seq.data(), T, M))
+            printf("error saving sequence\n");
+        if (show_filenames)
+            printf("\n%s className='%s' (%1.4g) = ", seq_filename.c_str(), className.c_str(), ddprm);
+        if (className.empty()) printf("\nWARN%s NO className", seq_filename.c_str());
+        if (show_filenames) {  // seq_show, symbol.c:84-98
+            const int lim = 40, mrg = 10;
+            printf("<(%d): ", T);
+            const char *comma = "";
+            for (int t = 0; t < T; t++) {
+                if (T > lim && t >= mrg && t < T - mrg) {
+                    printf(", ...");
+                    t = T - mrg;
+                }
+                printf("%s%d", comma, seq[t]);
+                comma = ", ";
+            }
+            printf(">\n");
+        }
+    }
+    if (num_seqs > 0)
+        printf("\ntotal: %d sequences; total  average distortion = %f\n", num_seqs,
+               ddprm_total / num_seqs);
+    return 0;
+}
+
+// ============================================================================ PART 2
+const char *ecoz2b200_version(void) { return "ecoz2_vq_b200 0.1 (sm_100a)"; }
+const char *ecoz2b200_last_error(void) { return vqb200::get_last_error(); }
+
+int ecoz2b200_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) {
+        cudaGetLastError();
+        return 0;
+    }
+    return n;
+}
+
+ecoz2b200_engine *ecoz2b200_create(const int *devices, int num_devices, int P, int max_M) {
+    ecoz2b200_engine *e = new ecoz2b200_engine(devices, num_devices, P, max_M);
+    if (!e->impl.ok()) {
+        delete e;
+        return nullptr;
+    }
+    return e;
+}
+void ecoz2b200_destroy(ecoz2b200_engine *e) { delete e; }
+
+#define ENG(e)                                  \
+    if (!(e)) return ECOZ2B200_ERR_ARG;         \
+    Engine &eng = (e)->impl
+
+int ecoz2b200_set_mode(ecoz2b200_engine *e, int mode) { ENG(e); return eng.set_mode(mode); }
+int ecoz2b200_set_recheck_kappa(ecoz2b200_engine *e, double k) { ENG(e); return eng.set_kappa(k); }
+
+int ecoz2b200_nccl_unique_id(unsigned char id_out[128]) {
+    const vqb200::NcclApi *api = vqb200::nccl_api();
+    if (!api) return ECOZ2B200_ERR_NCCL;
+    vqb200::NcclUniqueId id;
+    if (api->GetUniqueId(&id) != 0) return ECOZ2B200_ERR_NCCL;
+    memcpy(id_out, id.internal, 128);
+    return ECOZ2B200_OK;
+}
+int ecoz2b200_comm_init(ecoz2b200_engine *e, const unsigned char id[128], int rank, int world) {
+    ENG(e);
+    return eng.comm_init(id, rank, world);
+}
+
+int ecoz2b200_frames_clear(ecoz2b200_engine *e) { ENG(e); return eng.frames_clear(); }
+int ecoz2b200_frames_reserve(ecoz2b200_engine *e, long total) { ENG(e); return eng.frames_reserve(total); }
+int ecoz2b200_frames_append_host(ecoz2b200_engine *e, const double *x, long n) {
+    ENG(e);
+    return eng.frames_append_host(x, n);
+}
+int ecoz2b200_frames_append_device(ecoz2b200_engine *e, const double *x, long n) {
+    ENG(e);
+    return eng.frames_append_device(x, n);
+}
+int ecoz2b200_frames_commit(ecoz2b200_engine *e) { ENG(e); return eng.frames_commit(); }
+long ecoz2b200_frames_count(const ecoz2b200_engine *e) { return e ? e->impl.frames_count() : -1; }
+
+int ecoz2b200_codebook_initial(ecoz2b200_engine *e) { ENG(e); return eng.codebook_initial(); }
+int ecoz2b200_codebook_set_reflections(ecoz2b200_engine *e, const double *r, int K) {
+    ENG(e);
+    return eng.codebook_set_reflections(r, K);
+}
+int ecoz2b200_codebook_set_raas(ecoz2b200_engine *e, const double *r, int K) {
+    ENG(e);
+    return eng.codebook_set_raas(r, K);
+}
+int ecoz2b200_codebook_grow(ecoz2b200_engine *e) {
+    ENG(e);
+    int rc = eng.codebook_grow();
+    return rc;
+}
+int ecoz2b200_codebook_size(const ecoz2b200_engine *e) { return e ? e->impl.codebook_size() : -1; }
+int ecoz2b200_codebook_get(ecoz2b200_engine *e, double *refl, double *raas) {
+    ENG(e);
+    return eng.codebook_get(refl, raas);
+}
+
+int ecoz2b200_assign(ecoz2b200_engine *e, int32_t *idx, double *ddmin, long *nre) {
+    ENG(e);
+    return eng.assign(idx, ddmin, nre);
+}
+int ecoz2b200_kmeans_pass(ecoz2b200_engine *e, double *cells, int32_t *cardd, double *discel,
+                          double *DD) {
+    ENG(e);
+    return eng.kmeans_pass(cells, cardd, discel, DD);
+}
+int ecoz2b200_sigma(ecoz2b200_engine *e, double avg, double *out) { ENG(e); return eng.sigma(avg, out); }
+int ecoz2b200_inertia(ecoz2b200_engine *e, double *out) { ENG(e); return eng.inertia(out); }
+int ecoz2b200_last_assignment(ecoz2b200_engine *e, int32_t *idx, double *md) {
+    ENG(e);
+    return eng.last_assignment(idx, md);
+}
+int ecoz2b200_learn(ecoz2b200_engine *e, double eps, int stop_M, ecoz2b200_stage_cb on_stage,
+                    ecoz2b200_pass_cb on_pass_cb, void *ctx) {
+    ENG(e);
+    return eng.learn(eps, stop_M, on_stage, on_pass_cb, ctx);
+}
+int ecoz2b200_quantize_host(ecoz2b200_engine *e, const double *x, long T, uint16_t *seq,
+                            double *avg) {
+    ENG(e);
+    return eng.quantize_host(x, T, seq, avg);
+}
+int ecoz2b200_quantize_resident(ecoz2b200_engine *e, uint16_t *seq, double *avg) {
+    ENG(e);
+    return eng.quantize_resident(seq, avg);
+}
+
+int ecoz2b200_counters_reset(ecoz2b200_engine *e) { ENG(e); eng.counters_reset(); return 0; }
+int ecoz2b200_counters_get(ecoz2b200_engine *e, ecoz2b200_counters *out) {
+    ENG(e);
+    if (!out) return ECOZ2B200_ERR_ARG;
+    const vqb200::Counters &c = eng.counters();
+    out->assign_ms = c.assign_ms;
+    out->accumulate_ms = c.accumulate_ms;
+    out->update_ms = c.update_ms;
+    out->allreduce_ms = c.allreduce_ms;
+    out->kernel_launches = c.kernel_launches;
+    out->evals = c.evals;
+    out->rechecked = c.rechecked;
+    return ECOZ2B200_OK;
+}
+
+int ecoz2b200_prd_info(const char *path, int *P, int *T, char class_name[96]) {
+    return vqb200::prd_info(path, P, T, class_name) ? ECOZ2B200_ERR_IO : ECOZ2B200_OK;
+}
+int ecoz2b200_prd_read(const char *path, double *out, long cap) {
+    return vqb200::prd_read(path, out, cap) ? ECOZ2B200_ERR_IO : ECOZ2B200_OK;
+}
+int ecoz2b200_cbook_save(const char *path, const char *cls, const double *refl, int M, int P) {
+    return vqb200::cbook_save(path, cls, refl, M, P) ? ECOZ2B200_ERR_IO : ECOZ2B200_OK;
+}
+int ecoz2b200_cbook_info(const char *path, int *P, int *M, char class_name[96]) {
+    return vqb200::cbook_info(path, P, M, class_name) ? ECOZ2B200_ERR_IO : ECOZ2B200_OK;
+}
+int ecoz2b200_cbook_read(const char *path, double *out, long cap) {
+    return vqb200::cbook_read(path, out, cap) ? ECOZ2B200_ERR_IO : ECOZ2B200_OK;
+}
+int ecoz2b200_seq_save(const char *path, const char *cls, const uint16_t *seq, int T, int M) {
+    return vqb200::seq_save(path, cls, seq, T, M) ? ECOZ2B200_ERR_IO : ECOZ2B200_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,775 @@
+// vq_engine.cu -- device shards, the k-means pass and the LBG driver.
+//
+// Control flow restated from the reference (ecoz2/src/vq/vq_learn_par.c:42-163);
+// the arithmetic lives in vq_kernels.cu.  One host thread drives every local GPU
+// through its own stream; all cross-GPU / cross-rank traffic is ONE
+// ncclAllReduce(sum, f64) of the packed cell buffer per pass.
+#include "vq_engine.h"
+
+#include <cfloat>
+#include <chrono>
+#include <cmath>
+#include <cstdio>
+#include <cstring>
+
+#include "vq_nccl.h"
+
+namespace vqb200 {
+
+static thread_local std::string g_last_error;
+void set_last_error(const std::string &msg) {
+    g_last_error = msg;
+    fprintf(stderr, "ecoz2_vq_b200: %s\n", msg.c_str());
+}
+const char *get_last_error() { return g_last_error.c_str(); }
+
+#define CUDA_TRY(expr)                                                                     \
+    do {                                                                                   \
+        cudaError_t _e = (expr);                                                           \
+        if (_e != cudaSuccess) {                                                           \
+            set_last_error(std::string(#expr) + ": " + cudaGetErrorString(_e));            \
+            return ECOZ2B200_ERR_CUDA;                                                     \
+        }                                                                                  \
+    } while (0)
+
+#define NCCL_TRY(api, expr)                                                                \
+    do {                                                                                   \
+        int _r = (expr);                                                                   \
+        if (_r != 0) {                                                                     \
+            set_last_error(std::string(#expr) + ": " + (api)->GetErrorString(_r));         \
+            return ECOZ2B200_ERR_NCCL;                                                     \
+        }                                                                                  \
+    } while (0)
+
+static double now_s() {
+    using namespace std::chrono;
+    return duration<double>(steady_clock::now().time_since_epoch()).count();
+}
+
+// ---------------------------------------------------------------------------------
+Engine::Engine(const int *devices, int num_devices, int P, int max_M)
+    : P_(P), D_(P + 1), max_M_(max_M) {
+    if (P < 1 || D_ > kMaxD || max_M < 2 || max_M > 65536 || num_devices < 1) {
+        set_last_error("ecoz2b200_create: bad argument");
+        return;
+    }
+    int visible = 0;
+    if (cudaGetDeviceCount(&visible) != cudaSuccess || visible == 0) {
+        set_last_error("no CUDA device: the B200 VQ path has no CPU fallback");
+        return;
+    }
+    shards_.resize(num_devices);
+    qbuf_.resize(num_devices);
+    const PackedLayout L{max_M_, D_};
+    const size_t cb = sizeof(double) * (size_t) max_M_ * D_;
+    const int K32 = (max_M_ + kTileF32 - 1) / kTileF32 * kTileF32;
+    const int K64 = (max_M_ + kTileF64 - 1) / kTileF64 * kTileF64;
+    for (int i = 0; i < num_devices; i++) {
+        Shard &s = shards_[i];
+        s.device = devices ? devices[i] : i;
+        if (s.device < 0 || s.device >= visible) {
+            set_last_error("ecoz2b200_create: device ordinal out of range");
+            return;
+        }
+        auto chk = [&](cudaError_t e, const char *what) {
+            if (e != cudaSuccess) {
+                set_last_error(std::string(what) + ": " + cudaGetErrorString(e));
+                return false;
+            }
+            return true;
+        };
+        if (!chk(cudaSetDevice(s.device), "cudaSetDevice")) return;
+        cudaDeviceProp prop;
+        if (!chk(cudaGetDeviceProperties(&prop, s.device), "cudaGetDeviceProperties")) return;
+        s.num_sms = prop.multiProcessorCount;
+        if (!chk(cudaStreamCreateWithFlags(&s.stream, cudaStreamNonBlocking), "cudaStreamCreate")) return;
+        for (auto &e : s.ev)
+            if (!chk(cudaEventCreate(&e), "cudaEventCreate")) return;
+        if (!chk(cudaMalloc(&s.refl, cb), "cudaMalloc refl")) return;
+        if (!chk(cudaMalloc(&s.raas, cb), "cudaMalloc raas")) return;
+        if (!chk(cudaMalloc(&s.w32, sizeof(float) * (size_t) K32 * D_), "cudaMalloc w32")) return;
+        if (!chk(cudaMalloc(&s.w64, sizeof(double) * (size_t) K64 * D_), "cudaMalloc w64")) return;
+        if (!chk(cudaMalloc(&s.w1max, 16), "cudaMalloc w1max")) return;
+        if (!chk(cudaMalloc(&s.packed, sizeof(double) * L.size()), "cudaMalloc packed")) return;
+        if (!chk(cudaMalloc(&s.scalars, sizeof(double) * 8), "cudaMalloc scalars")) return;
+        if (!chk(cudaMalloc(&s.flag_count, 16), "cudaMalloc flag_count")) return;
+        cudaMemset(s.refl, 0, cb);
+        cudaMemset(s.raas, 0, cb);
+    }
+    ok_ = true;
+}
+
+Engine::~Engine() {
+    const NcclApi *api = (local_comms_ready_ || multi_process_) ? nccl_api() : nullptr;
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        cudaSetDevice(s.device);
+        if (s.stream) cudaStreamSynchronize(s.stream);
+        if (s.comm && api) api->CommDestroy(s.comm);
+        cudaFree(s.x64); cudaFree(s.x32); cudaFree(s.idx); cudaFree(s.idx_tmp); cudaFree(s.seq);
+        cudaFree(s.mindist); cudaFree(s.flag_list); cudaFree(s.flag_count);
+        cudaFree(s.refl); cudaFree(s.raas); cudaFree(s.w32); cudaFree(s.w64); cudaFree(s.w1max);
+        cudaFree(s.packed); cudaFree(s.scalars);
+        QBuf &q = qbuf_[i];
+        cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.flag_list); cudaFree(q.seq);
+        for (auto &e : s.ev)
+            if (e) cudaEventDestroy(e);
+        if (s.stream) cudaStreamDestroy(s.stream);
+    }
+}
+
+int Engine::set_mode(int mode) {
+    if (mode != ECOZ2B200_MODE_FP32 && mode != ECOZ2B200_MODE_FP64) {
+        set_last_error("set_mode: mode not available in this build");
+        return ECOZ2B200_ERR_ARG;
+    }
+    mode_ = mode;
+    return ECOZ2B200_OK;
+}
+int Engine::set_kappa(double kappa) {
+    if (!(kappa >= 0)) return ECOZ2B200_ERR_ARG;
+    kappa_ = kappa;
+    return ECOZ2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------
+// communicators
+int Engine::comm_init(const unsigned char id[128], int rank, int world) {
+    if (shards_.size() != 1) {
+        set_last_error("comm_init: multi-process mode needs exactly one device per engine");
+        return ECOZ2B200_ERR_ARG;
+    }
+    if (world < 1 || rank < 0 || rank >= world) return ECOZ2B200_ERR_ARG;
+    rank_ = rank;
+    world_ = world;
+    if (world == 1) return ECOZ2B200_OK;
+    const NcclApi *api = nccl_api();
+    if (!api) return ECOZ2B200_ERR_NCCL;
+    NcclUniqueId uid;
+    memcpy(uid.internal, id, 128);
+    CUDA_TRY(cudaSetDevice(shards_[0].device));
+    NCCL_TRY(api, api->CommInitRank(&shards_[0].comm, world, uid, rank));
+    multi_process_ = true;
+    return ECOZ2B200_OK;
+}
+
+int Engine::ensure_local_comms() {
+    if (shards_.size() == 1 || local_comms_ready_) return ECOZ2B200_OK;
+    const NcclApi *api = nccl_api();
+    if (!api) return ECOZ2B200_ERR_NCCL;
+    std::vector<void *> comms(shards_.size());
+    std::vector<int> devs(shards_.size());
+    for (size_t i = 0; i < shards_.size(); i++) devs[i] = shards_[i].device;
+    NCCL_TRY(api, api->CommInitAll(comms.data(), (int) shards_.size(), devs.data()));
+    for (size_t i = 0; i < shards_.size(); i++) shards_[i].comm = comms[i];
+    local_comms_ready_ = true;
+    return ECOZ2B200_OK;
+}
+
+// in-place sum over every shard of every rank of packed[first .. first+count)
+static int allreduce_range(std::vector<Shard> &shards, long first, long count, bool needed) {
+    if (!needed) return ECOZ2B200_OK;
+    const NcclApi *api = nccl_api();
+    if (!api) return ECOZ2B200_ERR_NCCL;
+    NCCL_TRY(api, api->GroupStart());
+    for (Shard &s : shards) {
+        int r = api->AllReduce(s.packed + first, s.packed + first, (size_t) count, kNcclFloat64,
+                               kNcclSum, s.comm, s.stream);
+        if (r != 0) {
+            api->GroupEnd();
+            set_last_error(std::string("ncclAllReduce: ") + api->GetErrorString(r));
+            return ECOZ2B200_ERR_NCCL;
+        }
+    }
+    NCCL_TRY(api, api->GroupEnd());
+    return ECOZ2B200_OK;
+}
+
+int Engine::sync_all() {
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+    }
+    return ECOZ2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------
+// frames
+int Engine::ensure_capacity(Shard &s, long n) {
+    if (n <= s.cap) return ECOZ2B200_OK;
+    CUDA_TRY(cudaSetDevice(s.device));
+    CUDA_TRY(cudaStreamSynchronize(s.stream));
+    double *nx64 = nullptr;
+    CUDA_TRY(cudaMalloc(&nx64, sizeof(double) * (size_t) n * D_));
+    if (s.x64 && s.n > 0)
+        CUDA_TRY(cudaMemcpy(nx64, s.x64, sizeof(double) * (size_t) s.n * D_, cudaMemcpyDeviceToDevice));
+    cudaFree(s.x64); s.x64 = nx64;
+    cudaFree(s.x32); cudaFree(s.idx); cudaFree(s.idx_tmp); cudaFree(s.seq); cudaFree(s.mindist);
+    cudaFree(s.flag_list);
+    s.x32 = nullptr; s.idx = s.idx_tmp = s.flag_list = nullptr; s.seq = nullptr; s.mindist = nullptr;
+    CUDA_TRY(cudaMalloc(&s.x32, sizeof(float) * (size_t) n * D_));
+    CUDA_TRY(cudaMalloc(&s.idx, sizeof(int32_t) * (size_t) n));
+    CUDA_TRY(cudaMalloc(&s.idx_tmp, sizeof(int32_t) * (size_t) n));
+    CUDA_TRY(cudaMalloc(&s.seq, sizeof(uint16_t) * (size_t) n));
+    CUDA_TRY(cudaMalloc(&s.mindist, sizeof(double) * (size_t) n));
+    CUDA_TRY(cudaMalloc(&s.flag_list, sizeof(int32_t) * (size_t) n));
+    s.cap = n;
+    return ECOZ2B200_OK;
+}
+
+int Engine::frames_clear() {
+    for (Shard &s : shards_) s.n = 0;
+    n_total_ = n_global_ = 0;
+    reserved_ = per_shard_ = appended_ = 0;
+    committed_ = false;
+    return ECOZ2B200_OK;
+}
+
+int Engine::frames_reserve(long total) {
+    if (total < 0) return ECOZ2B200_ERR_ARG;
+    if (appended_ > 0) {
+        set_last_error("frames_reserve: call before the first append");
+        return ECOZ2B200_ERR_ARG;
+    }
+    const long S = (long) shards_.size();
+    reserved_ = total;
+    per_shard_ = (total + S - 1) / S;
+    for (long i = 0; i < S; i++) {
+        shards_[i].frame_offset = i * per_shard_;
+        int rc = ensure_capacity(shards_[i], per_shard_ > 0 ? per_shard_ : 1);
+        if (rc) return rc;
+    }
+    return ECOZ2B200_OK;
+}
+
+int Engine::append_block(const double *x, long n, bool device_src) {
+    if (n < 0 || (n > 0 && !x)) return ECOZ2B200_ERR_ARG;
+    if (committed_) {  // appending after a commit starts a new frame set
+        set_last_error("frames_append: frames already committed; call frames_clear first");
+        return ECOZ2B200_ERR_ARG;
+    }
+    const cudaMemcpyKind kind = device_src ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice;
+    if (reserved_ == 0) {
+        if (shards_.size() != 1) {
+            set_last_error("frames_append: call frames_reserve first when using several devices");
+            return ECOZ2B200_ERR_ARG;
+        }
+        Shard &s = shards_[0];
+        if (s.n + n > s.cap) {
+            long want = s.cap * 2 > s.n + n ? s.cap * 2 : s.n + n;
+            int rc = ensure_capacity(s, want);
+            if (rc) return rc;
+        }
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaMemcpyAsync(s.x64 + (size_t) s.n * D_, x, sizeof(double) * (size_t) n * D_, kind, s.stream));
+        s.n += n;
+        appended_ += n;
+        return ECOZ2B200_OK;
+    }
+    if (appended_ + n > reserved_) {
+        set_last_error("frames_append: more frames than reserved");
+        return ECOZ2B200_ERR_ARG;
+    }
+    long pos = appended_, left = n;
+    const double *src = x;
+    while (left > 0) {
+        const long si = pos / per_shard_;
+        Shard &s = shards_[si];
+        const long room = s.frame_offset + per_shard_ - pos;
+        const long take = left < room ? left : room;
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaMemcpyAsync(s.x64 + (size_t) (pos - s.frame_offset) * D_, src,
+                                 sizeof(double) * (size_t) take * D_, kind, s.stream));
+        s.n = pos - s.frame_offset + take;
+        pos += take; left -= take; src += (size_t) take * D_;
+    }
+    appended_ += n;
+    return ECOZ2B200_OK;
+}
+
+int Engine::frames_append_host(const double *x, long n) { return append_block(x, n, false); }
+int Engine::frames_append_device(const double *x_dev, long n) {
+    // the source lives on devices[0]; make sure work queued there by the caller's
+    // (default / torch) stream is complete before our stream reads it
+    cudaSetDevice(shards_[0].device);
+    cudaDeviceSynchronize();
+    return append_block(x_dev, n, true);
+}
+
+int Engine::frames_commit() {
+    n_total_ = 0;
+    long off = 0;
+    for (Shard &s : shards_) {
+        if (reserved_ == 0) s.frame_offset = off;
+        off += s.n;
+        n_total_ += s.n;
+        if (s.n > 0) {
+            CUDA_TRY(cudaSetDevice(s.device));
+            launch_convert_frames(s.x64, s.x32, s.n, D_, s.stream);
+            ctr_.kernel_launches++;
+        }
+    }
+    n_global_ = n_total_;
+    if (multi_process_) {
+        Shard &s = shards_[0];
+        CUDA_TRY(cudaSetDevice(s.device));
+        const double mine = (double) n_total_;
+        CUDA_TRY(cudaMemcpyAsync(s.packed, &mine, sizeof(double), cudaMemcpyHostToDevice, s.stream));
+        int rc = allreduce_range(shards_, 0, 1, true);
+        if (rc) return rc;
+        double all = 0;
+        CUDA_TRY(cudaMemcpyAsync(&all, s.packed, sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+        n_global_ = (long) (all + 0.5);
+    } else if (shards_.size() > 1) {
+        int rc = ensure_local_comms();
+        if (rc) return rc;
+    }
+    int rc = sync_all();
+    if (rc) return rc;
+    CUDA_TRY(cudaGetLastError());
+    committed_ = true;
+    return ECOZ2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------
+// codebook
+int Engine::stage_codebook() {
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        launch_prepare_codebook(s.raas, K_, D_, s.w32, s.w64, s.w1max, s.stream);
+        ctr_.kernel_launches++;
+    }
+    return ECOZ2B200_OK;
+}
+
+int Engine::codebook_initial() {
+    // vq_learn.i:31-44 : reflections [_, -0.5, 0...] and [_, +0.5, 0...]
+    std::vector<double> r((size_t) 2 * D_, 0.0);
+    r[1] = -0.5;
+    r[D_ + 1] = 0.5;
+    return codebook_set_reflections(r.data(), 2);
+}
+
+int Engine::codebook_set_reflections(const double *refl, int K) {
+    if (!refl || K < 1 || K > max_M_) {
+        set_last_error("codebook_set_reflections: bad size");
+        return ECOZ2B200_ERR_ARG;
+    }
+    K_ = K;
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaMemcpyAsync(s.refl, refl, sizeof(double) * (size_t) K * D_, cudaMemcpyHostToDevice, s.stream));
+        launch_refl_to_raas(s.refl, s.raas, K, D_, s.stream);
+        ctr_.kernel_launches++;
+    }
+    int rc = stage_codebook();
+    if (rc) return rc;
+    return sync_all();
+}
+
+int Engine::codebook_set_raas(const double *raas, int K) {
+    if (!raas || K < 1 || K > max_M_) return ECOZ2B200_ERR_ARG;
+    K_ = K;
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaMemsetAsync(s.refl, 0, sizeof(double) * (size_t) K * D_, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(s.raas, raas, sizeof(double) * (size_t) K * D_, cudaMemcpyHostToDevice, s.stream));
+    }
+    int rc = stage_codebook();
+    if (rc) return rc;
+    return sync_all();
+}
+
+int Engine::codebook_grow() {
+    if (K_ < 1 || 2 * K_ > max_M_) {
+        set_last_error("codebook_grow: maximum codebook size reached");  // vq_learn.i:48-51
+        return ECOZ2B200_ERR_ARG;
+    }
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        launch_grow(s.refl, s.raas, K_, D_, s.stream);
+        ctr_.kernel_launches += 2;
+    }
+    K_ *= 2;
+    return stage_codebook();
+}
+
+int Engine::codebook_get(double *refl_out, double *raas_out) {
+    Shard &s = shards_[0];
+    CUDA_TRY(cudaSetDevice(s.device));
+    const size_t bytes = sizeof(double) * (size_t) K_ * D_;
+    if (refl_out) CUDA_TRY(cudaMemcpyAsync(refl_out, s.refl, bytes, cudaMemcpyDeviceToHost, s.stream));
+    if (raas_out) CUDA_TRY(cudaMemcpyAsync(raas_out, s.raas, bytes, cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaStreamSynchronize(s.stream));
+    return ECOZ2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------
+// (a) the search on one shard: FP32 main pass + FP64 re-evaluation of the frames
+// inside the FP32 ambiguity bound, or the all-FP64 verification mode.
+void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
+                    int32_t *flag_list) {
+    if (n <= 0) return;
+    if (mode_ == ECOZ2B200_MODE_FP64) {
+        launch_assign_f64(x64, n, D_, s.w64, K_, nullptr, nullptr, idx, s.num_sms, s.stream);
+        ctr_.kernel_launches += 1;
+    } else {
+        // |error| of one FP32 distortion <= kappa * 2^-24 * rx[0] * sum|w|; two values compared
+        const float gap_scale = (float) (2.0 * kappa_ * ldexp(1.0, -24));
+        cudaMemsetAsync(s.flag_count, 0, sizeof(int32_t), s.stream);
+        launch_assign_f32(x32, n, D_, s.w32, K_, s.w1max, gap_scale, idx, flag_list, s.flag_count,
+                          s.num_sms, s.stream);
+        launch_assign_f64(x64, n, D_, s.w64, K_, flag_list, s.flag_count, idx, s.num_sms, s.stream);
+        ctr_.kernel_launches += 2;
+    }
+    ctr_.evals += (double) n * K_;
+}
+
+int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked) {
+    if (!committed_ || K_ < 1) {
+        set_last_error("assign: frames not committed or no codebook");
+        return ECOZ2B200_ERR_ARG;
+    }
+    const PackedLayout L{K_, D_};
+    long rechecked = 0;
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        search(s, s.x64, s.x32, s.n, s.idx, s.flag_list);
+        CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
+        launch_accumulate(s.x64, s.idx, s.n, D_, s.raas, K_, s.packed, s.mindist, nullptr, false,
+                          s.num_sms, s.stream);
+        ctr_.kernel_launches++;
+    }
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        if (idx_out)
+            CUDA_TRY(cudaMemcpyAsync(idx_out + s.frame_offset, s.idx, sizeof(int32_t) * (size_t) s.n,
+                                     cudaMemcpyDeviceToHost, s.stream));
+        if (ddmin_out)
+            CUDA_TRY(cudaMemcpyAsync(ddmin_out + s.frame_offset, s.mindist, sizeof(double) * (size_t) s.n,
+                                     cudaMemcpyDeviceToHost, s.stream));
+        int32_t fc = 0;
+        if (mode_ != ECOZ2B200_MODE_FP64)
+            CUDA_TRY(cudaMemcpyAsync(&fc, s.flag_count, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+        rechecked += fc;
+    }
+    CUDA_TRY(cudaGetLastError());
+    if (ddmin_out)
+        for (long v = 0; v < n_total_; v++) ddmin_out[v] += 1.0;  // raw distortion (before the -1)
+    ctr_.rechecked += rechecked;
+    if (num_rechecked) *num_rechecked = rechecked;
+    return ECOZ2B200_OK;
+}
+
+void Engine::harvest_times(bool with_cells) {
+    // max over shards of every phase (events were recorded on each shard's stream)
+    double a = 0, b = 0, c = 0, d = 0;
+    for (Shard &s : shards_) {
+        cudaSetDevice(s.device);
+        float ms = 0;
+        if (cudaEventElapsedTime(&ms, s.ev[0], s.ev[1]) == cudaSuccess && ms > a) a = ms;
+        if (cudaEventElapsedTime(&ms, s.ev[1], s.ev[2]) == cudaSuccess && ms > b) b = ms;
+        if (with_cells) {
+            if (cudaEventElapsedTime(&ms, s.ev[2], s.ev[3]) == cudaSuccess && ms > c) c = ms;
+            if (cudaEventElapsedTime(&ms, s.ev[3], s.ev[4]) == cudaSuccess && ms > d) d = ms;
+        }
+    }
+    ctr_.assign_ms += a;
+    ctr_.accumulate_ms += b;
+    ctr_.allreduce_ms += c;
+    ctr_.update_ms += d;
+}
+
+// One k-means pass (vq_learn_par.c:50-125).
+int Engine::kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_out, double *DD_out) {
+    if (!committed_ || K_ < 1) {
+        set_last_error("kmeans_pass: frames not committed or no codebook");
+        return ECOZ2B200_ERR_ARG;
+    }
+    const PackedLayout L{K_, D_};
+    const bool reduce = shards_.size() > 1 || multi_process_;
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
+        CUDA_TRY(cudaMemsetAsync(s.packed, 0, sizeof(double) * L.size(), s.stream));
+        search(s, s.x64, s.x32, s.n, s.idx, s.flag_list);
+        CUDA_TRY(cudaEventRecord(s.ev[1], s.stream));
+        launch_accumulate(s.x64, s.idx, s.n, D_, s.raas, K_, s.packed, s.mindist, nullptr, true,
+                          s.num_sms, s.stream);
+        ctr_.kernel_launches++;
+        CUDA_TRY(cudaEventRecord(s.ev[2], s.stream));
+    }
+    int rc = allreduce_range(shards_, 0, L.size(), reduce);
+    if (rc) return rc;
+    h_packed_.resize((size_t) L.size());
+    {
+        Shard &s = shards_[0];
+        CUDA_TRY(cudaSetDevice(s.device));
+        // tail [counts | discel | DD | inertia] always; raw cell sums only on request
+        CUDA_TRY(cudaMemcpyAsync(h_packed_.data() + L.counts(), s.packed + L.counts(),
+                                 sizeof(double) * (size_t) (L.size() - L.counts()),
+                                 cudaMemcpyDeviceToHost, s.stream));
+        if (cells_out)
+            CUDA_TRY(cudaMemcpyAsync(cells_out, s.packed, sizeof(double) * (size_t) K_ * D_,
+                                     cudaMemcpyDeviceToHost, s.stream));
+    }
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaEventRecord(s.ev[3], s.stream));
+        launch_centroids(s.packed, K_, D_, s.refl, s.raas, s.stream);
+        launch_prepare_codebook(s.raas, K_, D_, s.w32, s.w64, s.w1max, s.stream);
+        ctr_.kernel_launches += 2;
+        CUDA_TRY(cudaEventRecord(s.ev[4], s.stream));
+    }
+    rc = sync_all();
+    if (rc) return rc;
+    CUDA_TRY(cudaGetLastError());
+    harvest_times(true);
+    if (mode_ != ECOZ2B200_MODE_FP64) {
+        for (Shard &s : shards_) {
+            int32_t fc = 0;
+            cudaSetDevice(s.device);
+            cudaMemcpy(&fc, s.flag_count, sizeof(int32_t), cudaMemcpyDeviceToHost);
+            ctr_.rechecked += fc;
+        }
+    }
+    if (cardd_out)
+        for (int i = 0; i < K_; i++) cardd_out[i] = (int32_t) (h_packed_[L.counts() + i] + 0.5);
+    if (discel_out) memcpy(discel_out, h_packed_.data() + L.discel(), sizeof(double) * K_);
+    if (DD_out) *DD_out = h_packed_[L.dd()];
+    return ECOZ2B200_OK;
+}
+
+int Engine::sigma(double avgDistortion, double *sigma_out) {
+    // sigma.c:12-29 on the post-update raas and the errPred-normalised cells
+    Shard &s = shards_[0];
+    CUDA_TRY(cudaSetDevice(s.device));
+    CUDA_TRY(cudaMemsetAsync(s.scalars, 0, sizeof(double), s.stream));
+    launch_sigma_sum(s.raas, s.packed, K_, D_, s.scalars, s.stream);
+    ctr_.kernel_launches++;
+    double sum = 0;
+    CUDA_TRY(cudaMemcpyAsync(&sum, s.scalars, sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+    CUDA_TRY(cudaStreamSynchronize(s.stream));
+    CUDA_TRY(cudaGetLastError());
+    const double dpc = sum / ((double) K_ * (double) (K_ - 1));
+    if (sigma_out) *sigma_out = dpc / avgDistortion;
+    return ECOZ2B200_OK;
+}
+
+int Engine::inertia(double *inertia_out) {
+    // inertia.c:10-31: sum_v min_i distortion^2 with the current (post-update) codebook.
+    // min of dd^2 == (min dd)^2 because dd >= 0 for gain-normalised frames.
+    const PackedLayout L{K_, D_};
+    const bool reduce = shards_.size() > 1 || multi_process_;
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
+        CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
+        search(s, s.x64, s.x32, s.n, s.idx_tmp, s.flag_list);
+        CUDA_TRY(cudaEventRecord(s.ev[1], s.stream));
+        launch_accumulate(s.x64, s.idx_tmp, s.n, D_, s.raas, K_, s.packed, nullptr, nullptr, false,
+                          s.num_sms, s.stream);
+        ctr_.kernel_launches++;
+        CUDA_TRY(cudaEventRecord(s.ev[2], s.stream));
+    }
+    int rc = allreduce_range(shards_, L.dd(), 2, reduce);
+    if (rc) return rc;
+    double tail[2] = {0, 0};
+    Shard &s0 = shards_[0];
+    CUDA_TRY(cudaSetDevice(s0.device));
+    CUDA_TRY(cudaMemcpyAsync(tail, s0.packed + L.dd(), 2 * sizeof(double), cudaMemcpyDeviceToHost, s0.stream));
+    rc = sync_all();
+    if (rc) return rc;
+    CUDA_TRY(cudaGetLastError());
+    harvest_times(false);
+    if (inertia_out) *inertia_out = tail[1];
+    return ECOZ2B200_OK;
+}
+
+int Engine::last_assignment(int32_t *idx_out, double *mindist_out) {
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        if (idx_out)
+            CUDA_TRY(cudaMemcpyAsync(idx_out + s.frame_offset, s.idx, sizeof(int32_t) * (size_t) s.n,
+                                     cudaMemcpyDeviceToHost, s.stream));
+        if (mindist_out)
+            CUDA_TRY(cudaMemcpyAsync(mindist_out + s.frame_offset, s.mindist, sizeof(double) * (size_t) s.n,
+                                     cudaMemcpyDeviceToHost, s.stream));
+    }
+    return sync_all();
+}
+
+// ---------------------------------------------------------------------------------
+// LBG driver (vq_learn_par.c:42-163):
+//   - DDprv starts at DBL_MAX and is NOT reset when the codebook grows;
+//   - a size is done when pass > 0 && (DDprv - DD) / DD < eps;
+//   - the centroid update runs before the convergence test: the saved codebook is
+//     post-update, the reported average distortion pre-update;
+//   - sigma / inertia use the post-update codebook.
+int Engine::learn(double eps, int stop_M, ecoz2b200_stage_cb on_stage, ecoz2b200_pass_cb on_pass,
+                  void *ctx) {
+    if (!committed_ || K_ < 1 || n_global_ < 1) {
+        set_last_error("learn: frames not committed or no codebook");
+        return ECOZ2B200_ERR_ARG;
+    }
+    if (stop_M > max_M_) stop_M = max_M_;
+    std::vector<double> h_refl, h_raas, h_discel;
+    std::vector<int32_t> h_cardd;
+    double DDprv = DBL_MAX;
+    int pass = 0;
+    double t_stage = now_s();
+    Counters at_stage_start = ctr_;
+    for (;;) {
+        const double t_pass = now_s();
+        double DD = 0;
+        h_cardd.resize(K_);
+        h_discel.resize(K_);
+        int rc = kmeans_pass(nullptr, h_cardd.data(), h_discel.data(), &DD);
+        if (rc) return rc;
+        const double avg = DD / (double) n_global_;
+        if (on_pass) {
+            int empty = 0;
+            for (int i = 0; i < K_; i++) empty += h_cardd[i] == 0;
+            on_pass(ctx, K_, pass, DD, now_s() - t_pass, empty);
+        }
+
+        if (pass > 0 && ((DDprv - DD) / DD) < eps) {
+            h_refl.resize((size_t) K_ * D_);
+            h_raas.resize((size_t) K_ * D_);
+            rc = codebook_get(h_refl.data(), h_raas.data());
+            if (rc) return rc;
+            double sig = 0, inert = 0;
+            rc = sigma(avg, &sig);
+            if (rc) return rc;
+            rc = inertia(&inert);
+            if (rc) return rc;
+            ecoz2b200_stage_info info;
+            info.M = K_;
+            info.passes = pass + 1;
+            info.avgDistortion = avg;
+            info.sigma = sig;
+            info.inertia = inert;
+            info.reflections = h_refl.data();
+            info.raas = h_raas.data();
+            info.cardd = h_cardd.data();
+            info.discel = h_discel.data();
+            info.stage_seconds = now_s() - t_stage;
+            info.assign_ms = ctr_.assign_ms - at_stage_start.assign_ms;
+            info.evals = (ctr_.evals - at_stage_start.evals);
+            if (on_stage) on_stage(ctx, &info);
+            if (K_ >= stop_M) break;
+            pass = 0;
+            rc = codebook_grow();
+            if (rc) return rc;
+            t_stage = now_s();
+            at_stage_start = ctr_;
+        } else {
+            pass++;
+        }
+        DDprv = DD;
+    }
+    return ECOZ2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------
+// quantize (quantize.c:8-34)
+int Engine::quantize_resident(uint16_t *seq_out, double *avg) {
+    if (!committed_ || K_ < 1) {
+        set_last_error("quantize_resident: frames not committed or no codebook");
+        return ECOZ2B200_ERR_ARG;
+    }
+    const PackedLayout L{K_, D_};
+    const bool reduce = shards_.size() > 1 || multi_process_;
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
+        CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
+        search(s, s.x64, s.x32, s.n, s.idx_tmp, s.flag_list);
+        CUDA_TRY(cudaEventRecord(s.ev[1], s.stream));
+        launch_accumulate(s.x64, s.idx_tmp, s.n, D_, s.raas, K_, s.packed, nullptr, s.seq, false,
+                          s.num_sms, s.stream);
+        ctr_.kernel_launches++;
+        CUDA_TRY(cudaEventRecord(s.ev[2], s.stream));
+        if (seq_out)
+            CUDA_TRY(cudaMemcpyAsync(seq_out + s.frame_offset, s.seq, sizeof(uint16_t) * (size_t) s.n,
+                                     cudaMemcpyDeviceToHost, s.stream));
+    }
+    int rc = allreduce_range(shards_, L.dd(), 2, reduce);
+    if (rc) return rc;
+    double tail[2] = {0, 0};
+    Shard &s0 = shards_[0];
+    CUDA_TRY(cudaSetDevice(s0.device));
+    CUDA_TRY(cudaMemcpyAsync(tail, s0.packed + L.dd(), 2 * sizeof(double), cudaMemcpyDeviceToHost, s0.stream));
+    rc = sync_all();
+    if (rc) return rc;
+    CUDA_TRY(cudaGetLastError());
+    harvest_times(false);
+    if (avg) *avg = n_global_ > 0 ? tail[0] / (double) n_global_ : 0.0;
+    return ECOZ2B200_OK;
+}
+
+int Engine::quantize_host(const double *x, long T, uint16_t *seq_out, double *avg) {
+    if (K_ < 1 || T < 0 || (T > 0 && !x)) {
+        set_last_error("quantize_host: no codebook or bad argument");
+        return ECOZ2B200_ERR_ARG;
+    }
+    const PackedLayout L{K_, D_};
+    const long S = (long) shards_.size();
+    const long chunk_cap = 1L << 20;  // frames per device chunk
+    for (long i = 0; i < S; i++) {
+        Shard &s = shards_[i];
+        QBuf &q = qbuf_[i];
+        CUDA_TRY(cudaSetDevice(s.device));
+        const long want = T < chunk_cap ? (T > 0 ? T : 1) : chunk_cap;
+        if (q.cap < want) {
+            CUDA_TRY(cudaStreamSynchronize(s.stream));
+            cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.flag_list); cudaFree(q.seq);
+            q = QBuf();
+            CUDA_TRY(cudaMalloc(&q.x64, sizeof(double) * (size_t) want * D_));
+            CUDA_TRY(cudaMalloc(&q.x32, sizeof(float) * (size_t) want * D_));
+            CUDA_TRY(cudaMalloc(&q.idx, sizeof(int32_t) * (size_t) want));
+            CUDA_TRY(cudaMalloc(&q.flag_list, sizeof(int32_t) * (size_t) want));
+            CUDA_TRY(cudaMalloc(&q.seq, sizeof(uint16_t) * (size_t) want));
+            q.cap = want;
+        }
+        CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
+    }
+    // contiguous chunks dealt round-robin to the devices; every chunk is
+    // H2D -> f32 copy -> search -> FP64 distortion + symbols -> D2H on its stream
+    long pos = 0;
+    int turn = 0;
+    while (pos < T) {
+        Shard &s = shards_[turn];
+        QBuf &q = qbuf_[turn];
+        const long n = T - pos < q.cap ? T - pos : q.cap;
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaMemcpyAsync(q.x64, x + (size_t) pos * D_, sizeof(double) * (size_t) n * D_,
+                                 cudaMemcpyHostToDevice, s.stream));
+        launch_convert_frames(q.x64, q.x32, n, D_, s.stream);
+        ctr_.kernel_launches++;
+        search(s, q.x64, q.x32, n, q.idx, q.flag_list);
+        launch_accumulate(q.x64, q.idx, n, D_, s.raas, K_, s.packed, nullptr, q.seq, false, s.num_sms,
+                          s.stream);
+        ctr_.kernel_launches++;
+        if (seq_out)
+            CUDA_TRY(cudaMemcpyAsync(seq_out + pos, q.seq, sizeof(uint16_t) * (size_t) n,
+                                     cudaMemcpyDeviceToHost, s.stream));
+        pos += n;
+        turn = (turn + 1) % (int) S;
+    }
+    double total = 0;
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        double tail[2] = {0, 0};
+        CUDA_TRY(cudaMemcpyAsync(tail, s.packed + L.dd(), 2 * sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+        total += tail[0];
+    }
+    CUDA_TRY(cudaGetLastError());
+    if (avg) *avg = T > 0 ? total / (double) T : 0.0;
+    return ECOZ2B200_OK;
+}
+
+}  // namespace vqb200

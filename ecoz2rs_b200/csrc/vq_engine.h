@@ -1,0 +1,133 @@
+// vq_engine.h -- host side of the B200 VQ path: device shards, the k-means pass,
+// the LBG driver.  Internal C++ interface behind include/ecoz2_vq_b200.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+#include "../../include/ecoz2_vq_b200.h"
+#include "vq_kernels.cuh"
+
+namespace vqb200 {
+
+void set_last_error(const std::string &msg);
+const char *get_last_error();
+
+struct NcclApi;  // dlopen'ed libnccl (vq_nccl.cpp)
+
+// One GPU's share of the frames + a replica of the codebook state.
+struct Shard {
+    int device = 0;
+    int num_sms = 148;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[6] = {};   // phase boundaries of the current pass
+    void *comm = nullptr;     // ncclComm_t
+
+    long n = 0;               // frames resident on this shard
+    long frame_offset = 0;    // index of its first frame in the engine's append order
+    double *x64 = nullptr;    // [n][D]   original FP64 frames (exact re-evaluation, cell sums)
+    float *x32 = nullptr;     // [n][D]   FP32 copy for the search
+    int32_t *idx = nullptr;   // [n]   assignment of the last k-means pass
+    int32_t *idx_tmp = nullptr;  // [n] scratch assignment (inertia / quantize)
+    uint16_t *seq = nullptr;  // [n]   symbols (quantize)
+    double *mindist = nullptr;  // [n]   ddmin - 1 of the last pass
+    int32_t *flag_list = nullptr;  // [n]
+    int32_t *flag_count = nullptr; // [1]
+    long cap = 0;             // capacity (frames) of the per-frame buffers
+
+    // codebook replica
+    double *refl = nullptr;   // [max_M][D]
+    double *raas = nullptr;   // [max_M][D]
+    float *w32 = nullptr;     // search tiles
+    double *w64 = nullptr;
+    float *w1max = nullptr;
+    double *packed = nullptr; // PackedLayout(max_M, D)
+    double *scalars = nullptr;  // [8] misc device scalars (sigma sum, ...)
+};
+
+struct Counters {
+    double assign_ms = 0, accumulate_ms = 0, update_ms = 0, allreduce_ms = 0;
+    long kernel_launches = 0;
+    double evals = 0;
+    long rechecked = 0;
+};
+
+class Engine {
+  public:
+    Engine(const int *devices, int num_devices, int P, int max_M);
+    ~Engine();
+    bool ok() const { return ok_; }
+
+    int set_mode(int mode);
+    int set_kappa(double kappa);
+    int comm_init(const unsigned char id[128], int rank, int world);
+
+    int frames_reserve(long total);
+    int frames_clear();
+    int frames_append_host(const double *x, long n);
+    int frames_append_device(const double *x_dev, long n);
+    int frames_commit();
+    long frames_count() const { return n_total_; }
+
+    int codebook_initial();
+    int codebook_set_reflections(const double *refl, int K);
+    int codebook_set_raas(const double *raas, int K);
+    int codebook_grow();
+    int codebook_size() const { return K_; }
+    int codebook_get(double *refl_out, double *raas_out);
+
+    int assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked);
+    int kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_out, double *DD_out);
+    int sigma(double avgDistortion, double *sigma_out);
+    int inertia(double *inertia_out);
+    int last_assignment(int32_t *idx_out, double *mindist_out);
+    int learn(double eps, int stop_M, ecoz2b200_stage_cb on_stage, ecoz2b200_pass_cb on_pass,
+              void *ctx);
+    int quantize_host(const double *x, long T, uint16_t *seq_out, double *avg);
+    int quantize_resident(uint16_t *seq_out, double *avg);
+
+    void counters_reset() { ctr_ = Counters(); }
+    const Counters &counters() const { return ctr_; }
+
+    int P() const { return P_; }
+    int D() const { return D_; }
+    long global_frames() const { return n_global_; }
+    int world() const { return world_; }
+    int rank() const { return rank_; }
+
+  private:
+    int ensure_capacity(Shard &s, long n);
+    int ensure_local_comms();
+    void search(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
+                int32_t *flag_list);
+    int stage_codebook();  // raas -> search operands on every shard
+    int sync_all();
+    void harvest_times(bool with_cells);
+
+    bool ok_ = false;
+    int P_, D_, max_M_;
+    int K_ = 0;
+    int mode_ = ECOZ2B200_MODE_FP32;
+    double kappa_ = 12.0;
+    std::vector<Shard> shards_;
+    long n_total_ = 0;   // local frames (all shards)
+    long n_global_ = 0;  // all ranks
+    long reserved_ = 0;  // frames_reserve() total (fixes the shard boundaries)
+    long per_shard_ = 0;
+    long appended_ = 0;
+    bool committed_ = false;
+    // scratch of quantize_host (per shard, lazily allocated)
+    struct QBuf { double *x64 = nullptr; float *x32 = nullptr; int32_t *idx = nullptr;
+                  int32_t *flag_list = nullptr; uint16_t *seq = nullptr; long cap = 0; };
+    std::vector<QBuf> qbuf_;
+    int append_block(const double *x, long n, bool device_src);
+    int rank_ = 0, world_ = 1;
+    bool multi_process_ = false;
+    bool local_comms_ready_ = false;
+    Counters ctr_;
+    std::vector<double> h_packed_;  // host mirror of the packed buffer tail / cells
+};
+
+}  // namespace vqb200

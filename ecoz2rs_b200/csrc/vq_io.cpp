@@ -1,0 +1,261 @@
+// vq_io.cpp -- ECOZ2 file formats, output paths and report writers (host only).
+// Written against the format descriptions in SURVEY.md §8(a) rows 1, 11, 12, 16, 18;
+// every function cites the reference code whose bytes it must reproduce.
+#include "vq_io.h"
+
+#include <errno.h>
+#include <string.h>
+#include <sys/stat.h>
+
+#include <memory>
+
+namespace vqb200 {
+
+int cb_errnum_last = 0;
+
+namespace {
+
+struct FileCloser {
+    void operator()(FILE *f) const { if (f) fclose(f); }
+};
+using FilePtr = std::unique_ptr<FILE, FileCloser>;
+
+// 16-byte ident, NUL padded (fileutil.c:121-139)
+bool write_ident(FILE *f, const char *ident) {
+    char chunk[kFileIdentLen];
+    memset(chunk, 0, sizeof chunk);
+    size_t len = strlen(ident);
+    if (len >= (size_t) kFileIdentLen) len = kFileIdentLen - 1;
+    memcpy(chunk, ident, len);
+    return fwrite(chunk, sizeof chunk, 1, f) == 1;
+}
+// prefix match on strlen(ident) bytes (fileutil.c:141-160)
+bool read_ident(FILE *f, const char *ident) {
+    char chunk[kFileIdentLen];
+    if (fread(chunk, sizeof chunk, 1, f) != 1) return false;
+    return strncmp(ident, chunk, strlen(ident)) == 0;
+}
+// 96 bytes: name, NUL, then '_' padding (fileutil.c:162-182)
+bool write_class(FILE *f, const char *name) {
+    char chunk[kMaxClassNameLen];
+    size_t len = strlen(name);
+    if (len >= (size_t) kMaxClassNameLen) len = kMaxClassNameLen - 1;
+    memcpy(chunk, name, len);
+    chunk[len] = 0;
+    for (size_t i = len + 1; i < (size_t) kMaxClassNameLen; i++) chunk[i] = '_';
+    return fwrite(chunk, sizeof chunk, 1, f) == 1;
+}
+bool read_class(FILE *f, char *name) {
+    if (fread(name, kMaxClassNameLen, 1, f) != 1) return false;
+    name[kMaxClassNameLen - 1] = 0;
+    return true;
+}
+
+int read_header(const char *path, const char *ident, int *a, int *b, char *class_name, FilePtr *keep) {
+    FilePtr f(fopen(path, "rb"));
+    if (!f) return 1;
+    if (!read_ident(f.get(), ident)) return 2;
+    char cls[kMaxClassNameLen];
+    if (!read_class(f.get(), cls)) return 2;
+    int32_t v[2];
+    if (fread(v, sizeof(int32_t), 2, f.get()) != 2) return 3;
+    if (a) *a = v[0];
+    if (b) *b = v[1];
+    if (class_name) memcpy(class_name, cls, kMaxClassNameLen);
+    if (keep) *keep = std::move(f);
+    return 0;
+}
+
+}  // namespace
+
+// ---- .prd ------------------------------------------------------------------------
+int prd_info(const char *path, int *P, int *T, char class_name[kMaxClassNameLen]) {
+    return read_header(path, "<predictor>", P, T, class_name, nullptr);
+}
+int prd_read(const char *path, double *out, long capacity_values) {
+    int P = 0, T = 0;
+    FilePtr f;
+    int rc = read_header(path, "<predictor>", &P, &T, nullptr, &f);
+    if (rc) return rc;
+    const long want = (long) T * (P + 1);
+    if (P < 0 || T < 0 || want > capacity_values) return 3;
+    if (want > 0 && fread(out, sizeof(double), (size_t) want, f.get()) != (size_t) want) return 4;
+    return 0;
+}
+
+// ---- .cbook ------------------------------------------------------------------------
+int cbook_save(const char *path, const char *class_name, const double *refl, int M, int P) {
+    FilePtr f(fopen(path, "wb"));
+    if (!f) return cb_errnum_last = 1;
+    const int32_t hdr[2] = {P, M};
+    if (!write_ident(f.get(), "<codebook>") || !write_class(f.get(), class_name) ||
+        fwrite(hdr, sizeof(int32_t), 2, f.get()) != 2)
+        return cb_errnum_last = 1;
+    const size_t n = (size_t) M * (P + 1);
+    if (n > 0 && fwrite(refl, sizeof(double), n, f.get()) != n) return cb_errnum_last = 1;
+    return cb_errnum_last = 0;
+}
+int cbook_info(const char *path, int *P, int *M, char class_name[kMaxClassNameLen]) {
+    return cb_errnum_last = read_header(path, "<codebook>", P, M, class_name, nullptr);
+}
+int cbook_read(const char *path, double *out, long capacity_values) {
+    int P = 0, M = 0;
+    FilePtr f;
+    int rc = read_header(path, "<codebook>", &P, &M, nullptr, &f);
+    if (rc) return cb_errnum_last = rc;
+    const long want = (long) M * (P + 1);
+    if (P < 0 || M < 0 || want > capacity_values) return cb_errnum_last = 3;
+    if (want > 0 && fread(out, sizeof(double), (size_t) want, f.get()) != (size_t) want)
+        return cb_errnum_last = 4;
+    return cb_errnum_last = 0;
+}
+
+// ---- .seq ------------------------------------------------------------------------
+int seq_save(const char *path, const char *class_name, const uint16_t *seq, int T, int M) {
+    FilePtr f(fopen(path, "wb"));
+    if (!f) return 1;
+    if (T <= 0) printf("WARN: seq_save: T=%d <= 0: %s\n", T, path);
+    const int32_t hdr[2] = {T, M};
+    if (!write_ident(f.get(), "<sequence>") || !write_class(f.get(), class_name) ||
+        fwrite(hdr, sizeof(int32_t), 2, f.get()) != 2)
+        return 2;
+    if (T > 0 && fwrite(seq, sizeof(uint16_t), (size_t) T, f.get()) != (size_t) T) return 2;
+    return 0;
+}
+
+// ---- paths -------------------------------------------------------------------------
+// class = name of the parent directory, "" if the path has fewer than two '/'
+// (fileutil.c:14-30)
+std::string get_class_name(const std::string &path) {
+    const size_t last = path.rfind('/');
+    if (last == std::string::npos) return "";
+    const std::string dir = path.substr(0, last);
+    const size_t prev = dir.rfind('/');
+    if (prev == std::string::npos) return "";
+    std::string cls = dir.substr(prev + 1);
+    if (cls.size() >= (size_t) kMaxClassNameLen) cls.resize(kMaxClassNameLen - 1);
+    return cls;
+}
+
+int mk_dirs(const std::string &path) {
+    // every prefix up to each '/', then the whole path; EEXIST is fine (fileutil.c:65-95)
+    for (size_t pos = path.find('/'); ; pos = path.find('/', pos + 1)) {
+        const std::string part = pos == std::string::npos ? path : path.substr(0, pos);
+        if (!part.empty() && mkdir(part.c_str(), S_IRWXU) != 0 && errno != EEXIST) {
+            printf("ERROR creating directory %s: %s\n", part.c_str(), strerror(errno));
+            return -1;
+        }
+        if (pos == std::string::npos) break;
+    }
+    return 0;
+}
+
+// extension swap as the reference's camext (fileutil.c:97-119): the last '.'
+// anywhere in the path; if fewer than 2 characters follow it the new extension
+// is appended instead.
+static std::string change_ext(const std::string &name, const std::string &ext) {
+    const size_t dot = name.rfind('.');
+    if (dot == std::string::npos) return name;
+    if (name.size() - dot < 3) return name + ext;
+    if (ext.empty() || ext == ".") return name.substr(0, dot);
+    if (ext[0] == '.') return name.substr(0, dot) + ext;
+    return name.substr(0, dot) + "." + ext;
+}
+
+std::string get_output_filename(const std::string &from, const std::string &base_dir,
+                                const std::string &ext) {
+    // fileutil.c:32-63: class "_" unless the path has a parent directory name
+    std::string tmp = change_ext(from, ext);
+    std::string cls = "_", simple = tmp;
+    const size_t last = tmp.rfind('/');
+    if (last != std::string::npos) {
+        simple = tmp.substr(last + 1);
+        const std::string dir = tmp.substr(0, last);
+        const size_t prev = dir.rfind('/');
+        if (prev != std::string::npos) cls = dir.substr(prev + 1);
+    }
+    const std::string class_dir = "data/" + base_dir + "/" + cls;
+    mk_dirs(class_dir);
+    return class_dir + "/" + simple;
+}
+
+// ---- report ------------------------------------------------------------------------
+void Report::prepare(const std::string &rpt_filename, long tot_vecs, double eps) {
+    tot_vecs_ = tot_vecs;
+    printf("Report: %s\n", rpt_filename.c_str());
+    file_ = fopen(rpt_filename.c_str(), "w");
+    if (!file_) printf("error creating report file %s\n", rpt_filename.c_str());
+    if (file_)
+        fprintf(file_, "Codebook generation\n\n%ld training vectors. (ε = %g)\n\n", tot_vecs, eps);
+    const std::string csv = rpt_filename + ".csv";
+    file_csv_ = fopen(csv.c_str(), "w");
+    if (!file_csv_) {
+        printf("error creating report file %s\n", csv.c_str());
+    } else {
+        fprintf(file_csv_, "# %ld training vectors. (ε = %g)\n", tot_vecs, eps);
+        fprintf(file_csv_, "%s,%s,%s,%s,%s\n", "M", "passes", "DDprm", "σ", "inertia");
+    }
+}
+
+void Report::cbook(const std::string &cb_filename, int num_pas, double DDprm, double sigma,
+                   double inertia, int M, const int32_t *cardd, const double *discel,
+                   const int32_t *codeword, const double *min_dist) {
+    if (!file_) return;
+    fprintf(file_, "### %s (%2d passes)  Dprm = %f  σ = %f  inertia = %f\n", cb_filename.c_str(),
+            num_pas, DDprm, sigma, inertia);
+    if (file_csv_) {
+        fprintf(file_csv_, "%d,%d,%f,%f,%f\n", M, num_pas, DDprm, sigma, inertia);
+        fflush(file_csv_);
+    }
+    int empty = 0;
+    for (int i = 0; i < M; i++)
+        if (!cardd[i]) empty++;
+    fprintf(file_, "Cardinalities:");
+    if (empty) fprintf(file_, "  (%d empty cells)", empty);
+    fprintf(file_, "\n");
+    for (int i = 0; i < M; i++) fprintf(file_, "%8d ", cardd[i]);
+    fprintf(file_, "\n");
+    fprintf(file_, "average cell distortion:\n");
+    for (int i = 0; i < M; i++) {
+        if (cardd[i]) fprintf(file_, "%8.3g ", discel[i] / cardd[i]);
+        else fprintf(file_, "%8s ", "_");
+    }
+    fprintf(file_, "\n\n");
+    fflush(file_);
+
+    {
+        const std::string name = cb_filename + ".cards_dists.csv";
+        FILE *f = fopen(name.c_str(), "w");
+        if (!f) {
+            printf("error creating %s\n", name.c_str());
+        } else {
+            fprintf(f, "%s,%s,%s\n", "index", "cardinality", "distortion");
+            for (int i = 0; i < M; i++) {
+                fprintf(f, "%d,%d,", i, cardd[i]);
+                if (cardd[i] > 0) fprintf(f, "%f\n", discel[i] / cardd[i]);
+                else fprintf(f, "NaN\n");
+            }
+            fclose(f);
+        }
+    }
+    if (codeword && min_dist) {
+        const std::string name = cb_filename + ".min_dists.csv";
+        FILE *f = fopen(name.c_str(), "w");
+        if (!f) {
+            printf("error creating %s\n", name.c_str());
+        } else {
+            static char big[1 << 20];
+            setvbuf(f, big, _IOFBF, sizeof big);
+            fprintf(f, "%s\n", "codeword,minDistortion");
+            for (long v = 0; v < tot_vecs_; v++) fprintf(f, "%d,%f\n", codeword[v], min_dist[v]);
+            fclose(f);
+        }
+    }
+}
+
+void Report::close() {
+    if (file_) { fclose(file_); file_ = nullptr; }
+    if (file_csv_) { fclose(file_csv_); file_csv_ = nullptr; }
+}
+
+}  // namespace vqb200

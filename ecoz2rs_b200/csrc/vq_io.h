@@ -1,0 +1,54 @@
+// vq_io.h -- ECOZ2 binary formats (.prd / .cbook / .seq), output-path rules and
+// the stage report writers, byte/column compatible with the reference.
+#pragma once
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+#include <vector>
+
+namespace vqb200 {
+
+constexpr int kFileIdentLen = 16;     // reference ecoz2/src/include/utl.h (FILE_IDENT_LEN)
+constexpr int kMaxClassNameLen = 96;  // reference ecoz2/src/include/utl.h (MAX_CLASS_NAME_LEN)
+
+// `.prd`  (reference ecoz2/src/lpc/prd.c:34-115):
+//   "<predictor>" ident | class name | i32 P | i32 T | T x (1+P) f64
+int prd_info(const char *path, int *P, int *T, char class_name[kMaxClassNameLen]);
+int prd_read(const char *path, double *out, long capacity_values);
+
+// `.cbook` (reference ecoz2/src/vq/vq.c:22-116):
+//   "<codebook>" ident | class name | i32 P | i32 M | M x (1+P) f64 reflections
+int cbook_save(const char *path, const char *class_name, const double *refl, int M, int P);
+int cbook_info(const char *path, int *P, int *M, char class_name[kMaxClassNameLen]);
+int cbook_read(const char *path, double *out, long capacity_values);
+extern int cb_errnum_last;  // reference cb_errnum (vq.c:20)
+
+// `.seq` (reference ecoz2/src/hmm/symbol.c:17-36):
+//   "<sequence>" ident | class name | i32 T | i32 M | T x u16
+int seq_save(const char *path, const char *class_name, const uint16_t *seq, int T, int M);
+
+// reference ecoz2/src/utl/fileutil.c:14-119
+std::string get_class_name(const std::string &path);
+int mk_dirs(const std::string &path);
+// data/<base_dir>/<class>/<stem><ext>; creates the directory
+std::string get_output_filename(const std::string &from, const std::string &base_dir,
+                                const std::string &ext);
+
+// reference ecoz2/src/vq/report.c:14-135
+class Report {
+  public:
+    void prepare(const std::string &rpt_filename, long tot_vecs, double eps);
+    void cbook(const std::string &cb_filename, int num_pas, double DDprm, double sigma,
+               double inertia, int M, const int32_t *cardd, const double *discel,
+               const int32_t *codeword, const double *min_dist /* both may be null */);
+    void close();
+    ~Report() { close(); }
+
+  private:
+    long tot_vecs_ = 0;
+    FILE *file_ = nullptr;
+    FILE *file_csv_ = nullptr;
+};
+
+}  // namespace vqb200

@@ -1,0 +1,687 @@
+// vq_kernels.cu -- hand-written sm_100a kernels of the ECOZ2 VQ hot path.
+//
+// Not a port of the reference's C loops: the reference (ecoz2/src/vq) walks
+// frame by frame and codeword by codeword on the CPU in FP64.  Here the search
+// is a skinny GEMM with a fused row-argmin epilogue (the N x K distortion
+// matrix never exists), the cell sums are run-length aggregated FP64 reductions
+// and the centroid / split step is one warp per codeword.
+//
+// Kernels:
+//   vq_assign_tiled<T,...>   (a) fused distortion + argmin (FP32 main pass with
+//                                ambiguity flagging, FP64 exact pass / re-evaluation)
+//   vq_accumulate<...>       (b) cell sums, counts, distortion, symbols
+//   vq_centroids, vq_grow,   (c) Levinson-Durbin centroid, split, step-up
+//   vq_refl_to_raas
+//   vq_sigma_sum, vq_prepare_codebook, vq_convert_frames
+#include "vq_kernels.cuh"
+
+#include <cfloat>
+#include <cmath>
+
+namespace vqb200 {
+
+// --------------------------------------------------------------------------------
+// small PTX helpers: mbarrier + 1-D bulk async copy (TMA engine, SASS UBLKCP)
+// --------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void *p) {
+    return (uint32_t) __cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void fence_barrier_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+// global -> shared bulk copy, completion signalled on an mbarrier (bytes % 16 == 0)
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes,
+                                         uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+            "r"(smem_u32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(smem_u32(bar))
+        : "memory");
+}
+
+template <typename T>
+__device__ __forceinline__ T fma_t(T a, T b, T c);
+template <>
+__device__ __forceinline__ float fma_t<float>(float a, float b, float c) {
+    return fmaf(a, b, c);
+}
+template <>
+__device__ __forceinline__ double fma_t<double>(double a, double b, double c) {
+    return fma(a, b, c);
+}
+
+__device__ __forceinline__ void ld4(const float *p, float (&v)[4]) {
+    const float4 t = *reinterpret_cast<const float4 *>(p);
+    v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+__device__ __forceinline__ void ld4(const double *p, double (&v)[4]) {
+    const double2 a = *reinterpret_cast<const double2 *>(p);
+    const double2 b = *reinterpret_cast<const double2 *>(p + 2);
+    v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+}
+
+template <typename T> struct Lim;
+template <> struct Lim<float> { static __device__ __forceinline__ float inf() { return INFINITY; } };
+template <> struct Lim<double> { static __device__ __forceinline__ double inf() { return (double) INFINITY; } };
+
+// --------------------------------------------------------------------------------
+// (a) fused distortion + argmin
+//
+// CTA = 256 threads as a 16 x 16 grid; CTA tile = BM frames x BN codewords with
+// BM = 16*4*RM, BN = 16*4*RN; every thread owns a (4*RM) x (4*RN) register tile.
+// The frame tile is transposed into shared memory once (Xs[n][frame]) and stays
+// there while ALL codeword tiles stream past it: codeword tiles are
+// pre-transposed in global memory ([tile][n][BN], built by vq_prepare_codebook)
+// so one cp.async.bulk brings a whole tile, double buffered on two mbarriers.
+// Inner step n: 2*RM + 2*RN 128-bit shared loads feed (4RM)(4RN) FMAs.
+// Epilogue per tile: running (best, second, argbest) per frame in registers;
+// after the last tile the 16 threads that share a frame merge with shuffles.
+//
+// Reference semantics restated: strict '<' scan in index order
+// (vq_learn_par.c:66-75, quantize.c:19-26) == lexicographic min of (dd, index).
+// --------------------------------------------------------------------------------
+template <typename T, int RM, int RN, int DT, bool TRACK2>
+__global__ void __launch_bounds__(256, 2)
+vq_assign_tiled(const T *__restrict__ x, long n_frames, int D_rt, const T *__restrict__ wt, int K,
+                const int32_t *__restrict__ list, const int32_t *__restrict__ list_count,
+                const float *__restrict__ w1max, float gap_scale, int32_t *__restrict__ idx_out,
+                int32_t *__restrict__ flag_list, int32_t *__restrict__ flag_count) {
+    constexpr int TM = 4 * RM, TN = 4 * RN;
+    constexpr int BM = 16 * TM, BN = 16 * TN;
+    constexpr int XS = BM + 4;  // padded row of the transposed frame tile
+    const int D = DT > 0 ? DT : D_rt;
+
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    // layout: [2 mbarriers | pad to 128][Ws0: D*BN][Ws1: D*BN][Xs: D*XS]
+    uint64_t *full = reinterpret_cast<uint64_t *>(smem_raw);
+    T *Ws0 = reinterpret_cast<T *>(smem_raw + 128);
+    T *Ws1 = Ws0 + (size_t) D * BN;
+    T *Xs = Ws1 + (size_t) D * BN;
+
+    const int tid = threadIdx.x;
+    const int tx = tid & 15, ty = tid >> 4;
+    const uint32_t tile_bytes = (uint32_t) ((size_t) D * BN * sizeof(T));
+    const int n_wtiles = (K + BN - 1) / BN;
+
+    if (tid == 0) {
+        mbar_init(&full[0], 1);
+        mbar_init(&full[1], 1);
+        fence_barrier_init();
+    }
+    __syncthreads();
+    uint32_t phase0 = 0, phase1 = 0;
+
+    const long total = list ? (long) *list_count : n_frames;
+    const long n_ftiles = (total + BM - 1) / BM;
+
+    for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x) {
+        const long base = ft * BM;
+        const int nvalid = (int) (total - base < BM ? total - base : BM);
+        __syncthreads();  // previous tile's epilogue is done with Xs
+
+        // -- stage + transpose the frame tile: Xs[n][f]
+        if (list == nullptr) {
+            const T *src = x + base * D;
+            const int count = nvalid * D;
+            for (int e = tid; e < BM * D; e += 256) {
+                const int f = e / D, n = e - f * D;
+                Xs[n * XS + f] = e < count ? src[e] : (T) 0;
+            }
+        } else {
+            for (int e = tid; e < BM * D; e += 256) {
+                const int f = e / D, n = e - f * D;
+                T v = (T) 0;
+                if (f < nvalid) v = x[(long) list[base + f] * D + n];
+                Xs[n * XS + f] = v;
+            }
+        }
+        if (tid == 0) {
+            mbar_expect_tx(&full[0], tile_bytes);
+            bulk_g2s(Ws0, wt, tile_bytes, &full[0]);
+            if (n_wtiles > 1) {
+                mbar_expect_tx(&full[1], tile_bytes);
+                bulk_g2s(Ws1, wt + (size_t) D * BN, tile_bytes, &full[1]);
+            }
+        }
+        __syncthreads();
+
+        T best[TM], second[TM];
+        int bidx[TM];
+#pragma unroll
+        for (int i = 0; i < TM; i++) {
+            best[i] = Lim<T>::inf();
+            second[i] = Lim<T>::inf();
+            bidx[i] = 0;
+        }
+
+        for (int t = 0; t < n_wtiles; t++) {
+            const T *Ws = (t & 1) ? Ws1 : Ws0;
+            if (t & 1) { mbar_wait(&full[1], phase1); phase1 ^= 1; }
+            else       { mbar_wait(&full[0], phase0); phase0 ^= 1; }
+
+            T acc[TM][TN];
+#pragma unroll
+            for (int i = 0; i < TM; i++)
+#pragma unroll
+                for (int j = 0; j < TN; j++) acc[i][j] = (T) 0;
+
+#pragma unroll 4
+            for (int n = 0; n < D; n++) {
+                T xa[TM], wb[TN];
+#pragma unroll
+                for (int r = 0; r < RM; r++) {
+                    T v[4];
+                    ld4(Xs + n * XS + r * (BM / RM) + ty * 4, v);
+#pragma unroll
+                    for (int q = 0; q < 4; q++) xa[r * 4 + q] = v[q];
+                }
+#pragma unroll
+                for (int r = 0; r < RN; r++) {
+                    T v[4];
+                    ld4(Ws + n * BN + r * (BN / RN) + tx * 4, v);
+#pragma unroll
+                    for (int q = 0; q < 4; q++) wb[r * 4 + q] = v[q];
+                }
+#pragma unroll
+                for (int i = 0; i < TM; i++)
+#pragma unroll
+                    for (int j = 0; j < TN; j++) acc[i][j] = fma_t<T>(xa[i], wb[j], acc[i][j]);
+            }
+
+            // -- fused argmin epilogue for this codeword tile (index order ascending in j)
+            const int c0 = t * BN + tx * 4;
+            const bool partial = (t + 1) * BN > K;
+#pragma unroll
+            for (int j = 0; j < TN; j++) {
+                const int c = c0 + (j >> 2) * (BN / RN) + (j & 3);
+                if (partial && c >= K) continue;
+#pragma unroll
+                for (int i = 0; i < TM; i++) {
+                    const T d = acc[i][j];
+                    if (TRACK2) second[i] = min(second[i], max(d, best[i]));
+                    bidx[i] = d < best[i] ? c : bidx[i];
+                    best[i] = min(best[i], d);
+                }
+            }
+
+            __syncthreads();  // everyone is done reading this buffer
+            if (tid == 0 && t + 2 < n_wtiles) {
+                uint64_t *bar = (t & 1) ? &full[1] : &full[0];
+                mbar_expect_tx(bar, tile_bytes);
+                bulk_g2s((t & 1) ? Ws1 : Ws0, wt + (size_t) (t + 2) * D * BN, tile_bytes, bar);
+            }
+        }
+
+        // -- merge the 16 threads (tx = low 4 lane bits) that share each frame
+#pragma unroll
+        for (int i = 0; i < TM; i++) {
+#pragma unroll
+            for (int off = 8; off >= 1; off >>= 1) {
+                const T ob = __shfl_xor_sync(0xffffffffu, best[i], off);
+                const int oi = __shfl_xor_sync(0xffffffffu, bidx[i], off);
+                if (TRACK2) {
+                    const T os = __shfl_xor_sync(0xffffffffu, second[i], off);
+                    second[i] = min(min(second[i], os), max(best[i], ob));
+                }
+                if (ob < best[i] || (ob == best[i] && oi < bidx[i])) {
+                    best[i] = ob;
+                    bidx[i] = oi;
+                }
+            }
+        }
+        if (tx == 0) {
+            float bound = 0.f;
+            if (TRACK2) bound = gap_scale * (*w1max);
+#pragma unroll
+            for (int i = 0; i < TM; i++) {
+                const int f = (i >> 2) * (BM / RM) + ty * 4 + (i & 3);
+                if (f < nvalid) {
+                    const long row = list ? (long) list[base + f] : base + f;
+                    idx_out[row] = bidx[i];
+                    if (TRACK2) {
+                        const float x0 = fabsf((float) Xs[f]);
+                        // NaN-safe: "not clearly separated" => re-evaluate
+                        if (!((float) (second[i] - best[i]) >= bound * x0)) {
+                            const int pos = atomicAdd(flag_count, 1);
+                            flag_list[pos] = (int32_t) row;
+                        }
+                    }
+                }
+            }
+        }
+    }
+}
+
+template <typename T, int RM, int RN>
+static size_t assign_smem_bytes(int D) {
+    constexpr int BM = 64 * RM, BN = 64 * RN;
+    return 128 + sizeof(T) * ((size_t) 2 * D * BN + (size_t) D * (BM + 4));
+}
+
+template <typename T, int RM, int RN, int DT, bool TRACK2>
+static void launch_assign_inst(const T *x, long n, int D, const T *wt, int K, const int32_t *list,
+                               const int32_t *list_count, const float *w1max, float gap_scale,
+                               int32_t *idx, int32_t *flag_list, int32_t *flag_count, int num_sms,
+                               cudaStream_t s) {
+    auto kern = vq_assign_tiled<T, RM, RN, DT, TRACK2>;
+    const size_t smem = assign_smem_bytes<T, RM, RN>(D);
+    cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+    constexpr int BM = 64 * RM;
+    long tiles = (n + BM - 1) / BM;
+    if (tiles < 1) tiles = 1;
+    long grid = tiles;
+    if (list != nullptr) {
+        // device-side count: persistent grid, CTAs loop over however many tiles there are
+        const long cap = (long) num_sms * 4;
+        if (grid > cap) grid = cap;
+    }
+    kern<<<(unsigned) grid, 256, smem, s>>>(x, n, D, wt, K, list, list_count, w1max, gap_scale, idx,
+                                            flag_list, flag_count);
+}
+
+void launch_assign_f32(const float *x32, long n, int D, const float *w32, int K,
+                       const float *w1max, float gap_scale, int32_t *idx, int32_t *flag_list,
+                       int32_t *flag_count, int num_sms, cudaStream_t s) {
+    if (n <= 0) return;
+    if (D == 37)
+        launch_assign_inst<float, 2, 2, 37, true>(x32, n, D, w32, K, nullptr, nullptr, w1max,
+                                                  gap_scale, idx, flag_list, flag_count, num_sms, s);
+    else if (D == 13)
+        launch_assign_inst<float, 2, 2, 13, true>(x32, n, D, w32, K, nullptr, nullptr, w1max,
+                                                  gap_scale, idx, flag_list, flag_count, num_sms, s);
+    else
+        launch_assign_inst<float, 2, 2, 0, true>(x32, n, D, w32, K, nullptr, nullptr, w1max,
+                                                 gap_scale, idx, flag_list, flag_count, num_sms, s);
+}
+
+void launch_assign_f64(const double *x64, long n, int D, const double *w64, int K,
+                       const int32_t *list, const int32_t *list_count, int32_t *idx, int num_sms,
+                       cudaStream_t s) {
+    if (n <= 0) return;
+    if (D == 37)
+        launch_assign_inst<double, 1, 1, 37, false>(x64, n, D, w64, K, list, list_count, nullptr,
+                                                    0.f, idx, nullptr, nullptr, num_sms, s);
+    else if (D == 13)
+        launch_assign_inst<double, 1, 1, 13, false>(x64, n, D, w64, K, list, list_count, nullptr,
+                                                    0.f, idx, nullptr, nullptr, num_sms, s);
+    else
+        launch_assign_inst<double, 1, 1, 0, false>(x64, n, D, w64, K, list, list_count, nullptr,
+                                                   0.f, idx, nullptr, nullptr, num_sms, s);
+}
+
+// --------------------------------------------------------------------------------
+// data staging
+// --------------------------------------------------------------------------------
+__global__ void vq_convert_frames(const double *__restrict__ x64, float *__restrict__ x32,
+                                  long total) {
+    const long stride = (long) gridDim.x * blockDim.x;
+    for (long e = (long) blockIdx.x * blockDim.x + threadIdx.x; e < total; e += stride)
+        x32[e] = (float) x64[e];
+}
+void launch_convert_frames(const double *x64, float *x32, long n, int D, cudaStream_t s) {
+    const long total = n * D;
+    if (total <= 0) return;
+    long blocks = (total + 255) / 256;
+    if (blocks > 148L * 32) blocks = 148L * 32;
+    vq_convert_frames<<<(unsigned) blocks, 256, 0, s>>>(x64, x32, total);
+}
+
+// one thread per (codeword slot, n) of the padded tile layouts
+__global__ void vq_prepare_codebook(const double *__restrict__ raas, int K, int D,
+                                    float *__restrict__ w32, double *__restrict__ w64,
+                                    float *__restrict__ w1max) {
+    const int K32 = (K + kTileF32 - 1) / kTileF32 * kTileF32;
+    const long total = (long) K32 * D;
+    const long e = (long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= total) return;
+    const int i = (int) (e / D), n = (int) (e - (long) i * D);
+    double w = 0.0;
+    if (i < K) {
+        w = raas[(long) i * D + n];
+        if (n > 0) w *= 2.0;
+    }
+    w32[((long) (i / kTileF32) * D + n) * kTileF32 + (i % kTileF32)] = (float) w;
+    const int K64 = (K + kTileF64 - 1) / kTileF64 * kTileF64;
+    if (i < K64) w64[((long) (i / kTileF64) * D + n) * kTileF64 + (i % kTileF64)] = w;
+    if (n == 0 && i < K) {
+        float s1 = 0.f;
+        for (int m = 0; m < D; m++) {
+            double v = raas[(long) i * D + m];
+            if (m > 0) v *= 2.0;
+            s1 += fabsf((float) v);
+        }
+        s1 *= 1.0001f;  // cover the rounding of this sum itself
+        atomicMax(reinterpret_cast<int *>(w1max), __float_as_int(s1));  // s1 >= 0
+    }
+}
+void launch_prepare_codebook(const double *raas, int K, int D, float *w32, double *w64,
+                             float *w1max, cudaStream_t s) {
+    cudaMemsetAsync(w1max, 0, sizeof(float), s);
+    const int K32 = (K + kTileF32 - 1) / kTileF32 * kTileF32;
+    const long total = (long) K32 * D;
+    vq_prepare_codebook<<<(unsigned) ((total + 255) / 256), 256, 0, s>>>(raas, K, D, w32, w64, w1max);
+}
+
+// --------------------------------------------------------------------------------
+// (b) cell accumulation: one warp walks a contiguous run of frames, lane l owns
+// components l, l+32, ... of the cell sum.  Consecutive frames that fall in the
+// same cell are summed in registers and flushed with ONE FP64 atomic per
+// component (run-length aggregation); the winner's distortion is recomputed in
+// FP64 so DD / discel / minDist do not depend on the FP32 search.
+// reference: add_to_cell, vq_learn.i:99-106; DD, vq_learn_par.c:77-79
+// --------------------------------------------------------------------------------
+__device__ __forceinline__ double warp_sum(double v) {
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) v += __shfl_xor_sync(0xffffffffu, v, off);
+    return v;
+}
+
+template <int NR, bool CELLS>
+__global__ void __launch_bounds__(256)
+vq_accumulate(const double *__restrict__ x64, const int32_t *__restrict__ idx, long n, int D,
+              const double *__restrict__ raas, PackedLayout L, double *__restrict__ packed,
+              double *__restrict__ mindist, uint16_t *__restrict__ seq) {
+    const int lane = threadIdx.x & 31;
+    const long warp = ((long) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long n_warps = ((long) gridDim.x * blockDim.x) >> 5;
+    const long chunk = (n + n_warps - 1) / n_warps;
+    const long lo = warp * chunk;
+    const long hi = lo + chunk < n ? lo + chunk : n;
+
+    double run[NR];
+#pragma unroll
+    for (int r = 0; r < NR; r++) run[r] = 0.0;
+    int run_idx = -1;
+    int run_cnt = 0;
+    double run_dis = 0.0, dd_sum = 0.0, in_sum = 0.0;
+
+    auto flush = [&]() {
+        if (run_idx >= 0) {
+#pragma unroll
+            for (int r = 0; r < NR; r++) {
+                const int m = lane + 32 * r;
+                if (m < D) atomicAdd(packed + L.cells() + (long) run_idx * D + m, run[r]);
+            }
+            if (lane == 0) {
+                atomicAdd(packed + L.counts() + run_idx, (double) run_cnt);
+                atomicAdd(packed + L.discel() + run_idx, run_dis);
+            }
+        }
+    };
+
+    constexpr int U = 4;
+    for (long v0 = lo; v0 < hi; v0 += U) {
+        int ci[U];
+        double xv[U][NR], wv[U][NR];
+#pragma unroll
+        for (int u = 0; u < U; u++) ci[u] = v0 + u < hi ? idx[v0 + u] : 0;
+#pragma unroll
+        for (int u = 0; u < U; u++)
+#pragma unroll
+            for (int r = 0; r < NR; r++) {
+                const int m = lane + 32 * r;
+                xv[u][r] = (v0 + u < hi && m < D) ? x64[(v0 + u) * D + m] : 0.0;
+            }
+#pragma unroll
+        for (int u = 0; u < U; u++)
+#pragma unroll
+            for (int r = 0; r < NR; r++) {
+                const int m = lane + 32 * r;
+                double w = (v0 + u < hi && m < D) ? raas[(long) ci[u] * D + m] : 0.0;
+                wv[u][r] = m > 0 ? 2.0 * w : w;
+            }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (v0 + u >= hi) break;
+            double part = 0.0;
+#pragma unroll
+            for (int r = 0; r < NR; r++) part = fma(xv[u][r], wv[u][r], part);
+            const double dd = warp_sum(part);
+            const double md = dd - 1.0;
+            dd_sum += md;
+            in_sum += dd * dd;
+            if (lane == 0) {
+                if (mindist) mindist[v0 + u] = md;
+                if (seq) seq[v0 + u] = (uint16_t) ci[u];
+            }
+            if (CELLS) {
+                if (ci[u] != run_idx) {
+                    flush();
+                    run_idx = ci[u];
+                    run_cnt = 0;
+                    run_dis = 0.0;
+#pragma unroll
+                    for (int r = 0; r < NR; r++) run[r] = 0.0;
+                }
+#pragma unroll
+                for (int r = 0; r < NR; r++) run[r] += xv[u][r];
+                run_cnt++;
+                run_dis += md;
+            }
+        }
+    }
+    if (CELLS) flush();
+
+    __shared__ double s_dd[8], s_in[8];
+    const int w = threadIdx.x >> 5;
+    if (lane == 0) { s_dd[w] = dd_sum; s_in[w] = in_sum; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int i = 0; i < (int) (blockDim.x >> 5); i++) { a += s_dd[i]; b += s_in[i]; }
+        atomicAdd(packed + L.dd(), a);
+        atomicAdd(packed + L.inertia(), b);
+    }
+}
+
+template <int NR>
+static void launch_accumulate_nr(const double *x64, const int32_t *idx, long n, int D,
+                                 const double *raas, int K, double *packed, double *mindist,
+                                 uint16_t *seq, bool with_cells, int num_sms, cudaStream_t s) {
+    PackedLayout L{K, D};
+    long warps_wanted = (n + 31) / 32;  // >= 32 frames per warp
+    long blocks = (warps_wanted + 7) / 8;
+    const long cap = (long) num_sms * 8;
+    if (blocks > cap) blocks = cap;
+    if (blocks < 1) blocks = 1;
+    if (with_cells)
+        vq_accumulate<NR, true><<<(unsigned) blocks, 256, 0, s>>>(x64, idx, n, D, raas, L, packed, mindist, seq);
+    else
+        vq_accumulate<NR, false><<<(unsigned) blocks, 256, 0, s>>>(x64, idx, n, D, raas, L, packed, mindist, seq);
+}
+
+void launch_accumulate(const double *x64, const int32_t *idx, long n, int D, const double *raas,
+                       int K, double *packed, double *mindist, uint16_t *seq, bool with_cells,
+                       int num_sms, cudaStream_t s) {
+    if (n <= 0) return;
+    const int nr = (D + 31) / 32;
+    switch (nr) {
+        case 1: launch_accumulate_nr<1>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s); break;
+        case 2: launch_accumulate_nr<2>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s); break;
+        case 3: launch_accumulate_nr<3>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s); break;
+        case 4: launch_accumulate_nr<4>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s); break;
+        default: launch_accumulate_nr<7>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s); break;
+    }
+}
+
+// --------------------------------------------------------------------------------
+// (c) centroid / split: one warp per codeword, FP64, shared-memory scratch
+// --------------------------------------------------------------------------------
+// step-up recursion rc -> predictor a (lpca_rc, lpca.c:106-125); a[] in shared
+__device__ __forceinline__ void warp_step_up(int P, const double *rc, double *a, int lane) {
+    if (lane == 0) a[0] = 1.0;
+    __syncwarp();
+    for (int k = 1; k <= P; k++) {
+        const double kk = rc[k];
+        const int half = k >> 1;
+        double lo[4], hi[4];  // P <= 207 -> half <= 103 -> <= 4 pairs per lane
+        int cnt = 0;
+        for (int i = 1 + lane; i <= half; i += 32, cnt++) { lo[cnt] = a[i]; hi[cnt] = a[k - i]; }
+        __syncwarp();
+        cnt = 0;
+        for (int i = 1 + lane; i <= half; i += 32, cnt++) {
+            a[i] = lo[cnt] + kk * hi[cnt];
+            a[k - i] = hi[cnt] + kk * lo[cnt];   // i == k-i: both writes give the same value
+        }
+        if (lane == 0) a[k] = kk;
+        __syncwarp();
+    }
+}
+// raa[n] = sum_{k=0}^{P-n} a[k] a[k+n]  (ref2raas.c:17-23, vq_learn.i:138-144)
+__device__ __forceinline__ void warp_autocorr(int P, const double *a, double *raa, int lane) {
+    for (int n = lane; n <= P; n += 32) {
+        double s = 0.0;
+        for (int k = 0; k <= P - n; k++) s += a[k] * a[k + n];
+        raa[n] = s;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+vq_centroids(double *__restrict__ packed, PackedLayout L, double *__restrict__ refl,
+             double *__restrict__ raas) {
+    __shared__ double s_a[8][kMaxD];
+    __shared__ double s_r[8][kMaxD];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int i = blockIdx.x * 8 + w;
+    const int D = L.D, P = D - 1;
+    if (i >= L.K) return;
+    if (!(packed[L.counts() + i] > 0.0)) return;  // empty cell: codeword unchanged (vq_learn.i:133)
+    double *cel = packed + L.cells() + (long) i * D;
+    double *a = s_a[w], *r = s_r[w];
+    double *rc = refl + (long) i * D;
+    for (int n = lane; n < D; n += 32) { r[n] = cel[n]; a[n] = 0.0; }
+    __syncwarp();
+    // lpca_r (lpca.c:64-101)
+    double pe = r[0];
+    if (pe == 0.0) {
+        for (int n = lane; n < D; n += 32) { rc[n] = 0.0; raas[(long) i * D + n] = 0.0; }
+        return;
+    }
+    if (lane == 0) a[0] = 1.0;
+    __syncwarp();
+    for (int k = 1; k <= P; k++) {
+        double part = 0.0;
+        for (int m = 1 + lane; m <= k; m += 32) part -= a[k - m] * r[m];
+        const double sum = warp_sum(part);
+        const double kk = sum / pe;
+        const int half = k >> 1;
+        double lo[4], hi[4];
+        int cnt = 0;
+        for (int m = 1 + lane; m <= half; m += 32, cnt++) { lo[cnt] = a[m]; hi[cnt] = a[k - m]; }
+        __syncwarp();
+        cnt = 0;
+        for (int m = 1 + lane; m <= half; m += 32, cnt++) {
+            a[m] = lo[cnt] + kk * hi[cnt];
+            a[k - m] = hi[cnt] + kk * lo[cnt];
+        }
+        if (lane == 0) { a[k] = kk; rc[k] = kk; }
+        __syncwarp();
+        pe *= 1.0 - kk * kk;
+        if (pe <= 0.0) break;  // lpca.c:97-98 (remaining predictor entries stay 0 here)
+    }
+    warp_autocorr(P, a, raas + (long) i * D, lane);
+    if (pe != 0.0)
+        for (int n = lane; n < D; n += 32) cel[n] = r[n] / pe;
+}
+void launch_centroids(double *packed, int K, int D, double *refl, double *raas, cudaStream_t s) {
+    PackedLayout L{K, D};
+    vq_centroids<<<(K + 7) / 8, 256, 0, s>>>(packed, L, refl, raas);
+}
+
+__global__ void __launch_bounds__(256)
+vq_refl_to_raas(const double *__restrict__ refl, double *__restrict__ raas, int K, int D) {
+    __shared__ double s_a[8][kMaxD];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int i = blockIdx.x * 8 + w;
+    if (i >= K) return;
+    warp_step_up(D - 1, refl + (long) i * D, s_a[w], lane);
+    warp_autocorr(D - 1, s_a[w], raas + (long) i * D, lane);
+}
+void launch_refl_to_raas(const double *refl, double *raas, int K, int D, cudaStream_t s) {
+    vq_refl_to_raas<<<(K + 7) / 8, 256, 0, s>>>(refl, raas, K, D);
+}
+
+// children 2j (x 0.99f) and 2j+1 (x 1.01f) of every row j, on ALL D entries; the
+// factors are float literals widened to double (vq_learn.i:54-55).  Written to a
+// scratch copy first so the in-place doubling has no ordering hazard.
+__global__ void vq_grow_copy(const double *__restrict__ refl_in, double *__restrict__ refl_out,
+                             int K, int D) {
+    const long e = (long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= (long) K * D) return;
+    const int j = (int) (e / D), n = (int) (e - (long) j * D);
+    const double v = refl_in[e];
+    refl_out[(long) (2 * j) * D + n] = v * (double) 0.99f;
+    refl_out[(long) (2 * j + 1) * D + n] = v * (double) 1.01f;
+}
+void launch_grow(double *refl, double *raas, int K, int D, cudaStream_t s) {
+    // raas is dead until refl_to_raas below: use it as the scratch for the old rows
+    const long total = (long) K * D;
+    cudaMemcpyAsync(raas, refl, sizeof(double) * total, cudaMemcpyDeviceToDevice, s);
+    vq_grow_copy<<<(unsigned) ((total + 255) / 256), 256, 0, s>>>(raas, refl, K, D);
+    launch_refl_to_raas(refl, raas, 2 * K, D, s);
+}
+
+// --------------------------------------------------------------------------------
+// sigma: sum_{i != j} [ distortion(cells_j, raas_i) - 1 ]  (sigma.c:14-25)
+// CTA per codeword i, threads over cells j.
+// --------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+vq_sigma_sum(const double *__restrict__ raas, const double *__restrict__ cells, int K, int D,
+             double *__restrict__ out) {
+    __shared__ double s_w[kMaxD];
+    __shared__ double s_part[8];
+    const int i = blockIdx.x;
+    for (int n = threadIdx.x; n < D; n += blockDim.x) {
+        const double v = raas[(long) i * D + n];
+        s_w[n] = n > 0 ? 2.0 * v : v;
+    }
+    __syncthreads();
+    double acc = 0.0;
+    for (int j = threadIdx.x; j < K; j += blockDim.x) {
+        if (j == i) continue;
+        const double *c = cells + (long) j * D;
+        double d = 0.0;
+        for (int n = 0; n < D; n++) d = fma(c[n], s_w[n], d);
+        acc += d - 1.0;
+    }
+    acc = warp_sum(acc);
+    if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = acc;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        for (int k = 0; k < 8; k++) t += s_part[k];
+        atomicAdd(out, t);
+    }
+}
+void launch_sigma_sum(const double *raas, const double *cells, int K, int D, double *out,
+                      cudaStream_t s) {
+    vq_sigma_sum<<<K, 256, 0, s>>>(raas, cells, K, D, out);
+}
+
+}  // namespace vqb200

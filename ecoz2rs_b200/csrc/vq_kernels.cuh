@@ -1,0 +1,84 @@
+// vq_kernels.cuh -- launch interface of the sm_100a kernels of the VQ path.
+//
+// Notation (reference ecoz2/src/vq): N frames, K codewords, P prediction order,
+// D = P + 1.  A frame is the gain-normalised autocorrelation rx[0..P]; a
+// codeword is the predictor autocorrelation raa[0..P]; the distortion is
+//     rx[0]*raa[0] + 2 * sum_{n=1..P} rx[n]*raa[n]        (distortion.c:6-13)
+// which the kernels evaluate as the plain inner product rx . w with
+//     w = (raa[0], 2 raa[1], ..., 2 raa[P]).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace vqb200 {
+
+// codewords per shared-memory tile of the search kernels
+constexpr int kTileF32 = 128;   // FP32 search:  128 frames x 128 codewords per CTA step
+constexpr int kTileF64 = 64;    // FP64 search:   64 frames x  64 codewords per CTA step
+constexpr int kMaxD = 208;      // >= 1 + MAX_PREDICTION_ORDER (reference include/vq.h:13)
+
+// Packed accumulation buffer of one k-means pass (what the NCCL allreduce sums):
+//   [K*D cell sums | K counts | K cell distortions | DD | inertia | pad]
+struct PackedLayout {
+    int K, D;
+    __host__ __device__ long cells() const { return 0; }
+    __host__ __device__ long counts() const { return (long) K * D; }
+    __host__ __device__ long discel() const { return (long) K * D + K; }
+    __host__ __device__ long dd() const { return (long) K * D + 2L * K; }
+    __host__ __device__ long inertia() const { return dd() + 1; }
+    __host__ __device__ long size() const { return dd() + 2; }
+};
+
+// ---- data staging -----------------------------------------------------------
+// x64 [n][D] f64 -> x32 [n][D] f32 (dense rows, round-to-nearest)
+void launch_convert_frames(const double *x64, float *x32, long n, int D, cudaStream_t s);
+
+// raas f64 [K][D] -> search operands:
+//   w32 tiles [ceil(K/128)][D][128] f32, w64 tiles [ceil(K/64)][D][64] f64 (zero padded)
+//   *w1max (f32) = max_i sum_n |w_i[n]|   (for the FP32 ambiguity bound)
+void launch_prepare_codebook(const double *raas, int K, int D, float *w32, double *w64,
+                             float *w1max, cudaStream_t s);
+
+// ---- (a) fused distortion + argmin ------------------------------------------
+// FP32 search over all n frames.  idx[v] = argmin (first index on ties among the
+// FP32 values); frames whose best-two gap is below
+//     gap_scale * rx[0] * (*w1max)
+// are appended to flag_list (count in *flag_count, which the caller zeroes).
+void launch_assign_f32(const float *x32, long n, int D, const float *w32, int K,
+                       const float *w1max, float gap_scale, int32_t *idx,
+                       int32_t *flag_list, int32_t *flag_count, int num_sms,
+                       cudaStream_t s);
+
+// FP64 search.  list == nullptr: all n frames.  Otherwise only the frames
+// list[0 .. *list_count) (device-side count; no host sync).  Exact reference
+// semantics: strict '<' in index order, so the first of equal minima wins.
+void launch_assign_f64(const double *x64, long n, int D, const double *w64, int K,
+                       const int32_t *list, const int32_t *list_count, int32_t *idx,
+                       int num_sms, cudaStream_t s);
+
+// ---- (b) cell accumulation ----------------------------------------------------
+// For every frame: dd = FP64 distortion against its codeword raas[idx];
+//   mindist[v] = dd - 1 (if mindist != nullptr); seq[v] = (u16) idx (if seq != nullptr)
+//   with_cells: packed.cells[idx] += rx, counts[idx] += 1, discel[idx] += dd - 1
+//   packed.dd += dd - 1 ; packed.inertia += dd * dd
+void launch_accumulate(const double *x64, const int32_t *idx, long n, int D,
+                       const double *raas, int K, double *packed, double *mindist,
+                       uint16_t *seq, bool with_cells, int num_sms, cudaStream_t s);
+
+// ---- (c) centroid update / split ----------------------------------------------
+// calculate_reflections (vq_learn.i:125-155): for every cell with count > 0,
+// Levinson-Durbin on the raw cell sum -> refl, raas; cell sum /= errPred.
+void launch_centroids(double *packed, int K, int D, double *refl, double *raas,
+                      cudaStream_t s);
+// grow_codebook (vq_learn.i:47-72): refl K -> 2K rows (x 0.99f / x 1.01f), then
+// reflections_to_raas over all 2K rows.
+void launch_grow(double *refl, double *raas, int K, int D, cudaStream_t s);
+// reflections_to_raas (ref2raas.c:8-26)
+void launch_refl_to_raas(const double *refl, double *raas, int K, int D, cudaStream_t s);
+
+// ---- stage evaluation -----------------------------------------------------------
+// *out += sum_{i != j} [ distortion(cells_j, raas_i) - 1 ]      (sigma.c:14-25)
+void launch_sigma_sum(const double *raas, const double *cells, int K, int D, double *out,
+                      cudaStream_t s);
+
+}  // namespace vqb200

@@ -1,0 +1,250 @@
+/* ecoz2_vq_b200.h -- C ABI of the B200-native ECOZ2 vector-quantization path.
+ *
+ * Shared library: ecoz2rs_b200/csrc/libecoz2_vq_b200.so (built by
+ * ecoz2rs_b200/csrc/Makefile, CUDA sm_100a).  No torch / C++ types cross this
+ * boundary: plain pointers, sizes and opaque handles only.
+ *
+ * PART 1 is the drop-in boundary: the three `ecoz2_vq_*` entry points of the
+ * reference's public C API with identical signatures and file/callback
+ * behaviour, i.e. exactly what the Rust crate's `extern "C"` block
+ * (reference src/ecoz2_lib/mod.rs:96-122) and the C mains
+ * (reference ecoz2/src/x/vq.learn.c:107-128, vq.quantize.c:41) bind.
+ *
+ * PART 2 is the in-memory API the host mirror (ecoz2rs_b200/vq.py), the parity
+ * tests and bench.py call: the same algorithm steps with the frames / codebooks
+ * passed as arrays instead of `.prd` / `.cbook` files.
+ *
+ * There is NO CPU fallback: every compute entry point needs a CUDA device and
+ * returns ECOZ2B200_ERR_CUDA (with a message on stderr) when there is none.
+ */
+#ifndef ECOZ2_VQ_B200_H
+#define ECOZ2_VQ_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ===================================================================== PART 1
+ * Drop-in replacements (reference ecoz2/src/include/ecoz2.h).               */
+
+/* reference ecoz2/src/include/ecoz2.h:56-59.  Invoked synchronously on the
+ * calling thread once per finished codebook size, after the `.cbook` is saved
+ * and before the stage report is written (ecoz2/src/vq/vq_learn_par.c:133-143). */
+typedef void (*vq_learn_callback_t)(void *callback_target, int M,
+                                    double avgDistortion, double sigma,
+                                    double inertia);
+
+/* reference ecoz2/src/include/ecoz2.h:62-70 -> ecoz2/src/ecoz2/ecoz2.c:109-129
+ * -> ecoz2/src/vq/vq_learn.c:7-32.  LBG from 2 codewords up to
+ * ECOZ2_VQ_MAX_M (env, default 4096 = the reference's MAX_CODEBOOK_SIZE).
+ * Writes data/codebooks/<class>/eps_<e>_M_<KKKK>.cbook (+ .rpt, .rpt.csv,
+ * .cards_dists.csv, .min_dists.csv) relative to the CWD.
+ * Returns 0 ok, 2 predictor load failure, 1 memory/codebook, 3 CUDA failure. */
+int ecoz2_vq_learn(int prediction_order, double epsilon,
+                   const char *codebook_class_name,
+                   const char *predictor_filenames[], int num_predictors,
+                   void *callback_target, vq_learn_callback_t callback);
+
+/* reference ecoz2/src/include/ecoz2.h:73-80 -> ecoz2/src/vq/vq_learn.c:34-77.
+ * Resume: loads reflections from `base_codebook`, starts at twice its size. */
+int ecoz2_vq_learn_using_base_codebook(char *base_codebook, double epsilon,
+                                       const char *predictor_filenames[],
+                                       int num_predictors,
+                                       void *callback_target,
+                                       vq_learn_callback_t callback);
+
+/* reference ecoz2/src/include/ecoz2.h:82-87 -> ecoz2/src/vq/vq_quantize.c:13-111.
+ * One `.seq` per `.prd` under data/sequences[/TRAIN|/TEST]/M<K>/<class>/. */
+int ecoz2_vq_quantize(const char *nom_raas, const char *predictor_filenames[],
+                      int num_predictors, int show_filenames);
+
+/* ===================================================================== PART 2
+ * In-memory API.                                                            */
+
+#define ECOZ2B200_OK 0
+#define ECOZ2B200_ERR_ARG 1
+#define ECOZ2B200_ERR_IO 2
+#define ECOZ2B200_ERR_CUDA 3
+#define ECOZ2B200_ERR_NCCL 4
+
+/* Arithmetic mode of the nearest-codeword search (reference
+ * ecoz2/src/vq/vq_learn_par.c:62-81, quantize.c:14-30 are FP64).
+ *   FP32:  FP32 FFMA search + FP64 re-evaluation of every frame whose best-two
+ *          gap is inside the FP32 error bound (default; index-exact vs FP64).
+ *   FP64:  the whole search in FP64 (verification mode).
+ *   TF32X3: tcgen05 tensor-core search with split-TF32 operands + the same
+ *          FP64 re-evaluation (when compiled in; else ERR_ARG).               */
+#define ECOZ2B200_MODE_FP32 0
+#define ECOZ2B200_MODE_FP64 1
+#define ECOZ2B200_MODE_TF32X3 2
+
+typedef struct ecoz2b200_engine ecoz2b200_engine;
+
+const char *ecoz2b200_version(void);
+/* last error message of the calling thread ("" if none) */
+const char *ecoz2b200_last_error(void);
+/* number of visible CUDA devices (0 if none / no driver) */
+int ecoz2b200_device_count(void);
+
+/* One engine = the frames of ONE process, sharded over `num_devices` local
+ * GPUs (device ordinals in `devices`), plus the replicated codebook state.
+ * `max_M` bounds the codebook size (<= 65536, Symbol is u16:
+ * reference ecoz2/src/include/symbol.h:7).                                   */
+ecoz2b200_engine *ecoz2b200_create(const int *devices, int num_devices, int P,
+                                   int max_M);
+void ecoz2b200_destroy(ecoz2b200_engine *e);
+
+int ecoz2b200_set_mode(ecoz2b200_engine *e, int mode);
+/* kappa of the FP32 ambiguity bound: a frame is re-evaluated in FP64 when
+ * d2 - d1 < 2 * kappa * 2^-24 * rx[0] * max_i sum_n |w_i[n]|.                 */
+int ecoz2b200_set_recheck_kappa(ecoz2b200_engine *e, double kappa);
+
+/* Multi-process sharding (one process per GPU, e.g. under torchrun): all ranks
+ * call comm_init with the same 128-byte id obtained once from
+ * ecoz2b200_nccl_unique_id().  Afterwards every k-means pass ends with ONE
+ * ncclAllReduce(sum, f64) of the packed [K*(P+1) cell sums | K counts |
+ * K cell distortions | DD] buffer.  Engines with several local devices and no
+ * comm_init use ncclCommInitAll internally.                                   */
+int ecoz2b200_nccl_unique_id(unsigned char id_out[128]);
+int ecoz2b200_comm_init(ecoz2b200_engine *e, const unsigned char id[128],
+                        int rank, int world_size);
+
+/* ---- frames (the Predictor vectors, reference ecoz2/src/include/lpc.h:29-34:
+ * N rows of D = P+1 gain-normalised autocorrelations, FP64).
+ * Frames are appended in call order and split into contiguous blocks over the
+ * engine's devices when `frames_commit` is called.                            */
+int ecoz2b200_frames_clear(ecoz2b200_engine *e);
+/* Announce the total number of frames that will be appended: fixes the shard
+ * boundaries so every append is copied straight to its GPU.  Required before
+ * appending when the engine has more than one device; optional otherwise.    */
+int ecoz2b200_frames_reserve(ecoz2b200_engine *e, long total);
+/* host buffer, row-major [n][P+1] f64 (copied) */
+int ecoz2b200_frames_append_host(ecoz2b200_engine *e, const double *x, long n);
+/* device buffer on devices[0], row-major [n][P+1] f64 (copied device->device) */
+int ecoz2b200_frames_append_device(ecoz2b200_engine *e, const double *x_dev,
+                                   long n);
+int ecoz2b200_frames_commit(ecoz2b200_engine *e);
+long ecoz2b200_frames_count(const ecoz2b200_engine *e);
+
+/* ---- codebook state (replicated on every device) -------------------------- */
+/* reference ecoz2/src/vq/vq_learn.i:31-44 : 2 codewords, k1 = -/+0.5 */
+int ecoz2b200_codebook_initial(ecoz2b200_engine *e);
+/* set from reflections [K][P+1] (reference cb_load + reflections_to_raas,
+ * ecoz2/src/vq/vq_quantize.c:25-40, ecoz2/src/lpc/ref2raas.c:8-26) */
+int ecoz2b200_codebook_set_reflections(ecoz2b200_engine *e, const double *refl,
+                                       int K);
+/* set raas directly [K][P+1] (teacher forcing in tests; reflections zeroed) */
+int ecoz2b200_codebook_set_raas(ecoz2b200_engine *e, const double *raas, int K);
+/* reference grow_codebook, ecoz2/src/vq/vq_learn.i:47-72 : K -> 2K */
+int ecoz2b200_codebook_grow(ecoz2b200_engine *e);
+int ecoz2b200_codebook_size(const ecoz2b200_engine *e);
+/* copy out [K][P+1] f64; either pointer may be NULL */
+int ecoz2b200_codebook_get(ecoz2b200_engine *e, double *refl_out,
+                           double *raas_out);
+
+/* ---- steps ------------------------------------------------------------------ */
+/* Nearest codeword for every frame (strict '<', first index wins).
+ * Outputs are host buffers over ALL local frames in append order; any may be
+ * NULL.  idx: int32 [N]; ddmin: f64 [N] raw distortion of the winner (the
+ * reference's ddmin, before the -1).  *num_rechecked: frames re-evaluated in
+ * FP64.  reference ecoz2/src/vq/vq_learn_par.c:62-81                           */
+int ecoz2b200_assign(ecoz2b200_engine *e, int32_t *idx_out, double *ddmin_out,
+                     long *num_rechecked);
+
+/* One k-means pass: assign + cell accumulation (+ allreduce) + centroid update.
+ * reference ecoz2/src/vq/vq_learn_par.c:50-125, vq_learn.i:84-155.
+ * Host outputs (any may be NULL): cells [K][P+1] raw sums (before the errPred
+ * normalisation), cardd int32 [K], discel f64 [K], *DD.
+ * After the call the engine's codebook is the post-update one and its cell
+ * buffer holds the errPred-normalised sums (for sigma).                        */
+int ecoz2b200_kmeans_pass(ecoz2b200_engine *e, double *cells_out,
+                          int32_t *cardd_out, double *discel_out,
+                          double *DD_out);
+
+/* reference calculateSigma, ecoz2/src/vq/sigma.c:12-29, on the engine's current
+ * codebook and normalised cells (i.e. right after kmeans_pass). */
+int ecoz2b200_sigma(ecoz2b200_engine *e, double avgDistortion, double *sigma_out);
+/* reference calculateInertia, ecoz2/src/vq/inertia.c:10-31 (global over ranks) */
+int ecoz2b200_inertia(ecoz2b200_engine *e, double *inertia_out);
+
+/* Per-frame assignment of the LAST pass (local frames): idx int32 [N] and
+ * minDist f64 [N] (= ddmin - 1, reference CodewordAndMinDist,
+ * ecoz2/src/include/vq.h:60-63).                                               */
+int ecoz2b200_last_assignment(ecoz2b200_engine *e, int32_t *idx_out,
+                              double *mindist_out);
+
+/* ---- whole LBG run (reference learn_par, ecoz2/src/vq/vq_learn_par.c:3-167) -- */
+typedef struct {
+    int M;                 /* codebook size of the finished stage */
+    int passes;            /* pass + 1 */
+    double avgDistortion;  /* DD / N of the last pass (pre-update codebook) */
+    double sigma;
+    double inertia;
+    const double *reflections; /* [M][P+1] post-update (what cb_save writes) */
+    const double *raas;        /* [M][P+1] post-update */
+    const int32_t *cardd;      /* [M] */
+    const double *discel;      /* [M] */
+    double stage_seconds;      /* wall time of this stage (host clock) */
+    double assign_ms;          /* device time in the search kernels, this stage */
+    double evals;              /* frame x codeword evaluations, this stage (global) */
+} ecoz2b200_stage_info;
+
+typedef void (*ecoz2b200_stage_cb)(void *ctx, const ecoz2b200_stage_info *info);
+typedef void (*ecoz2b200_pass_cb)(void *ctx, int M, int pass, double DD,
+                                  double pass_seconds, int empty_cells);
+
+/* Starts from the engine's current codebook (initial / set_reflections+grow),
+ * runs until the codebook size reaches `stop_M` (the reference's
+ * MAX_CODEBOOK_SIZE, ecoz2/src/vq/vq_learn_par.c:147).  Both callbacks run on
+ * the calling thread.                                                          */
+int ecoz2b200_learn(ecoz2b200_engine *e, double epsilon, int stop_M,
+                    ecoz2b200_stage_cb on_stage, ecoz2b200_pass_cb on_pass,
+                    void *ctx);
+
+/* ---- quantize (reference quantize, ecoz2/src/vq/quantize.c:8-34) ------------ */
+/* Host in, host out: frames [T][P+1] f64 against the engine's current codebook;
+ * seq u16 [T] (may be NULL), *avg_distortion = sum(ddmin - 1) / T.
+ * Includes the host->device and device->host copies (the e2e path); uses the
+ * engine's devices, T split in contiguous blocks.  Does not disturb the
+ * engine's resident training frames.                                           */
+int ecoz2b200_quantize_host(ecoz2b200_engine *e, const double *x, long T,
+                            uint16_t *seq_out, double *avg_distortion);
+/* Same on the engine's resident frames (inputs already in HBM); seq_out is a
+ * host buffer of frames_count() entries or NULL.                               */
+int ecoz2b200_quantize_resident(ecoz2b200_engine *e, uint16_t *seq_out,
+                                double *avg_distortion);
+
+/* ---- timing / counters (CUDA events on the engine's own streams) ------------ */
+typedef struct {
+    double assign_ms;      /* search kernels (incl. FP64 re-evaluation) */
+    double accumulate_ms;  /* cell accumulation */
+    double update_ms;      /* centroid / split / codebook staging */
+    double allreduce_ms;   /* NCCL */
+    long kernel_launches;  /* kernels launched by this library since reset */
+    double evals;          /* frame x codeword evaluations since reset (local) */
+    long rechecked;        /* frames re-evaluated in FP64 since reset */
+} ecoz2b200_counters;
+int ecoz2b200_counters_reset(ecoz2b200_engine *e);
+int ecoz2b200_counters_get(ecoz2b200_engine *e, ecoz2b200_counters *out);
+
+/* ---- file formats (byte-compatible with the reference) ---------------------- */
+/* `.prd` header probe, reference ecoz2/src/lpc/prd.c:34-74 */
+int ecoz2b200_prd_info(const char *path, int *P, int *T, char class_name[96]);
+/* reads the T x (P+1) f64 payload into `out` */
+int ecoz2b200_prd_read(const char *path, double *out, long capacity_values);
+/* reference cb_save / cb_load, ecoz2/src/vq/vq.c:22-116 */
+int ecoz2b200_cbook_save(const char *path, const char *class_name,
+                         const double *reflections, int M, int P);
+int ecoz2b200_cbook_info(const char *path, int *P, int *M, char class_name[96]);
+int ecoz2b200_cbook_read(const char *path, double *refl_out,
+                         long capacity_values);
+/* reference seq_save, ecoz2/src/hmm/symbol.c:17-36 */
+int ecoz2b200_seq_save(const char *path, const char *class_name,
+                       const uint16_t *seq, int T, int M);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* ECOZ2_VQ_B200_H */
