@@ -436,7 +436,39 @@ int ecoz2b200_counters_get(ecoz2b200_engine *e, ecoz2b200_counters *out) {
     out->kernel_launches = c.kernel_launches;
     out->evals = c.evals;
     out->rechecked = c.rechecked;
+    out->search_main_ms = c.search_main_ms;
+    out->search_main_launches = c.search_main_launches;
     return ECOZ2B200_OK;
+}
+
+double ecoz2b200_ffma_peak_tflops(int device, double millis) {
+    if (cudaSetDevice(device) != cudaSuccess) return 0.0;
+    cudaDeviceProp prop;
+    if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 0.0;
+    float *out = nullptr;
+    if (cudaMalloc(&out, 16) != cudaSuccess) return 0.0;
+    cudaEvent_t a, b;
+    cudaEventCreate(&a);
+    cudaEventCreate(&b);
+    const int blocks = prop.multiProcessorCount * 8;
+    int iters = 2000;
+    double best = 0.0;
+    for (int rep = 0; rep < 6; rep++) {
+        cudaEventRecord(a, 0);
+        vqb200::launch_ffma_probe(out, blocks, iters, 0);
+        cudaEventRecord(b, 0);
+        if (cudaEventSynchronize(b) != cudaSuccess) break;
+        float ms = 0;
+        cudaEventElapsedTime(&ms, a, b);
+        const double flops = 2.0 * 128.0 * iters * 256.0 * blocks;
+        const double tf = flops / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+        if (ms < millis && iters < (1 << 24)) iters = (int) (iters * (millis / (ms > 0.01 ? ms : 0.01)) * 1.05) + 1;
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    cudaFree(out);
+    return best;
 }
 
 int ecoz2b200_prd_info(const char *path, int *P, int *T, char class_name[96]) {

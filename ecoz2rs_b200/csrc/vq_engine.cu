@@ -411,8 +411,10 @@ int Engine::codebook_get(double *refl_out, double *raas_out) {
 void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
                     int32_t *flag_list) {
     if (n <= 0) return;
+    cudaEventRecord(s.ev[6], s.stream);
     if (mode_ == ECOZ2B200_MODE_FP64) {
         launch_assign_f64(x64, n, D_, s.w64, K_, nullptr, nullptr, idx, s.num_sms, s.stream);
+        cudaEventRecord(s.ev[7], s.stream);
         ctr_.kernel_launches += 1;
     } else {
         // |error| of one FP32 distortion <= kappa * 2^-24 * rx[0] * sum|w|; two values compared
@@ -420,6 +422,7 @@ void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32
         cudaMemsetAsync(s.flag_count, 0, sizeof(int32_t), s.stream);
         launch_assign_f32(x32, n, D_, s.w32, K_, s.w1max, gap_scale, idx, flag_list, s.flag_count,
                           s.num_sms, s.stream);
+        cudaEventRecord(s.ev[7], s.stream);
         launch_assign_f64(x64, n, D_, s.w64, K_, flag_list, s.flag_count, idx, s.num_sms, s.stream);
         ctr_.kernel_launches += 2;
     }
@@ -476,6 +479,14 @@ void Engine::harvest_times(bool with_cells) {
             if (cudaEventElapsedTime(&ms, s.ev[3], s.ev[4]) == cudaSuccess && ms > d) d = ms;
         }
     }
+    double m = 0;
+    for (Shard &s : shards_) {
+        cudaSetDevice(s.device);
+        float ms = 0;
+        if (s.n > 0 && cudaEventElapsedTime(&ms, s.ev[6], s.ev[7]) == cudaSuccess && ms > m) m = ms;
+    }
+    ctr_.search_main_ms += m;
+    ctr_.search_main_launches += 1;
     ctr_.assign_ms += a;
     ctr_.accumulate_ms += b;
     ctr_.allreduce_ms += c;

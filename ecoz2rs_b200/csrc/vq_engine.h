@@ -22,7 +22,7 @@ struct Shard {
     int device = 0;
     int num_sms = 148;
     cudaStream_t stream = nullptr;
-    cudaEvent_t ev[6] = {};   // phase boundaries of the current pass
+    cudaEvent_t ev[8] = {};   // phase boundaries of the current pass (ev[6], ev[7]: FP32 search)
     void *comm = nullptr;     // ncclComm_t
 
     long n = 0;               // frames resident on this shard
@@ -49,6 +49,8 @@ struct Shard {
 
 struct Counters {
     double assign_ms = 0, accumulate_ms = 0, update_ms = 0, allreduce_ms = 0;
+    double search_main_ms = 0;  // the dominant kernel alone (FP32 / FP64 full search)
+    long search_main_launches = 0;
     long kernel_launches = 0;
     double evals = 0;
     long rechecked = 0;

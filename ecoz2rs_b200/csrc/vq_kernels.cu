@@ -684,4 +684,25 @@ void launch_sigma_sum(const double *raas, const double *cells, int K, int D, dou
     vq_sigma_sum<<<K, 256, 0, s>>>(raas, cells, K, D, out);
 }
 
+// --------------------------------------------------------------------------------
+// FP32 FFMA peak probe: 8 independent FMA chains per thread, nothing else.  Gives
+// the measured denominator of the FP32 roofline on the box the bench runs on.
+// --------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) vq_ffma_probe(float *out, int iters, float a, float b) {
+    float c0 = threadIdx.x, c1 = c0 + 1.f, c2 = c0 + 2.f, c3 = c0 + 3.f;
+    float c4 = c0 + 4.f, c5 = c0 + 5.f, c6 = c0 + 6.f, c7 = c0 + 7.f;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            c0 = fmaf(c0, a, b); c1 = fmaf(c1, a, b); c2 = fmaf(c2, a, b); c3 = fmaf(c3, a, b);
+            c4 = fmaf(c4, a, b); c5 = fmaf(c5, a, b); c6 = fmaf(c6, a, b); c7 = fmaf(c7, a, b);
+        }
+    }
+    const float r = ((c0 + c1) + (c2 + c3)) + ((c4 + c5) + (c6 + c7));
+    if (r == 123.456f) out[0] = r;  // keep the chains alive
+}
+void launch_ffma_probe(float *out, int blocks, int iters, cudaStream_t s) {
+    vq_ffma_probe<<<blocks, 256, 0, s>>>(out, iters, 0.999f, 0.001f);
+}
+
 }  // namespace vqb200

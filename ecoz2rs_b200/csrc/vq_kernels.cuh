@@ -81,4 +81,7 @@ void launch_refl_to_raas(const double *refl, double *raas, int K, int D, cudaStr
 void launch_sigma_sum(const double *raas, const double *cells, int K, int D, double *out,
                       cudaStream_t s);
 
+// FP32 FFMA probe: blocks x 256 threads x iters x 128 FMAs each
+void launch_ffma_probe(float *out, int blocks, int iters, cudaStream_t s);
+
 }  // namespace vqb200

@@ -84,8 +84,9 @@ def ar_mix(N: int, P: int, C: int = DEFAULT_CENTRES, seed: int = 0,
 
 
 def ar_mix_torch(N: int, P: int, C: int = DEFAULT_CENTRES, seed: int = 0,
-                 device="cuda", chunk: int = 1 << 20, out=None):
-    """torch back end (same formulae; torch's random stream).  float64 [N, P+1] on `device`."""
+                 device="cuda", chunk: int = 1 << 20, out=None, stream_id: int = 0):
+    """torch back end (same formulae; torch's random stream).  float64 [N, P+1] on `device`.
+    `stream_id` selects an independent frame stream of the SAME mixture (one per rank)."""
     import torch
 
     rng = np.random.default_rng(seed)
@@ -93,7 +94,7 @@ def ar_mix_torch(N: int, P: int, C: int = DEFAULT_CENTRES, seed: int = 0,
     centres = torch.from_numpy(rng.normal(size=(C, P)) * sig_np).to(device)
     sig = torch.from_numpy(sig_np).to(device)
     gen = torch.Generator(device=device)
-    gen.manual_seed(int(seed))
+    gen.manual_seed(int(seed) + 1000003 * int(stream_id))
     if out is None:
         out = torch.empty((N, P + 1), dtype=torch.float64, device=device)
     for lo in range(0, N, chunk):

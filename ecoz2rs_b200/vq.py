@@ -43,7 +43,8 @@ class StageInfo(C.Structure):
 class Counters(C.Structure):
     _fields_ = [("assign_ms", C.c_double), ("accumulate_ms", C.c_double),
                 ("update_ms", C.c_double), ("allreduce_ms", C.c_double),
-                ("kernel_launches", C.c_long), ("evals", C.c_double), ("rechecked", C.c_long)]
+                ("kernel_launches", C.c_long), ("evals", C.c_double), ("rechecked", C.c_long),
+                ("search_main_ms", C.c_double), ("search_main_launches", C.c_long)]
 
 
 _STAGE_CB = C.CFUNCTYPE(None, C.c_void_p, C.POINTER(StageInfo))
@@ -63,7 +64,7 @@ EXPORTED_SYMBOLS = (
     "ecoz2b200_assign", "ecoz2b200_kmeans_pass", "ecoz2b200_sigma", "ecoz2b200_inertia",
     "ecoz2b200_last_assignment", "ecoz2b200_learn",
     "ecoz2b200_quantize_host", "ecoz2b200_quantize_resident",
-    "ecoz2b200_counters_reset", "ecoz2b200_counters_get",
+    "ecoz2b200_counters_reset", "ecoz2b200_counters_get", "ecoz2b200_ffma_peak_tflops",
     "ecoz2b200_prd_info", "ecoz2b200_prd_read", "ecoz2b200_cbook_save", "ecoz2b200_cbook_info",
     "ecoz2b200_cbook_read", "ecoz2b200_seq_save",
 )
@@ -117,6 +118,7 @@ def lib():
             "ecoz2b200_quantize_resident": (i, [vp, vp, _dp]),
             "ecoz2b200_counters_reset": (i, [vp]),
             "ecoz2b200_counters_get": (i, [vp, C.POINTER(Counters)]),
+            "ecoz2b200_ffma_peak_tflops": (d, [i, d]),
             "ecoz2b200_prd_info": (i, [C.c_char_p, C.POINTER(i), C.POINTER(i), C.c_char_p]),
             "ecoz2b200_prd_read": (i, [C.c_char_p, _dp, l]),
             "ecoz2b200_cbook_save": (i, [C.c_char_p, C.c_char_p, _dp, i, i]),
@@ -379,6 +381,11 @@ def vq_quantize(nom_raas: str, predictor_filenames: Sequence[str], show_filename
     """`ecoz2_vq_quantize` (reference src/ecoz2_lib/mod.rs:325-342)."""
     return lib().ecoz2_vq_quantize(os.fsencode(nom_raas), _file_array(predictor_filenames),
                                    len(predictor_filenames), int(show_filenames))
+
+
+def ffma_peak_tflops(device: int = 0, millis: float = 20.0) -> float:
+    """Measured FP32 FFMA peak of `device` (TFLOP/s): denominator of the FP32 roofline."""
+    return lib().ecoz2b200_ffma_peak_tflops(device, millis)
 
 
 def nccl_unique_id() -> bytes:

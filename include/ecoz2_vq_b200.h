@@ -225,9 +225,16 @@ typedef struct {
     long kernel_launches;  /* kernels launched by this library since reset */
     double evals;          /* frame x codeword evaluations since reset (local) */
     long rechecked;        /* frames re-evaluated in FP64 since reset */
+    double search_main_ms; /* the dominant kernel alone: the full search over all frames
+                              (FP32 pass in FP32 mode), CUDA events on its stream */
+    long search_main_launches;
 } ecoz2b200_counters;
 int ecoz2b200_counters_reset(ecoz2b200_engine *e);
 int ecoz2b200_counters_get(ecoz2b200_engine *e, ecoz2b200_counters *out);
+
+/* Measured FP32 FFMA throughput of `device` in TFLOP/s (a pure FMA-chain kernel
+ * filling every SM for ~`millis` ms): the denominator of the FP32 roofline.    */
+double ecoz2b200_ffma_peak_tflops(int device, double millis);
 
 /* ---- file formats (byte-compatible with the reference) ---------------------- */
 /* `.prd` header probe, reference ecoz2/src/lpc/prd.c:34-74 */

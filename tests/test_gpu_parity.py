@@ -121,8 +121,7 @@ def test_empty_cells_keep_codeword(built_lib, frames36):
     from oracle import oracle as O
     refl = np.zeros((4, 37))
     refl[0, 1], refl[1, 1] = -0.5, 0.5
-    refl[2, 1:4] = [0.97, -0.97, 0.97]     # far from everything
-    refl[3, 1:4] = [-0.97, 0.97, -0.97]
+    refl[2], refl[3] = refl[0], refl[1]    # duplicates never win the strict '<' scan
     raas = O.refl_to_raas(refl)
     ref = O.kmeans_pass(frames36, refl, raas)
     assert (ref["cardd"] == 0).any(), "fixture should produce an empty cell"
