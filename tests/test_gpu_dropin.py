@@ -1,0 +1,136 @@
+"""GPU tests of the drop-in boundary: the three `ecoz2_vq_*` entry points (and the
+`ecoz2` CLI on top of them) run on `.prd` files and their output files are compared
+with what the REFERENCE executables wrote for the same inputs (tests/golden)."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def _read_rpt_csv(path):
+    rows = []
+    for line in open(path, encoding="utf-8"):
+        if line.startswith("#") or line.startswith("M,"):
+            continue
+        p = line.strip().split(",")
+        rows.append((int(p[0]), int(p[1]), float(p[2]), float(p[3]), float(p[4])))
+    return rows
+
+
+@pytest.fixture()
+def in_tmp_cwd(tmp_path, monkeypatch):
+    monkeypatch.chdir(tmp_path)
+    return tmp_path
+
+
+@pytest.mark.parametrize("tag,P", [("P36", 36), ("P12", 12)])
+def test_vq_learn_files_match_reference(built_lib, in_tmp_cwd, monkeypatch, tag, P):
+    from ecoz2rs_b200 import formats, vq
+    g = np.load(os.path.join(GOLD, f"learn_{tag}.npz"))
+    x = g["x"]
+    # two .prd files: the learner concatenates them in argument order (vq_learn.i:198-217)
+    half = len(x) // 2
+    f1 = str(in_tmp_cwd / "predictors" / "TRAIN" / "gold" / "a.prd")
+    f2 = str(in_tmp_cwd / "predictors" / "TRAIN" / "gold" / "b.prd")
+    formats.write_prd(f1, x[:half], "gold")
+    formats.write_prd(f2, x[half:], "gold")
+    monkeypatch.setenv("ECOZ2_VQ_MAX_M", "256")
+    calls = []
+    rc = vq.vq_learn(P, 0.05, "gold", [f1, f2], callback=lambda M, a, s, i: calls.append((M, a, s, i)))
+    assert rc == 0
+    cdir = in_tmp_cwd / "data" / "codebooks" / "gold"
+    rows = _read_rpt_csv(cdir / "eps_0.05.rpt.csv")
+    ref_rows = g["rpt_csv"]
+    assert [(r[0], r[1]) for r in rows] == [(int(r[0]), int(r[1])) for r in ref_rows]
+    assert [c[0] for c in calls] == [r[0] for r in rows]
+    for r, rr, c in zip(rows, ref_rows, calls):
+        assert abs(r[2] - rr[2]) <= 1e-4 * rr[2] + 2e-6
+        assert abs(r[3] - rr[3]) <= 1e-4 * abs(rr[3]) + 2e-6
+        assert abs(r[4] - rr[4]) <= 1e-4 * abs(rr[4]) + 2e-6
+        assert abs(c[1] - rr[2]) <= 1e-4 * rr[2] + 2e-6      # callback carries the same values
+        M = r[0]
+        cls, refl = formats.read_cbook(str(cdir / f"eps_0.05_M_{M:04d}.cbook"))
+        assert cls == "gold"
+        ref_refl = g[f"refl_{M}"]
+        scale = np.abs(ref_refl).max(axis=1, keepdims=True)
+        assert np.all(np.abs(refl - ref_refl) <= 1e-4 * scale)
+        assert np.all(refl[:, 0] == 0)                        # reflections[.][0] stays 0
+        cards = np.genfromtxt(cdir / f"eps_0.05_M_{M:04d}.cbook.cards_dists.csv", delimiter=",",
+                              skip_header=1).reshape(-1, 3)
+        assert np.abs(cards[:, 1] - g[f"cards_{M}"][:, 1]).sum() <= 2
+    md = np.genfromtxt(cdir / f"eps_0.05_M_{rows[-1][0]:04d}.cbook.min_dists.csv", delimiter=",",
+                       skip_header=1)
+    ref_md = g["last_min_dists"]
+    assert (md[:, 0] != ref_md[:, 0]).mean() <= 1e-3
+    same = md[:, 0] == ref_md[:, 0]
+    assert np.allclose(md[same, 1], ref_md[same, 1], rtol=0, atol=2e-6)
+    # header lines of the report files are the reference's
+    head = open(cdir / "eps_0.05.rpt.csv", encoding="utf-8").read().splitlines()[:2]
+    ref_head = g["rpt_csv_text"].tobytes().decode("utf-8").splitlines()[:2]
+    assert head == ref_head
+    assert (cdir / "eps_0.05.rpt").exists()
+
+
+def test_vq_learn_from_base_codebook_and_errors(built_lib, in_tmp_cwd, monkeypatch):
+    from ecoz2rs_b200 import formats, vq
+    g = np.load(os.path.join(GOLD, "learn_P36.npz"))
+    f1 = str(in_tmp_cwd / "predictors" / "TRAIN" / "gold" / "a.prd")
+    formats.write_prd(f1, g["x"], "gold")
+    base = str(in_tmp_cwd / "base.cbook")
+    formats.write_cbook(base, g["refl_16"], "gold")
+    monkeypatch.setenv("ECOZ2_VQ_MAX_M", "64")
+    monkeypatch.setenv("ECOZ2_VQ_MIN_DISTS", "0")
+    assert vq.vq_learn_using_base_codebook(base, 0.05, [f1]) == 0
+    cdir = in_tmp_cwd / "data" / "codebooks" / "gold"
+    assert sorted(p.name for p in cdir.glob("*.cbook")) == ["eps_0.05_M_0032.cbook", "eps_0.05_M_0064.cbook"]
+    assert not list(cdir.glob("*.min_dists.csv"))
+    for M in (32, 64):
+        _, refl = formats.read_cbook(str(cdir / f"eps_0.05_M_{M:04d}.cbook"))
+        ref = g[f"refl_{M}"]
+        assert np.all(np.abs(refl - ref) <= 1e-4 * np.abs(ref).max(axis=1, keepdims=True))
+    # error codes: missing predictor -> 2 ; missing base codebook -> 2 (vq_learn.i:203-206, vq_learn.c:49-52)
+    assert vq.vq_learn(36, 0.05, "gold", [str(in_tmp_cwd / "nope.prd")]) == 2
+    assert vq.vq_learn_using_base_codebook(str(in_tmp_cwd / "nope.cbook"), 0.05, [f1]) == 2
+    assert vq.vq_quantize(str(in_tmp_cwd / "nope.cbook"), [f1]) == 1
+
+
+def test_vq_quantize_seq_bytes_match_reference(built_lib, in_tmp_cwd):
+    from ecoz2rs_b200 import formats, vq
+    q = np.load(os.path.join(GOLD, "quantize_P36.npz"))
+    prd = str(in_tmp_cwd / "predictors" / "TRAIN" / "gold" / "x.prd")
+    formats.write_prd(prd, q["x"], "gold")
+    cb = str(in_tmp_cwd / "cb.cbook")
+    formats.write_cbook(cb, q["refl"], "gold")
+    assert vq.vq_quantize(cb, [prd], show_filenames=False) == 0
+    M = q["refl"].shape[0]
+    out = in_tmp_cwd / "data" / "sequences" / "TRAIN" / f"M{M}" / "gold" / "x.seq"
+    assert out.read_bytes() == q["seq_file_bytes"].tobytes()
+
+
+def test_cli_learn_and_quantize(built_lib, in_tmp_cwd):
+    """`ecoz2 vq learn` / `ecoz2 vq quantize` with the reference's option names."""
+    from ecoz2rs_b200 import formats
+    q = np.load(os.path.join(GOLD, "quantize_P36.npz"))
+    d = in_tmp_cwd / "predictors" / "TEST" / "gold"
+    formats.write_prd(str(d / "x.prd"), q["x"], "gold")
+    exe = os.path.join(ROOT, "ecoz2rs_b200", "csrc", "ecoz2")
+    env = dict(os.environ, ECOZ2_VQ_MAX_M="8", ECOZ2_VQ_MIN_DISTS="0")
+    r = subprocess.run([exe, "vq", "learn", "-P", "36", "-e", "0.05", "--class-name", "gold",
+                        "--predictors", str(in_tmp_cwd / "predictors")], env=env, capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "Ecoz2ObserverRef.step: M=8" in r.stdout
+    cb = in_tmp_cwd / "data" / "codebooks" / "gold" / "eps_0.05_M_0008.cbook"
+    assert cb.exists()
+    r = subprocess.run([exe, "vq", "quantize", "--codebook", str(cb), "--predictors", str(d / "x.prd")],
+                       env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "number of predictor files: 1" in r.stdout
+    cls, M, seq = formats.read_seq(str(in_tmp_cwd / "data" / "sequences" / "TEST" / "M8" / "gold" / "x.seq"))
+    assert (cls, M, len(seq)) == ("gold", 8, len(q["x"]))

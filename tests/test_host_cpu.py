@@ -1,0 +1,115 @@
+"""CPU tests of the host side: the C-ABI library loads and exports every symbol the
+header declares, refuses to compute without a GPU (no CPU fallback), and its file
+formats / path rules are byte-compatible with the reference (golden .cbook / .seq
+bytes written by the reference itself, tests/golden/make_golden.py)."""
+import ctypes as C
+import os
+import re
+
+import numpy as np
+import pytest
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+
+def test_library_exports_every_declared_symbol(built_lib):
+    from ecoz2rs_b200 import vq
+    with open(os.path.join(ROOT, "include", "ecoz2_vq_b200.h")) as f:
+        header = f.read()
+    declared = set(re.findall(r"\b(ecoz2b200_[a-z0-9_]+|ecoz2_vq_[a-z_]+)\s*\(", header))
+    declared -= {"ecoz2b200_stage_cb", "ecoz2b200_pass_cb"}
+    assert declared == set(vq.EXPORTED_SYMBOLS), declared ^ set(vq.EXPORTED_SYMBOLS)
+    for name in declared:
+        assert hasattr(built_lib, name), name
+
+
+def test_no_cpu_fallback(built_lib):
+    """Without a CUDA device the engine cannot be created and says why."""
+    from ecoz2rs_b200 import vq
+    if vq.device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(vq.VqError, match="no CUDA device"):
+        vq.VqEngine(36)
+    # the drop-in entry points fail with the CUDA error code instead of computing on the CPU
+    import tempfile
+    from ecoz2rs_b200 import formats
+    with tempfile.TemporaryDirectory() as tmp:
+        prd = os.path.join(tmp, "TRAIN", "c", "x.prd")
+        formats.write_prd(prd, np.ones((4, 13)), "c")
+        cwd = os.getcwd()
+        os.chdir(tmp)
+        try:
+            assert vq.vq_learn(12, 0.05, "c", [prd]) == 3
+        finally:
+            os.chdir(cwd)
+
+
+def test_product_never_imports_oracle():
+    """The oracle is test infrastructure: nothing under ecoz2rs_b200/ may reference it."""
+    pkg = os.path.join(ROOT, "ecoz2rs_b200")
+    for dirpath, _, files in os.walk(pkg):
+        if "build" in dirpath:
+            continue
+        for fn in files:
+            if fn.endswith((".py", ".cu", ".cpp", ".h", ".cuh")):
+                with open(os.path.join(dirpath, fn), errors="ignore") as f:
+                    src = f.read()
+                assert "import oracle" not in src and "from oracle" not in src, fn
+                assert "vq_oracle" not in src and "oracle/_ref" not in src, fn
+
+
+def test_formats_roundtrip_and_reference_bytes(built_lib, tmp_path):
+    from ecoz2rs_b200 import formats
+    L = built_lib
+    g = np.load(os.path.join(GOLD, "learn_P36.npz"))
+    refl = g["refl_4"]
+    ref_bytes = g["cbook_bytes_stage2"].tobytes()
+    # C++ writer == the reference's cb_save bytes
+    p = str(tmp_path / "a.cbook").encode()
+    assert L.ecoz2b200_cbook_save(p, b"gold", refl.ctypes.data_as(C.POINTER(C.c_double)), 4, 36) == 0
+    assert open(p, "rb").read() == ref_bytes
+    # numpy writer too
+    formats.write_cbook(str(tmp_path / "b.cbook"), refl, "gold")
+    assert open(tmp_path / "b.cbook", "rb").read() == ref_bytes
+    # C++ reader
+    Pp, M = C.c_int(), C.c_int()
+    cls = C.create_string_buffer(96)
+    assert L.ecoz2b200_cbook_info(p, C.byref(Pp), C.byref(M), cls) == 0
+    assert (Pp.value, M.value, cls.value) == (36, 4, b"gold")
+    out = np.empty((4, 37))
+    assert L.ecoz2b200_cbook_read(p, out.ctypes.data_as(C.POINTER(C.c_double)), out.size) == 0
+    assert np.array_equal(out, refl)
+    # .seq: C++ writer == bytes the reference's vq.quantize wrote
+    q = np.load(os.path.join(GOLD, "quantize_P36.npz"))
+    seq = np.ascontiguousarray(q["seq"], np.uint16)
+    sp = str(tmp_path / "x.seq").encode()
+    assert L.ecoz2b200_seq_save(sp, b"gold", seq.ctypes.data_as(C.POINTER(C.c_uint16)), len(seq),
+                                q["refl"].shape[0]) == 0
+    assert open(sp, "rb").read() == q["seq_file_bytes"].tobytes()
+    # .prd: numpy writer -> C++ reader
+    x = g["x"][:17]
+    pp = str(tmp_path / "TRAIN" / "cls" / "f.prd")
+    formats.write_prd(pp, x, "cls")
+    T = C.c_int()
+    assert L.ecoz2b200_prd_info(pp.encode(), C.byref(Pp), C.byref(T), cls) == 0
+    assert (Pp.value, T.value, cls.value) == (36, 17, b"cls")
+    back = np.empty_like(x)
+    assert L.ecoz2b200_prd_read(pp.encode(), back.ctypes.data_as(C.POINTER(C.c_double)), back.size) == 0
+    assert np.array_equal(back, x)
+    # errors: missing file, wrong ident, too small a buffer
+    assert L.ecoz2b200_prd_info(b"/nonexistent.prd", C.byref(Pp), C.byref(T), cls) != 0
+    assert L.ecoz2b200_prd_info(p, C.byref(Pp), C.byref(T), cls) != 0
+    assert L.ecoz2b200_prd_read(pp.encode(), back.ctypes.data_as(C.POINTER(C.c_double)), 5) != 0
+
+
+def test_class_name_header_padding(tmp_path):
+    """96-byte class field: name, NUL, then '_' padding (fileutil.c:162-182)."""
+    from ecoz2rs_b200 import formats
+    p = tmp_path / "c.cbook"
+    formats.write_cbook(str(p), np.zeros((1, 3)), "ab")
+    raw = open(p, "rb").read()
+    assert raw[:16] == b"<codebook>" + b"\0" * 6
+    assert raw[16:16 + 96] == b"ab\0" + b"_" * 93
+    assert raw[112:120] == np.array([2, 1], "<i4").tobytes()
+    assert len(raw) == 120 + 3 * 8
