@@ -90,9 +90,9 @@ Engine::Engine(const int *devices, int num_devices, int P, int max_M)
         if (!chk(cudaMalloc(&s.w32, sizeof(float) * (size_t) K32 * D_), "cudaMalloc w32")) return;
         if (!chk(cudaMalloc(&s.w64, sizeof(double) * (size_t) K64 * D_), "cudaMalloc w64")) return;
         if (!chk(cudaMalloc(&s.w1max, 16), "cudaMalloc w1max")) return;
+        if (!chk(cudaMalloc(&s.w1, sizeof(float) * (size_t) K32), "cudaMalloc w1")) return;
         if (!chk(cudaMalloc(&s.packed, sizeof(double) * L.size()), "cudaMalloc packed")) return;
         if (!chk(cudaMalloc(&s.scalars, sizeof(double) * 8), "cudaMalloc scalars")) return;
-        if (!chk(cudaMalloc(&s.flag_count, 16), "cudaMalloc flag_count")) return;
         cudaMemset(s.refl, 0, cb);
         cudaMemset(s.raas, 0, cb);
     }
@@ -107,11 +107,11 @@ Engine::~Engine() {
         if (s.stream) cudaStreamSynchronize(s.stream);
         if (s.comm && api) api->CommDestroy(s.comm);
         cudaFree(s.x64); cudaFree(s.x32); cudaFree(s.idx); cudaFree(s.idx_tmp); cudaFree(s.seq);
-        cudaFree(s.mindist); cudaFree(s.flag_list); cudaFree(s.flag_count);
-        cudaFree(s.refl); cudaFree(s.raas); cudaFree(s.w32); cudaFree(s.w64); cudaFree(s.w1max);
+        cudaFree(s.mindist); cudaFree(s.sc_mem);
+        cudaFree(s.refl); cudaFree(s.raas); cudaFree(s.w32); cudaFree(s.w64); cudaFree(s.w1max); cudaFree(s.w1);
         cudaFree(s.packed); cudaFree(s.scalars);
         QBuf &q = qbuf_[i];
-        cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.flag_list); cudaFree(q.seq);
+        cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
         for (auto &e : s.ev)
             if (e) cudaEventDestroy(e);
         if (s.stream) cudaStreamDestroy(s.stream);
@@ -205,14 +205,15 @@ int Engine::ensure_capacity(Shard &s, long n) {
         CUDA_TRY(cudaMemcpy(nx64, s.x64, sizeof(double) * (size_t) s.n * D_, cudaMemcpyDeviceToDevice));
     cudaFree(s.x64); s.x64 = nx64;
     cudaFree(s.x32); cudaFree(s.idx); cudaFree(s.idx_tmp); cudaFree(s.seq); cudaFree(s.mindist);
-    cudaFree(s.flag_list);
-    s.x32 = nullptr; s.idx = s.idx_tmp = s.flag_list = nullptr; s.seq = nullptr; s.mindist = nullptr;
+    cudaFree(s.sc_mem);
+    s.x32 = nullptr; s.idx = s.idx_tmp = nullptr; s.sc_mem = nullptr; s.seq = nullptr; s.mindist = nullptr;
     CUDA_TRY(cudaMalloc(&s.x32, sizeof(float) * (size_t) n * D_));
     CUDA_TRY(cudaMalloc(&s.idx, sizeof(int32_t) * (size_t) n));
     CUDA_TRY(cudaMalloc(&s.idx_tmp, sizeof(int32_t) * (size_t) n));
     CUDA_TRY(cudaMalloc(&s.seq, sizeof(uint16_t) * (size_t) n));
     CUDA_TRY(cudaMalloc(&s.mindist, sizeof(double) * (size_t) n));
-    CUDA_TRY(cudaMalloc(&s.flag_list, sizeof(int32_t) * (size_t) n));
+    CUDA_TRY(cudaMalloc(&s.sc_mem, scratch_bytes(n)));
+    scratch_carve(s.sc_mem, n, &s.sc);
     s.cap = n;
     return ECOZ2B200_OK;
 }
@@ -337,7 +338,7 @@ int Engine::frames_commit() {
 int Engine::stage_codebook() {
     for (Shard &s : shards_) {
         CUDA_TRY(cudaSetDevice(s.device));
-        launch_prepare_codebook(s.raas, K_, D_, s.w32, s.w64, s.w1max, s.stream);
+        launch_prepare_codebook(s.raas, K_, D_, s.w32, s.w64, s.w1, s.w1max, s.stream);
         ctr_.kernel_launches++;
     }
     return ECOZ2B200_OK;
@@ -409,7 +410,7 @@ int Engine::codebook_get(double *refl_out, double *raas_out) {
 // (a) the search on one shard: FP32 main pass + FP64 re-evaluation of the frames
 // inside the FP32 ambiguity bound, or the all-FP64 verification mode.
 void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
-                    int32_t *flag_list) {
+                    const SearchScratch &sc) {
     if (n <= 0) return;
     cudaEventRecord(s.ev[6], s.stream);
     if (mode_ == ECOZ2B200_MODE_FP64) {
@@ -417,14 +418,17 @@ void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32
         cudaEventRecord(s.ev[7], s.stream);
         ctr_.kernel_launches += 1;
     } else {
-        // |error| of one FP32 distortion <= kappa * 2^-24 * rx[0] * sum|w|; two values compared
-        const float gap_scale = (float) (2.0 * kappa_ * ldexp(1.0, -24));
-        cudaMemsetAsync(s.flag_count, 0, sizeof(int32_t), s.stream);
-        launch_assign_f32(x32, n, D_, s.w32, K_, s.w1max, gap_scale, idx, flag_list, s.flag_count,
-                          s.num_sms, s.stream);
+        // |error| of one FP32 distortion <= kappa * 2^-24 * |rx[0]| * sum_n |w[n]|.
+        // Main pass: flag when the best-two gap is below twice that bound taken with the
+        // largest codeword norm.  Re-evaluation: per-codeword norms, twice the kappa.
+        const float err_scale = (float) (kappa_ * ldexp(1.0, -24));
+        cudaMemsetAsync(sc.counters, 0, 4 * sizeof(int32_t), s.stream);
+        launch_assign_f32(x32, n, D_, s.w32, K_, sc, s.w1, s.w1max, err_scale, idx, s.num_sms,
+                          s.stream);
         cudaEventRecord(s.ev[7], s.stream);
-        launch_assign_f64(x64, n, D_, s.w64, K_, flag_list, s.flag_count, idx, s.num_sms, s.stream);
-        ctr_.kernel_launches += 2;
+        launch_recheck(x32, x64, n, D_, s.w32, s.w64, s.w1, s.w1max, s.raas, K_, 2.f * err_scale, sc,
+                       idx, s.num_sms, s.stream);
+        ctr_.kernel_launches += 5;
     }
     ctr_.evals += (double) n * K_;
 }
@@ -438,7 +442,7 @@ int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked) {
     long rechecked = 0;
     for (Shard &s : shards_) {
         CUDA_TRY(cudaSetDevice(s.device));
-        search(s, s.x64, s.x32, s.n, s.idx, s.flag_list);
+        search(s, s.x64, s.x32, s.n, s.idx, s.sc);
         CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
         launch_accumulate(s.x64, s.idx, s.n, D_, s.raas, K_, s.packed, s.mindist, nullptr, false,
                           s.num_sms, s.stream);
@@ -454,7 +458,7 @@ int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked) {
                                      cudaMemcpyDeviceToHost, s.stream));
         int32_t fc = 0;
         if (mode_ != ECOZ2B200_MODE_FP64)
-            CUDA_TRY(cudaMemcpyAsync(&fc, s.flag_count, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
+            CUDA_TRY(cudaMemcpyAsync(&fc, s.sc.counters, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
         CUDA_TRY(cudaStreamSynchronize(s.stream));
         rechecked += fc;
     }
@@ -505,7 +509,7 @@ int Engine::kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_ou
         CUDA_TRY(cudaSetDevice(s.device));
         CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
         CUDA_TRY(cudaMemsetAsync(s.packed, 0, sizeof(double) * L.size(), s.stream));
-        search(s, s.x64, s.x32, s.n, s.idx, s.flag_list);
+        search(s, s.x64, s.x32, s.n, s.idx, s.sc);
         CUDA_TRY(cudaEventRecord(s.ev[1], s.stream));
         launch_accumulate(s.x64, s.idx, s.n, D_, s.raas, K_, s.packed, s.mindist, nullptr, true,
                           s.num_sms, s.stream);
@@ -530,7 +534,7 @@ int Engine::kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_ou
         CUDA_TRY(cudaSetDevice(s.device));
         CUDA_TRY(cudaEventRecord(s.ev[3], s.stream));
         launch_centroids(s.packed, K_, D_, s.refl, s.raas, s.stream);
-        launch_prepare_codebook(s.raas, K_, D_, s.w32, s.w64, s.w1max, s.stream);
+        launch_prepare_codebook(s.raas, K_, D_, s.w32, s.w64, s.w1, s.w1max, s.stream);
         ctr_.kernel_launches += 2;
         CUDA_TRY(cudaEventRecord(s.ev[4], s.stream));
     }
@@ -542,7 +546,7 @@ int Engine::kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_ou
         for (Shard &s : shards_) {
             int32_t fc = 0;
             cudaSetDevice(s.device);
-            cudaMemcpy(&fc, s.flag_count, sizeof(int32_t), cudaMemcpyDeviceToHost);
+            cudaMemcpy(&fc, s.sc.counters, sizeof(int32_t), cudaMemcpyDeviceToHost);
             ctr_.rechecked += fc;
         }
     }
@@ -578,7 +582,7 @@ int Engine::inertia(double *inertia_out) {
         CUDA_TRY(cudaSetDevice(s.device));
         CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
         CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
-        search(s, s.x64, s.x32, s.n, s.idx_tmp, s.flag_list);
+        search(s, s.x64, s.x32, s.n, s.idx_tmp, s.sc);
         CUDA_TRY(cudaEventRecord(s.ev[1], s.stream));
         launch_accumulate(s.x64, s.idx_tmp, s.n, D_, s.raas, K_, s.packed, nullptr, nullptr, false,
                           s.num_sms, s.stream);
@@ -697,7 +701,7 @@ int Engine::quantize_resident(uint16_t *seq_out, double *avg) {
         CUDA_TRY(cudaSetDevice(s.device));
         CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
         CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
-        search(s, s.x64, s.x32, s.n, s.idx_tmp, s.flag_list);
+        search(s, s.x64, s.x32, s.n, s.idx_tmp, s.sc);
         CUDA_TRY(cudaEventRecord(s.ev[1], s.stream));
         launch_accumulate(s.x64, s.idx_tmp, s.n, D_, s.raas, K_, s.packed, nullptr, s.seq, false,
                           s.num_sms, s.stream);
@@ -736,12 +740,13 @@ int Engine::quantize_host(const double *x, long T, uint16_t *seq_out, double *av
         const long want = T < chunk_cap ? (T > 0 ? T : 1) : chunk_cap;
         if (q.cap < want) {
             CUDA_TRY(cudaStreamSynchronize(s.stream));
-            cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.flag_list); cudaFree(q.seq);
+            cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
             q = QBuf();
             CUDA_TRY(cudaMalloc(&q.x64, sizeof(double) * (size_t) want * D_));
             CUDA_TRY(cudaMalloc(&q.x32, sizeof(float) * (size_t) want * D_));
             CUDA_TRY(cudaMalloc(&q.idx, sizeof(int32_t) * (size_t) want));
-            CUDA_TRY(cudaMalloc(&q.flag_list, sizeof(int32_t) * (size_t) want));
+            CUDA_TRY(cudaMalloc(&q.sc_mem, scratch_bytes(want)));
+            scratch_carve(q.sc_mem, want, &q.sc);
             CUDA_TRY(cudaMalloc(&q.seq, sizeof(uint16_t) * (size_t) want));
             q.cap = want;
         }
@@ -760,7 +765,7 @@ int Engine::quantize_host(const double *x, long T, uint16_t *seq_out, double *av
                                  cudaMemcpyHostToDevice, s.stream));
         launch_convert_frames(q.x64, q.x32, n, D_, s.stream);
         ctr_.kernel_launches++;
-        search(s, q.x64, q.x32, n, q.idx, q.flag_list);
+        search(s, q.x64, q.x32, n, q.idx, q.sc);
         launch_accumulate(q.x64, q.idx, n, D_, s.raas, K_, s.packed, nullptr, q.seq, false, s.num_sms,
                           s.stream);
         ctr_.kernel_launches++;

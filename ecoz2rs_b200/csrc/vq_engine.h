@@ -33,8 +33,8 @@ struct Shard {
     int32_t *idx_tmp = nullptr;  // [n] scratch assignment (inertia / quantize)
     uint16_t *seq = nullptr;  // [n]   symbols (quantize)
     double *mindist = nullptr;  // [n]   ddmin - 1 of the last pass
-    int32_t *flag_list = nullptr;  // [n]
-    int32_t *flag_count = nullptr; // [1]
+    void *sc_mem = nullptr;   // scratch of the FP32 search / FP64 re-evaluation
+    SearchScratch sc;
     long cap = 0;             // capacity (frames) of the per-frame buffers
 
     // codebook replica
@@ -43,6 +43,7 @@ struct Shard {
     float *w32 = nullptr;     // search tiles
     double *w64 = nullptr;
     float *w1max = nullptr;
+    float *w1 = nullptr;      // [K] sum_n |w_i[n]|
     double *packed = nullptr; // PackedLayout(max_M, D)
     double *scalars = nullptr;  // [8] misc device scalars (sigma sum, ...)
 };
@@ -103,7 +104,7 @@ class Engine {
     int ensure_capacity(Shard &s, long n);
     int ensure_local_comms();
     void search(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
-                int32_t *flag_list);
+                const SearchScratch &sc);
     int stage_codebook();  // raas -> search operands on every shard
     int sync_all();
     void harvest_times(bool with_cells);
@@ -112,7 +113,7 @@ class Engine {
     int P_, D_, max_M_;
     int K_ = 0;
     int mode_ = ECOZ2B200_MODE_FP32;
-    double kappa_ = 12.0;
+    double kappa_ = 8.0;
     std::vector<Shard> shards_;
     long n_total_ = 0;   // local frames (all shards)
     long n_global_ = 0;  // all ranks
@@ -122,7 +123,7 @@ class Engine {
     bool committed_ = false;
     // scratch of quantize_host (per shard, lazily allocated)
     struct QBuf { double *x64 = nullptr; float *x32 = nullptr; int32_t *idx = nullptr;
-                  int32_t *flag_list = nullptr; uint16_t *seq = nullptr; long cap = 0; };
+                  void *sc_mem = nullptr; SearchScratch sc; uint16_t *seq = nullptr; long cap = 0; };
     std::vector<QBuf> qbuf_;
     int append_block(const double *x, long n, bool device_src);
     int rank_ = 0, world_ = 1;

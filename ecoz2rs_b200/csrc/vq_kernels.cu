@@ -17,6 +17,7 @@
 
 #include <cfloat>
 #include <cmath>
+#include <type_traits>
 
 namespace vqb200 {
 
@@ -106,16 +107,57 @@ template <> struct Lim<double> { static __device__ __forceinline__ double inf() 
 // Reference semantics restated: strict '<' scan in index order
 // (vq_learn_par.c:66-75, quantize.c:19-26) == lexicographic min of (dd, index).
 // --------------------------------------------------------------------------------
-template <typename T, int RM, int RN, int DT, bool TRACK2>
+enum { kModeMain = 0, kModeExact = 1, kModeFilter = 2 };
+
+template <typename T>
+struct AssignParams {
+    const T *x;                 // frames [n][D] in the search precision
+    long n_frames;
+    int D_rt;
+    const T *wt;                // codeword tiles [tile][D][BN]
+    int K;
+    const int32_t *list;        // optional gather list (+ device-side count)
+    const int32_t *list_count;
+    const float *w1max;         // max_i sum_n |w_i[n]|
+    float err_scale;            // kappa * 2^-24
+    int32_t *idx_out;
+    int32_t *flag_list;         // kModeMain: frames to re-evaluate ...
+    int32_t *flag_count;
+    float *flag_ub;             // ... with an upper bound of their true minimum,
+    unsigned long long *min_key;  //   and their slot of the FP64 minimum (set to "max")
+    const float *w1;            // sum_n |w_i[n]| per codeword
+    // kModeFilter outputs: (list position, codeword) candidates, or -- when the
+    // candidate buffer is full -- the frames of the tile for the all-FP64 search
+    int2 *cand;
+    int32_t *cand_count;
+    int cand_cap;
+    int32_t *exact_list;
+    int32_t *exact_count;
+};
+
+constexpr int kCandBuf = 4096;  // candidates staged per CTA frame tile (shared memory)
+
+// MODE kModeMain  : T = float. argmin + runner-up; frames whose best-two gap is inside
+//                   the FP32 error bound go to flag_list.
+// MODE kModeExact : plain (FP64) argmin, optional gather list.
+// MODE kModeFilter: T = float over the gather list: the FP32 values only SELECT the
+//                   candidates (d32_j - c W1_j <= ub, c = err_scale |rx0|, ub = upper bound
+//                   of the true minimum); vq_candidates_eval / _select then evaluate every
+//                   candidate in FP64 and let the FP64 values decide.
+template <typename T, int RM, int RN, int DT, int MODE>
 __global__ void __launch_bounds__(256, 2)
-vq_assign_tiled(const T *__restrict__ x, long n_frames, int D_rt, const T *__restrict__ wt, int K,
-                const int32_t *__restrict__ list, const int32_t *__restrict__ list_count,
-                const float *__restrict__ w1max, float gap_scale, int32_t *__restrict__ idx_out,
-                int32_t *__restrict__ flag_list, int32_t *__restrict__ flag_count) {
+vq_assign_tiled(const AssignParams<T> p) {
     constexpr int TM = 4 * RM, TN = 4 * RN;
     constexpr int BM = 16 * TM, BN = 16 * TN;
     constexpr int XS = BM + 4;  // padded row of the transposed frame tile
-    const int D = DT > 0 ? DT : D_rt;
+    constexpr bool TRACK2 = MODE == kModeMain;
+    constexpr bool FILTER = MODE == kModeFilter;
+    using R = T;
+    const int D = DT > 0 ? DT : p.D_rt;
+    const T *__restrict__ x = p.x;
+    const T *__restrict__ wt = p.wt;
+    const int32_t *__restrict__ list = p.list;
+    const int K = p.K;
 
     extern __shared__ __align__(128) unsigned char smem_raw[];
     // layout: [2 mbarriers | pad to 128][Ws0: D*BN][Ws1: D*BN][Xs: D*XS]
@@ -123,6 +165,9 @@ vq_assign_tiled(const T *__restrict__ x, long n_frames, int D_rt, const T *__res
     T *Ws0 = reinterpret_cast<T *>(smem_raw + 128);
     T *Ws1 = Ws0 + (size_t) D * BN;
     T *Xs = Ws1 + (size_t) D * BN;
+    // kModeFilter only: [Xs][int2 cbuf[kCandBuf]][int s_count, s_base]
+    int2 *cbuf = reinterpret_cast<int2 *>(Xs + (size_t) D * XS);
+    int *s_ctl = reinterpret_cast<int *>(cbuf + kCandBuf);
 
     const int tid = threadIdx.x;
     const int tx = tid & 15, ty = tid >> 4;
@@ -133,12 +178,15 @@ vq_assign_tiled(const T *__restrict__ x, long n_frames, int D_rt, const T *__res
         mbar_init(&full[0], 1);
         mbar_init(&full[1], 1);
         fence_barrier_init();
+        if (FILTER) s_ctl[0] = 0;
     }
     __syncthreads();
     uint32_t phase0 = 0, phase1 = 0;
 
-    const long total = list ? (long) *list_count : n_frames;
+    const long total = list ? (long) *p.list_count : p.n_frames;
     const long n_ftiles = (total + BM - 1) / BM;
+    float w1max = 0.f;
+    if (TRACK2 || FILTER) w1max = *p.w1max;
 
     for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x) {
         const long base = ft * BM;
@@ -171,13 +219,22 @@ vq_assign_tiled(const T *__restrict__ x, long n_frames, int D_rt, const T *__res
         }
         __syncthreads();
 
-        T best[TM], second[TM];
+        R best[TM];
+        T second[TRACK2 ? TM : 1];
         int bidx[TM];
+        float cand_c[FILTER ? TM : 1], cand_b[FILTER ? TM : 1];  // c_i and best32_i + c_i W1max
 #pragma unroll
         for (int i = 0; i < TM; i++) {
-            best[i] = Lim<T>::inf();
-            second[i] = Lim<T>::inf();
+            best[i] = Lim<R>::inf();
+            if (TRACK2) second[i] = Lim<T>::inf();
             bidx[i] = 0;
+            if (FILTER) {
+                const int f = (i >> 2) * (BM / RM) + ty * 4 + (i & 3);
+                const float c = p.err_scale * fabsf((float) Xs[f]);
+                cand_c[i] = c;
+                // frames beyond the list never produce a candidate
+                cand_b[i] = f < nvalid ? p.flag_ub[base + f] : -INFINITY;
+            }
         }
 
         for (int t = 0; t < n_wtiles; t++) {
@@ -221,12 +278,24 @@ vq_assign_tiled(const T *__restrict__ x, long n_frames, int D_rt, const T *__res
             for (int j = 0; j < TN; j++) {
                 const int c = c0 + (j >> 2) * (BN / RN) + (j & 3);
                 if (partial && c >= K) continue;
+                if (FILTER) {
+                    const float w1j = p.w1[c];
 #pragma unroll
-                for (int i = 0; i < TM; i++) {
-                    const T d = acc[i][j];
-                    if (TRACK2) second[i] = min(second[i], max(d, best[i]));
-                    bidx[i] = d < best[i] ? c : bidx[i];
-                    best[i] = min(best[i], d);
+                    for (int i = 0; i < TM; i++) {
+                        if ((float) acc[i][j] <= fmaf(cand_c[i], w1j, cand_b[i])) {
+                            const int f = (i >> 2) * (BM / RM) + ty * 4 + (i & 3);
+                            const int slot = atomicAdd(&s_ctl[0], 1);
+                            if (slot < kCandBuf) cbuf[slot] = make_int2((int) (base + f), c);
+                        }
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < TM; i++) {
+                        const T d = acc[i][j];
+                        if (TRACK2) second[i] = min(second[i], max(d, (T) best[i]));
+                        bidx[i] = d < (T) best[i] ? c : bidx[i];
+                        best[i] = min((T) best[i], d);
+                    }
                 }
             }
 
@@ -238,16 +307,43 @@ vq_assign_tiled(const T *__restrict__ x, long n_frames, int D_rt, const T *__res
             }
         }
 
+        if (FILTER) {
+            // publish this tile's candidates (all or nothing); a full buffer sends the
+            // tile's frames to the all-FP64 search instead
+            __syncthreads();
+            const int m = s_ctl[0];
+            if (tid == 0) {
+                int gbase = -1;
+                if (m <= kCandBuf) {
+                    const int g = atomicAdd(p.cand_count, m);
+                    if (g + m <= p.cand_cap) gbase = g;
+                }
+                if (gbase < 0) gbase = -1 - atomicAdd(p.exact_count, nvalid);
+                s_ctl[1] = gbase;
+            }
+            __syncthreads();
+            const int gbase = s_ctl[1];
+            if (gbase >= 0) {
+                for (int e = tid; e < m; e += 256) p.cand[gbase + e] = cbuf[e];
+            } else {
+                const int ebase = -1 - gbase;
+                for (int e = tid; e < nvalid; e += 256) p.exact_list[ebase + e] = list[base + e];
+            }
+            __syncthreads();
+            if (tid == 0) s_ctl[0] = 0;
+            continue;
+        }
+
         // -- merge the 16 threads (tx = low 4 lane bits) that share each frame
 #pragma unroll
         for (int i = 0; i < TM; i++) {
 #pragma unroll
             for (int off = 8; off >= 1; off >>= 1) {
-                const T ob = __shfl_xor_sync(0xffffffffu, best[i], off);
+                const R ob = __shfl_xor_sync(0xffffffffu, best[i], off);
                 const int oi = __shfl_xor_sync(0xffffffffu, bidx[i], off);
                 if (TRACK2) {
                     const T os = __shfl_xor_sync(0xffffffffu, second[i], off);
-                    second[i] = min(min(second[i], os), max(best[i], ob));
+                    second[i] = min(min(second[i], os), max((T) best[i], (T) ob));
                 }
                 if (ob < best[i] || (ob == best[i] && oi < bidx[i])) {
                     best[i] = ob;
@@ -256,20 +352,22 @@ vq_assign_tiled(const T *__restrict__ x, long n_frames, int D_rt, const T *__res
             }
         }
         if (tx == 0) {
-            float bound = 0.f;
-            if (TRACK2) bound = gap_scale * (*w1max);
+            const float bound = 2.f * p.err_scale * w1max;
 #pragma unroll
             for (int i = 0; i < TM; i++) {
                 const int f = (i >> 2) * (BM / RM) + ty * 4 + (i & 3);
                 if (f < nvalid) {
                     const long row = list ? (long) list[base + f] : base + f;
-                    idx_out[row] = bidx[i];
+                    p.idx_out[row] = bidx[i];
                     if (TRACK2) {
                         const float x0 = fabsf((float) Xs[f]);
                         // NaN-safe: "not clearly separated" => re-evaluate
-                        if (!((float) (second[i] - best[i]) >= bound * x0)) {
-                            const int pos = atomicAdd(flag_count, 1);
-                            flag_list[pos] = (int32_t) row;
+                        if (!((float) (second[i] - (T) best[i]) >= bound * x0)) {
+                            const int pos = atomicAdd(p.flag_count, 1);
+                            p.flag_list[pos] = (int32_t) row;
+                            // true minimum <= d64(best) <= best32 + (2 err_scale) |rx0| W1_best
+                            p.flag_ub[pos] = fmaf(2.f * p.err_scale * x0, p.w1[bidx[i]], (float) best[i]);
+                            p.min_key[pos] = ~0ull;
                         }
                     }
                 }
@@ -279,60 +377,152 @@ vq_assign_tiled(const T *__restrict__ x, long n_frames, int D_rt, const T *__res
 }
 
 template <typename T, int RM, int RN>
-static size_t assign_smem_bytes(int D) {
+static size_t assign_smem_bytes(int D, bool filter) {
     constexpr int BM = 64 * RM, BN = 64 * RN;
-    return 128 + sizeof(T) * ((size_t) 2 * D * BN + (size_t) D * (BM + 4));
+    return 128 + sizeof(T) * ((size_t) 2 * D * BN + (size_t) D * (BM + 4)) +
+           (filter ? sizeof(int2) * kCandBuf + 16 : 0);
 }
 
-template <typename T, int RM, int RN, int DT, bool TRACK2>
-static void launch_assign_inst(const T *x, long n, int D, const T *wt, int K, const int32_t *list,
-                               const int32_t *list_count, const float *w1max, float gap_scale,
-                               int32_t *idx, int32_t *flag_list, int32_t *flag_count, int num_sms,
-                               cudaStream_t s) {
-    auto kern = vq_assign_tiled<T, RM, RN, DT, TRACK2>;
-    const size_t smem = assign_smem_bytes<T, RM, RN>(D);
+template <typename T, int RM, int RN, int DT, int MODE>
+static void launch_assign_inst(const AssignParams<T> &p, int num_sms, cudaStream_t s) {
+    auto kern = vq_assign_tiled<T, RM, RN, DT, MODE>;
+    const size_t smem = assign_smem_bytes<T, RM, RN>(p.D_rt, MODE == kModeFilter);
     cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
     constexpr int BM = 64 * RM;
-    long tiles = (n + BM - 1) / BM;
+    long tiles = (p.n_frames + BM - 1) / BM;
     if (tiles < 1) tiles = 1;
     long grid = tiles;
-    if (list != nullptr) {
+    if (p.list != nullptr) {
         // device-side count: persistent grid, CTAs loop over however many tiles there are
         const long cap = (long) num_sms * 4;
         if (grid > cap) grid = cap;
     }
-    kern<<<(unsigned) grid, 256, smem, s>>>(x, n, D, wt, K, list, list_count, w1max, gap_scale, idx,
-                                            flag_list, flag_count);
+    kern<<<(unsigned) grid, 256, smem, s>>>(p);
+}
+
+template <typename T, int RM, int RN, int MODE>
+static void launch_assign_d(const AssignParams<T> &p, int num_sms, cudaStream_t s) {
+    if (p.D_rt == 37) launch_assign_inst<T, RM, RN, 37, MODE>(p, num_sms, s);
+    else if (p.D_rt == 13) launch_assign_inst<T, RM, RN, 13, MODE>(p, num_sms, s);
+    else launch_assign_inst<T, RM, RN, 0, MODE>(p, num_sms, s);
+}
+
+static size_t align256(size_t v) { return (v + 255) & ~(size_t) 255; }
+size_t scratch_bytes(long cap) {
+    const long cand_cap = cap < 4096 ? 4096 : cap;
+    return align256(sizeof(int32_t) * cap) * 2 + align256(sizeof(float) * cap) +
+           align256(sizeof(unsigned long long) * cap) + align256(sizeof(int2) * cand_cap) +
+           align256(sizeof(double) * cand_cap) + 256;
+}
+void scratch_carve(void *base, long cap, SearchScratch *out) {
+    const long cand_cap = cap < 4096 ? 4096 : cap;
+    char *p = static_cast<char *>(base);
+    out->counters = reinterpret_cast<int32_t *>(p); p += 256;
+    out->min_key = reinterpret_cast<unsigned long long *>(p); p += align256(sizeof(unsigned long long) * cap);
+    out->cand_d = reinterpret_cast<double *>(p); p += align256(sizeof(double) * cand_cap);
+    out->cand = reinterpret_cast<int2 *>(p); p += align256(sizeof(int2) * cand_cap);
+    out->flag_list = reinterpret_cast<int32_t *>(p); p += align256(sizeof(int32_t) * cap);
+    out->exact_list = reinterpret_cast<int32_t *>(p); p += align256(sizeof(int32_t) * cap);
+    out->flag_ub = reinterpret_cast<float *>(p);
+    out->cap = cap;
+    out->cand_cap = cand_cap;
 }
 
 void launch_assign_f32(const float *x32, long n, int D, const float *w32, int K,
-                       const float *w1max, float gap_scale, int32_t *idx, int32_t *flag_list,
-                       int32_t *flag_count, int num_sms, cudaStream_t s) {
+                       const SearchScratch &sc, const float *w1, const float *w1max,
+                       float err_scale, int32_t *idx, int num_sms, cudaStream_t s) {
     if (n <= 0) return;
-    if (D == 37)
-        launch_assign_inst<float, 2, 2, 37, true>(x32, n, D, w32, K, nullptr, nullptr, w1max,
-                                                  gap_scale, idx, flag_list, flag_count, num_sms, s);
-    else if (D == 13)
-        launch_assign_inst<float, 2, 2, 13, true>(x32, n, D, w32, K, nullptr, nullptr, w1max,
-                                                  gap_scale, idx, flag_list, flag_count, num_sms, s);
-    else
-        launch_assign_inst<float, 2, 2, 0, true>(x32, n, D, w32, K, nullptr, nullptr, w1max,
-                                                 gap_scale, idx, flag_list, flag_count, num_sms, s);
+    AssignParams<float> p{};
+    p.x = x32; p.n_frames = n; p.D_rt = D; p.wt = w32; p.K = K;
+    p.w1 = w1; p.w1max = w1max; p.err_scale = err_scale; p.idx_out = idx;
+    p.flag_list = sc.flag_list; p.flag_count = sc.counters + 0; p.flag_ub = sc.flag_ub;
+    p.min_key = sc.min_key;
+    launch_assign_d<float, 2, 2, kModeMain>(p, num_sms, s);
 }
 
 void launch_assign_f64(const double *x64, long n, int D, const double *w64, int K,
                        const int32_t *list, const int32_t *list_count, int32_t *idx, int num_sms,
                        cudaStream_t s) {
     if (n <= 0) return;
-    if (D == 37)
-        launch_assign_inst<double, 1, 1, 37, false>(x64, n, D, w64, K, list, list_count, nullptr,
-                                                    0.f, idx, nullptr, nullptr, num_sms, s);
-    else if (D == 13)
-        launch_assign_inst<double, 1, 1, 13, false>(x64, n, D, w64, K, list, list_count, nullptr,
-                                                    0.f, idx, nullptr, nullptr, num_sms, s);
-    else
-        launch_assign_inst<double, 1, 1, 0, false>(x64, n, D, w64, K, list, list_count, nullptr,
-                                                   0.f, idx, nullptr, nullptr, num_sms, s);
+    AssignParams<double> p{};
+    p.x = x64; p.n_frames = n; p.D_rt = D; p.wt = w64; p.K = K;
+    p.list = list; p.list_count = list_count; p.idx_out = idx;
+    launch_assign_d<double, 1, 1, kModeExact>(p, num_sms, s);
+}
+
+// --------------------------------------------------------------------------------
+// FP64 evaluation of the candidates: one warp per (frame, codeword) pair, lanes over
+// the D components (coalesced 8 D-byte rows), fixed shuffle tree => bit-identical
+// values for identical codewords, so exact ties resolve to the lower index.
+// --------------------------------------------------------------------------------
+__device__ __forceinline__ unsigned long long order_key(double d) {
+    const unsigned long long b = (unsigned long long) __double_as_longlong(d);
+    return (b >> 63) ? ~b : (b | 0x8000000000000000ull);   // monotone in d
+}
+
+__global__ void __launch_bounds__(256)
+vq_candidates_eval(const double *__restrict__ x64, const double *__restrict__ raas, int D,
+                   const int32_t *__restrict__ list, const int2 *__restrict__ cand,
+                   const int32_t *__restrict__ cand_count, int cand_cap,
+                   double *__restrict__ cand_d, unsigned long long *__restrict__ min_key,
+                   int32_t *__restrict__ idx_out) {
+    const int lane = threadIdx.x & 31;
+    const long warp = ((long) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long n_warps = ((long) gridDim.x * blockDim.x) >> 5;
+    long total = *cand_count;
+    if (total > cand_cap) total = cand_cap;
+    for (long k = warp; k < total; k += n_warps) {
+        const int2 cd = cand[k];
+        const long row = list[cd.x];
+        const double *xr = x64 + row * D, *rr = raas + (long) cd.y * D;
+        double part = 0.0;
+        for (int m = lane; m < D; m += 32) {
+            const double w = m > 0 ? 2.0 * rr[m] : rr[m];
+            part = fma(xr[m], w, part);
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) part += __shfl_xor_sync(0xffffffffu, part, off);
+        if (lane == 0) {
+            cand_d[k] = part;
+            atomicMin(min_key + cd.x, order_key(part));
+            idx_out[row] = 0x7fffffff;   // every candidate of the row writes the same value
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256)
+vq_candidates_select(const int32_t *__restrict__ list, const int2 *__restrict__ cand,
+                     const int32_t *__restrict__ cand_count, int cand_cap,
+                     const double *__restrict__ cand_d,
+                     const unsigned long long *__restrict__ min_key, int32_t *__restrict__ idx_out) {
+    long total = *cand_count;
+    if (total > cand_cap) total = cand_cap;
+    const long stride = (long) gridDim.x * blockDim.x;
+    for (long k = (long) blockIdx.x * blockDim.x + threadIdx.x; k < total; k += stride) {
+        const int2 cd = cand[k];
+        if (order_key(cand_d[k]) == min_key[cd.x]) atomicMin(idx_out + list[cd.x], cd.y);
+    }
+}
+
+void launch_recheck(const float *x32, const double *x64, long n, int D, const float *w32,
+                    const double *w64, const float *w1, const float *w1max, const double *raas,
+                    int K, float err_scale, const SearchScratch &sc, int32_t *idx, int num_sms,
+                    cudaStream_t s) {
+    if (n <= 0) return;
+    AssignParams<float> p{};
+    p.x = x32; p.n_frames = n; p.D_rt = D; p.wt = w32; p.K = K;
+    p.list = sc.flag_list; p.list_count = sc.counters + 0; p.w1max = w1max; p.err_scale = err_scale;
+    p.idx_out = idx; p.flag_ub = sc.flag_ub; p.w1 = w1;
+    p.cand = sc.cand; p.cand_count = sc.counters + 1; p.cand_cap = (int) sc.cand_cap;
+    p.exact_list = sc.exact_list; p.exact_count = sc.counters + 2;
+    launch_assign_d<float, 2, 2, kModeFilter>(p, num_sms, s);
+    const int blocks = num_sms * 8;
+    vq_candidates_eval<<<blocks, 256, 0, s>>>(x64, raas, D, sc.flag_list, sc.cand, sc.counters + 1,
+                                              (int) sc.cand_cap, sc.cand_d, sc.min_key, idx);
+    vq_candidates_select<<<blocks, 256, 0, s>>>(sc.flag_list, sc.cand, sc.counters + 1,
+                                                (int) sc.cand_cap, sc.cand_d, sc.min_key, idx);
+    // tiles whose candidates did not fit: the all-FP64 search (normally an empty list)
+    launch_assign_f64(x64, n, D, w64, K, sc.exact_list, sc.counters + 2, idx, num_sms, s);
 }
 
 // --------------------------------------------------------------------------------
@@ -355,7 +545,7 @@ void launch_convert_frames(const double *x64, float *x32, long n, int D, cudaStr
 // one thread per (codeword slot, n) of the padded tile layouts
 __global__ void vq_prepare_codebook(const double *__restrict__ raas, int K, int D,
                                     float *__restrict__ w32, double *__restrict__ w64,
-                                    float *__restrict__ w1max) {
+                                    float *__restrict__ w1, float *__restrict__ w1max) {
     const int K32 = (K + kTileF32 - 1) / kTileF32 * kTileF32;
     const long total = (long) K32 * D;
     const long e = (long) blockIdx.x * blockDim.x + threadIdx.x;
@@ -377,15 +567,16 @@ __global__ void vq_prepare_codebook(const double *__restrict__ raas, int K, int 
             s1 += fabsf((float) v);
         }
         s1 *= 1.0001f;  // cover the rounding of this sum itself
+        w1[i] = s1;
         atomicMax(reinterpret_cast<int *>(w1max), __float_as_int(s1));  // s1 >= 0
     }
 }
 void launch_prepare_codebook(const double *raas, int K, int D, float *w32, double *w64,
-                             float *w1max, cudaStream_t s) {
+                             float *w1, float *w1max, cudaStream_t s) {
     cudaMemsetAsync(w1max, 0, sizeof(float), s);
     const int K32 = (K + kTileF32 - 1) / kTileF32 * kTileF32;
     const long total = (long) K32 * D;
-    vq_prepare_codebook<<<(unsigned) ((total + 255) / 256), 256, 0, s>>>(raas, K, D, w32, w64, w1max);
+    vq_prepare_codebook<<<(unsigned) ((total + 255) / 256), 256, 0, s>>>(raas, K, D, w32, w64, w1, w1max);
 }
 
 // --------------------------------------------------------------------------------

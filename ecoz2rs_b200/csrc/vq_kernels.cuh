@@ -36,18 +36,33 @@ void launch_convert_frames(const double *x64, float *x32, long n, int D, cudaStr
 // raas f64 [K][D] -> search operands:
 //   w32 tiles [ceil(K/128)][D][128] f32, w64 tiles [ceil(K/64)][D][64] f64 (zero padded)
 //   *w1max (f32) = max_i sum_n |w_i[n]|   (for the FP32 ambiguity bound)
+//   w1[i] (f32) = sum_n |w_i[n]|, *w1max = max_i w1[i]
 void launch_prepare_codebook(const double *raas, int K, int D, float *w32, double *w64,
-                             float *w1max, cudaStream_t s);
+                             float *w1, float *w1max, cudaStream_t s);
 
 // ---- (a) fused distortion + argmin ------------------------------------------
+// Device scratch of the FP32 search + FP64 re-evaluation of one frame block of
+// capacity `cap` frames (one cudaMalloc, carved by scratch_carve).
+struct SearchScratch {
+    int32_t *flag_list = nullptr;          // [cap]  frames whose FP32 best-two gap is ambiguous
+    float *flag_ub = nullptr;              // [cap]  upper bound of their true minimum
+    unsigned long long *min_key = nullptr; // [cap]  ordered bits of their FP64 minimum
+    int2 *cand = nullptr;                  // [cand_cap] (list position, codeword) candidates
+    double *cand_d = nullptr;              // [cand_cap] their FP64 distortions
+    int32_t *exact_list = nullptr;         // [cap]  frames sent to the all-FP64 search
+    int32_t *counters = nullptr;           // [4]    flag_count, cand_count, exact_count, -
+    long cap = 0, cand_cap = 0;
+};
+size_t scratch_bytes(long cap);
+void scratch_carve(void *base, long cap, SearchScratch *out);
+
 // FP32 search over all n frames.  idx[v] = argmin (first index on ties among the
 // FP32 values); frames whose best-two gap is below
-//     gap_scale * rx[0] * (*w1max)
-// are appended to flag_list (count in *flag_count, which the caller zeroes).
+//     2 * err_scale * |rx[0]| * (*w1max)          (err_scale = kappa * 2^-24)
+// are appended to sc.flag_list (sc.counters must be zeroed by the caller).
 void launch_assign_f32(const float *x32, long n, int D, const float *w32, int K,
-                       const float *w1max, float gap_scale, int32_t *idx,
-                       int32_t *flag_list, int32_t *flag_count, int num_sms,
-                       cudaStream_t s);
+                       const SearchScratch &sc, const float *w1, const float *w1max,
+                       float err_scale, int32_t *idx, int num_sms, cudaStream_t s);
 
 // FP64 search.  list == nullptr: all n frames.  Otherwise only the frames
 // list[0 .. *list_count) (device-side count; no host sync).  Exact reference
@@ -55,6 +70,17 @@ void launch_assign_f32(const float *x32, long n, int D, const float *w32, int K,
 void launch_assign_f64(const double *x64, long n, int D, const double *w64, int K,
                        const int32_t *list, const int32_t *list_count, int32_t *idx,
                        int num_sms, cudaStream_t s);
+
+// Re-evaluation of the flagged frames (4 launches, no host sync):
+//  1. the FP32 tile search repeated over the flagged frames only SELECTS candidates
+//     (d32_j - c W1_j <= ub, c = 2 err_scale |rx0|);
+//  2. vq_candidates_eval: every candidate's distortion in FP64 + per-frame minimum;
+//  3. vq_candidates_select: lowest codeword index among the FP64-minimal candidates;
+//  4. all-FP64 search of the (normally zero) frames whose candidates overflowed.
+void launch_recheck(const float *x32, const double *x64, long n, int D, const float *w32,
+                    const double *w64, const float *w1, const float *w1max, const double *raas,
+                    int K, float err_scale, const SearchScratch &sc, int32_t *idx, int num_sms,
+                    cudaStream_t s);
 
 // ---- (b) cell accumulation ----------------------------------------------------
 // For every frame: dd = FP64 distortion against its codeword raas[idx];
