@@ -10,6 +10,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
 
 #include "vq_nccl.h"
@@ -96,6 +97,8 @@ Engine::Engine(const int *devices, int num_devices, int P, int max_M)
         cudaMemset(s.refl, 0, cb);
         cudaMemset(s.raas, 0, cb);
     }
+    const char *fs = getenv("ECOZ2_VQ_FUSED_SMALL");
+    if (fs && fs[0] == '0') use_small_ = false;
     ok_ = true;
 }
 
@@ -406,12 +409,29 @@ int Engine::codebook_get(double *refl_out, double *raas_out) {
     return ECOZ2B200_OK;
 }
 
+// debug aid (ECOZ2_VQ_DEBUG_POISON=1): fill every SM's shared memory with NaN patterns
+// before a search so any read of not-yet-delivered tile data becomes visible.
+__global__ void vq_debug_poison_smem() {
+    extern __shared__ unsigned int poison[];
+    for (int i = threadIdx.x; i < 50 * 1024; i += blockDim.x) poison[i] = 0x7fc00000u + i;
+    __syncthreads();
+    if (poison[(threadIdx.x * 7919) % (50 * 1024)] == 1u) printf("x");
+}
+static void debug_poison(const Shard &s) {
+    static int on = -1;
+    if (on < 0) on = getenv("ECOZ2_VQ_DEBUG_POISON") ? 1 : 0;
+    if (!on) return;
+    cudaFuncSetAttribute(vq_debug_poison_smem, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    vq_debug_poison_smem<<<s.num_sms, 256, 200 * 1024, s.stream>>>();
+}
+
 // ---------------------------------------------------------------------------------
 // (a) the search on one shard: FP32 main pass + FP64 re-evaluation of the frames
 // inside the FP32 ambiguity bound, or the all-FP64 verification mode.
 void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
                     const SearchScratch &sc) {
     if (n <= 0) return;
+    debug_poison(s);
     cudaEventRecord(s.ev[6], s.stream);
     if (mode_ == ECOZ2B200_MODE_FP64) {
         launch_assign_f64(x64, n, D_, s.w64, K_, nullptr, nullptr, idx, s.num_sms, s.stream);
@@ -433,6 +453,26 @@ void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32
     ctr_.evals += (double) n * K_;
 }
 
+void Engine::pass_kernels(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
+                          const SearchScratch &sc, double *mindist, uint16_t *seq, bool with_cells) {
+    if (small_path()) {
+        // small codebooks are HBM-bound: one all-FP64 sweep does search + sums
+        cudaEventRecord(s.ev[6], s.stream);
+        launch_pass_small(x64, n, D_, s.raas, K_, s.packed, idx, mindist, seq, with_cells, s.num_sms,
+                          s.stream);
+        cudaEventRecord(s.ev[7], s.stream);
+        cudaEventRecord(s.ev[1], s.stream);
+        ctr_.kernel_launches += n > 0;
+        ctr_.evals += (double) n * K_;
+        return;
+    }
+    search(s, x64, x32, n, idx, sc);
+    cudaEventRecord(s.ev[1], s.stream);
+    launch_accumulate(x64, idx, n, D_, s.raas, K_, s.packed, mindist, seq, with_cells, s.num_sms,
+                      s.stream);
+    ctr_.kernel_launches += n > 0;
+}
+
 int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked) {
     if (!committed_ || K_ < 1) {
         set_last_error("assign: frames not committed or no codebook");
@@ -442,11 +482,8 @@ int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked) {
     long rechecked = 0;
     for (Shard &s : shards_) {
         CUDA_TRY(cudaSetDevice(s.device));
-        search(s, s.x64, s.x32, s.n, s.idx, s.sc);
         CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
-        launch_accumulate(s.x64, s.idx, s.n, D_, s.raas, K_, s.packed, s.mindist, nullptr, false,
-                          s.num_sms, s.stream);
-        ctr_.kernel_launches++;
+        pass_kernels(s, s.x64, s.x32, s.n, s.idx, s.sc, s.mindist, nullptr, false);
     }
     for (Shard &s : shards_) {
         CUDA_TRY(cudaSetDevice(s.device));
@@ -457,7 +494,7 @@ int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked) {
             CUDA_TRY(cudaMemcpyAsync(ddmin_out + s.frame_offset, s.mindist, sizeof(double) * (size_t) s.n,
                                      cudaMemcpyDeviceToHost, s.stream));
         int32_t fc = 0;
-        if (mode_ != ECOZ2B200_MODE_FP64)
+        if (mode_ != ECOZ2B200_MODE_FP64 && !small_path())
             CUDA_TRY(cudaMemcpyAsync(&fc, s.sc.counters, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
         CUDA_TRY(cudaStreamSynchronize(s.stream));
         rechecked += fc;
@@ -509,11 +546,7 @@ int Engine::kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_ou
         CUDA_TRY(cudaSetDevice(s.device));
         CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
         CUDA_TRY(cudaMemsetAsync(s.packed, 0, sizeof(double) * L.size(), s.stream));
-        search(s, s.x64, s.x32, s.n, s.idx, s.sc);
-        CUDA_TRY(cudaEventRecord(s.ev[1], s.stream));
-        launch_accumulate(s.x64, s.idx, s.n, D_, s.raas, K_, s.packed, s.mindist, nullptr, true,
-                          s.num_sms, s.stream);
-        ctr_.kernel_launches++;
+        pass_kernels(s, s.x64, s.x32, s.n, s.idx, s.sc, s.mindist, nullptr, true);
         CUDA_TRY(cudaEventRecord(s.ev[2], s.stream));
     }
     int rc = allreduce_range(shards_, 0, L.size(), reduce);
@@ -542,7 +575,7 @@ int Engine::kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_ou
     if (rc) return rc;
     CUDA_TRY(cudaGetLastError());
     harvest_times(true);
-    if (mode_ != ECOZ2B200_MODE_FP64) {
+    if (mode_ != ECOZ2B200_MODE_FP64 && !small_path()) {
         for (Shard &s : shards_) {
             int32_t fc = 0;
             cudaSetDevice(s.device);
@@ -582,11 +615,7 @@ int Engine::inertia(double *inertia_out) {
         CUDA_TRY(cudaSetDevice(s.device));
         CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
         CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
-        search(s, s.x64, s.x32, s.n, s.idx_tmp, s.sc);
-        CUDA_TRY(cudaEventRecord(s.ev[1], s.stream));
-        launch_accumulate(s.x64, s.idx_tmp, s.n, D_, s.raas, K_, s.packed, nullptr, nullptr, false,
-                          s.num_sms, s.stream);
-        ctr_.kernel_launches++;
+        pass_kernels(s, s.x64, s.x32, s.n, s.idx_tmp, s.sc, nullptr, nullptr, false);
         CUDA_TRY(cudaEventRecord(s.ev[2], s.stream));
     }
     int rc = allreduce_range(shards_, L.dd(), 2, reduce);
@@ -701,11 +730,7 @@ int Engine::quantize_resident(uint16_t *seq_out, double *avg) {
         CUDA_TRY(cudaSetDevice(s.device));
         CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
         CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
-        search(s, s.x64, s.x32, s.n, s.idx_tmp, s.sc);
-        CUDA_TRY(cudaEventRecord(s.ev[1], s.stream));
-        launch_accumulate(s.x64, s.idx_tmp, s.n, D_, s.raas, K_, s.packed, nullptr, s.seq, false,
-                          s.num_sms, s.stream);
-        ctr_.kernel_launches++;
+        pass_kernels(s, s.x64, s.x32, s.n, s.idx_tmp, s.sc, nullptr, s.seq, false);
         CUDA_TRY(cudaEventRecord(s.ev[2], s.stream));
         if (seq_out)
             CUDA_TRY(cudaMemcpyAsync(seq_out + s.frame_offset, s.seq, sizeof(uint16_t) * (size_t) s.n,
@@ -763,12 +788,11 @@ int Engine::quantize_host(const double *x, long T, uint16_t *seq_out, double *av
         CUDA_TRY(cudaSetDevice(s.device));
         CUDA_TRY(cudaMemcpyAsync(q.x64, x + (size_t) pos * D_, sizeof(double) * (size_t) n * D_,
                                  cudaMemcpyHostToDevice, s.stream));
-        launch_convert_frames(q.x64, q.x32, n, D_, s.stream);
-        ctr_.kernel_launches++;
-        search(s, q.x64, q.x32, n, q.idx, q.sc);
-        launch_accumulate(q.x64, q.idx, n, D_, s.raas, K_, s.packed, nullptr, q.seq, false, s.num_sms,
-                          s.stream);
-        ctr_.kernel_launches++;
+        if (!small_path()) {
+            launch_convert_frames(q.x64, q.x32, n, D_, s.stream);
+            ctr_.kernel_launches++;
+        }
+        pass_kernels(s, q.x64, q.x32, n, q.idx, q.sc, nullptr, q.seq, false);
         if (seq_out)
             CUDA_TRY(cudaMemcpyAsync(seq_out + pos, q.seq, sizeof(uint16_t) * (size_t) n,
                                      cudaMemcpyDeviceToHost, s.stream));

@@ -105,10 +105,16 @@ class Engine {
     int ensure_local_comms();
     void search(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
                 const SearchScratch &sc);
+    // search + winner distortion (+ cell sums) of one block of frames; records ev[1]
+    // between the two phases.  K <= 32: one fused FP64 kernel.
+    void pass_kernels(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
+                      const SearchScratch &sc, double *mindist, uint16_t *seq, bool with_cells);
     int stage_codebook();  // raas -> search operands on every shard
     int sync_all();
     void harvest_times(bool with_cells);
 
+    bool small_path() const { return use_small_ && pass_small_supported(K_, D_); }
+    bool use_small_ = true;   // ECOZ2_VQ_FUSED_SMALL=0 forces the tiled path at every K
     bool ok_ = false;
     int P_, D_, max_M_;
     int K_ = 0;

@@ -722,6 +722,192 @@ void launch_accumulate(const double *x64, const int32_t *idx, long n, int D, con
 }
 
 // --------------------------------------------------------------------------------
+// (a+b) fused small-codebook pass, K <= 32: search, cell sums, counts and distortions
+// in ONE sweep over the FP64 frames -- all FP64, so there is nothing to re-evaluate.
+//   * lane j owns codeword j: its D weights live in registers;
+//   * the warp loads frames coalesced (lane l holds components l, l+32), parks them in a
+//     small per-warp shared buffer and every lane reads them back as broadcasts;
+//   * min over lanes by xor-shuffles, argmin = lowest lane holding the minimum
+//     (== strict '<' scan in index order, vq_learn_par.c:66-75);
+//   * cell sums go to per-WARP private shared-memory cells (no atomics); counts and
+//     cell distortions stay in the owning lane's registers; one flush per CTA at the end.
+// Small codebooks are HBM-bound (intensity K/2 flop/byte): this kernel reads 8 D bytes
+// per frame once instead of 4 D (search) + 8 D (accumulate) + contended atomics.
+// --------------------------------------------------------------------------------
+template <int DT, bool CELLS>
+__global__ void __launch_bounds__(128)
+vq_pass_small(const double *__restrict__ x64, long n, const double *__restrict__ raas, PackedLayout L,
+              double *__restrict__ packed, int32_t *__restrict__ idx_out,
+              double *__restrict__ mindist, uint16_t *__restrict__ seq) {
+    constexpr int D = DT;
+    constexpr int NR = (D + 31) / 32;
+    constexpr int U = 4;              // frames in flight per warp
+    constexpr int XROW = (D + 1) & ~1;  // even: 16-byte aligned rows for the double2 reads
+    const int K = L.K;
+    extern __shared__ __align__(16) unsigned char smem_small[];
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    const int n_w = blockDim.x >> 5;
+    double *xs = reinterpret_cast<double *>(smem_small) + (size_t) w * U * XROW;  // [U][XROW]
+    double *cells = reinterpret_cast<double *>(smem_small) + (size_t) n_w * U * XROW +
+                    (size_t) w * K * D;                                         // [K][D]
+    if (CELLS)
+        for (int e = lane; e < K * D; e += 32) cells[e] = 0.0;
+
+    // codeword of this lane (w = (raa0, 2 raa1, ..)); lanes >= K never win
+    double wv[D];
+    const bool owner = lane < K;
+#pragma unroll
+    for (int m = 0; m < D; m++) {
+        double v = owner ? raas[(long) lane * D + m] : 0.0;
+        wv[m] = m > 0 ? 2.0 * v : v;
+    }
+    __syncwarp();
+
+    const long warp = ((long) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long n_warps = ((long) gridDim.x * blockDim.x) >> 5;
+    const long chunk = ((n + n_warps - 1) / n_warps + U - 1) / U * U;
+    const long lo = warp * chunk;
+    const long hi = lo + chunk < n ? lo + chunk : n;
+
+    int my_cnt = 0;
+    double my_dis = 0.0, dd_sum = 0.0, in_sum = 0.0;
+
+    double xr[U][NR];
+    auto load = [&](long v0) {
+#pragma unroll
+        for (int u = 0; u < U; u++)
+#pragma unroll
+            for (int r = 0; r < NR; r++) {
+                const int m = lane + 32 * r;
+                xr[u][r] = (v0 + u < hi && m < D) ? x64[(v0 + u) * D + m] : 0.0;
+            }
+    };
+    if (lo < hi) load(lo);
+    for (long v0 = lo; v0 < hi; v0 += U) {
+        // park the U frames in shared memory, then prefetch the next group
+#pragma unroll
+        for (int u = 0; u < U; u++)
+#pragma unroll
+            for (int r = 0; r < NR; r++) {
+                const int m = lane + 32 * r;
+                if (m < XROW) xs[u * XROW + m] = xr[u][r];
+            }
+        __syncwarp();
+        if (v0 + U < hi) load(v0 + U);
+
+        // broadcast reads, software pipelined one step ahead; volatile asm keeps the
+        // loads in program order so the unrolled loop does not hoist all of them
+        double acc[U];
+        double2 cur[U], nxt[U];
+        const uint32_t xs_addr = smem_u32(xs);
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            acc[u] = 0.0;
+            asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(cur[u].x), "=d"(cur[u].y)
+                         : "r"(xs_addr + (uint32_t) (u * XROW) * 8u));
+        }
+#pragma unroll
+        for (int m = 0; m < D; m += 2) {
+            if (m + 2 < D) {
+#pragma unroll
+                for (int u = 0; u < U; u++)
+                    asm volatile("ld.shared.v2.f64 {%0, %1}, [%2];" : "=d"(nxt[u].x), "=d"(nxt[u].y)
+                                 : "r"(xs_addr + (uint32_t) (u * XROW + m + 2) * 8u));
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                acc[u] = fma(cur[u].x, wv[m], acc[u]);
+                if (m + 1 < D) acc[u] = fma(cur[u].y, wv[m + 1], acc[u]);
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) cur[u] = nxt[u];
+        }
+#pragma unroll
+        for (int u = 0; u < U; u++) {
+            if (v0 + u >= hi) break;
+            const double mine = owner ? acc[u] : (double) INFINITY;
+            double mn = mine;
+#pragma unroll
+            for (int off = 16; off >= 1; off >>= 1) mn = fmin(mn, __shfl_xor_sync(0xffffffffu, mn, off));
+            const unsigned hit = __ballot_sync(0xffffffffu, mine == mn);
+            const int ci = hit ? __ffs(hit) - 1 : 0;    // NaN frame: reference quantize keeps 0
+            const double md = mn - 1.0;
+            dd_sum += md;
+            in_sum += mn * mn;
+            if (lane == 0) {
+                idx_out[v0 + u] = ci;
+                if (mindist) mindist[v0 + u] = md;
+                if (seq) seq[v0 + u] = (uint16_t) ci;
+            }
+            if (CELLS) {
+                if (lane == ci) { my_cnt++; my_dis += md; }
+#pragma unroll
+                for (int r = 0; r < NR; r++) {
+                    const int m = lane + 32 * r;
+                    if (m < D) cells[ci * D + m] += xs[u * XROW + m];
+                }
+            }
+        }
+        __syncwarp();
+    }
+
+    // ---- flush: per-warp partials -> global packed buffer
+    __shared__ double s_dd[8], s_in[8];
+    if (lane == 0) { s_dd[w] = dd_sum; s_in[w] = in_sum; }
+    if (CELLS && owner && my_cnt > 0) {
+        atomicAdd(packed + L.counts() + lane, (double) my_cnt);
+        atomicAdd(packed + L.discel() + lane, my_dis);
+    }
+    __syncthreads();
+    if (CELLS) {
+        const double *all = reinterpret_cast<double *>(smem_small) + (size_t) n_w * U * XROW;
+        for (int e = threadIdx.x; e < K * D; e += blockDim.x) {
+            double t = 0.0;
+            for (int ww = 0; ww < n_w; ww++) t += all[(size_t) ww * K * D + e];
+            if (t != 0.0) atomicAdd(packed + L.cells() + e, t);
+        }
+    }
+    if (threadIdx.x == 0) {
+        double a = 0.0, b = 0.0;
+        for (int i = 0; i < n_w; i++) { a += s_dd[i]; b += s_in[i]; }
+        atomicAdd(packed + L.dd(), a);
+        atomicAdd(packed + L.inertia(), b);
+    }
+}
+
+bool pass_small_supported(int K, int D) { return K <= 32 && (D == 37 || D == 13); }
+
+template <int DT>
+static void launch_pass_small_d(const double *x64, long n, const double *raas, int K, double *packed,
+                                int32_t *idx, double *mindist, uint16_t *seq, bool with_cells,
+                                int num_sms, cudaStream_t s) {
+    constexpr int XROW = (DT + 1) & ~1;
+    PackedLayout L{K, DT};
+    constexpr int kWarps = 4;   // 128 threads: ~160 registers/thread still leaves 3 CTAs per SM
+    const size_t smem = sizeof(double) * (kWarps * (size_t) 4 * XROW + kWarps * (size_t) K * DT);
+    int per_sm = (int) ((200 * 1024) / (smem + 1024));
+    if (per_sm > 3) per_sm = 3;
+    if (per_sm < 1) per_sm = 1;
+    long blocks = (long) num_sms * per_sm;
+    const long need = (n + 127) / 128;
+    if (blocks > need) blocks = need < 1 ? 1 : need;
+    if (with_cells) {
+        cudaFuncSetAttribute(vq_pass_small<DT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        vq_pass_small<DT, true><<<(unsigned) blocks, 128, smem, s>>>(x64, n, raas, L, packed, idx, mindist, seq);
+    } else {
+        cudaFuncSetAttribute(vq_pass_small<DT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        vq_pass_small<DT, false><<<(unsigned) blocks, 128, smem, s>>>(x64, n, raas, L, packed, idx, mindist, seq);
+    }
+}
+void launch_pass_small(const double *x64, long n, int D, const double *raas, int K, double *packed,
+                       int32_t *idx, double *mindist, uint16_t *seq, bool with_cells, int num_sms,
+                       cudaStream_t s) {
+    if (n <= 0) return;
+    if (D == 37) launch_pass_small_d<37>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
+    else launch_pass_small_d<13>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
+}
+
+// --------------------------------------------------------------------------------
 // (c) centroid / split: one warp per codeword, FP64, shared-memory scratch
 // --------------------------------------------------------------------------------
 // step-up recursion rc -> predictor a (lpca_rc, lpca.c:106-125); a[] in shared

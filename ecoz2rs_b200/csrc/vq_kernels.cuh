@@ -91,6 +91,14 @@ void launch_accumulate(const double *x64, const int32_t *idx, long n, int D,
                        const double *raas, int K, double *packed, double *mindist,
                        uint16_t *seq, bool with_cells, int num_sms, cudaStream_t s);
 
+// ---- (a+b) fused small-codebook pass (K <= 32, D = 37 or 13), all FP64 ----------
+// One sweep over the FP64 frames: exact argmin (first index on ties), idx / mindist / seq
+// outputs, and (with_cells) the packed cell sums, counts, distortions; DD and inertia always.
+bool pass_small_supported(int K, int D);
+void launch_pass_small(const double *x64, long n, int D, const double *raas, int K, double *packed,
+                       int32_t *idx, double *mindist, uint16_t *seq, bool with_cells, int num_sms,
+                       cudaStream_t s);
+
 // ---- (c) centroid update / split ----------------------------------------------
 // calculate_reflections (vq_learn.i:125-155): for every cell with count > 0,
 // Levinson-Durbin on the raw cell sum -> refl, raas; cell sum /= errPred.
