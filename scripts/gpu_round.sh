@@ -1,0 +1,26 @@
+#!/bin/bash
+# One gpurun call: GPU parity tests, smoke, both bench arms, ncu launch list, ncu --set full capture
+# of the search and accumulate kernels at K=2048. Everything lands in gpurun_out/.
+# usage: scripts/gpu_round.sh <tag>
+TAG=${1:-r01}
+O=gpurun_out
+mkdir -p $O
+nvidia-smi --query-gpu=name,clocks.max.sm,clocks.sm,power.limit --format=csv > $O/smi_$TAG.txt 2>&1
+nproc >> $O/smi_$TAG.txt
+timeout 1200 python -m pytest tests -m gpu -x -q > $O/pytest_gpu_$TAG.log 2>&1
+echo "pytest exit $?" >> $O/pytest_gpu_$TAG.log
+timeout 300 python __graft_entry__.py smoke > $O/smoke_$TAG.log 2>&1
+echo "smoke exit $?" >> $O/smoke_$TAG.log
+timeout 900 python bench.py > $O/bench_$TAG.json 2> $O/bench_$TAG.err
+echo "bench exit $?" >> $O/bench_$TAG.err
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref_$TAG.json 2> $O/bench_ref_$TAG.err
+echo "bench ref exit $?" >> $O/bench_ref_$TAG.err
+timeout 600 python scripts/perf_probe.py --n 10000000 --ks 2,4,8,16,32,64,128,256,512,1024,2048,4096 > $O/probe_$TAG.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
+    --log-file $O/launches_$TAG.csv python bench.py --frames 2000000 --steps 3 --warmup 3 \
+    --no-cpu-baseline --e2e-steps 1 > $O/ncu_launches_$TAG.log 2>&1
+timeout 900 ncu --set full --clock-control none --import-source on \
+    -k regex:"vq_assign_tiled|vq_accumulate" --launch-skip 20 --launch-count 4 \
+    -o $O/search_$TAG -f python scripts/perf_probe.py --n 2000000 --ks 2048 --reps 2 \
+    > $O/ncu_full_$TAG.log 2>&1
+ls -la $O
