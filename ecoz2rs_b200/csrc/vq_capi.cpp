@@ -347,6 +347,11 @@ void ecoz2b200_destroy(ecoz2b200_engine *e) { delete e; }
 
 int ecoz2b200_set_mode(ecoz2b200_engine *e, int mode) { ENG(e); return eng.set_mode(mode); }
 int ecoz2b200_set_recheck_kappa(ecoz2b200_engine *e, double k) { ENG(e); return eng.set_kappa(k); }
+int ecoz2b200_set_recheck_kappa_tc(ecoz2b200_engine *e, double k) { ENG(e); return eng.set_kappa_tc(k); }
+int ecoz2b200_debug_tc_distortions(ecoz2b200_engine *e, float *out, long n_rows) {
+    ENG(e);
+    return eng.debug_tc_distortions(out, n_rows);
+}
 
 int ecoz2b200_nccl_unique_id(unsigned char id_out[128]) {
     const vqb200::NcclApi *api = vqb200::nccl_api();

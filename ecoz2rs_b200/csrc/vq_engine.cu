@@ -91,6 +91,9 @@ Engine::Engine(const int *devices, int num_devices, int P, int max_M)
         if (!chk(cudaMalloc(&s.w32, sizeof(float) * (size_t) K32 * D_), "cudaMalloc w32")) return;
         if (!chk(cudaMalloc(&s.w64, sizeof(double) * (size_t) K64 * D_), "cudaMalloc w64")) return;
         if (!chk(cudaMalloc(&s.w1max, 16), "cudaMalloc w1max")) return;
+        if (tc_codebook_floats(max_M_, D_) > 0 &&
+            !chk(cudaMalloc(&s.wtc, sizeof(float) * tc_codebook_floats(max_M_ < 256 ? 256 : max_M_, D_)),
+                 "cudaMalloc wtc")) return;
         if (!chk(cudaMalloc(&s.w1, sizeof(float) * (size_t) K32), "cudaMalloc w1")) return;
         if (!chk(cudaMalloc(&s.packed, sizeof(double) * L.size()), "cudaMalloc packed")) return;
         if (!chk(cudaMalloc(&s.scalars, sizeof(double) * 8), "cudaMalloc scalars")) return;
@@ -112,6 +115,7 @@ Engine::~Engine() {
         cudaFree(s.x64); cudaFree(s.x32); cudaFree(s.idx); cudaFree(s.idx_tmp); cudaFree(s.seq);
         cudaFree(s.mindist); cudaFree(s.sc_mem);
         cudaFree(s.refl); cudaFree(s.raas); cudaFree(s.w32); cudaFree(s.w64); cudaFree(s.w1max); cudaFree(s.w1);
+        cudaFree(s.wtc);
         cudaFree(s.packed); cudaFree(s.scalars);
         QBuf &q = qbuf_[i];
         cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
@@ -122,16 +126,26 @@ Engine::~Engine() {
 }
 
 int Engine::set_mode(int mode) {
-    if (mode != ECOZ2B200_MODE_FP32 && mode != ECOZ2B200_MODE_FP64) {
+    if (mode != ECOZ2B200_MODE_FP32 && mode != ECOZ2B200_MODE_FP64 && mode != ECOZ2B200_MODE_TF32X3) {
         set_last_error("set_mode: mode not available in this build");
         return ECOZ2B200_ERR_ARG;
     }
     mode_ = mode;
+    if (K_ > 0) {   // the tensor-core operand exists only in its mode
+        int rc = stage_codebook();
+        if (rc) return rc;
+        return sync_all();
+    }
     return ECOZ2B200_OK;
 }
 int Engine::set_kappa(double kappa) {
     if (!(kappa >= 0)) return ECOZ2B200_ERR_ARG;
     kappa_ = kappa;
+    return ECOZ2B200_OK;
+}
+int Engine::set_kappa_tc(double kappa) {
+    if (!(kappa >= 0)) return ECOZ2B200_ERR_ARG;
+    kappa_tc_ = kappa;
     return ECOZ2B200_OK;
 }
 
@@ -343,6 +357,10 @@ int Engine::stage_codebook() {
         CUDA_TRY(cudaSetDevice(s.device));
         launch_prepare_codebook(s.raas, K_, D_, s.w32, s.w64, s.w1, s.w1max, s.stream);
         ctr_.kernel_launches++;
+        if (tc_path()) {
+            launch_prepare_codebook_tc(s.raas, K_, D_, s.wtc, s.stream);
+            ctr_.kernel_launches++;
+        }
     }
     return ECOZ2B200_OK;
 }
@@ -437,6 +455,17 @@ void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32
         launch_assign_f64(x64, n, D_, s.w64, K_, nullptr, nullptr, idx, s.num_sms, s.stream);
         cudaEventRecord(s.ev[7], s.stream);
         ctr_.kernel_launches += 1;
+    } else if (tc_path()) {
+        // tcgen05 split-TF32 search; same flag / re-evaluation protocol with its own kappa.
+        const float err_tc = (float) (kappa_tc_ * ldexp(1.0, -24));
+        const float err_scale = (float) (kappa_ * ldexp(1.0, -24));
+        cudaMemsetAsync(sc.counters, 0, 4 * sizeof(int32_t), s.stream);
+        launch_assign_tc(x32, n, D_, s.wtc, K_, nullptr, nullptr, sc, true, s.w1, s.w1max, err_tc, idx,
+                         nullptr, 0, s.num_sms, s.stream);
+        cudaEventRecord(s.ev[7], s.stream);
+        launch_recheck(x32, x64, n, D_, s.w32, s.w64, s.w1, s.w1max, s.raas, K_, 2.f * err_scale, sc,
+                       idx, s.num_sms, s.stream);
+        ctr_.kernel_launches += 5;
     } else {
         // |error| of one FP32 distortion <= kappa * 2^-24 * |rx[0]| * sum_n |w[n]|.
         // Main pass: flag when the best-two gap is below twice that bound taken with the
@@ -471,6 +500,29 @@ void Engine::pass_kernels(Shard &s, const double *x64, const float *x32, long n,
     launch_accumulate(x64, idx, n, D_, s.raas, K_, s.packed, mindist, seq, with_cells, s.num_sms,
                       s.stream);
     ctr_.kernel_launches += n > 0;
+}
+
+int Engine::debug_tc_distortions(float *out, long n_rows) {
+    if (!committed_ || K_ < 1 || !tc_path()) {
+        set_last_error("debug_tc_distortions: needs committed frames, a codebook and TF32X3 mode");
+        return ECOZ2B200_ERR_ARG;
+    }
+    Shard &s = shards_[0];
+    CUDA_TRY(cudaSetDevice(s.device));
+    if (n_rows > s.n) n_rows = s.n;
+    const int BN = tc_tile_cols(K_);
+    const int ld = (K_ + BN - 1) / BN * BN;
+    float *dump = nullptr;
+    CUDA_TRY(cudaMalloc(&dump, sizeof(float) * (size_t) n_rows * ld));
+    launch_assign_tc(s.x32, n_rows, D_, s.wtc, K_, nullptr, nullptr, s.sc, false, s.w1, s.w1max, 0.f,
+                     s.idx_tmp, dump, ld, s.num_sms, s.stream);
+    cudaError_t e = cudaMemcpy2DAsync(out, sizeof(float) * K_, dump, sizeof(float) * ld,
+                                      sizeof(float) * K_, (size_t) n_rows, cudaMemcpyDeviceToHost,
+                                      s.stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s.stream);
+    cudaFree(dump);
+    CUDA_TRY(e);
+    return ECOZ2B200_OK;
 }
 
 int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked) {
@@ -569,6 +621,10 @@ int Engine::kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_ou
         launch_centroids(s.packed, K_, D_, s.refl, s.raas, s.stream);
         launch_prepare_codebook(s.raas, K_, D_, s.w32, s.w64, s.w1, s.w1max, s.stream);
         ctr_.kernel_launches += 2;
+        if (tc_path()) {
+            launch_prepare_codebook_tc(s.raas, K_, D_, s.wtc, s.stream);
+            ctr_.kernel_launches++;
+        }
         CUDA_TRY(cudaEventRecord(s.ev[4], s.stream));
     }
     rc = sync_all();

@@ -44,6 +44,7 @@ struct Shard {
     double *w64 = nullptr;
     float *w1max = nullptr;
     float *w1 = nullptr;      // [K] sum_n |w_i[n]|
+    float *wtc = nullptr;     // tensor-core search operand (UMMA canonical layout, TF32 hi/lo)
     double *packed = nullptr; // PackedLayout(max_M, D)
     double *scalars = nullptr;  // [8] misc device scalars (sigma sum, ...)
 };
@@ -65,6 +66,10 @@ class Engine {
 
     int set_mode(int mode);
     int set_kappa(double kappa);
+    int set_kappa_tc(double kappa);
+    // debug: the tensor-core search's raw distortion values of the first n_rows frames of
+    // shard 0 against the current codebook, [n_rows][K] floats
+    int debug_tc_distortions(float *out, long n_rows);
     int comm_init(const unsigned char id[128], int rank, int world);
 
     int frames_reserve(long total);
@@ -114,12 +119,14 @@ class Engine {
     void harvest_times(bool with_cells);
 
     bool small_path() const { return use_small_ && pass_small_supported(K_, D_); }
+    bool tc_path() const { return mode_ == ECOZ2B200_MODE_TF32X3 && assign_tc_supported(K_, D_); }
     bool use_small_ = true;   // ECOZ2_VQ_FUSED_SMALL=0 forces the tiled path at every K
     bool ok_ = false;
     int P_, D_, max_M_;
     int K_ = 0;
     int mode_ = ECOZ2B200_MODE_FP32;
     double kappa_ = 8.0;
+    double kappa_tc_ = 16.0;
     std::vector<Shard> shards_;
     long n_total_ = 0;   // local frames (all shards)
     long n_global_ = 0;  // all ranks

@@ -82,6 +82,21 @@ void launch_recheck(const float *x32, const double *x64, long n, int D, const fl
                     int K, float err_scale, const SearchScratch &sc, int32_t *idx, int num_sms,
                     cudaStream_t s);
 
+// ---- (a') tensor-core search (vq_tc.cu): tcgen05 split-TF32, FP32 accumulate in TMEM --------
+// Supported for K >= 64 and D <= 40.  wtc = codebook in the UMMA canonical K-major layout,
+// split into TF32 (hi, lo) parts (tc_codebook_floats(K, D) floats, built from raas).
+// Same outputs as launch_assign_f32 (idx + flag_list of frames inside the error bound when
+// `flag`); list / list_count optionally restrict the search to a gathered subset.
+// dump (debug): every distortion value, [n][dump_ld] floats.
+bool assign_tc_supported(int K, int D);
+int tc_tile_cols(int K);
+size_t tc_codebook_floats(int K, int D);
+void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, cudaStream_t s);
+void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
+                      const int32_t *list, const int32_t *list_count, const SearchScratch &sc,
+                      bool flag, const float *w1, const float *w1max, float err_scale, int32_t *idx,
+                      float *dump, int dump_ld, int num_sms, cudaStream_t s);
+
 // ---- (b) cell accumulation ----------------------------------------------------
 // For every frame: dd = FP64 distortion against its codeword raas[idx];
 //   mindist[v] = dd - 1 (if mindist != nullptr); seq[v] = (u16) idx (if seq != nullptr)

@@ -1,0 +1,505 @@
+// vq_tc.cu -- tensor-core (tcgen05 / TMEM) variant of kernel (a), the fused
+// distortion + argmin search, for sm_100a.
+//
+// The distortion of frame i against codeword j is the inner product x_i . w_j
+// (w = (raa0, 2 raa1 .. 2 raaP), reference distortion.c:6-13).  Here the N x K
+// products run on the 5th-generation tensor cores as split-TF32 ("3xTF32"):
+//     x = xh + xl,  w = wh + wl   (each part representable in TF32)
+//     x . w  ~=  xl.wh + xh.wl + xh.wh          (xl.wl ~ 2^-22 relative, dropped)
+// accumulated in FP32 in tensor memory.  One CTA per SM walks frame tiles of 128
+// frames (UMMA M = 128, one TMEM lane per frame); for each frame tile all codeword
+// tiles (UMMA N = BN <= 256) stream past it:
+//
+//   warp 0      B producer: one cp.async.bulk (TMA engine) per (codeword tile, k-step)
+//               stage; the codebook is pre-laid-out in global memory in the UMMA
+//               canonical K-major core-matrix order, so a stage is one contiguous run
+//   warp 1      MMA issuer: one thread issues 3 tcgen05.mma.kind::tf32 per k-step into
+//               one of two TMEM accumulators, tcgen05.commit releases stages / signals
+//               the epilogue
+//   warps 2-3   A loaders: FP32 frames -> (hi, lo) split -> canonical smem layout,
+//               double buffered (next frame tile is staged while this one is searched)
+//   warps 4-7   epilogue: tcgen05.ld the accumulator (thread = frame, registers =
+//               codewords), running (best, second, argbest) per frame; the N x K
+//               matrix never leaves the SM.
+//
+// The values are only as good as 3xTF32, so -- exactly like the FP32 FFMA search --
+// a frame whose best-two gap is inside the error bound is appended to flag_list and
+// re-evaluated in FP64 by launch_recheck (vq_kernels.cu).  The reference semantics
+// (strict '<' scan in index order, vq_learn_par.c:66-75, quantize.c:19-26) are kept:
+// first index among equal values wins.
+#include "vq_kernels.cuh"
+
+#include <cfloat>
+#include <cmath>
+
+namespace vqb200 {
+
+namespace {
+
+constexpr int kBM = 128;        // frames per tile = UMMA M = TMEM lanes
+constexpr int kStages = 6;      // B stage ring
+constexpr int kMaxKSteps = 5;   // D <= 40
+constexpr int kThreads = 256;
+constexpr int kLoaderThreads = 64;
+constexpr int kEpiWarp0 = 4;
+
+// ---- PTX wrappers -----------------------------------------------------------------
+__device__ __forceinline__ uint32_t s32(const void *p) {
+    return (uint32_t) __cvta_generic_to_shared(p);
+}
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bar)),
+                 "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(bar)) : "memory");
+}
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
+    uint32_t ok;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(s32(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes,
+                                         uint64_t *bar) {
+    asm volatile(
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+            "r"(s32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(s32(bar))
+        : "memory");
+}
+__device__ __forceinline__ void fence_barrier_init() {
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void fence_proxy_async() {
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_before() {
+    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tc_fence_after() {
+    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t *slot_smem, uint32_t cols) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
+                     s32(slot_smem)),
+                 "r"(cols)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
+                 : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem], TF32 inputs, FP32 accumulate
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
+                                          uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// mbarrier arrives when every tcgen05.mma issued so far by this thread has completed
+__device__ __forceinline__ void umma_commit(uint64_t *bar) {
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::
+                     "r"(s32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+          "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+          "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr)
+        : "memory");
+}
+__device__ __forceinline__ void tmem_ld_wait() {
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ float tf32_rna(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return __uint_as_float(r);
+}
+
+// UMMA shared-memory matrix descriptor, K-major, no swizzle: core matrix = 8 rows x 16 B
+// stored as 128 contiguous bytes; lbo = byte distance between the two core matrices of a
+// k-step (K direction), sbo = byte distance between 8-row groups (M/N direction).
+__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
+    return (uint64_t) ((saddr >> 4) & 0x3FFFu) | ((uint64_t) ((lbo >> 4) & 0x3FFFu) << 16) |
+           ((uint64_t) ((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46);
+}
+// instruction descriptor: D = F32, A = B = TF32, both K-major, M x N
+__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
+    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t) (N >> 3) << 17) |
+           ((uint32_t) (M >> 4) << 24);
+}
+
+}  // namespace
+
+struct TcParams {
+    const float *x;             // frames [n][D] FP32
+    long n_frames;
+    int D;
+    int ksteps;                 // ceil(D / 8)
+    const int32_t *list;        // optional gather list (+ device-side count)
+    const int32_t *list_count;
+    const float *wtc;           // codeword stages, see tc_stage layout below
+    int K;
+    int BN;                     // codewords per tile (UMMA N): 64, 128 or 256
+    const float *w1;            // sum_n |w_i[n]| per codeword
+    const float *w1max;         // max_i w1[i]
+    float err_scale;            // kappa * 2^-24
+    int32_t *idx_out;
+    int32_t *flag_list;
+    int32_t *flag_count;
+    float *flag_ub;
+    unsigned long long *min_key;
+    float *dump;                // debug: all distortions [n][dump_ld]
+    int dump_ld;
+};
+
+// Global layout of the search operand built by vq_prepare_codebook_tc:
+//   stage (t, s) = codeword tile t, k-step s, contiguous 4 * BN * 16 bytes:
+//     [part: hi, lo][k-chunk c: 0, 1][row r: 0..BN)[e: 0..4)  = element k = 8 s + 4 c + e
+//   of codeword t * BN + r (zero beyond K / beyond D).
+// Shared memory (dynamic):
+//   [barriers, tmem slot | 1 KB][x0: 2 x 128 f32 | 1 KB]
+//   [A: 2 buffers x (2 parts x 2 ksteps chunks x 128 rows x 16 B)][B: kStages x 4 BN x 16 B]
+struct TcSmem {
+    uint64_t full[kStages], empty[kStages];
+    uint64_t tmem_full[2], tmem_empty[2];
+    uint64_t a_full[2], a_empty[2];
+    uint32_t tmem_slot;
+};
+
+__device__ __forceinline__ float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }
+
+__global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    TcSmem *sm = reinterpret_cast<TcSmem *>(smem_raw);
+    float *s_x0 = reinterpret_cast<float *>(smem_raw + 1024);
+    const int ksteps = p.ksteps;
+    const int KC = 2 * ksteps;                              // 16-byte k-chunks per row
+    const uint32_t a_part_bytes = (uint32_t) KC * kBM * 16;  // one part (hi or lo) of a frame tile
+    const uint32_t a_buf_bytes = 2 * a_part_bytes;
+    const int BN = p.BN;
+    const uint32_t stage_bytes = (uint32_t) 4 * BN * 16;
+    unsigned char *a_base = smem_raw + 2048;
+    unsigned char *b_base = a_base + 2 * a_buf_bytes;
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int K = p.K;
+    const int n_wtiles = (K + BN - 1) / BN;
+    const long total = p.list ? (long) *p.list_count : p.n_frames;
+    const long n_ftiles = (total + kBM - 1) / kBM;
+
+    if (tid == 0) {
+        for (int i = 0; i < kStages; i++) {
+            mbar_init(&sm->full[i], 1);
+            mbar_init(&sm->empty[i], 1);
+        }
+        for (int i = 0; i < 2; i++) {
+            mbar_init(&sm->tmem_full[i], 1);
+            mbar_init(&sm->tmem_empty[i], 4);
+            mbar_init(&sm->a_full[i], kLoaderThreads);
+            mbar_init(&sm->a_empty[i], 1 + 4);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc(&sm->tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = sm->tmem_slot;
+
+    if (warp == 0) {
+        // ===== B producer =====
+        if (lane == 0) {
+            uint32_t st = 0, ph = 0;
+            for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x) {
+                const float *src = p.wtc;
+                for (int t = 0; t < n_wtiles; t++) {
+                    for (int s = 0; s < ksteps; s++) {
+                        mbar_wait(&sm->empty[st], ph ^ 1);
+                        mbar_expect_tx(&sm->full[st], stage_bytes);
+                        bulk_g2s(b_base + (size_t) st * stage_bytes, src, stage_bytes, &sm->full[st]);
+                        src += (size_t) BN * 16;
+                        if (++st == kStages) { st = 0; ph ^= 1; }
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_tf32(kBM, BN);
+            uint32_t st = 0, ph = 0;
+            uint32_t tc = 0;  // accumulator tiles issued so far
+            uint32_t it = 0;
+            for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+                const uint32_t ab = it & 1;
+                mbar_wait(&sm->a_full[ab], (it >> 1) & 1);
+                tc_fence_after();
+                const uint32_t a_hi = s32(a_base + (size_t) ab * a_buf_bytes);
+                const uint32_t a_lo = a_hi + a_part_bytes;
+                for (int t = 0; t < n_wtiles; t++, tc++) {
+                    const uint32_t acc = tc & 1;
+                    mbar_wait(&sm->tmem_empty[acc], ((tc >> 1) & 1) ^ 1);
+                    tc_fence_after();
+                    const uint32_t d_tmem = tmem_base + acc * 256;
+                    for (int s = 0; s < ksteps; s++) {
+                        mbar_wait(&sm->full[st], ph);
+                        tc_fence_after();
+                        const uint32_t b_hi = s32(b_base + (size_t) st * stage_bytes);
+                        const uint32_t b_lo = b_hi + 2 * BN * 16;
+                        const uint32_t koff = (uint32_t) (2 * s) * kBM * 16;
+                        const uint64_t dah = umma_desc(a_hi + koff, kBM * 16, 128);
+                        const uint64_t dal = umma_desc(a_lo + koff, kBM * 16, 128);
+                        const uint64_t dbh = umma_desc(b_hi, BN * 16, 128);
+                        const uint64_t dbl = umma_desc(b_lo, BN * 16, 128);
+                        // small terms first
+                        umma_tf32(d_tmem, dal, dbh, idesc, s > 0);
+                        umma_tf32(d_tmem, dah, dbl, idesc, 1);
+                        umma_tf32(d_tmem, dah, dbh, idesc, 1);
+                        umma_commit(&sm->empty[st]);
+                        if (++st == kStages) { st = 0; ph ^= 1; }
+                    }
+                    umma_commit(&sm->tmem_full[acc]);
+                }
+                umma_commit(&sm->a_empty[ab]);
+            }
+        }
+    } else if (warp < kEpiWarp0) {
+        // ===== A loaders: FP32 rows -> TF32 (hi, lo) -> canonical K-major layout =====
+        const int lt = tid - 64;
+        const int D = p.D;
+        uint32_t it = 0;
+        for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+            const uint32_t ab = it & 1;
+            const long base = ft * kBM;
+            const int nvalid = (int) (total - base < kBM ? total - base : kBM);
+            mbar_wait(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1);
+            unsigned char *hi = a_base + (size_t) ab * a_buf_bytes;
+            unsigned char *lo = hi + a_part_bytes;
+            for (int item = lt; item < KC * kBM; item += kLoaderThreads) {
+                const int f = item & (kBM - 1), c = item >> 7;
+                float v[4] = {0.f, 0.f, 0.f, 0.f};
+                if (f < nvalid) {
+                    const long row = p.list ? (long) p.list[base + f] : base + f;
+                    const float *xr = p.x + row * D + 4 * c;
+#pragma unroll
+                    for (int e = 0; e < 4; e++)
+                        if (4 * c + e < D) v[e] = __ldg(xr + e);
+                }
+                float4 h, l;
+                h.x = tf32_rna(v[0]); h.y = tf32_rna(v[1]); h.z = tf32_rna(v[2]); h.w = tf32_rna(v[3]);
+                l.x = tf32_rna(v[0] - h.x); l.y = tf32_rna(v[1] - h.y);
+                l.z = tf32_rna(v[2] - h.z); l.w = tf32_rna(v[3] - h.w);
+                *reinterpret_cast<float4 *>(hi + ((size_t) c * kBM + f) * 16) = h;
+                *reinterpret_cast<float4 *>(lo + ((size_t) c * kBM + f) * 16) = l;
+                if (c == 0) s_x0[ab * kBM + f] = fabsf(v[0]);
+            }
+            fence_proxy_async();
+            mbar_arrive(&sm->a_full[ab]);
+        }
+    } else {
+        // ===== epilogue: thread = frame (TMEM lane), registers = codewords =====
+        const int q = warp & 3;                 // TMEM lane quarter this warp may read
+        const int f = q * 32 + lane;            // frame within the tile
+        const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
+        const float w1max = *p.w1max;
+        const int n_chunks = BN / 16;
+        uint32_t tc = 0, it = 0;
+        for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+            const uint32_t ab = it & 1;
+            const long base = ft * kBM;
+            const int nvalid = (int) (total - base < kBM ? total - base : kBM);
+            mbar_wait(&sm->a_full[ab], (it >> 1) & 1);
+            const float x0 = s_x0[ab * kBM + f];
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm->a_empty[ab]);
+            const long row = f < nvalid ? (p.list ? (long) p.list[base + f] : base + f) : -1;
+
+            float best = INFINITY, second = INFINITY;
+            int bidx = 0;
+            for (int t = 0; t < n_wtiles; t++, tc++) {
+                const uint32_t acc = tc & 1;
+                mbar_wait(&sm->tmem_full[acc], (tc >> 1) & 1);
+                tc_fence_after();
+                const int nv = K - t * BN < BN ? K - t * BN : BN;   // valid codewords in this tile
+                const uint32_t taddr = lane_addr + acc * 256;
+                for (int c = 0; c < n_chunks; c++) {
+                    if (c * 16 >= nv) break;
+                    uint32_t r[16];
+                    tmem_ld16(taddr + c * 16, r);
+                    tmem_ld_wait();
+                    float v[16];
+#pragma unroll
+                    for (int j = 0; j < 16; j++) v[j] = __uint_as_float(r[j]);
+                    if (c * 16 + 16 > nv) {
+#pragma unroll
+                        for (int j = 0; j < 16; j++)
+                            if (c * 16 + j >= nv) v[j] = INFINITY;
+                    }
+                    if (p.dump != nullptr && row >= 0) {
+#pragma unroll
+                        for (int j = 0; j < 16; j++)
+                            p.dump[row * p.dump_ld + t * BN + c * 16 + j] = v[j];
+                    }
+                    // chunk minimum (FMNMX3 tree)
+                    const float q0 = fminf(min3f(v[0], v[1], v[2]), v[3]);
+                    const float q1 = fminf(min3f(v[4], v[5], v[6]), v[7]);
+                    const float q2 = fminf(min3f(v[8], v[9], v[10]), v[11]);
+                    const float q3 = fminf(min3f(v[12], v[13], v[14]), v[15]);
+                    const float m = fminf(min3f(q0, q1, q2), q3);
+                    const bool rec = m < best;
+                    // not a record: every value of the chunk is >= m >= best, so m is the
+                    // chunk's only contender for runner-up.  record: the old best is.
+                    second = fminf(second, fmaxf(m, best));
+                    best = fminf(best, m);
+                    if (__any_sync(0xffffffffu, rec)) {
+                        if (rec) {
+                            // first position of the minimum + runner-up inside the chunk
+                            int jm = 15;
+                            float s2 = INFINITY;
+#pragma unroll
+                            for (int j = 15; j >= 0; j--) jm = v[j] == m ? j : jm;
+#pragma unroll
+                            for (int j = 0; j < 16; j++) s2 = fminf(s2, j == jm ? INFINITY : v[j]);
+                            second = fminf(second, s2);
+                            bidx = t * BN + c * 16 + jm;
+                        }
+                    }
+                }
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm->tmem_empty[acc]);
+            }
+            if (row >= 0) {
+                p.idx_out[row] = bidx;
+                if (p.flag_list != nullptr) {
+                    const float bound = 2.f * p.err_scale * w1max;
+                    // NaN-safe: "not clearly separated" => re-evaluate
+                    if (!(second - best >= bound * x0)) {
+                        const int pos = atomicAdd(p.flag_count, 1);
+                        p.flag_list[pos] = (int32_t) row;
+                        p.flag_ub[pos] = fmaf(2.f * p.err_scale * x0, p.w1[bidx], best);
+                        p.min_key[pos] = ~0ull;
+                    }
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// raas f64 [K][D] -> stages [tile][k-step][hi, lo][k-chunk][row][4]  (zero padded)
+__global__ void vq_prepare_codebook_tc(const double *__restrict__ raas, int K, int D, int BN,
+                                       int ksteps, float *__restrict__ wtc) {
+    const int n_wtiles = (K + BN - 1) / BN;
+    const long items = (long) n_wtiles * ksteps * 2 * BN;   // (t, s, c, r)
+    for (long it = (long) blockIdx.x * blockDim.x + threadIdx.x; it < items;
+         it += (long) gridDim.x * blockDim.x) {
+        const int r = (int) (it % BN);
+        const int c = (int) ((it / BN) & 1);
+        const int s = (int) ((it / (2 * BN)) % ksteps);
+        const int t = (int) (it / ((long) 2 * BN * ksteps));
+        const int cw = t * BN + r;
+        float4 h = make_float4(0.f, 0.f, 0.f, 0.f), l = h;
+        float *hp = &h.x, *lp = &l.x;
+        if (cw < K) {
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const int k = 8 * s + 4 * c + e;
+                if (k < D) {
+                    const double w = k > 0 ? 2.0 * raas[(long) cw * D + k] : raas[(long) cw * D];
+                    const float hi = tf32_rna((float) w);
+                    hp[e] = hi;
+                    lp[e] = tf32_rna((float) (w - (double) hi));
+                }
+            }
+        }
+        float *stage = wtc + ((size_t) t * ksteps + s) * (size_t) (4 * BN * 4);
+        *reinterpret_cast<float4 *>(stage + ((size_t) (0 * 2 + c) * BN + r) * 4) = h;
+        *reinterpret_cast<float4 *>(stage + ((size_t) (1 * 2 + c) * BN + r) * 4) = l;
+    }
+}
+
+static int tc_ksteps(int D) { return (D + 7) / 8; }
+
+int tc_tile_cols(int K) { return K >= 256 ? 256 : (K > 64 ? 128 : 64); }
+
+bool assign_tc_supported(int K, int D) { return K >= 64 && tc_ksteps(D) <= kMaxKSteps; }
+
+size_t tc_codebook_floats(int K, int D) {
+    const int BN = tc_tile_cols(K);
+    const int n_wtiles = (K + BN - 1) / BN;
+    return (size_t) n_wtiles * tc_ksteps(D) * 4 * BN * 4;
+}
+
+void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, cudaStream_t s) {
+    const int BN = tc_tile_cols(K), ksteps = tc_ksteps(D);
+    const long items = (long) ((K + BN - 1) / BN) * ksteps * 2 * BN;
+    const int blocks = (int) ((items + 255) / 256);
+    vq_prepare_codebook_tc<<<blocks, 256, 0, s>>>(raas, K, D, BN, ksteps, wtc);
+}
+
+static size_t tc_smem_bytes(int D, int BN) {
+    const int ksteps = tc_ksteps(D);
+    return 2048 + (size_t) 2 * 2 * (2 * ksteps) * kBM * 16 + (size_t) kStages * 4 * BN * 16;
+}
+
+void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
+                      const int32_t *list, const int32_t *list_count, const SearchScratch &sc,
+                      bool flag, const float *w1, const float *w1max, float err_scale, int32_t *idx,
+                      float *dump, int dump_ld, int num_sms, cudaStream_t s) {
+    if (n <= 0) return;
+    TcParams p{};
+    p.x = x32; p.n_frames = n; p.D = D; p.ksteps = tc_ksteps(D);
+    p.list = list; p.list_count = list_count;
+    p.wtc = wtc; p.K = K; p.BN = tc_tile_cols(K);
+    p.w1 = w1; p.w1max = w1max; p.err_scale = err_scale; p.idx_out = idx;
+    if (flag) {
+        p.flag_list = sc.flag_list; p.flag_count = sc.counters + 0; p.flag_ub = sc.flag_ub;
+        p.min_key = sc.min_key;
+    }
+    p.dump = dump; p.dump_ld = dump_ld;
+    const size_t smem = tc_smem_bytes(D, p.BN);
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(vq_assign_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        attr_set = true;
+    }
+    long tiles = (n + kBM - 1) / kBM;
+    long grid = tiles < num_sms ? tiles : num_sms;
+    if (grid < 1) grid = 1;
+    vq_assign_tc<<<(unsigned) grid, kThreads, smem, s>>>(p);
+}
+
+}  // namespace vqb200

@@ -55,6 +55,7 @@ EXPORTED_SYMBOLS = (
     "ecoz2_vq_learn", "ecoz2_vq_learn_using_base_codebook", "ecoz2_vq_quantize",
     "ecoz2b200_version", "ecoz2b200_last_error", "ecoz2b200_device_count",
     "ecoz2b200_create", "ecoz2b200_destroy", "ecoz2b200_set_mode", "ecoz2b200_set_recheck_kappa",
+    "ecoz2b200_set_recheck_kappa_tc", "ecoz2b200_debug_tc_distortions",
     "ecoz2b200_nccl_unique_id", "ecoz2b200_comm_init",
     "ecoz2b200_frames_clear", "ecoz2b200_frames_reserve", "ecoz2b200_frames_append_host",
     "ecoz2b200_frames_append_device", "ecoz2b200_frames_commit", "ecoz2b200_frames_count",
@@ -94,6 +95,8 @@ def lib():
             "ecoz2b200_destroy": (None, [vp]),
             "ecoz2b200_set_mode": (i, [vp, i]),
             "ecoz2b200_set_recheck_kappa": (i, [vp, d]),
+            "ecoz2b200_set_recheck_kappa_tc": (i, [vp, d]),
+            "ecoz2b200_debug_tc_distortions": (i, [vp, vp, l]),
             "ecoz2b200_nccl_unique_id": (i, [C.c_char_p]),
             "ecoz2b200_comm_init": (i, [vp, C.c_char_p, i, i]),
             "ecoz2b200_frames_clear": (i, [vp]),
@@ -188,6 +191,16 @@ class VqEngine:
 
     def set_recheck_kappa(self, kappa: float):
         _check(lib().ecoz2b200_set_recheck_kappa(self._h, kappa), "set_recheck_kappa")
+
+    def set_recheck_kappa_tc(self, kappa: float):
+        _check(lib().ecoz2b200_set_recheck_kappa_tc(self._h, kappa), "set_recheck_kappa_tc")
+
+    def debug_tc_distortions(self, n_rows: int) -> np.ndarray:
+        """Raw tensor-core (split-TF32) distortion values of the first n_rows resident frames."""
+        out = np.empty((n_rows, self.K), dtype=np.float32)
+        _check(lib().ecoz2b200_debug_tc_distortions(self._h, out.ctypes.data, n_rows),
+               "debug_tc_distortions")
+        return out
 
     def comm_init(self, unique_id: bytes, rank: int, world_size: int):
         assert len(unique_id) == 128

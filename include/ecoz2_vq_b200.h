@@ -100,6 +100,11 @@ int ecoz2b200_set_mode(ecoz2b200_engine *e, int mode);
 /* kappa of the FP32 ambiguity bound: a frame is re-evaluated in FP64 when
  * d2 - d1 < 2 * kappa * 2^-24 * rx[0] * max_i sum_n |w_i[n]|.                 */
 int ecoz2b200_set_recheck_kappa(ecoz2b200_engine *e, double kappa);
+/* same for the TF32X3 tensor-core search (its own error constant)             */
+int ecoz2b200_set_recheck_kappa_tc(ecoz2b200_engine *e, double kappa);
+/* test aid: the raw tensor-core distortion values of the first n_rows resident
+ * frames of shard 0 against the current codebook, out[n_rows][K] (TF32X3 mode) */
+int ecoz2b200_debug_tc_distortions(ecoz2b200_engine *e, float *out, long n_rows);
 
 /* Multi-process sharding (one process per GPU, e.g. under torchrun): all ranks
  * call comm_init with the same 128-byte id obtained once from

@@ -45,6 +45,7 @@ for K in [int(k) for k in a.ks.split(",")]:
     c = eng.counters()
     am, cm, um = c["assign_ms"] / a.reps, c["accumulate_ms"] / a.reps, c["update_ms"] / a.reps
     evals = a.n * K
-    print(f"K={K:5d} pass wall {wall*1e3:8.2f} ms | assign {am:8.2f} ms accumulate {cm:7.2f} ms update {um:6.2f} ms "
+    sm = c["search_main_ms"] / max(1, c["search_main_launches"])
+    print(f"K={K:5d} pass wall {wall*1e3:8.2f} ms | main search {sm:8.2f} ms ({evals/sm/1e6:7.1f} G evals/s) | assign {am:8.2f} ms accumulate {cm:7.2f} ms update {um:6.2f} ms "
           f"| {evals/am/1e6:9.1f} G evals/s (assign)  {evals*2*(a.p+1)/(am*1e-3)/peak*100:5.1f}% of FP32 peak "
           f"| rechecked/pass {c['rechecked']/a.reps:.0f} ({c['rechecked']/a.reps/a.n*100:.3f}%)", flush=True)
