@@ -126,7 +126,7 @@ class Engine {
     int K_ = 0;
     int mode_ = ECOZ2B200_MODE_FP32;
     double kappa_ = 8.0;
-    double kappa_tc_ = 16.0;
+    double kappa_tc_ = 40.0;
     std::vector<Shard> shards_;
     long n_total_ = 0;   // local frames (all shards)
     long n_global_ = 0;  // all ranks

@@ -39,9 +39,10 @@ namespace {
 constexpr int kBM = 128;        // frames per tile = UMMA M = TMEM lanes
 constexpr int kStages = 6;      // B stage ring
 constexpr int kMaxKSteps = 5;   // D <= 40
-constexpr int kThreads = 256;
+constexpr int kThreads = 384;    // 4 role warps + 8 epilogue warps
 constexpr int kLoaderThreads = 64;
 constexpr int kEpiWarp0 = 4;
+constexpr int kEpiWarps = 8;     // two per TMEM lane quarter, each takes half of the columns
 
 // ---- PTX wrappers -----------------------------------------------------------------
 __device__ __forceinline__ uint32_t s32(const void *p) {
@@ -162,7 +163,7 @@ struct TcParams {
     const float *x;             // frames [n][D] FP32
     long n_frames;
     int D;
-    int ksteps;                 // ceil(D / 8)
+    int ksteps;                 // ceil((D + 1) / 8): D elements + the bound slot
     const int32_t *list;        // optional gather list (+ device-side count)
     const int32_t *list_count;
     const float *wtc;           // codeword stages, see tc_stage layout below
@@ -185,7 +186,7 @@ struct TcParams {
 //     [part: hi, lo][k-chunk c: 0, 1][row r: 0..BN)[e: 0..4)  = element k = 8 s + 4 c + e
 //   of codeword t * BN + r (zero beyond K / beyond D).
 // Shared memory (dynamic):
-//   [barriers, tmem slot | 1 KB][x0: 2 x 128 f32 | 1 KB]
+//   [barriers, tmem slot | 1 KB][x0: 2 x 128 f32 | 1 KB][epilogue merge slots: 2 x 128 float4 | 4 KB]
 //   [A: 2 buffers x (2 parts x 2 ksteps chunks x 128 rows x 16 B)][B: kStages x 4 BN x 16 B]
 struct TcSmem {
     uint64_t full[kStages], empty[kStages];
@@ -196,17 +197,57 @@ struct TcSmem {
 
 __device__ __forceinline__ float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }
 
+
+// One chunk of 16 consecutive codewords of one frame: update the running minimum, its
+// codeword and the runner-up.  Fast path: 10 FMNMX(3) for the chunk minimum + 4 ops; only
+// when some lane of the warp sees a new minimum is the position inside the chunk resolved
+// (by quads: first quad that holds m, then first element of that quad).
+__device__ __forceinline__ void epi_chunk(const float (&v)[16], int col0, float &best,
+                                          float &second, int &bidx) {
+    const float q0 = fminf(min3f(v[0], v[1], v[2]), v[3]);
+    const float q1 = fminf(min3f(v[4], v[5], v[6]), v[7]);
+    const float q2 = fminf(min3f(v[8], v[9], v[10]), v[11]);
+    const float q3 = fminf(min3f(v[12], v[13], v[14]), v[15]);
+    const float m = fminf(min3f(q0, q1, q2), q3);
+    const bool rec = m < best;
+    // not a record: every value of the chunk is >= m >= best, so m is the chunk's only
+    // contender for runner-up.  record: the old best is.
+    second = fminf(second, fmaxf(m, best));
+    best = fminf(best, m);
+    if (__any_sync(0xffffffffu, rec)) {
+        if (rec) {
+            const bool p0 = q0 == m, p1 = !p0 && q1 == m, p2 = !p0 && !p1 && q2 == m;
+            const bool p3 = !p0 && !p1 && !p2;
+            const int g = p0 ? 0 : p1 ? 1 : p2 ? 2 : 3;
+            const float a = p0 ? v[0] : p1 ? v[4] : p2 ? v[8] : v[12];
+            const float b = p0 ? v[1] : p1 ? v[5] : p2 ? v[9] : v[13];
+            const float c = p0 ? v[2] : p1 ? v[6] : p2 ? v[10] : v[14];
+            const float d = p0 ? v[3] : p1 ? v[7] : p2 ? v[11] : v[15];
+            const float o = fminf(min3f(p0 ? INFINITY : q0, p1 ? INFINITY : q1, p2 ? INFINITY : q2),
+                                  p3 ? INFINITY : q3);
+            const bool e0 = a == m, e1 = !e0 && b == m, e2 = !e0 && !e1 && c == m;
+            const bool e3 = !e0 && !e1 && !e2;
+            const int jq = e0 ? 0 : e1 ? 1 : e2 ? 2 : 3;
+            const float s2 = fminf(min3f(e0 ? INFINITY : a, e1 ? INFINITY : b, e2 ? INFINITY : c),
+                                   e3 ? INFINITY : d);
+            second = min3f(second, o, s2);
+            bidx = col0 + 4 * g + jq;
+        }
+    }
+}
+
 __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     TcSmem *sm = reinterpret_cast<TcSmem *>(smem_raw);
     float *s_x0 = reinterpret_cast<float *>(smem_raw + 1024);
+    float4 *s_merge = reinterpret_cast<float4 *>(smem_raw + 2048);
     const int ksteps = p.ksteps;
     const int KC = 2 * ksteps;                              // 16-byte k-chunks per row
     const uint32_t a_part_bytes = (uint32_t) KC * kBM * 16;  // one part (hi or lo) of a frame tile
     const uint32_t a_buf_bytes = 2 * a_part_bytes;
     const int BN = p.BN;
     const uint32_t stage_bytes = (uint32_t) 4 * BN * 16;
-    unsigned char *a_base = smem_raw + 2048;
+    unsigned char *a_base = smem_raw + 6144;
     unsigned char *b_base = a_base + 2 * a_buf_bytes;
 
     const int tid = threadIdx.x;
@@ -223,9 +264,9 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
         }
         for (int i = 0; i < 2; i++) {
             mbar_init(&sm->tmem_full[i], 1);
-            mbar_init(&sm->tmem_empty[i], 4);
+            mbar_init(&sm->tmem_empty[i], kEpiWarps);
             mbar_init(&sm->a_full[i], kLoaderThreads);
-            mbar_init(&sm->a_empty[i], 1 + 4);
+            mbar_init(&sm->a_empty[i], 1 + kEpiWarps);
         }
         fence_barrier_init();
     }
@@ -313,6 +354,14 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
 #pragma unroll
                     for (int e = 0; e < 4; e++)
                         if (4 * c + e < D) v[e] = __ldg(xr + e);
+                    // slot D carries -e |x0|: with W1_j in the codeword's slot D the accumulator
+                    // becomes the lower bound d~_ij - e |x0| W1_j
+                    if (c == (D >> 2)) {
+                        const float bs = -1.001f * p.err_scale * fabsf(__ldg(p.x + row * D));
+#pragma unroll
+                        for (int e = 0; e < 4; e++)
+                            if (e == (D & 3)) v[e] = bs;
+                    }
                 }
                 float4 h, l;
                 h.x = tf32_rna(v[0]); h.y = tf32_rna(v[1]); h.z = tf32_rna(v[2]); h.w = tf32_rna(v[3]);
@@ -328,10 +377,12 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
     } else {
         // ===== epilogue: thread = frame (TMEM lane), registers = codewords =====
         const int q = warp & 3;                 // TMEM lane quarter this warp may read
+        const int h = (warp - kEpiWarp0) >> 2;  // which half of every tile's columns
         const int f = q * 32 + lane;            // frame within the tile
         const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
-        const float w1max = *p.w1max;
         const int n_chunks = BN / 16;
+        const int c_lo = h * (n_chunks / 2), c_hi = c_lo + n_chunks / 2;
+        const float e2 = 2.f * 1.001f * p.err_scale;
         uint32_t tc = 0, it = 0;
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
             const uint32_t ab = it & 1;
@@ -350,64 +401,63 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
                 mbar_wait(&sm->tmem_full[acc], (tc >> 1) & 1);
                 tc_fence_after();
                 const int nv = K - t * BN < BN ? K - t * BN : BN;   // valid codewords in this tile
+                const int c_end = (nv + 15) / 16 < c_hi ? (nv + 15) / 16 : c_hi;
                 const uint32_t taddr = lane_addr + acc * 256;
-                for (int c = 0; c < n_chunks; c++) {
-                    if (c * 16 >= nv) break;
-                    uint32_t r[16];
-                    tmem_ld16(taddr + c * 16, r);
+                uint32_t ra[16], rb[16];
+                int c = c_lo;
+                if (c < c_end) tmem_ld16(taddr + c * 16, ra);
+                // software pipeline: the next chunk's tcgen05.ld is in flight while this one
+                // is reduced
+#define VQ_TC_CHUNK(R)                                                                    \
+    {                                                                                     \
+        float v[16];                                                                      \
+        _Pragma("unroll") for (int j = 0; j < 16; j++) v[j] = __uint_as_float(R[j]);      \
+        if (c * 16 + 16 > nv) {                                                           \
+            _Pragma("unroll") for (int j = 0; j < 16; j++) if (c * 16 + j >= nv) v[j] = INFINITY; \
+        }                                                                                 \
+        if (p.dump != nullptr && row >= 0) {                                              \
+            _Pragma("unroll") for (int j = 0; j < 16; j++)                                \
+                p.dump[row * p.dump_ld + t * BN + c * 16 + j] = v[j];                     \
+        }                                                                                 \
+        epi_chunk(v, t * BN + c * 16, best, second, bidx);                                \
+    }
+                while (c < c_end) {
                     tmem_ld_wait();
-                    float v[16];
-#pragma unroll
-                    for (int j = 0; j < 16; j++) v[j] = __uint_as_float(r[j]);
-                    if (c * 16 + 16 > nv) {
-#pragma unroll
-                        for (int j = 0; j < 16; j++)
-                            if (c * 16 + j >= nv) v[j] = INFINITY;
-                    }
-                    if (p.dump != nullptr && row >= 0) {
-#pragma unroll
-                        for (int j = 0; j < 16; j++)
-                            p.dump[row * p.dump_ld + t * BN + c * 16 + j] = v[j];
-                    }
-                    // chunk minimum (FMNMX3 tree)
-                    const float q0 = fminf(min3f(v[0], v[1], v[2]), v[3]);
-                    const float q1 = fminf(min3f(v[4], v[5], v[6]), v[7]);
-                    const float q2 = fminf(min3f(v[8], v[9], v[10]), v[11]);
-                    const float q3 = fminf(min3f(v[12], v[13], v[14]), v[15]);
-                    const float m = fminf(min3f(q0, q1, q2), q3);
-                    const bool rec = m < best;
-                    // not a record: every value of the chunk is >= m >= best, so m is the
-                    // chunk's only contender for runner-up.  record: the old best is.
-                    second = fminf(second, fmaxf(m, best));
-                    best = fminf(best, m);
-                    if (__any_sync(0xffffffffu, rec)) {
-                        if (rec) {
-                            // first position of the minimum + runner-up inside the chunk
-                            int jm = 15;
-                            float s2 = INFINITY;
-#pragma unroll
-                            for (int j = 15; j >= 0; j--) jm = v[j] == m ? j : jm;
-#pragma unroll
-                            for (int j = 0; j < 16; j++) s2 = fminf(s2, j == jm ? INFINITY : v[j]);
-                            second = fminf(second, s2);
-                            bidx = t * BN + c * 16 + jm;
-                        }
-                    }
+                    if (c + 1 < c_end) tmem_ld16(taddr + (c + 1) * 16, rb);
+                    VQ_TC_CHUNK(ra);
+                    if (++c >= c_end) break;
+                    tmem_ld_wait();
+                    if (c + 1 < c_end) tmem_ld16(taddr + (c + 1) * 16, ra);
+                    VQ_TC_CHUNK(rb);
+                    ++c;
                 }
+#undef VQ_TC_CHUNK
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm->tmem_empty[acc]);
             }
-            if (row >= 0) {
-                p.idx_out[row] = bidx;
-                if (p.flag_list != nullptr) {
-                    const float bound = 2.f * p.err_scale * w1max;
-                    // NaN-safe: "not clearly separated" => re-evaluate
-                    if (!(second - best >= bound * x0)) {
-                        const int pos = atomicAdd(p.flag_count, 1);
-                        p.flag_list[pos] = (int32_t) row;
-                        p.flag_ub[pos] = fmaf(2.f * p.err_scale * x0, p.w1[bidx], best);
-                        p.min_key[pos] = ~0ull;
+            // merge the two column halves of each frame (upper half hands over via smem)
+            float4 *slot = s_merge + (it & 1) * kBM + f;
+            if (h == 1) *slot = make_float4(best, second, __int_as_float(bidx), 0.f);
+            asm volatile("bar.sync %0, 64;" ::"r"(1 + q) : "memory");
+            if (h == 0) {
+                const float4 o = *slot;
+                const int oi = __float_as_int(o.z);
+                second = min3f(second, o.y, fmaxf(best, o.x));
+                if (o.x < best || (o.x == best && oi < bidx)) { best = o.x; bidx = oi; }
+                if (row >= 0) {
+                    p.idx_out[row] = bidx;
+                    if (p.flag_list != nullptr) {
+                        // accumulator = lower bound L_ij = d~_ij - e |x0| W1_j of the true
+                        // distortion; bidx is certainly the true argmin when every other lower
+                        // bound exceeds its upper bound L + 2 e |x0| W1.  NaN-safe.
+                        const float ub = fmaf(e2 * x0, p.w1[bidx], best);
+                        if (!(second > ub)) {
+                            const int pos = atomicAdd(p.flag_count, 1);
+                            p.flag_list[pos] = (int32_t) row;
+                            p.flag_ub[pos] = ub;
+                            p.min_key[pos] = ~0ull;
+                        }
                     }
                 }
             }
@@ -437,8 +487,15 @@ __global__ void vq_prepare_codebook_tc(const double *__restrict__ raas, int K, i
 #pragma unroll
             for (int e = 0; e < 4; e++) {
                 const int k = 8 * s + 4 * c + e;
-                if (k < D) {
-                    const double w = k > 0 ? 2.0 * raas[(long) cw * D + k] : raas[(long) cw * D];
+                if (k <= D) {
+                    double w;
+                    if (k < D) {
+                        w = k > 0 ? 2.0 * raas[(long) cw * D + k] : raas[(long) cw * D];
+                    } else {   // slot D: W1 = sum_n |w[n]|
+                        w = fabs(raas[(long) cw * D]);
+                        for (int n = 1; n < D; n++) w += 2.0 * fabs(raas[(long) cw * D + n]);
+                        w *= 1.0 + 1e-6;
+                    }
                     const float hi = tf32_rna((float) w);
                     hp[e] = hi;
                     lp[e] = tf32_rna((float) (w - (double) hi));
@@ -451,7 +508,7 @@ __global__ void vq_prepare_codebook_tc(const double *__restrict__ raas, int K, i
     }
 }
 
-static int tc_ksteps(int D) { return (D + 7) / 8; }
+static int tc_ksteps(int D) { return (D + 8) / 8; }   // D elements + the bound slot
 
 int tc_tile_cols(int K) { return K >= 256 ? 256 : (K > 64 ? 128 : 64); }
 
@@ -472,7 +529,7 @@ void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, cu
 
 static size_t tc_smem_bytes(int D, int BN) {
     const int ksteps = tc_ksteps(D);
-    return 2048 + (size_t) 2 * 2 * (2 * ksteps) * kBM * 16 + (size_t) kStages * 4 * BN * 16;
+    return 6144 + (size_t) 2 * 2 * (2 * ksteps) * kBM * 16 + (size_t) kStages * 4 * BN * 16;
 }
 
 void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,

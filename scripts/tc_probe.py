@@ -44,7 +44,7 @@ for K in [int(k) for k in a.ks.split(",")]:
     print(f"   max |err| {err.max():.3e}  max err/(x0 W1) {np.max(err/scale)/u:.3f} u24  "
           f"rms {np.sqrt(np.mean((err/scale)**2))/u:.4f} u24  max rel err {np.max(err/np.abs(ref)):.3e}",
           flush=True)
-    for kap in (4, 8, 16, 32):
+    for kap in (16, 32, 48, 64):
         eng.set_recheck_kappa_tc(kap)
         eng.counters_reset()
         idx, dd, nre = eng.assign()
