@@ -31,6 +31,7 @@
 
 #include <cfloat>
 #include <cmath>
+#include <cstdlib>
 
 namespace vqb200 {
 
@@ -135,6 +136,19 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
         : "r"(taddr)
         : "memory");
 }
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
+        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
+        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
+          "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
+          "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
+          "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
+          "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+        : "r"(taddr)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_ld_wait() {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
@@ -179,6 +193,7 @@ struct TcParams {
     unsigned long long *min_key;
     float *dump;                // debug: all distortions [n][dump_ld]
     int dump_ld;
+    int exp;                    // dev experiments (ECOZ2_VQ_TC_EXP): bit mask 1 no record path, 2 trivial reduction, 4 no tcgen05.ld, 8 no MMA, 16 no tcgen05.st, 32 no B copy
 };
 
 // Global layout of the search operand built by vq_prepare_codebook_tc:
@@ -192,48 +207,145 @@ struct TcSmem {
     uint64_t full[kStages], empty[kStages];
     uint64_t tmem_full[2], tmem_empty[2];
     uint64_t a_full[2], a_empty[2];
+    uint64_t raw_full;
     uint32_t tmem_slot;
 };
 
 __device__ __forceinline__ float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }
 
 
-// One chunk of 16 consecutive codewords of one frame: update the running minimum, its
-// codeword and the runner-up.  Fast path: 10 FMNMX(3) for the chunk minimum + 4 ops; only
-// when some lane of the warp sees a new minimum is the position inside the chunk resolved
-// (by quads: first quad that holds m, then first element of that quad).
-__device__ __forceinline__ void epi_chunk(const float (&v)[16], int col0, float &best,
-                                          float &second, int &bidx) {
+// Running state of one frame (one epilogue thread): minimum, runner-up, and a snapshot of
+// the 16-codeword chunk that holds the minimum.  Only the FINAL minimum's chunk matters for
+// the runner-up inside a chunk (a superseded minimum is itself a smaller-or-equal contender
+// than anything else in its chunk), so the position inside the chunk is resolved once per
+// frame (epi_finish), not per record.
+struct EpiState {
+    float best, second;
+    int col;          // first codeword of the snapshot chunk
+    float snap[16];
+    __device__ __forceinline__ void init() {
+        best = INFINITY; second = INFINITY; col = 0;
+#pragma unroll
+        for (int j = 0; j < 16; j++) snap[j] = INFINITY;
+    }
+};
+
+// One chunk of 16 consecutive codewords: 10 FMNMX(3) for the chunk minimum + 4 ops; when some
+// lane of the warp sees a new minimum those lanes copy the chunk (predicated moves).
+__device__ __forceinline__ void epi_chunk(const float (&v)[16], int col0, EpiState &st, int exp = 0) {
+    if (exp & 2) { st.best = fminf(st.best, v[0]); return; }
     const float q0 = fminf(min3f(v[0], v[1], v[2]), v[3]);
     const float q1 = fminf(min3f(v[4], v[5], v[6]), v[7]);
     const float q2 = fminf(min3f(v[8], v[9], v[10]), v[11]);
     const float q3 = fminf(min3f(v[12], v[13], v[14]), v[15]);
     const float m = fminf(min3f(q0, q1, q2), q3);
-    const bool rec = m < best;
+    const bool rec = m < st.best;
     // not a record: every value of the chunk is >= m >= best, so m is the chunk's only
     // contender for runner-up.  record: the old best is.
-    second = fminf(second, fmaxf(m, best));
-    best = fminf(best, m);
-    if (__any_sync(0xffffffffu, rec)) {
+    st.second = fminf(st.second, fmaxf(m, st.best));
+    st.best = fminf(st.best, m);
+    if (!(exp & 1) && __any_sync(0xffffffffu, rec)) {
         if (rec) {
-            const bool p0 = q0 == m, p1 = !p0 && q1 == m, p2 = !p0 && !p1 && q2 == m;
-            const bool p3 = !p0 && !p1 && !p2;
-            const int g = p0 ? 0 : p1 ? 1 : p2 ? 2 : 3;
-            const float a = p0 ? v[0] : p1 ? v[4] : p2 ? v[8] : v[12];
-            const float b = p0 ? v[1] : p1 ? v[5] : p2 ? v[9] : v[13];
-            const float c = p0 ? v[2] : p1 ? v[6] : p2 ? v[10] : v[14];
-            const float d = p0 ? v[3] : p1 ? v[7] : p2 ? v[11] : v[15];
-            const float o = fminf(min3f(p0 ? INFINITY : q0, p1 ? INFINITY : q1, p2 ? INFINITY : q2),
-                                  p3 ? INFINITY : q3);
-            const bool e0 = a == m, e1 = !e0 && b == m, e2 = !e0 && !e1 && c == m;
-            const bool e3 = !e0 && !e1 && !e2;
-            const int jq = e0 ? 0 : e1 ? 1 : e2 ? 2 : 3;
-            const float s2 = fminf(min3f(e0 ? INFINITY : a, e1 ? INFINITY : b, e2 ? INFINITY : c),
-                                   e3 ? INFINITY : d);
-            second = min3f(second, o, s2);
-            bidx = col0 + 4 * g + jq;
+#pragma unroll
+            for (int j = 0; j < 16; j++) st.snap[j] = v[j];
+            st.col = col0;
         }
     }
+}
+
+// 32 consecutive codewords (two independent 16-chunks -> two min trees in flight).
+// nv_rel = number of valid codewords from col0 on (>= 32 except at the end of the codebook).
+__device__ __forceinline__ void epi_step32(const uint32_t (&r)[32], int col0, int nv_rel,
+                                           EpiState &st, int exp) {
+#define F(i) __uint_as_float(r[i])
+    if (exp & 2) { st.best = fminf(st.best, F(0)); return; }
+    if (nv_rel < 32) {   // ragged end of the codebook: generic path
+        float v[16];
+#pragma unroll
+        for (int j = 0; j < 16; j++) v[j] = j < nv_rel ? F(j) : INFINITY;
+        epi_chunk(v, col0, st, exp);
+        if (nv_rel > 16) {
+#pragma unroll
+            for (int j = 0; j < 16; j++) v[j] = 16 + j < nv_rel ? F(16 + j) : INFINITY;
+            epi_chunk(v, col0 + 16, st, exp);
+        }
+        return;
+    }
+    const float a0 = fminf(min3f(F(0), F(1), F(2)), F(3));
+    const float b0 = fminf(min3f(F(16), F(17), F(18)), F(19));
+    const float a1 = fminf(min3f(F(4), F(5), F(6)), F(7));
+    const float b1 = fminf(min3f(F(20), F(21), F(22)), F(23));
+    const float a2 = fminf(min3f(F(8), F(9), F(10)), F(11));
+    const float b2 = fminf(min3f(F(24), F(25), F(26)), F(27));
+    const float a3 = fminf(min3f(F(12), F(13), F(14)), F(15));
+    const float b3 = fminf(min3f(F(28), F(29), F(30)), F(31));
+    const float mA = fminf(min3f(a0, a1, a2), a3);
+    const float mB = fminf(min3f(b0, b1, b2), b3);
+    const float m = fminf(mA, mB);
+    const bool rec = m < st.best;
+    // contenders for runner-up: the larger chunk minimum always; m itself unless it is the new
+    // best, in which case the old best is
+    st.second = min3f(st.second, fmaxf(m, st.best), fmaxf(mA, mB));
+    st.best = fminf(st.best, m);
+    if (!(exp & 1) && __any_sync(0xffffffffu, rec)) {
+        const bool ra_ = rec && mA <= mB, rb_ = rec && !(mA <= mB);
+        if (ra_) {
+#pragma unroll
+            for (int j = 0; j < 16; j++) st.snap[j] = F(j);
+            st.col = col0;
+        }
+        if (rb_) {
+#pragma unroll
+            for (int j = 0; j < 16; j++) st.snap[j] = F(16 + j);
+            st.col = col0 + 16;
+        }
+    }
+#undef F
+}
+
+// -> codeword of the minimum (first position among equal values) and the overall runner-up
+__device__ __forceinline__ void epi_finish(const EpiState &st, float &second, int &bidx) {
+    int jm = 15;
+#pragma unroll
+    for (int j = 14; j >= 0; j--) jm = st.snap[j] == st.best ? j : jm;
+    float s2 = INFINITY;
+#pragma unroll
+    for (int j = 0; j < 16; j++) s2 = fminf(s2, j == jm ? INFINITY : st.snap[j]);
+    second = fminf(st.second, s2);
+    bidx = st.col + jm;
+}
+
+// Columns [c_lo, c_hi) of one accumulator (thread = its TMEM lane), 32 at a time; the next
+// tcgen05.ld is in flight while the current 32 values are reduced.  nv = valid codewords in
+// this tile, tcol0 = codeword index of the tile's column 0.
+__device__ __forceinline__ void epi_tile(uint32_t taddr, int c_lo, int c_hi, int tcol0, int nv,
+                                         EpiState &est, const TcParams &p, long row) {
+    if (p.exp & 4) return;
+    const int nv32 = (nv + 31) & ~31;
+    const int c_end = nv32 < c_hi ? nv32 : c_hi;
+    uint32_t ra[32], rb[32];
+    int c = c_lo;
+    if (c < c_end) tmem_ld32(taddr + c, ra);
+#define VQ_TC_STEP(R)                                                                     \
+    {                                                                                     \
+        if (p.dump != nullptr && row >= 0) {                                              \
+            _Pragma("unroll") for (int j = 0; j < 32; j++)                                \
+                if (c + j < nv) p.dump[row * p.dump_ld + tcol0 + c + j] = __uint_as_float(R[j]); \
+        }                                                                                 \
+        epi_step32(R, tcol0 + c, nv - c, est, p.exp);                                     \
+    }
+    while (c < c_end) {
+        tmem_ld_wait();
+        if (c + 32 < c_end) tmem_ld32(taddr + c + 32, rb);
+        VQ_TC_STEP(ra);
+        c += 32;
+        if (c >= c_end) break;
+        tmem_ld_wait();
+        if (c + 32 < c_end) tmem_ld32(taddr + c + 32, ra);
+        VQ_TC_STEP(rb);
+        c += 32;
+    }
+#undef VQ_TC_STEP
 }
 
 __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
@@ -249,6 +361,7 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
     const uint32_t stage_bytes = (uint32_t) 4 * BN * 16;
     unsigned char *a_base = smem_raw + 6144;
     unsigned char *b_base = a_base + 2 * a_buf_bytes;
+    unsigned char *raw_base = b_base + (size_t) kStages * stage_bytes;   // one tile of raw FP32 rows
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -268,6 +381,7 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
             mbar_init(&sm->a_full[i], kLoaderThreads);
             mbar_init(&sm->a_empty[i], 1 + kEpiWarps);
         }
+        mbar_init(&sm->raw_full, 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc(&sm->tmem_slot, 512);
@@ -322,9 +436,11 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
                         const uint64_t dbh = umma_desc(b_hi, BN * 16, 128);
                         const uint64_t dbl = umma_desc(b_lo, BN * 16, 128);
                         // small terms first
-                        umma_tf32(d_tmem, dal, dbh, idesc, s > 0);
-                        umma_tf32(d_tmem, dah, dbl, idesc, 1);
-                        umma_tf32(d_tmem, dah, dbh, idesc, 1);
+                        if (!(p.exp & 8)) {
+                            umma_tf32(d_tmem, dal, dbh, idesc, s > 0);
+                            umma_tf32(d_tmem, dah, dbl, idesc, 1);
+                            umma_tf32(d_tmem, dah, dbh, idesc, 1);
+                        }
                         umma_commit(&sm->empty[st]);
                         if (++st == kStages) { st = 0; ph ^= 1; }
                     }
@@ -335,44 +451,68 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
         }
     } else if (warp < kEpiWarp0) {
         // ===== A loaders: FP32 rows -> TF32 (hi, lo) -> canonical K-major layout =====
+        // Full contiguous tiles arrive as ONE bulk copy into a raw staging buffer (issued a
+        // tile ahead by loader thread 0); each loader thread then converts two rows.  Gathered
+        // (list) or partial tiles are read straight from global memory.
         const int lt = tid - 64;
         const int D = p.D;
-        uint32_t it = 0;
+        const uint32_t raw_bytes = (uint32_t) kBM * D * 4;
+        const bool contiguous = p.list == nullptr;
+        if (lt == 0 && contiguous && (long) blockIdx.x * kBM + kBM <= total) {
+            mbar_expect_tx(&sm->raw_full, raw_bytes);
+            bulk_g2s(raw_base, p.x + (long) blockIdx.x * kBM * D, raw_bytes, &sm->raw_full);
+        }
+        uint32_t it = 0, rs = 0;
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
             const uint32_t ab = it & 1;
             const long base = ft * kBM;
             const int nvalid = (int) (total - base < kBM ? total - base : kBM);
+            const bool staged = contiguous && nvalid == kBM;
+            if (staged) mbar_wait(&sm->raw_full, rs & 1);
             mbar_wait(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1);
             unsigned char *hi = a_base + (size_t) ab * a_buf_bytes;
             unsigned char *lo = hi + a_part_bytes;
-            for (int item = lt; item < KC * kBM; item += kLoaderThreads) {
-                const int f = item & (kBM - 1), c = item >> 7;
-                float v[4] = {0.f, 0.f, 0.f, 0.f};
-                if (f < nvalid) {
-                    const long row = p.list ? (long) p.list[base + f] : base + f;
-                    const float *xr = p.x + row * D + 4 * c;
-#pragma unroll
-                    for (int e = 0; e < 4; e++)
-                        if (4 * c + e < D) v[e] = __ldg(xr + e);
-                    // slot D carries -e |x0|: with W1_j in the codeword's slot D the accumulator
-                    // becomes the lower bound d~_ij - e |x0| W1_j
-                    if (c == (D >> 2)) {
-                        const float bs = -1.001f * p.err_scale * fabsf(__ldg(p.x + row * D));
-#pragma unroll
-                        for (int e = 0; e < 4; e++)
-                            if (e == (D & 3)) v[e] = bs;
-                    }
+            for (int f = lt; f < kBM; f += kLoaderThreads) {
+                const float *src;
+                if (staged) {
+                    src = reinterpret_cast<const float *>(raw_base) + f * D;
+                } else {
+                    const long row = f < nvalid ? (p.list ? (long) p.list[base + f] : base + f) : 0;
+                    src = p.x + row * D;
                 }
-                float4 h, l;
-                h.x = tf32_rna(v[0]); h.y = tf32_rna(v[1]); h.z = tf32_rna(v[2]); h.w = tf32_rna(v[3]);
-                l.x = tf32_rna(v[0] - h.x); l.y = tf32_rna(v[1] - h.y);
-                l.z = tf32_rna(v[2] - h.z); l.w = tf32_rna(v[3] - h.w);
-                *reinterpret_cast<float4 *>(hi + ((size_t) c * kBM + f) * 16) = h;
-                *reinterpret_cast<float4 *>(lo + ((size_t) c * kBM + f) * 16) = l;
-                if (c == 0) s_x0[ab * kBM + f] = fabsf(v[0]);
+                const bool valid = f < nvalid;
+                const float x0 = valid ? fabsf(src[0]) : 0.f;
+                for (int c = 0; c < KC; c++) {
+                    float v[4];
+#pragma unroll
+                    for (int e = 0; e < 4; e++) {
+                        const int k = 4 * c + e;
+                        v[e] = (valid && k < D) ? src[k] : 0.f;
+                        // slot D carries -e |x0|: with W1_j in the codeword's slot D the
+                        // accumulator becomes the lower bound d~_ij - e |x0| W1_j
+                        if (k == D) v[e] = -1.001f * p.err_scale * x0;
+                    }
+                    float4 h, l;
+                    h.x = tf32_rna(v[0]); h.y = tf32_rna(v[1]); h.z = tf32_rna(v[2]); h.w = tf32_rna(v[3]);
+                    l.x = tf32_rna(v[0] - h.x); l.y = tf32_rna(v[1] - h.y);
+                    l.z = tf32_rna(v[2] - h.z); l.w = tf32_rna(v[3] - h.w);
+                    *reinterpret_cast<float4 *>(hi + ((size_t) c * kBM + f) * 16) = h;
+                    *reinterpret_cast<float4 *>(lo + ((size_t) c * kBM + f) * 16) = l;
+                }
+                s_x0[ab * kBM + f] = x0;
             }
             fence_proxy_async();
             mbar_arrive(&sm->a_full[ab]);
+            if (staged) {
+                rs++;
+                // every loader thread is done with the staging buffer: fetch the next tile
+                asm volatile("bar.sync 5, 64;" ::: "memory");
+                const long nbase = (ft + gridDim.x) * kBM;
+                if (lt == 0 && nbase + kBM <= total) {
+                    mbar_expect_tx(&sm->raw_full, raw_bytes);
+                    bulk_g2s(raw_base, p.x + nbase * D, raw_bytes, &sm->raw_full);
+                }
+            }
         }
     } else {
         // ===== epilogue: thread = frame (TMEM lane), registers = codewords =====
@@ -394,48 +534,21 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
             if (lane == 0) mbar_arrive(&sm->a_empty[ab]);
             const long row = f < nvalid ? (p.list ? (long) p.list[base + f] : base + f) : -1;
 
-            float best = INFINITY, second = INFINITY;
-            int bidx = 0;
+            EpiState est;
+            est.init();
             for (int t = 0; t < n_wtiles; t++, tc++) {
                 const uint32_t acc = tc & 1;
                 mbar_wait(&sm->tmem_full[acc], (tc >> 1) & 1);
                 tc_fence_after();
                 const int nv = K - t * BN < BN ? K - t * BN : BN;   // valid codewords in this tile
-                const int c_end = (nv + 15) / 16 < c_hi ? (nv + 15) / 16 : c_hi;
-                const uint32_t taddr = lane_addr + acc * 256;
-                uint32_t ra[16], rb[16];
-                int c = c_lo;
-                if (c < c_end) tmem_ld16(taddr + c * 16, ra);
-                // software pipeline: the next chunk's tcgen05.ld is in flight while this one
-                // is reduced
-#define VQ_TC_CHUNK(R)                                                                    \
-    {                                                                                     \
-        float v[16];                                                                      \
-        _Pragma("unroll") for (int j = 0; j < 16; j++) v[j] = __uint_as_float(R[j]);      \
-        if (c * 16 + 16 > nv) {                                                           \
-            _Pragma("unroll") for (int j = 0; j < 16; j++) if (c * 16 + j >= nv) v[j] = INFINITY; \
-        }                                                                                 \
-        if (p.dump != nullptr && row >= 0) {                                              \
-            _Pragma("unroll") for (int j = 0; j < 16; j++)                                \
-                p.dump[row * p.dump_ld + t * BN + c * 16 + j] = v[j];                     \
-        }                                                                                 \
-        epi_chunk(v, t * BN + c * 16, best, second, bidx);                                \
-    }
-                while (c < c_end) {
-                    tmem_ld_wait();
-                    if (c + 1 < c_end) tmem_ld16(taddr + (c + 1) * 16, rb);
-                    VQ_TC_CHUNK(ra);
-                    if (++c >= c_end) break;
-                    tmem_ld_wait();
-                    if (c + 1 < c_end) tmem_ld16(taddr + (c + 1) * 16, ra);
-                    VQ_TC_CHUNK(rb);
-                    ++c;
-                }
-#undef VQ_TC_CHUNK
+                epi_tile(lane_addr + acc * 256, c_lo * 16, c_hi * 16, t * BN, nv, est, p, row);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm->tmem_empty[acc]);
             }
+            float best = est.best, second;
+            int bidx;
+            epi_finish(est, second, bidx);
             // merge the two column halves of each frame (upper half hands over via smem)
             float4 *slot = s_merge + (it & 1) * kBM + f;
             if (h == 1) *slot = make_float4(best, second, __int_as_float(bidx), 0.f);
@@ -467,6 +580,322 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
     tc_fence_before();
     __syncthreads();
     if (warp == 1) tmem_dealloc(tmem_base, 512);
+}
+
+// =====================================================================================
+// Variant 2 ("TS"): A operand in tensor memory.
+//
+// The frame tile is 256 frames = two UMMA M=128 halves whose split-TF32 rows live in TMEM
+// (written by tcgen05.st, one thread per frame row), so a tcgen05.mma reads only the codeword
+// tile from shared memory (64 B/clk instead of 96-128) and every codeword tile fetched from
+// L2 is used by 256 frames (half the L2 traffic of variant 1).  The two halves ping-pong:
+// while the epilogue warps of half 0 reduce codeword tile t, the tensor core computes
+// half 1 of tile t, so one 128-column accumulator per half is enough.
+//
+//   warps 0-3    frame loaders (warp = TMEM lane quarter): raw FP32 rows (TMA-staged in smem,
+//                or gathered from global) -> TF32 hi/lo -> tcgen05.st into A[half]
+//   warps 4-7    epilogue of half 0,  warps 8-11 epilogue of half 1
+//   warp 12      codeword-tile producer (cp.async.bulk, whole tiles, kB2Stages ring)
+//   warp 13      MMA issuer
+//   warp 14      raw-frame producer (cp.async.bulk of 128 contiguous rows per half)
+//
+// TMEM columns: A[h] at h * 16 KS (hi: 8 KS columns, lo: 8 KS), accumulator[h] at 256 + 128 h.
+// Global codeword layout (vq_prepare_codebook_tc2): [tile][hi, lo][k-chunk][row][4 floats].
+// =====================================================================================
+namespace {
+constexpr int k2Threads = 480;
+constexpr int kB2Stages = 4;
+
+struct Tc2Smem {
+    uint64_t b_full[kB2Stages], b_empty[kB2Stages];
+    uint64_t raw_full[2], raw_empty[2];
+    uint64_t a_full[2], a_free[2];
+    uint64_t acc_full[2], acc_empty[2];
+    uint32_t tmem_slot;
+};
+
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr),
+        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() {
+    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]
+__device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc,
+                                             uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem),
+        "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+}  // namespace
+
+template <int KS>
+__global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) {
+    extern __shared__ __align__(1024) unsigned char smem_raw[];
+    Tc2Smem *sm = reinterpret_cast<Tc2Smem *>(smem_raw);
+    float *s_x0 = reinterpret_cast<float *>(smem_raw + 1024);      // [2 slots][2 halves][128]
+    const int D = p.D;
+    const int BN = p.BN;
+    constexpr int KC = 2 * KS;
+    const uint32_t raw_bytes = (uint32_t) kBM * D * 4;               // one half's rows
+    const uint32_t raw_stride = (raw_bytes + 127u) & ~127u;
+    float *raw_base = reinterpret_cast<float *>(smem_raw + 3072);
+    const uint32_t tile_bytes = (uint32_t) 2 * KC * BN * 16;
+    unsigned char *b_base = smem_raw + 3072 + 2 * raw_stride;
+
+    const int tid = threadIdx.x;
+    const int warp = tid >> 5, lane = tid & 31;
+    const int K = p.K;
+    const int n_wtiles = (K + BN - 1) / BN;
+    const long total = p.list ? (long) *p.list_count : p.n_frames;
+    const long n_ftiles = (total + 2 * kBM - 1) / (2 * kBM);
+
+    if (tid == 0) {
+        for (int i = 0; i < kB2Stages; i++) {
+            mbar_init(&sm->b_full[i], 1);
+            mbar_init(&sm->b_empty[i], 1);
+        }
+        for (int i = 0; i < 2; i++) {
+            mbar_init(&sm->raw_full[i], 1);
+            mbar_init(&sm->raw_empty[i], 4);
+            mbar_init(&sm->a_full[i], 4);
+            mbar_init(&sm->a_free[i], 1);
+            mbar_init(&sm->acc_full[i], 1);
+            mbar_init(&sm->acc_empty[i], 4);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 13) tmem_alloc(&sm->tmem_slot, 512);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = sm->tmem_slot;
+
+    if (warp == 12) {
+        // ===== codeword tile producer =====
+        if (lane == 0) {
+            uint32_t st = 0, ph = 0;
+            for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x) {
+                const unsigned char *src = reinterpret_cast<const unsigned char *>(p.wtc);
+                for (int t = 0; t < n_wtiles; t++) {
+                    mbar_wait(&sm->b_empty[st], ph ^ 1);
+                    if (p.exp & 32) {
+                        mbar_arrive(&sm->b_full[st]);
+                    } else {
+                        mbar_expect_tx(&sm->b_full[st], tile_bytes);
+                        bulk_g2s(b_base + (size_t) st * tile_bytes, src, tile_bytes, &sm->b_full[st]);
+                    }
+                    src += tile_bytes;
+                    if (++st == kB2Stages) { st = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 14) {
+        // ===== raw frame producer (full, contiguous halves only) =====
+        if (lane == 0 && p.list == nullptr) {
+            uint32_t it = 0;
+            for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+                for (int h = 0; h < 2; h++) {
+                    const long base = ft * (2 * kBM) + h * kBM;
+                    if (base + kBM > total) continue;
+                    mbar_wait(&sm->raw_empty[h], (it & 1) ^ 1);
+                    mbar_expect_tx(&sm->raw_full[h], raw_bytes);
+                    bulk_g2s(reinterpret_cast<unsigned char *>(raw_base) + h * raw_stride,
+                             p.x + base * D, raw_bytes, &sm->raw_full[h]);
+                }
+            }
+        }
+    } else if (warp == 13) {
+        // ===== MMA issuer =====
+        if (lane == 0) {
+            const uint32_t idesc = umma_idesc_tf32(kBM, BN);
+            uint32_t st = 0, ph = 0, u = 0, it = 0;
+            for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+                for (int t = 0; t < n_wtiles; t++, u++) {
+                    for (int h = 0; h < 2; h++) {
+                        if (t == 0) mbar_wait(&sm->a_full[h], it & 1);
+                        mbar_wait(&sm->acc_empty[h], (u & 1) ^ 1);
+                        if (h == 0) mbar_wait(&sm->b_full[st], ph);
+                        tc_fence_after();
+                        const uint32_t a_hi = tmem_base + h * (16 * KS);
+                        const uint32_t a_lo = a_hi + 8 * KS;
+                        const uint32_t d_tmem = tmem_base + 256 + h * 128;
+                        const uint32_t b_hi = s32(b_base + (size_t) st * tile_bytes);
+                        const uint32_t b_lo = b_hi + KC * BN * 16;
+                        // small cross terms first, the dominant hi*hi products last
+                        if (!(p.exp & 8)) {
+#pragma unroll
+                        for (int s = 0; s < KS; s++)
+                            umma_tf32_ts(d_tmem, a_lo + 8 * s,
+                                         umma_desc(b_hi + 2 * s * BN * 16, BN * 16, 128), idesc, s > 0);
+#pragma unroll
+                        for (int s = 0; s < KS; s++)
+                            umma_tf32_ts(d_tmem, a_hi + 8 * s,
+                                         umma_desc(b_lo + 2 * s * BN * 16, BN * 16, 128), idesc, 1);
+#pragma unroll
+                        for (int s = 0; s < KS; s++)
+                            umma_tf32_ts(d_tmem, a_hi + 8 * s,
+                                         umma_desc(b_hi + 2 * s * BN * 16, BN * 16, 128), idesc, 1);
+                        }
+                        umma_commit(&sm->acc_full[h]);
+                        if (t == n_wtiles - 1) umma_commit(&sm->a_free[h]);
+                        if (h == 1) {
+                            umma_commit(&sm->b_empty[st]);
+                            if (++st == kB2Stages) { st = 0; ph ^= 1; }
+                        }
+                    }
+                }
+            }
+        }
+    } else if (warp < 4) {
+        // ===== frame loaders: thread = frame row =====
+        const int q = warp;
+        const int r = q * 32 + lane;
+        const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
+        uint32_t it = 0;
+        for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+            for (int h = 0; h < 2; h++) {
+                const long base = ft * (2 * kBM) + h * kBM;
+                const bool staged = p.list == nullptr && base + kBM <= total;
+                float v[8 * KS];
+                if (staged) {
+                    mbar_wait(&sm->raw_full[h], it & 1);
+                    const float *src = raw_base + h * (raw_stride / 4) + r * D;
+#pragma unroll
+                    for (int k = 0; k < 8 * KS; k++) v[k] = k < D ? src[k] : 0.f;
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&sm->raw_empty[h]);
+                } else {
+                    const bool valid = base + r < total;
+                    const long row = valid ? (p.list ? (long) p.list[base + r] : base + r) : 0;
+                    const float *src = p.x + row * D;
+#pragma unroll
+                    for (int k = 0; k < 8 * KS; k++) v[k] = (valid && k < D) ? __ldg(src + k) : 0.f;
+                }
+                const float x0 = fabsf(v[0]);
+                // slot D carries -e |x0|; with W1_j in the codeword's slot D the accumulator
+                // becomes the lower bound d~_ij - e |x0| W1_j
+#pragma unroll
+                for (int k = 0; k < 8 * KS; k++)
+                    if (k == D) v[k] = -1.001f * p.err_scale * x0;
+                mbar_wait(&sm->a_free[h], (it & 1) ^ 1);
+                tc_fence_after();
+                const uint32_t a_hi = lane_addr + h * (16 * KS);
+#pragma unroll
+                for (int g = 0; g < KS; g++) {
+                    uint32_t hi[8], lo[8];
+#pragma unroll
+                    for (int j = 0; j < 8; j++) {
+                        const float hv = tf32_rna(v[8 * g + j]);
+                        hi[j] = __float_as_uint(hv);
+                        lo[j] = __float_as_uint(tf32_rna(v[8 * g + j] - hv));
+                    }
+                    if (!(p.exp & 16)) {
+                        tmem_st8(a_hi + 8 * g, hi);
+                        tmem_st8(a_hi + 8 * KS + 8 * g, lo);
+                    }
+                }
+                tmem_st_wait();
+                s_x0[((it & 1) * 2 + h) * kBM + r] = x0;
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm->a_full[h]);
+            }
+        }
+    } else if (warp < 12) {
+        // ===== epilogue: thread = frame (TMEM lane), registers = codewords =====
+        const int q = warp & 3;
+        const int h = (warp - 4) >> 2;
+        const int r = q * 32 + lane;
+        const uint32_t taddr = tmem_base + ((uint32_t) (q * 32) << 16) + 256 + h * 128;
+        const float e2 = 2.f * 1.001f * p.err_scale;
+        uint32_t u = 0, it = 0;
+        for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+            const long base = ft * (2 * kBM) + h * kBM;
+            const long row = base + r < total ? (p.list ? (long) p.list[base + r] : base + r) : -1;
+            EpiState est;
+            est.init();
+            for (int t = 0; t < n_wtiles; t++, u++) {
+                mbar_wait(&sm->acc_full[h], u & 1);
+                tc_fence_after();
+                const int nv = K - t * BN < BN ? K - t * BN : BN;
+                epi_tile(taddr, 0, BN, t * BN, nv, est, p, row);
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm->acc_empty[h]);
+            }
+            float best = est.best, second;
+            int bidx;
+            epi_finish(est, second, bidx);
+            if (row >= 0) {
+                p.idx_out[row] = bidx;
+                if (p.flag_list != nullptr) {
+                    // accumulator = lower bound L_ij = d~_ij - e |x0| W1_j of the true distortion;
+                    // bidx is certainly the true argmin when every other lower bound exceeds its
+                    // upper bound L + 2 e |x0| W1.  NaN-safe.
+                    const float x0 = s_x0[((it & 1) * 2 + h) * kBM + r];
+                    const float ub = fmaf(e2 * x0, p.w1[bidx], best);
+                    if (!(second > ub)) {
+                        const int pos = atomicAdd(p.flag_count, 1);
+                        p.flag_list[pos] = (int32_t) row;
+                        p.flag_ub[pos] = ub;
+                        p.min_key[pos] = ~0ull;
+                    }
+                }
+            }
+        }
+    }
+
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 13) tmem_dealloc(tmem_base, 512);
+}
+
+// raas f64 [K][D] -> tiles [tile][hi, lo][k-chunk][row][4]  (zero padded; slot D = W1)
+__global__ void vq_prepare_codebook_tc2(const double *__restrict__ raas, int K, int D, int BN,
+                                        int ksteps, float *__restrict__ wtc) {
+    const int KC = 2 * ksteps;
+    const int n_wtiles = (K + BN - 1) / BN;
+    const long items = (long) n_wtiles * KC * BN;   // (t, c, r)
+    for (long it = (long) blockIdx.x * blockDim.x + threadIdx.x; it < items;
+         it += (long) gridDim.x * blockDim.x) {
+        const int r = (int) (it % BN);
+        const int c = (int) ((it / BN) % KC);
+        const int t = (int) (it / ((long) BN * KC));
+        const int cw = t * BN + r;
+        float4 h = make_float4(0.f, 0.f, 0.f, 0.f), l = h;
+        float *hp = &h.x, *lp = &l.x;
+        if (cw < K) {
+#pragma unroll
+            for (int e = 0; e < 4; e++) {
+                const int k = 4 * c + e;
+                if (k <= D) {
+                    double w;
+                    if (k < D) {
+                        w = k > 0 ? 2.0 * raas[(long) cw * D + k] : raas[(long) cw * D];
+                    } else {   // slot D: W1 = sum_n |w[n]|
+                        w = fabs(raas[(long) cw * D]);
+                        for (int n = 1; n < D; n++) w += 2.0 * fabs(raas[(long) cw * D + n]);
+                        w *= 1.0 + 1e-6;
+                    }
+                    const float hi = tf32_rna((float) w);
+                    hp[e] = hi;
+                    lp[e] = tf32_rna((float) (w - (double) hi));
+                }
+            }
+        }
+        float *tile = wtc + (size_t) t * (2 * KC * BN * 4);
+        *reinterpret_cast<float4 *>(tile + ((size_t) c * BN + r) * 4) = h;
+        *reinterpret_cast<float4 *>(tile + ((size_t) (KC + c) * BN + r) * 4) = l;
+    }
 }
 
 // raas f64 [K][D] -> stages [tile][k-step][hi, lo][k-chunk][row][4]  (zero padded)
@@ -510,7 +939,21 @@ __global__ void vq_prepare_codebook_tc(const double *__restrict__ raas, int K, i
 
 static int tc_ksteps(int D) { return (D + 8) / 8; }   // D elements + the bound slot
 
-int tc_tile_cols(int K) { return K >= 256 ? 256 : (K > 64 ? 128 : 64); }
+// ECOZ2_VQ_TC_VARIANT=1: both operands from shared memory (first version, kept for A/B runs);
+// default 2: frame operand in tensor memory.
+static int tc_variant() {
+    static int v = 0;
+    if (v == 0) {
+        const char *e = getenv("ECOZ2_VQ_TC_VARIANT");
+        v = (e && e[0] == '1') ? 1 : 2;
+    }
+    return v;
+}
+
+int tc_tile_cols(int K) {
+    if (tc_variant() == 2) return K >= 128 ? 128 : 64;
+    return K >= 256 ? 256 : (K > 64 ? 128 : 64);
+}
 
 bool assign_tc_supported(int K, int D) { return K >= 64 && tc_ksteps(D) <= kMaxKSteps; }
 
@@ -524,12 +967,30 @@ void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, cu
     const int BN = tc_tile_cols(K), ksteps = tc_ksteps(D);
     const long items = (long) ((K + BN - 1) / BN) * ksteps * 2 * BN;
     const int blocks = (int) ((items + 255) / 256);
-    vq_prepare_codebook_tc<<<blocks, 256, 0, s>>>(raas, K, D, BN, ksteps, wtc);
+    if (tc_variant() == 2)
+        vq_prepare_codebook_tc2<<<blocks, 256, 0, s>>>(raas, K, D, BN, ksteps, wtc);
+    else
+        vq_prepare_codebook_tc<<<blocks, 256, 0, s>>>(raas, K, D, BN, ksteps, wtc);
 }
 
 static size_t tc_smem_bytes(int D, int BN) {
     const int ksteps = tc_ksteps(D);
-    return 6144 + (size_t) 2 * 2 * (2 * ksteps) * kBM * 16 + (size_t) kStages * 4 * BN * 16;
+    return 6144 + (size_t) 2 * 2 * (2 * ksteps) * kBM * 16 + (size_t) kStages * 4 * BN * 16 +
+           (((size_t) kBM * D * 4 + 127) & ~(size_t) 127);
+}
+static size_t tc2_smem_bytes(int D, int BN) {
+    const size_t raw_stride = ((size_t) kBM * D * 4 + 127) & ~(size_t) 127;
+    return 3072 + 2 * raw_stride + (size_t) kB2Stages * 2 * (2 * tc_ksteps(D)) * BN * 16;
+}
+
+template <int KS>
+static void launch_tc2_inst(const TcParams &p, long grid, cudaStream_t s) {
+    static bool attr_set = false;
+    if (!attr_set) {
+        cudaFuncSetAttribute(vq_assign_tc2<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        attr_set = true;
+    }
+    vq_assign_tc2<KS><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN), s>>>(p);
 }
 
 void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
@@ -547,6 +1008,23 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
         p.min_key = sc.min_key;
     }
     p.dump = dump; p.dump_ld = dump_ld;
+    {
+        static int exp = -1;
+        if (exp < 0) { const char *e = getenv("ECOZ2_VQ_TC_EXP"); exp = e ? atoi(e) : 0; }
+        p.exp = exp;
+    }
+    if (tc_variant() == 2) {
+        long tiles = (n + 2 * kBM - 1) / (2 * kBM);
+        long grid = tiles < num_sms ? tiles : num_sms;
+        switch (p.ksteps) {
+            case 1: launch_tc2_inst<1>(p, grid, s); break;
+            case 2: launch_tc2_inst<2>(p, grid, s); break;
+            case 3: launch_tc2_inst<3>(p, grid, s); break;
+            case 4: launch_tc2_inst<4>(p, grid, s); break;
+            default: launch_tc2_inst<5>(p, grid, s); break;
+        }
+        return;
+    }
     const size_t smem = tc_smem_bytes(D, p.BN);
     static bool attr_set = false;
     if (!attr_set) {
