@@ -60,6 +60,10 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(bar)) : "memory");
 }
+// arrive whose issue depends on `dep` having been computed
+__device__ __forceinline__ void mbar_arrive_dep(uint64_t *bar, uint32_t dep) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0]; // %1" ::"r"(s32(bar)), "r"(dep) : "memory");
+}
 __device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
     uint32_t ok;
     asm volatile(
@@ -126,15 +130,31 @@ __device__ __forceinline__ void umma_commit(uint64_t *bar) {
                      "r"(s32(bar))
                  : "memory");
 }
-__device__ __forceinline__ void tmem_ld16(uint32_t taddr, uint32_t (&v)[16]) {
+// multicast variants (thread-block cluster of 2): the copy lands at the same CTA-relative
+// offset in every CTA of cta_mask and signals each one's mbarrier at that offset
+__device__ __forceinline__ void bulk_g2s_mc(void *dst_smem, const void *src_gmem, uint32_t bytes,
+                                            uint64_t *bar, uint16_t cta_mask) {
     asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x16.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
-          "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
-          "=r"(v[14]), "=r"(v[15])
-        : "r"(taddr)
+        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
+        "[%0], [%1], %2, [%3], %4;" ::"r"(s32(dst_smem)),
+        "l"(src_gmem), "r"(bytes), "r"(s32(bar)), "h"(cta_mask)
         : "memory");
+}
+__device__ __forceinline__ void umma_commit_mc(uint64_t *bar, uint16_t cta_mask) {
+    asm volatile(
+        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
+        "[%0], %1;" ::"r"(s32(bar)),
+        "h"(cta_mask)
+        : "memory");
+}
+__device__ __forceinline__ void cluster_sync_all() {
+    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
+    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
+}
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+    uint32_t r;
+    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
+    return r;
 }
 __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
     asm volatile(
@@ -193,6 +213,7 @@ struct TcParams {
     unsigned long long *min_key;
     float *dump;                // debug: all distortions [n][dump_ld]
     int dump_ld;
+    int mc;                     // 1: launched as clusters of 2 CTAs that share the codeword stream
     int exp;                    // dev experiments (ECOZ2_VQ_TC_EXP): bit mask 1 no record path, 2 trivial reduction, 4 no tcgen05.ld, 8 no MMA, 16 no tcgen05.st, 32 no B copy
 };
 
@@ -369,11 +390,15 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
     const int n_wtiles = (K + BN - 1) / BN;
     const long total = p.list ? (long) *p.list_count : p.n_frames;
     const long n_ftiles = (total + kBM - 1) / kBM;
+    // cluster mode: the two CTAs of a pair run the same number of frame tiles (the odd CTA's
+    // last one may be empty) because they consume the shared codeword stream in lock step
+    const long lead_off = p.mc ? (long) (blockIdx.x & 1) : 0;
+    const uint32_t cta_rank = p.mc ? cluster_ctarank() : 0;
 
     if (tid == 0) {
         for (int i = 0; i < kStages; i++) {
             mbar_init(&sm->full[i], 1);
-            mbar_init(&sm->empty[i], 1);
+            mbar_init(&sm->empty[i], p.mc ? 2 : 1);
         }
         for (int i = 0; i < 2; i++) {
             mbar_init(&sm->tmem_full[i], 1);
@@ -387,6 +412,7 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
     if (warp == 1) tmem_alloc(&sm->tmem_slot, 512);
     tc_fence_before();
     __syncthreads();
+    if (p.mc) cluster_sync_all();   // the peer's barriers exist before anything is sent to them
     tc_fence_after();
     const uint32_t tmem_base = sm->tmem_slot;
 
@@ -394,13 +420,21 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
         // ===== B producer =====
         if (lane == 0) {
             uint32_t st = 0, ph = 0;
-            for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x) {
+            for (long ft = blockIdx.x; ft - lead_off < n_ftiles; ft += gridDim.x) {
                 const float *src = p.wtc;
                 for (int t = 0; t < n_wtiles; t++) {
                     for (int s = 0; s < ksteps; s++) {
                         mbar_wait(&sm->empty[st], ph ^ 1);
                         mbar_expect_tx(&sm->full[st], stage_bytes);
-                        bulk_g2s(b_base + (size_t) st * stage_bytes, src, stage_bytes, &sm->full[st]);
+                        if (p.mc) {
+                            // each CTA of the pair fetches half of the stage for both
+                            const uint32_t half = stage_bytes / 2;
+                            bulk_g2s_mc(b_base + (size_t) st * stage_bytes + cta_rank * half,
+                                        reinterpret_cast<const unsigned char *>(src) + cta_rank * half,
+                                        half, &sm->full[st], (uint16_t) 3);
+                        } else {
+                            bulk_g2s(b_base + (size_t) st * stage_bytes, src, stage_bytes, &sm->full[st]);
+                        }
                         src += (size_t) BN * 16;
                         if (++st == kStages) { st = 0; ph ^= 1; }
                     }
@@ -414,7 +448,7 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
             uint32_t st = 0, ph = 0;
             uint32_t tc = 0;  // accumulator tiles issued so far
             uint32_t it = 0;
-            for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+            for (long ft = blockIdx.x; ft - lead_off < n_ftiles; ft += gridDim.x, it++) {
                 const uint32_t ab = it & 1;
                 mbar_wait(&sm->a_full[ab], (it >> 1) & 1);
                 tc_fence_after();
@@ -441,7 +475,8 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
                             umma_tf32(d_tmem, dah, dbl, idesc, 1);
                             umma_tf32(d_tmem, dah, dbh, idesc, 1);
                         }
-                        umma_commit(&sm->empty[st]);
+                        if (p.mc) umma_commit_mc(&sm->empty[st], (uint16_t) 3);
+                        else umma_commit(&sm->empty[st]);
                         if (++st == kStages) { st = 0; ph ^= 1; }
                     }
                     umma_commit(&sm->tmem_full[acc]);
@@ -463,10 +498,10 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
             bulk_g2s(raw_base, p.x + (long) blockIdx.x * kBM * D, raw_bytes, &sm->raw_full);
         }
         uint32_t it = 0, rs = 0;
-        for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+        for (long ft = blockIdx.x; ft - lead_off < n_ftiles; ft += gridDim.x, it++) {
             const uint32_t ab = it & 1;
             const long base = ft * kBM;
-            const int nvalid = (int) (total - base < kBM ? total - base : kBM);
+            const int nvalid = (int) (total - base < kBM ? (total - base > 0 ? total - base : 0) : kBM);
             const bool staged = contiguous && nvalid == kBM;
             if (staged) mbar_wait(&sm->raw_full, rs & 1);
             mbar_wait(&sm->a_empty[ab], ((it >> 1) & 1) ^ 1);
@@ -524,10 +559,10 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
         const int c_lo = h * (n_chunks / 2), c_hi = c_lo + n_chunks / 2;
         const float e2 = 2.f * 1.001f * p.err_scale;
         uint32_t tc = 0, it = 0;
-        for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+        for (long ft = blockIdx.x; ft - lead_off < n_ftiles; ft += gridDim.x, it++) {
             const uint32_t ab = it & 1;
             const long base = ft * kBM;
-            const int nvalid = (int) (total - base < kBM ? total - base : kBM);
+            const int nvalid = (int) (total - base < kBM ? (total - base > 0 ? total - base : 0) : kBM);
             mbar_wait(&sm->a_full[ab], (it >> 1) & 1);
             const float x0 = s_x0[ab * kBM + f];
             __syncwarp();
@@ -579,77 +614,61 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
 
     tc_fence_before();
     __syncthreads();
+    if (p.mc) cluster_sync_all();   // nothing of the peer is still in flight towards this CTA
     if (warp == 1) tmem_dealloc(tmem_base, 512);
 }
 
 // =====================================================================================
-// Variant 2 ("TS"): A operand in tensor memory.
+// Variant 2: 256-frame tiles.
 //
-// The frame tile is 256 frames = two UMMA M=128 halves whose split-TF32 rows live in TMEM
-// (written by tcgen05.st, one thread per frame row), so a tcgen05.mma reads only the codeword
-// tile from shared memory (64 B/clk instead of 96-128) and every codeword tile fetched from
-// L2 is used by 256 frames (half the L2 traffic of variant 1).  The two halves ping-pong:
-// while the epilogue warps of half 0 reduce codeword tile t, the tensor core computes
-// half 1 of tile t, so one 128-column accumulator per half is enough.
+// Measured on B200 (scripts/exp): one SM ingests at most ~45 B/clk of bulk copies, and
+// variant 1 needs 43 B/clk of codeword stages at the MMA floor -- it is bound by that stream.
+// Here a frame tile is 256 frames = two UMMA M=128 halves that share every codeword tile, so
+// the stream is halved.  Both operands come from shared memory (a tcgen05.mma.kind::tf32 with
+// the A operand in TMEM was measured at 76-81 clk per 128x128x8 instead of 64), the codeword
+// tile is whole (all k-steps), so the 3 KS MMAs of a tile run small cross terms first, and
+// each half owns two 128-column accumulators: the tensor core never waits for an epilogue
+// that keeps up on average.
 //
-//   warps 0-3    frame loaders (warp = TMEM lane quarter): raw FP32 rows (TMA-staged in smem,
-//                or gathered from global) -> TF32 hi/lo -> tcgen05.st into A[half]
-//   warps 4-7    epilogue of half 0,  warps 8-11 epilogue of half 1
+//   warps 0-3    frame loaders, thread = frame row: raw FP32 row (TMA-staged in smem, or
+//                gathered from global) -> TF32 hi/lo -> canonical K-major A[half] in smem
+//   warps 4-7    epilogue of half 0,  warps 8-11 epilogue of half 1 (warp = TMEM lane quarter)
 //   warp 12      codeword-tile producer (cp.async.bulk, whole tiles, kB2Stages ring)
 //   warp 13      MMA issuer
-//   warp 14      raw-frame producer (cp.async.bulk of 128 contiguous rows per half)
+//   warp 14      raw-frame producer (cp.async.bulk of 128 contiguous rows)
 //
-// TMEM columns: A[h] at h * 16 KS (hi: 8 KS columns, lo: 8 KS), accumulator[h] at 256 + 128 h.
+// TMEM columns: accumulator[half h][buffer b] at (2 b + h) * 128.
 // Global codeword layout (vq_prepare_codebook_tc2): [tile][hi, lo][k-chunk][row][4 floats].
 // =====================================================================================
 namespace {
 constexpr int k2Threads = 480;
-constexpr int kB2Stages = 4;
+constexpr int kB2Stages = 3;
 
 struct Tc2Smem {
     uint64_t b_full[kB2Stages], b_empty[kB2Stages];
-    uint64_t raw_full[2], raw_empty[2];
+    uint64_t raw_full, raw_empty;
     uint64_t a_full[2], a_free[2];
-    uint64_t acc_full[2], acc_empty[2];
+    uint64_t acc_full[4], acc_empty[4];   // [2 * buffer + half]
     uint32_t tmem_slot;
 };
-
-__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8]) {
-    asm volatile(
-        "tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr),
-        "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7])
-        : "memory");
-}
-__device__ __forceinline__ void tmem_st_wait() {
-    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-}
-// D[tmem] (+)= A[tmem] * B[smem]
-__device__ __forceinline__ void umma_tf32_ts(uint32_t d_tmem, uint32_t a_tmem, uint64_t bdesc,
-                                             uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p;\n"
-        "}\n" ::"r"(d_tmem),
-        "r"(a_tmem), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
 }  // namespace
 
 template <int KS>
 __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     Tc2Smem *sm = reinterpret_cast<Tc2Smem *>(smem_raw);
-    float *s_x0 = reinterpret_cast<float *>(smem_raw + 1024);      // [2 slots][2 halves][128]
+    float *s_x0 = reinterpret_cast<float *>(smem_raw + 1024);      // [4 slots][2 halves][128]
     const int D = p.D;
     const int BN = p.BN;
     constexpr int KC = 2 * KS;
-    const uint32_t raw_bytes = (uint32_t) kBM * D * 4;               // one half's rows
+    constexpr uint32_t a_part_bytes = (uint32_t) KC * kBM * 16;      // hi or lo of one half
+    constexpr uint32_t a_half_bytes = 2 * a_part_bytes;
+    const uint32_t raw_bytes = (uint32_t) kBM * D * 4;               // 128 rows
     const uint32_t raw_stride = (raw_bytes + 127u) & ~127u;
-    float *raw_base = reinterpret_cast<float *>(smem_raw + 3072);
+    float *raw_base = reinterpret_cast<float *>(smem_raw + 5120);
+    unsigned char *a_base = smem_raw + 5120 + raw_stride;
     const uint32_t tile_bytes = (uint32_t) 2 * KC * BN * 16;
-    unsigned char *b_base = smem_raw + 3072 + 2 * raw_stride;
+    unsigned char *b_base = a_base + 2 * a_half_bytes;
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -663,11 +682,13 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             mbar_init(&sm->b_full[i], 1);
             mbar_init(&sm->b_empty[i], 1);
         }
+        mbar_init(&sm->raw_full, 1);
+        mbar_init(&sm->raw_empty, 4);
         for (int i = 0; i < 2; i++) {
-            mbar_init(&sm->raw_full[i], 1);
-            mbar_init(&sm->raw_empty[i], 4);
             mbar_init(&sm->a_full[i], 4);
             mbar_init(&sm->a_free[i], 1);
+        }
+        for (int i = 0; i < 4; i++) {
             mbar_init(&sm->acc_full[i], 1);
             mbar_init(&sm->acc_empty[i], 4);
         }
@@ -700,16 +721,16 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         }
     } else if (warp == 14) {
         // ===== raw frame producer (full, contiguous halves only) =====
-        if (lane == 0 && p.list == nullptr) {
-            uint32_t it = 0;
-            for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+        if (lane == 0 && p.list == nullptr && !(p.exp & 64)) {
+            uint32_t rs = 0;   // staged halves so far
+            for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x) {
                 for (int h = 0; h < 2; h++) {
                     const long base = ft * (2 * kBM) + h * kBM;
                     if (base + kBM > total) continue;
-                    mbar_wait(&sm->raw_empty[h], (it & 1) ^ 1);
-                    mbar_expect_tx(&sm->raw_full[h], raw_bytes);
-                    bulk_g2s(reinterpret_cast<unsigned char *>(raw_base) + h * raw_stride,
-                             p.x + base * D, raw_bytes, &sm->raw_full[h]);
+                    mbar_wait(&sm->raw_empty, (rs & 1) ^ 1);
+                    mbar_expect_tx(&sm->raw_full, raw_bytes);
+                    bulk_g2s(raw_base, p.x + base * D, raw_bytes, &sm->raw_full);
+                    rs++;
                 }
             }
         }
@@ -720,32 +741,33 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             uint32_t st = 0, ph = 0, u = 0, it = 0;
             for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
                 for (int t = 0; t < n_wtiles; t++, u++) {
+                    const uint32_t buf = u & 1;
                     for (int h = 0; h < 2; h++) {
                         if (t == 0) mbar_wait(&sm->a_full[h], it & 1);
-                        mbar_wait(&sm->acc_empty[h], (u & 1) ^ 1);
+                        mbar_wait(&sm->acc_empty[2 * buf + h], ((u >> 1) & 1) ^ 1);
                         if (h == 0) mbar_wait(&sm->b_full[st], ph);
                         tc_fence_after();
-                        const uint32_t a_hi = tmem_base + h * (16 * KS);
-                        const uint32_t a_lo = a_hi + 8 * KS;
-                        const uint32_t d_tmem = tmem_base + 256 + h * 128;
+                        const uint32_t a_hi = s32(a_base + (size_t) h * a_half_bytes);
+                        const uint32_t a_lo = a_hi + a_part_bytes;
+                        const uint32_t d_tmem = tmem_base + (2 * buf + h) * 128;
                         const uint32_t b_hi = s32(b_base + (size_t) st * tile_bytes);
                         const uint32_t b_lo = b_hi + KC * BN * 16;
                         // small cross terms first, the dominant hi*hi products last
                         if (!(p.exp & 8)) {
 #pragma unroll
-                        for (int s = 0; s < KS; s++)
-                            umma_tf32_ts(d_tmem, a_lo + 8 * s,
-                                         umma_desc(b_hi + 2 * s * BN * 16, BN * 16, 128), idesc, s > 0);
+                            for (int s = 0; s < KS; s++)
+                                umma_tf32(d_tmem, umma_desc(a_lo + 2 * s * kBM * 16, kBM * 16, 128),
+                                          umma_desc(b_hi + 2 * s * BN * 16, BN * 16, 128), idesc, s > 0);
 #pragma unroll
-                        for (int s = 0; s < KS; s++)
-                            umma_tf32_ts(d_tmem, a_hi + 8 * s,
-                                         umma_desc(b_lo + 2 * s * BN * 16, BN * 16, 128), idesc, 1);
+                            for (int s = 0; s < KS; s++)
+                                umma_tf32(d_tmem, umma_desc(a_hi + 2 * s * kBM * 16, kBM * 16, 128),
+                                          umma_desc(b_lo + 2 * s * BN * 16, BN * 16, 128), idesc, 1);
 #pragma unroll
-                        for (int s = 0; s < KS; s++)
-                            umma_tf32_ts(d_tmem, a_hi + 8 * s,
-                                         umma_desc(b_hi + 2 * s * BN * 16, BN * 16, 128), idesc, 1);
+                            for (int s = 0; s < KS; s++)
+                                umma_tf32(d_tmem, umma_desc(a_hi + 2 * s * kBM * 16, kBM * 16, 128),
+                                          umma_desc(b_hi + 2 * s * BN * 16, BN * 16, 128), idesc, 1);
                         }
-                        umma_commit(&sm->acc_full[h]);
+                        umma_commit(&sm->acc_full[2 * buf + h]);
                         if (t == n_wtiles - 1) umma_commit(&sm->a_free[h]);
                         if (h == 1) {
                             umma_commit(&sm->b_empty[st]);
@@ -757,22 +779,28 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         }
     } else if (warp < 4) {
         // ===== frame loaders: thread = frame row =====
-        const int q = warp;
-        const int r = q * 32 + lane;
-        const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
-        uint32_t it = 0;
+        const int r = warp * 32 + lane;
+        uint32_t it = 0, rs = 0;
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
             for (int h = 0; h < 2; h++) {
                 const long base = ft * (2 * kBM) + h * kBM;
-                const bool staged = p.list == nullptr && base + kBM <= total;
+                const bool staged = p.list == nullptr && base + kBM <= total && !(p.exp & 64);
                 float v[8 * KS];
                 if (staged) {
-                    mbar_wait(&sm->raw_full[h], it & 1);
-                    const float *src = raw_base + h * (raw_stride / 4) + r * D;
+                    mbar_wait(&sm->raw_full, rs & 1);
+                    rs++;
+                    const float *src = raw_base + r * D;
 #pragma unroll
                     for (int k = 0; k < 8 * KS; k++) v[k] = k < D ? src[k] : 0.f;
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&sm->raw_empty[h]);
+                    // the staging buffer may be overwritten as soon as raw_empty completes: the
+                    // arrive must not be issued before every lane's loads have RETURNED, so it is
+                    // made data dependent on all of them (a vote over a value built from them)
+                    uint32_t dep = 0;
+#pragma unroll
+                    for (int k = 0; k < 8 * KS; k++) dep ^= __float_as_uint(v[k]);
+                    fence_proxy_async();   // generic reads before the async-proxy overwrite
+                    const uint32_t all_in = __all_sync(0xffffffffu, dep != 0x7fc12345u);
+                    if (lane == 0) mbar_arrive_dep(&sm->raw_empty, all_in);
                 } else {
                     const bool valid = base + r < total;
                     const long row = valid ? (p.list ? (long) p.list[base + r] : base + r) : 0;
@@ -787,25 +815,20 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 for (int k = 0; k < 8 * KS; k++)
                     if (k == D) v[k] = -1.001f * p.err_scale * x0;
                 mbar_wait(&sm->a_free[h], (it & 1) ^ 1);
-                tc_fence_after();
-                const uint32_t a_hi = lane_addr + h * (16 * KS);
+                unsigned char *hi = a_base + (size_t) h * a_half_bytes;
+                unsigned char *lo = hi + a_part_bytes;
 #pragma unroll
-                for (int g = 0; g < KS; g++) {
-                    uint32_t hi[8], lo[8];
-#pragma unroll
-                    for (int j = 0; j < 8; j++) {
-                        const float hv = tf32_rna(v[8 * g + j]);
-                        hi[j] = __float_as_uint(hv);
-                        lo[j] = __float_as_uint(tf32_rna(v[8 * g + j] - hv));
-                    }
-                    if (!(p.exp & 16)) {
-                        tmem_st8(a_hi + 8 * g, hi);
-                        tmem_st8(a_hi + 8 * KS + 8 * g, lo);
-                    }
+                for (int c = 0; c < KC; c++) {
+                    float4 hv, lv;
+                    hv.x = tf32_rna(v[4 * c + 0]); hv.y = tf32_rna(v[4 * c + 1]);
+                    hv.z = tf32_rna(v[4 * c + 2]); hv.w = tf32_rna(v[4 * c + 3]);
+                    lv.x = tf32_rna(v[4 * c + 0] - hv.x); lv.y = tf32_rna(v[4 * c + 1] - hv.y);
+                    lv.z = tf32_rna(v[4 * c + 2] - hv.z); lv.w = tf32_rna(v[4 * c + 3] - hv.w);
+                    *reinterpret_cast<float4 *>(hi + ((size_t) c * kBM + r) * 16) = hv;
+                    *reinterpret_cast<float4 *>(lo + ((size_t) c * kBM + r) * 16) = lv;
                 }
-                tmem_st_wait();
-                s_x0[((it & 1) * 2 + h) * kBM + r] = x0;
-                tc_fence_before();
+                s_x0[((it & 3) * 2 + h) * kBM + r] = x0;
+                fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm->a_full[h]);
             }
@@ -815,7 +838,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         const int q = warp & 3;
         const int h = (warp - 4) >> 2;
         const int r = q * 32 + lane;
-        const uint32_t taddr = tmem_base + ((uint32_t) (q * 32) << 16) + 256 + h * 128;
+        const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
         const float e2 = 2.f * 1.001f * p.err_scale;
         uint32_t u = 0, it = 0;
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
@@ -824,13 +847,14 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             EpiState est;
             est.init();
             for (int t = 0; t < n_wtiles; t++, u++) {
-                mbar_wait(&sm->acc_full[h], u & 1);
+                const uint32_t buf = u & 1;
+                mbar_wait(&sm->acc_full[2 * buf + h], (u >> 1) & 1);
                 tc_fence_after();
                 const int nv = K - t * BN < BN ? K - t * BN : BN;
-                epi_tile(taddr, 0, BN, t * BN, nv, est, p, row);
+                epi_tile(lane_addr + (2 * buf + h) * 128, 0, BN, t * BN, nv, est, p, row);
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&sm->acc_empty[h]);
+                if (lane == 0) mbar_arrive(&sm->acc_empty[2 * buf + h]);
             }
             float best = est.best, second;
             int bidx;
@@ -841,7 +865,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                     // accumulator = lower bound L_ij = d~_ij - e |x0| W1_j of the true distortion;
                     // bidx is certainly the true argmin when every other lower bound exceeds its
                     // upper bound L + 2 e |x0| W1.  NaN-safe.
-                    const float x0 = s_x0[((it & 1) * 2 + h) * kBM + r];
+                    const float x0 = s_x0[((it & 3) * 2 + h) * kBM + r];
                     const float ub = fmaf(e2 * x0, p.w1[bidx], best);
                     if (!(second > ub)) {
                         const int pos = atomicAdd(p.flag_count, 1);
@@ -980,14 +1004,15 @@ static size_t tc_smem_bytes(int D, int BN) {
 }
 static size_t tc2_smem_bytes(int D, int BN) {
     const size_t raw_stride = ((size_t) kBM * D * 4 + 127) & ~(size_t) 127;
-    return 3072 + 2 * raw_stride + (size_t) kB2Stages * 2 * (2 * tc_ksteps(D)) * BN * 16;
+    const size_t KC = 2 * (size_t) tc_ksteps(D);
+    return 5120 + raw_stride + 2 * (2 * KC * kBM * 16) + (size_t) kB2Stages * 2 * KC * BN * 16;
 }
 
 template <int KS>
 static void launch_tc2_inst(const TcParams &p, long grid, cudaStream_t s) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(vq_assign_tc2<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+        cudaFuncSetAttribute(vq_assign_tc2<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         attr_set = true;
     }
     vq_assign_tc2<KS><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN), s>>>(p);
@@ -1034,6 +1059,27 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
     long tiles = (n + kBM - 1) / kBM;
     long grid = tiles < num_sms ? tiles : num_sms;
     if (grid < 1) grid = 1;
+    static int use_mc = -1;
+    if (use_mc < 0) { const char *e = getenv("ECOZ2_VQ_TC_MULTICAST"); use_mc = (e && e[0] == '0') ? 0 : 1; }
+    if (use_mc && grid >= 2) {
+        // clusters of 2 CTAs share the codeword stream through TMA multicast
+        grid &= ~1L;
+        p.mc = 1;
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3((unsigned) grid);
+        cfg.blockDim = dim3(kThreads);
+        cfg.dynamicSmemBytes = smem;
+        cfg.stream = s;
+        cudaLaunchAttribute attr[1];
+        attr[0].id = cudaLaunchAttributeClusterDimension;
+        attr[0].val.clusterDim.x = 2;
+        attr[0].val.clusterDim.y = 1;
+        attr[0].val.clusterDim.z = 1;
+        cfg.attrs = attr;
+        cfg.numAttrs = 1;
+        cudaLaunchKernelEx(&cfg, vq_assign_tc, p);
+        return;
+    }
     vq_assign_tc<<<(unsigned) grid, kThreads, smem, s>>>(p);
 }
 

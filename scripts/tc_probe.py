@@ -49,5 +49,12 @@ for K in [int(k) for k in a.ks.split(",")]:
         eng.counters_reset()
         idx, dd, nre = eng.assign()
         bad = int((idx != idx64).sum())
+        if bad and kap == 32:
+            rows = np.nonzero(idx != idx64)[0][:12]
+            dd = x[rows] @ w.T
+            for rr, drow in zip(rows, dd):
+                srt = np.sort(drow)
+                print(f"      row {rr} (tile {rr // 256}, pos {rr % 256}): got {idx[rr]} want {idx64[rr]} "
+                      f"d[got]-dmin {drow[idx[rr]] - srt[0]:.3e}  gap12 {srt[1] - srt[0]:.3e}  x0 {x[rr, 0]:.3f}")
         print(f"   kappa_tc={kap:3d}: rechecked {nre} ({nre/a.n*100:.3f}%)  index mismatches vs FP64 mode: {bad}",
               flush=True)
