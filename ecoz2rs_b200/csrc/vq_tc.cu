@@ -169,6 +169,17 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
         : "r"(taddr)
         : "memory");
 }
+__device__ __forceinline__ bool elect_one() {
+    uint32_t pred;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "elect.sync _|p, 0xffffffff;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(pred));
+    return pred != 0;
+}
 __device__ __forceinline__ void tmem_ld_wait() {
     asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
 }
@@ -736,44 +747,48 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         }
     } else if (warp == 13) {
         // ===== MMA issuer =====
-        if (lane == 0) {
-            const uint32_t idesc = umma_idesc_tf32(kBM, BN);
-            uint32_t st = 0, ph = 0, u = 0, it = 0;
-            for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
-                for (int t = 0; t < n_wtiles; t++, u++) {
-                    const uint32_t buf = u & 1;
-                    for (int h = 0; h < 2; h++) {
-                        if (t == 0) mbar_wait(&sm->a_full[h], it & 1);
-                        mbar_wait(&sm->acc_empty[2 * buf + h], ((u >> 1) & 1) ^ 1);
-                        if (h == 0) mbar_wait(&sm->b_full[st], ph);
-                        tc_fence_after();
-                        const uint32_t a_hi = s32(a_base + (size_t) h * a_half_bytes);
-                        const uint32_t a_lo = a_hi + a_part_bytes;
-                        const uint32_t d_tmem = tmem_base + (2 * buf + h) * 128;
-                        const uint32_t b_hi = s32(b_base + (size_t) st * tile_bytes);
-                        const uint32_t b_lo = b_hi + KC * BN * 16;
+        // The whole warp runs the loop (uniform control flow keeps descriptors in uniform
+        // registers); one elected lane issues the MMAs and their commits.
+        const uint32_t idesc = umma_idesc_tf32(kBM, BN);
+        // descriptor of (half 0, hi, k-step 0) / (stage 0, hi, k-step 0); the start-address
+        // field counts 16-byte units, so other operands are reached by adding bytes >> 4
+        const uint64_t dA0 = umma_desc(s32(a_base), kBM * 16, 128);
+        const uint64_t dB0 = umma_desc(s32(b_base), BN * 16, 128);
+        constexpr uint32_t a_half16 = a_half_bytes >> 4, a_part16 = a_part_bytes >> 4;
+        constexpr uint32_t a_k16 = (2 * kBM * 16) >> 4;
+        const uint32_t b_tile16 = tile_bytes >> 4, b_part16 = (uint32_t) (KC * BN * 16) >> 4;
+        const uint32_t b_k16 = (uint32_t) (2 * BN * 16) >> 4;
+        uint32_t st = 0, ph = 0, u = 0, it = 0;
+        for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+            for (int t = 0; t < n_wtiles; t++, u++) {
+                const uint32_t buf = u & 1;
+                for (int h = 0; h < 2; h++) {
+                    if (t == 0) mbar_wait(&sm->a_full[h], it & 1);
+                    mbar_wait(&sm->acc_empty[2 * buf + h], ((u >> 1) & 1) ^ 1);
+                    if (h == 0) mbar_wait(&sm->b_full[st], ph);
+                    tc_fence_after();
+                    const uint64_t dah = dA0 + (uint32_t) h * a_half16, dal = dah + a_part16;
+                    const uint64_t dbh = dB0 + st * b_tile16, dbl = dbh + b_part16;
+                    const uint32_t d_tmem = tmem_base + (2 * buf + h) * 128;
+                    if (elect_one()) {
                         // small cross terms first, the dominant hi*hi products last
                         if (!(p.exp & 8)) {
 #pragma unroll
                             for (int s = 0; s < KS; s++)
-                                umma_tf32(d_tmem, umma_desc(a_lo + 2 * s * kBM * 16, kBM * 16, 128),
-                                          umma_desc(b_hi + 2 * s * BN * 16, BN * 16, 128), idesc, s > 0);
+                                umma_tf32(d_tmem, dal + s * a_k16, dbh + s * b_k16, idesc, s > 0);
 #pragma unroll
                             for (int s = 0; s < KS; s++)
-                                umma_tf32(d_tmem, umma_desc(a_hi + 2 * s * kBM * 16, kBM * 16, 128),
-                                          umma_desc(b_lo + 2 * s * BN * 16, BN * 16, 128), idesc, 1);
+                                umma_tf32(d_tmem, dah + s * a_k16, dbl + s * b_k16, idesc, 1);
 #pragma unroll
                             for (int s = 0; s < KS; s++)
-                                umma_tf32(d_tmem, umma_desc(a_hi + 2 * s * kBM * 16, kBM * 16, 128),
-                                          umma_desc(b_hi + 2 * s * BN * 16, BN * 16, 128), idesc, 1);
+                                umma_tf32(d_tmem, dah + s * a_k16, dbh + s * b_k16, idesc, 1);
                         }
                         umma_commit(&sm->acc_full[2 * buf + h]);
                         if (t == n_wtiles - 1) umma_commit(&sm->a_free[h]);
-                        if (h == 1) {
-                            umma_commit(&sm->b_empty[st]);
-                            if (++st == kB2Stages) { st = 0; ph ^= 1; }
-                        }
+                        if (h == 1) umma_commit(&sm->b_empty[st]);
                     }
+                    __syncwarp();
+                    if (h == 1 && ++st == kB2Stages) { st = 0; ph ^= 1; }
                 }
             }
         }
