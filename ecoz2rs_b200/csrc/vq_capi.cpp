@@ -31,6 +31,15 @@ double wall_s() {
     return duration<double>(steady_clock::now().time_since_epoch()).count();
 }
 
+// ECOZ2_VQ_MODE=fp32|fp64|tf32x3 overrides the search arithmetic (default tf32x3)
+static void apply_mode_env(vqb200::Engine &eng) {
+    const char *m = getenv("ECOZ2_VQ_MODE");
+    if (!m) return;
+    if (strcmp(m, "fp64") == 0) eng.set_mode(ECOZ2B200_MODE_FP64);
+    else if (strcmp(m, "fp32") == 0) eng.set_mode(ECOZ2B200_MODE_FP32);
+    else if (strcmp(m, "tf32x3") == 0) eng.set_mode(ECOZ2B200_MODE_TF32X3);
+}
+
 // ECOZ2_VQ_GPUS: unset/"" -> device 0; "all" -> every visible device; else "0,2,3"
 std::vector<int> devices_from_env() {
     std::vector<int> devs;
@@ -140,8 +149,7 @@ int learn_files(const double *base_refl, int base_K, int P, double eps, const ch
         new ecoz2b200_engine(devs.data(), (int) devs.size(), P, stop_M < 2 ? 2 : stop_M));
     Engine &eng = h->impl;
     if (!eng.ok()) return ECOZ2B200_ERR_CUDA;
-    if (getenv("ECOZ2_VQ_MODE") && strcmp(getenv("ECOZ2_VQ_MODE"), "fp64") == 0)
-        eng.set_mode(ECOZ2B200_MODE_FP64);
+    apply_mode_env(eng);
     int rc = eng.frames_reserve(tot_vecs);
     if (rc) return ECOZ2B200_ERR_CUDA;
     {
@@ -259,6 +267,7 @@ int ecoz2_vq_quantize(const char *nom_raas, const char *predictor_filenames[], i
         new ecoz2b200_engine(devs.data(), (int) devs.size(), P, M < 2 ? 2 : M));
     Engine &eng = h->impl;
     if (!eng.ok()) return ECOZ2B200_ERR_CUDA;
+    apply_mode_env(eng);
     if (eng.codebook_set_reflections(refl.data(), M)) return ECOZ2B200_ERR_CUDA;
     printf("%s: %d symbols\n", nom_raas, M);
 

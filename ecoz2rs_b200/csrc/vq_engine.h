@@ -124,7 +124,7 @@ class Engine {
     bool ok_ = false;
     int P_, D_, max_M_;
     int K_ = 0;
-    int mode_ = ECOZ2B200_MODE_FP32;
+    int mode_ = ECOZ2B200_MODE_TF32X3;   // falls back to the FFMA search where unsupported
     double kappa_ = 8.0;
     double kappa_tc_ = 40.0;
     std::vector<Shard> shards_;

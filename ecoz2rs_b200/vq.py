@@ -161,7 +161,7 @@ def _check(rc: int, what: str):
 class VqEngine:
     """Frames of this process on one or more local B200s + the replicated codebook."""
 
-    def __init__(self, P: int, max_M: int = 4096, devices: Sequence[int] = (0,), mode: int = MODE_FP32):
+    def __init__(self, P: int, max_M: int = 4096, devices: Sequence[int] = (0,), mode: Optional[int] = None):
         L = lib()
         devs = (C.c_int32 * len(devices))(*devices)
         self._h = L.ecoz2b200_create(devs, len(devices), P, max_M)
@@ -169,7 +169,7 @@ class VqEngine:
             raise VqError("ecoz2b200_create failed: " + L.ecoz2b200_last_error().decode())
         self.P, self.D, self.max_M = P, P + 1, max_M
         self.devices = tuple(devices)
-        if mode != MODE_FP32:
+        if mode is not None:
             self.set_mode(mode)
 
     def close(self):

@@ -71,11 +71,12 @@ int ecoz2_vq_quantize(const char *nom_raas, const char *predictor_filenames[],
 
 /* Arithmetic mode of the nearest-codeword search (reference
  * ecoz2/src/vq/vq_learn_par.c:62-81, quantize.c:14-30 are FP64).
- *   FP32:  FP32 FFMA search + FP64 re-evaluation of every frame whose best-two
- *          gap is inside the FP32 error bound (default; index-exact vs FP64).
- *   FP64:  the whole search in FP64 (verification mode).
- *   TF32X3: tcgen05 tensor-core search with split-TF32 operands + the same
- *          FP64 re-evaluation (when compiled in; else ERR_ARG).               */
+ *   TF32X3: tcgen05 tensor-core search with split-TF32 operands (FP32 accumulate
+ *          in tensor memory) + FP64 re-evaluation of every frame whose best-two
+ *          gap is inside the error bound (default; index-exact vs FP64).  Used for
+ *          K >= 64 and P <= 38; smaller / wider codebooks take the FP32 path.
+ *   FP32:  FP32 FFMA search + the same FP64 re-evaluation.
+ *   FP64:  the whole search in FP64 (verification mode).                      */
 #define ECOZ2B200_MODE_FP32 0
 #define ECOZ2B200_MODE_FP64 1
 #define ECOZ2B200_MODE_TF32X3 2

@@ -32,7 +32,7 @@ def _coef_close(a, b, rel=REL_COEF):
     return np.all(np.abs(a - b) <= rel * scale)
 
 
-@pytest.mark.parametrize("mode", [0, 1], ids=["fp32+recheck", "fp64"])
+@pytest.mark.parametrize("mode", [2, 0, 1], ids=["tf32x3+recheck", "fp32+recheck", "fp64"])
 @pytest.mark.parametrize("stage_i", [0, 3, 5, 7], ids=["K2", "K16", "K64", "K256"])
 def test_assign_matches_oracle(built_lib, frames36, oracle_run36, mode, stage_i):
     from oracle import oracle as O
@@ -47,7 +47,7 @@ def test_assign_matches_oracle(built_lib, frames36, oracle_run36, mode, stage_i)
     assert bad.size == 0, f"{bad.size} non-exempt index mismatches, first {bad[:5]}"
     same = idx == idx_ref
     assert np.allclose(dd[same], dd_ref[same], rtol=1e-12, atol=0)
-    if mode == 0:
+    if mode != 1:
         assert nre < 0.25 * len(idx), f"FP64 re-evaluation of {nre} frames is not 'rare'"
 
 
@@ -62,7 +62,7 @@ def test_assign_odd_sizes(built_lib, frames36):
         raas = O.refl_to_raas(refl)
         x = frames36[:N]
         idx_ref, dd_ref, d2_ref = O.assign(x, raas)
-        for mode in (0, 1):
+        for mode in (2, 0, 1):
             with _engine(36, max_M=512, mode=mode) as eng:
                 eng.set_frames(x)
                 eng.set_raas(raas)
@@ -80,7 +80,7 @@ def test_exact_ties_first_index_wins(built_lib, frames36):
     refl[3, 1] = 0.3
     raas = O.refl_to_raas(refl)
     idx_ref, _, _ = O.assign(frames36[:3000], raas)
-    for mode in (0, 1):
+    for mode in (2, 0, 1):
         with _engine(36, max_M=8, mode=mode) as eng:
             eng.set_frames(frames36[:3000])
             eng.set_raas(raas)
