@@ -223,6 +223,20 @@ def run_reference_arm(args):
     print(json.dumps(line))
 
 
+def measured_peaks():
+    """MEASURED_PEAKS.json (driver-written) or the profiling recipe's stated fallback."""
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            d = json.load(f)
+        if "bf16_tflops" in d:
+            return d, "of measured (MEASURED_PEAKS.json)"
+    except (OSError, ValueError):
+        pass
+    return {"bf16_tflops": 1590.0, "bf16_tflops_sustained": 1400.0, "hbm_gbs": 6650.0}, \
+        "of fallback (B200_PROFILING.md: 1.59 PFLOP/s burst, ~1.4 sustained)"
+
+
 # ------------------------------------------------------------------------------------
 def run_b200_arm(args):
     import torch
@@ -271,7 +285,9 @@ def run_b200_arm(args):
     torch.cuda.synchronize()
     log(f"[rank {rank}] {n_local} synthetic frames generated on device in {time.time() - t0:.1f}s")
 
-    eng = vq.VqEngine(P, max_M=K, devices=(local_rank,))
+    tc_mode = args.mode == "tf32x3"
+    eng = vq.VqEngine(P, max_M=K, devices=(local_rank,),
+                      mode=vq.MODE_TF32X3 if tc_mode else vq.MODE_FP32)
     if world > 1:
         ids = [vq.nccl_unique_id() if rank == 0 else None]
         dist.broadcast_object_list(ids, src=0)
@@ -346,8 +362,8 @@ def run_b200_arm(args):
     h2d = n_local * D * 8 + K * D * 8
     d2h = K * D * 8 + K * 8 * 2 + 16 + 2 * K * D * 8
 
-    # ---- roofline of the dominant kernel (the FP32 search), measured with CUDA events on
-    # the engine's own stream inside the timed region above
+    # ---- roofline of the dominant kernel (the search), measured with CUDA events on the
+    # engine's own stream inside the timed region above
     main_ms = ctr["search_main_ms"] / max(1, ctr["search_main_launches"])
     flops_per_launch = float(n_local) * K * FLOPS_PER_EVAL
     achieved = flops_per_launch / (main_ms * 1e-3) / 1e12 if main_ms > 0 else 0.0
@@ -356,21 +372,44 @@ def run_b200_arm(args):
     if os.path.exists(tpath):
         try:
             with open(tpath) as f:
-                traffic = json.load(f).get(f"vq_assign_f32_K{K}")
+                traffic = json.load(f).get(f"{'vq_assign_tc' if tc_mode else 'vq_assign_f32'}_K{K}")
         except (OSError, ValueError):
             traffic = None
-    roofline = {
-        "bound": "fp32_ffma", "kernel": "vq_assign_tiled<float> (fused distortion+argmin)",
-        "achieved": achieved, "peak": ffma_peak, "unit": "TFLOP/s",
-        "frac": achieved / ffma_peak if ffma_peak > 0 else None,
-        "peak_source": "measured live: ecoz2b200_ffma_peak_tflops (pure FFMA chains, all SMs); "
-                       "MEASURED_PEAKS.json holds no FP32 figure",
-        "peak_nominal": NOMINAL_FP32_TFLOPS, "frac_of_nominal": achieved / NOMINAL_FP32_TFLOPS,
-        "traffic": traffic,
-        "algorithmic_flops_per_launch": flops_per_launch, "kernel_ms": main_ms,
+    common = {
+        "traffic": traffic, "algorithmic_flops_per_launch": flops_per_launch, "kernel_ms": main_ms,
         "kernel_share_of_step": main_ms * args.steps / (wall * 1e3),
         "hbm_gbs_of_pass": (n_local * D * (4 + 8) + n_local * 4 * 2) / (wall / args.steps) / 1e9,
+        "fp32_ffma_peak_measured": ffma_peak,
     }
+    if tc_mode:
+        # Split-TF32: every algorithmic FMA is 3 TF32 tensor FMAs (xl.wh + xh.wl + xh.wh) and the
+        # inner dimension is padded 37 -> 40.  Denominator = measured tensor peak / 3;
+        # MEASURED_PEAKS.json holds the cuBLAS bf16 figure, TF32 runs at half the bf16 rate.
+        peaks, src = measured_peaks()
+        bf16_sus = peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
+        peak = bf16_sus / 2.0 / 3.0
+        peak_burst = peaks["bf16_tflops"] / 2.0 / 3.0
+        issued = float(n_local) * K * 2 * 8 * ((D + 8) // 8) * 3
+        roofline = {
+            "bound": "tensor", "kernel": "vq_assign_tc2 (tcgen05 split-TF32 distortion + fused argmin)",
+            "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
+            "peak_source": f"{src}: cuBLAS bf16 sustained {bf16_sus:.1f} TFLOP/s / 2 (TF32 rate) / 3 "
+                           "(three TF32 MMAs per product); the kernel is timed inside a long step",
+            "peak_burst": peak_burst, "frac_of_burst": achieved / peak_burst,
+            "tensor_tflops_issued": issued / (main_ms * 1e-3) / 1e12 if main_ms > 0 else 0.0,
+            "tensor_frac_of_tf32_sustained": (issued / (main_ms * 1e-3) / 1e12) / (bf16_sus / 2.0) if main_ms > 0 else None,
+            **common,
+        }
+    else:
+        roofline = {
+            "bound": "fp32_ffma", "kernel": "vq_assign_tiled<float> (fused distortion+argmin)",
+            "achieved": achieved, "peak": ffma_peak, "unit": "TFLOP/s",
+            "frac": achieved / ffma_peak if ffma_peak > 0 else None,
+            "peak_source": "measured live: ecoz2b200_ffma_peak_tflops (pure FFMA chains, all SMs); "
+                           "MEASURED_PEAKS.json holds no FP32 figure",
+            "peak_nominal": NOMINAL_FP32_TFLOPS, "frac_of_nominal": achieved / NOMINAL_FP32_TFLOPS,
+            **common,
+        }
 
     # ---- CPU baseline: the reference C code on this box's host cores, bounded sample
     cpu_baseline = None
@@ -404,13 +443,14 @@ def run_b200_arm(args):
             "metric": "frame x codeword evals/sec per k-means pass", "value": value, "unit": "evals/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": wall / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "vs_baseline": None, "dtype": "tf32x3" if tc_mode else "f32", "data": "synthetic",
             "config": {
                 "workload": (f"vq learn P=36, k-means pass at K={K} on {n_total} synthetic ar_mix frames"
                              + (" (configs[1], 1 B200)" if world == 1 else
                                 f" sharded over {world} B200 with one NCCL allreduce of the packed cell sums per pass (configs[2])")),
                 "P": P, "K": K, "frames": n_total, "frames_per_gpu": n_local, "epsilon": EPS,
-                "search": "FP32 FFMA + FP64 re-evaluation of near-ties",
+                "search": ("tcgen05 split-TF32 (FP32 accumulate in TMEM) + FP64 re-evaluation of near-ties"
+                           if tc_mode else "FP32 FFMA + FP64 re-evaluation of near-ties"),
                 "l2": "inputs (1.48 GB f32 + 2.96 GB f64 frames per 10M) exceed the 126 MB L2; no flush needed",
             },
             "e2e": {"value": e2e_value, "unit": "evals/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
@@ -443,6 +483,8 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--ref-sample", type=int, default=1_000_000)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--mode", default="tf32x3", choices=["tf32x3", "fp32"],
+                    help="search arithmetic of the b200 arm (both end in the FP64 re-evaluation)")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         log("note: timing rules ask for >= 3 warm-up steps")

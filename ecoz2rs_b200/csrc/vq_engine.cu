@@ -96,12 +96,16 @@ Engine::Engine(const int *devices, int num_devices, int P, int max_M)
                  "cudaMalloc wtc")) return;
         if (!chk(cudaMalloc(&s.w1, sizeof(float) * (size_t) K32), "cudaMalloc w1")) return;
         if (!chk(cudaMalloc(&s.packed, sizeof(double) * L.size()), "cudaMalloc packed")) return;
+        if (!chk(cudaMalloc(&s.packed_scratch, sizeof(double) * L.size()), "cudaMalloc packed_scratch")) return;
+        if (!chk(cudaMalloc(&s.raas_prev, cb), "cudaMalloc raas_prev")) return;
         if (!chk(cudaMalloc(&s.scalars, sizeof(double) * 8), "cudaMalloc scalars")) return;
         cudaMemset(s.refl, 0, cb);
         cudaMemset(s.raas, 0, cb);
     }
     const char *fs = getenv("ECOZ2_VQ_FUSED_SMALL");
     if (fs && fs[0] == '0') use_small_ = false;
+    const char *csort = getenv("ECOZ2_VQ_CELL_SORT");
+    if (csort && csort[0] == '0') use_cell_sort_ = false;
     ok_ = true;
 }
 
@@ -115,7 +119,7 @@ Engine::~Engine() {
         cudaFree(s.x64); cudaFree(s.x32); cudaFree(s.idx); cudaFree(s.idx_tmp); cudaFree(s.seq);
         cudaFree(s.mindist); cudaFree(s.sc_mem);
         cudaFree(s.refl); cudaFree(s.raas); cudaFree(s.w32); cudaFree(s.w64); cudaFree(s.w1max); cudaFree(s.w1);
-        cudaFree(s.wtc);
+        cudaFree(s.wtc); cudaFree(s.cs_mem); cudaFree(s.packed_scratch); cudaFree(s.raas_prev);
         cudaFree(s.packed); cudaFree(s.scalars);
         QBuf &q = qbuf_[i];
         cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
@@ -222,8 +226,9 @@ int Engine::ensure_capacity(Shard &s, long n) {
         CUDA_TRY(cudaMemcpy(nx64, s.x64, sizeof(double) * (size_t) s.n * D_, cudaMemcpyDeviceToDevice));
     cudaFree(s.x64); s.x64 = nx64;
     cudaFree(s.x32); cudaFree(s.idx); cudaFree(s.idx_tmp); cudaFree(s.seq); cudaFree(s.mindist);
-    cudaFree(s.sc_mem);
+    cudaFree(s.sc_mem); cudaFree(s.cs_mem);
     s.x32 = nullptr; s.idx = s.idx_tmp = nullptr; s.sc_mem = nullptr; s.seq = nullptr; s.mindist = nullptr;
+    s.cs_mem = nullptr;
     CUDA_TRY(cudaMalloc(&s.x32, sizeof(float) * (size_t) n * D_));
     CUDA_TRY(cudaMalloc(&s.idx, sizeof(int32_t) * (size_t) n));
     CUDA_TRY(cudaMalloc(&s.idx_tmp, sizeof(int32_t) * (size_t) n));
@@ -231,6 +236,8 @@ int Engine::ensure_capacity(Shard &s, long n) {
     CUDA_TRY(cudaMalloc(&s.mindist, sizeof(double) * (size_t) n));
     CUDA_TRY(cudaMalloc(&s.sc_mem, scratch_bytes(n)));
     scratch_carve(s.sc_mem, n, &s.sc);
+    CUDA_TRY(cudaMalloc(&s.cs_mem, cell_scratch_bytes(n, max_M_)));
+    cell_scratch_carve(s.cs_mem, n, max_M_, &s.cs);
     s.cap = n;
     return ECOZ2B200_OK;
 }
@@ -493,13 +500,38 @@ void Engine::pass_kernels(Shard &s, const double *x64, const float *x32, long n,
         cudaEventRecord(s.ev[1], s.stream);
         ctr_.kernel_launches += n > 0;
         ctr_.evals += (double) n * K_;
+        if (mindist == s.mindist) mindist_valid_ = true;
         return;
     }
     search(s, x64, x32, n, idx, sc);
     cudaEventRecord(s.ev[1], s.stream);
+    if (with_cells && use_cell_sort_ && cell_sort_supported(K_) && x64 == s.x64) {
+        // grouped accumulation; per-frame minDist values are produced on demand from the
+        // codebook this assignment was made against
+        cudaMemcpyAsync(s.raas_prev, s.raas, sizeof(double) * (size_t) K_ * D_, cudaMemcpyDeviceToDevice,
+                        s.stream);
+        launch_cell_sums(x64, idx, n, D_, s.raas, K_, s.packed, seq, s.cs, s.num_sms, s.stream);
+        K_prev_ = K_;
+        mindist_valid_ = false;
+        ctr_.kernel_launches += n > 0 ? 5 : 2;
+        return;
+    }
     launch_accumulate(x64, idx, n, D_, s.raas, K_, s.packed, mindist, seq, with_cells, s.num_sms,
                       s.stream);
+    if (mindist == s.mindist) mindist_valid_ = true;
     ctr_.kernel_launches += n > 0;
+}
+
+int Engine::ensure_mindist() {
+    if (mindist_valid_) return ECOZ2B200_OK;
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        launch_accumulate(s.x64, s.idx, s.n, D_, s.raas_prev, K_prev_, s.packed_scratch, s.mindist, nullptr,
+                          false, s.num_sms, s.stream);
+        ctr_.kernel_launches += s.n > 0;
+    }
+    mindist_valid_ = true;
+    return ECOZ2B200_OK;
 }
 
 int Engine::debug_tc_distortions(float *out, long n_rows) {
@@ -689,6 +721,10 @@ int Engine::inertia(double *inertia_out) {
 }
 
 int Engine::last_assignment(int32_t *idx_out, double *mindist_out) {
+    if (mindist_out) {
+        int rc = ensure_mindist();
+        if (rc) return rc;
+    }
     for (Shard &s : shards_) {
         CUDA_TRY(cudaSetDevice(s.device));
         if (idx_out)

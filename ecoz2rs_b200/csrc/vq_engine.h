@@ -35,6 +35,8 @@ struct Shard {
     double *mindist = nullptr;  // [n]   ddmin - 1 of the last pass
     void *sc_mem = nullptr;   // scratch of the FP32 search / FP64 re-evaluation
     SearchScratch sc;
+    void *cs_mem = nullptr;   // scratch of the sorted cell accumulation
+    CellScratch cs;
     long cap = 0;             // capacity (frames) of the per-frame buffers
 
     // codebook replica
@@ -46,6 +48,8 @@ struct Shard {
     float *w1 = nullptr;      // [K] sum_n |w_i[n]|
     float *wtc = nullptr;     // tensor-core search operand (UMMA canonical layout, TF32 hi/lo)
     double *packed = nullptr; // PackedLayout(max_M, D)
+    double *packed_scratch = nullptr;  // same size: sink of the on-demand minDist pass
+    double *raas_prev = nullptr;       // [max_M][D] codebook the last assignment was made against
     double *scalars = nullptr;  // [8] misc device scalars (sigma sum, ...)
 };
 
@@ -121,6 +125,10 @@ class Engine {
     bool small_path() const { return use_small_ && pass_small_supported(K_, D_); }
     bool tc_path() const { return mode_ == ECOZ2B200_MODE_TF32X3 && assign_tc_supported(K_, D_); }
     bool use_small_ = true;   // ECOZ2_VQ_FUSED_SMALL=0 forces the tiled path at every K
+    bool use_cell_sort_ = true;  // ECOZ2_VQ_CELL_SORT=0: per-frame atomics (vq_accumulate) instead
+    bool mindist_valid_ = true;  // s.mindist holds the last pass's values (else: compute on demand)
+    int K_prev_ = 0;             // rows of raas_prev
+    int ensure_mindist();
     bool ok_ = false;
     int P_, D_, max_M_;
     int K_ = 0;

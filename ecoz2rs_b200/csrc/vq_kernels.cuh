@@ -106,6 +106,26 @@ void launch_accumulate(const double *x64, const int32_t *idx, long n, int D,
                        const double *raas, int K, double *packed, double *mindist,
                        uint16_t *seq, bool with_cells, int num_sms, cudaStream_t s);
 
+// ---- (b') cell accumulation by counting sort + gather (vq_cells.cu) ---------------------
+// Same packed outputs as launch_accumulate(with_cells = true) -- cell sums, counts, cell
+// distortions, DD -- without per-frame atomics and without per-frame distortions (the cell
+// distortion is cellsum . w - count).  mindist is NOT produced: call launch_accumulate's
+// distortion-only form when per-frame values are wanted.  2 <= K <= 8192.
+struct CellScratch {
+    int32_t *perm = nullptr;        // [cap]  frame indices grouped by cell
+    int32_t *hist = nullptr;        // [K+1]  frames per cell
+    int32_t *offsets = nullptr;     // [K+1]  first position of each cell in perm
+    int32_t *cursor = nullptr;      // [K+1]  scatter cursors
+    int32_t *item_start = nullptr;  // [K+1]  first 256-frame work item of each cell
+    long cap = 0;
+};
+bool cell_sort_supported(int K);
+size_t cell_scratch_bytes(long cap, int max_K);
+void cell_scratch_carve(void *base, long cap, int max_K, CellScratch *out);
+void launch_cell_sums(const double *x64, const int32_t *idx, long n, int D, const double *raas,
+                      int K, double *packed, uint16_t *seq, const CellScratch &cs, int num_sms,
+                      cudaStream_t s);
+
 // ---- (a+b) fused small-codebook pass (K <= 32, D = 37 or 13), all FP64 ----------
 // One sweep over the FP64 frames: exact argmin (first index on ties), idx / mindist / seq
 // outputs, and (with_cells) the packed cell sums, counts, distortions; DD and inertia always.

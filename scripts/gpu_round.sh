@@ -16,11 +16,13 @@ echo "bench exit $?" >> $O/bench_$TAG.err
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref_$TAG.json 2> $O/bench_ref_$TAG.err
 echo "bench ref exit $?" >> $O/bench_ref_$TAG.err
 timeout 600 python scripts/perf_probe.py --n 10000000 --ks 2,4,8,16,32,64,128,256,512,1024,2048,4096 > $O/probe_$TAG.log 2>&1
+timeout 600 python scripts/perf_probe.py --n 10000000 --ks 64,256,1024,2048,4096 --mode 0 > $O/probe_fp32_$TAG.log 2>&1
+timeout 600 python scripts/perf_probe.py --n 20000000 --p 12 --ks 2,16,64,256,1024 > $O/probe_p12_$TAG.log 2>&1
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
     --log-file $O/launches_$TAG.csv python bench.py --frames 2000000 --steps 3 --warmup 3 \
     --no-cpu-baseline --e2e-steps 1 > $O/ncu_launches_$TAG.log 2>&1
 timeout 900 ncu --set full --clock-control none --import-source on \
-    -k regex:"vq_assign_tiled|vq_accumulate" --launch-skip 20 --launch-count 4 \
+    -k regex:"vq_assign_tc2|vq_accumulate" --launch-skip 12 --launch-count 2 \
     -o $O/search_$TAG -f python scripts/perf_probe.py --n 2000000 --ks 2048 --reps 2 \
     > $O/ncu_full_$TAG.log 2>&1
 ls -la $O

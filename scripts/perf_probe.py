@@ -15,7 +15,7 @@ ap = argparse.ArgumentParser()
 ap.add_argument("--n", type=int, default=2_000_000)
 ap.add_argument("--p", type=int, default=36)
 ap.add_argument("--ks", type=str, default="2,16,64,256,1024,2048")
-ap.add_argument("--mode", type=int, default=0)
+ap.add_argument("--mode", type=int, default=2)
 ap.add_argument("--reps", type=int, default=3)
 a = ap.parse_args()
 
