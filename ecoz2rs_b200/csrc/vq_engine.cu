@@ -471,7 +471,7 @@ void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32
                          nullptr, 0, s.num_sms, s.stream);
         cudaEventRecord(s.ev[7], s.stream);
         launch_recheck(x32, x64, n, D_, s.w32, s.w64, s.w1, s.w1max, s.raas, K_, 2.f * err_scale, sc,
-                       idx, s.num_sms, s.stream);
+                       idx, s.num_sms, s.stream, s.wtc, err_tc);
         ctr_.kernel_launches += 5;
     } else {
         // |error| of one FP32 distortion <= kappa * 2^-24 * |rx[0]| * sum_n |w[n]|.

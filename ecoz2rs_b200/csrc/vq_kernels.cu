@@ -507,8 +507,19 @@ vq_candidates_select(const int32_t *__restrict__ list, const int2 *__restrict__ 
 void launch_recheck(const float *x32, const double *x64, long n, int D, const float *w32,
                     const double *w64, const float *w1, const float *w1max, const double *raas,
                     int K, float err_scale, const SearchScratch &sc, int32_t *idx, int num_sms,
-                    cudaStream_t s) {
+                    cudaStream_t s, const float *wtc, float err_tc) {
     if (n <= 0) return;
+    if (wtc != nullptr && filter_tc_supported()) {
+        // candidates selected by the tensor-core kernel over the flagged frames
+        launch_filter_tc(x32, n, D, wtc, K, sc, err_tc, num_sms, s);
+        const int blocks = num_sms * 8;
+        vq_candidates_eval<<<blocks, 256, 0, s>>>(x64, raas, D, sc.flag_list, sc.cand, sc.counters + 1,
+                                                  (int) sc.cand_cap, sc.cand_d, sc.min_key, idx);
+        vq_candidates_select<<<blocks, 256, 0, s>>>(sc.flag_list, sc.cand, sc.counters + 1,
+                                                    (int) sc.cand_cap, sc.cand_d, sc.min_key, idx);
+        launch_assign_f64(x64, n, D, w64, K, sc.exact_list, sc.counters + 2, idx, num_sms, s);
+        return;
+    }
     AssignParams<float> p{};
     p.x = x32; p.n_frames = n; p.D_rt = D; p.wt = w32; p.K = K;
     p.list = sc.flag_list; p.list_count = sc.counters + 0; p.w1max = w1max; p.err_scale = err_scale;

@@ -80,7 +80,7 @@ void launch_assign_f64(const double *x64, long n, int D, const double *w64, int 
 void launch_recheck(const float *x32, const double *x64, long n, int D, const float *w32,
                     const double *w64, const float *w1, const float *w1max, const double *raas,
                     int K, float err_scale, const SearchScratch &sc, int32_t *idx, int num_sms,
-                    cudaStream_t s);
+                    cudaStream_t s, const float *wtc = nullptr, float err_tc = 0.f);
 
 // ---- (a') tensor-core search (vq_tc.cu): tcgen05 split-TF32, FP32 accumulate in TMEM --------
 // Supported for K >= 64 and D <= 40.  wtc = codebook in the UMMA canonical K-major layout,
@@ -89,6 +89,11 @@ void launch_recheck(const float *x32, const double *x64, long n, int D, const fl
 // `flag`); list / list_count optionally restrict the search to a gathered subset.
 // dump (debug): every distortion value, [n][dump_ld] floats.
 bool assign_tc_supported(int K, int D);
+// step 1 of launch_recheck on the tensor cores: candidates (lower bound <= flag_ub) of the
+// frames in sc.flag_list, same outputs as the FP32 filter
+bool filter_tc_supported();
+void launch_filter_tc(const float *x32, long n_cap, int D, const float *wtc, int K,
+                      const SearchScratch &sc, float err_scale, int num_sms, cudaStream_t s);
 int tc_tile_cols(int K);
 size_t tc_codebook_floats(int K, int D);
 void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, cudaStream_t s);

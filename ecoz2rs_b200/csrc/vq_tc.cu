@@ -224,6 +224,14 @@ struct TcParams {
     unsigned long long *min_key;
     float *dump;                // debug: all distortions [n][dump_ld]
     int dump_ld;
+    // filter mode (re-evaluation of flagged frames over the gather list): no argmin; every
+    // (list position, codeword) whose lower bound is <= the frame's upper bound flag_ub[pos]
+    // of the true minimum becomes a candidate for the FP64 evaluation
+    int2 *cand;
+    int32_t *cand_count;
+    int cand_cap;
+    int32_t *exact_list;        // frames whose candidates did not fit: all-FP64 search
+    int32_t *exact_count;
     int mc;                     // 1: launched as clusters of 2 CTAs that share the codeword stream
     int exp;                    // dev experiments (ECOZ2_VQ_TC_EXP): bit mask 1 no record path, 2 trivial reduction, 4 no tcgen05.ld, 8 no MMA, 16 no tcgen05.st, 32 no B copy
 };
@@ -347,11 +355,84 @@ __device__ __forceinline__ void epi_finish(const EpiState &st, float &second, in
     bidx = st.col + jm;
 }
 
+// filter mode (see TcParams::cand): a frame's candidates are collected in registers (a
+// flagged frame typically has 2-3) and published once per frame tile with one atomic per
+// warp; a frame with more than kFilterSlots candidates goes to the all-FP64 search instead.
+constexpr int kFilterSlots = 6;
+struct FilterState {
+    int cnt;
+    int c[kFilterSlots];
+    __device__ __forceinline__ void init() {
+        cnt = 0;
+#pragma unroll
+        for (int k = 0; k < kFilterSlots; k++) c[k] = 0;
+    }
+    __device__ __forceinline__ void push(int col) {
+#pragma unroll
+        for (int k = kFilterSlots - 1; k > 0; k--) c[k] = c[k - 1];
+        c[0] = col;
+        cnt++;
+    }
+};
+
+__device__ __forceinline__ void epi_filter32(const uint32_t (&r)[32], int col0, int nv_rel, float thr,
+                                             FilterState &fs) {
+#define F(i) __uint_as_float(r[i])
+    float m = INFINITY;
+#pragma unroll
+    for (int j = 0; j < 32; j += 2) m = min3f(m, F(j), F(j + 1));
+    if (nv_rel < 32) m = -INFINITY;   // ragged end: take the slow path, it masks per column
+    if (__any_sync(0xffffffffu, m <= thr)) {
+        uint32_t mask = 0;
+#pragma unroll
+        for (int j = 0; j < 32; j++) mask |= (j < nv_rel && F(j) <= thr) ? (1u << j) : 0u;
+        while (mask) {
+            const int j = __ffs(mask) - 1;
+            mask &= mask - 1;
+            fs.push(col0 + j);
+        }
+    }
+#undef F
+}
+
+// publish the candidates of one warp's 32 frames; pos = list position of this lane's frame
+__device__ __forceinline__ void epi_filter_flush(const FilterState &fs, int pos, long row,
+                                                 const TcParams &p) {
+    const int lane = threadIdx.x & 31;
+    const bool over = fs.cnt > kFilterSlots;
+    const int mine = (row >= 0 && !over) ? fs.cnt : 0;
+    int incl = mine;
+#pragma unroll
+    for (int off = 1; off < 32; off <<= 1) {
+        const int v = __shfl_up_sync(0xffffffffu, incl, off);
+        if (lane >= off) incl += v;
+    }
+    const int total = __shfl_sync(0xffffffffu, incl, 31);
+    int base = 0;
+    if (lane == 31 && total > 0) base = atomicAdd(p.cand_count, total);
+    base = __shfl_sync(0xffffffffu, base, 31);
+    const int first = base + incl - mine;
+    // a flagged frame always has its own best among the candidates; none at all means the
+    // tensor-core values were unusable (NaN input ...): let the FP64 search decide
+    bool spill = row >= 0 && (over || fs.cnt == 0);
+#pragma unroll
+    for (int k = 0; k < kFilterSlots; k++) {
+        if (k < mine) {
+            // c[0] is the newest; order inside the buffer is irrelevant
+            if (first + k < p.cand_cap) p.cand[first + k] = make_int2(pos, fs.c[k]);
+            else spill = true;
+        }
+    }
+    if (spill) p.exact_list[atomicAdd(p.exact_count, 1)] = (int32_t) row;
+}
+
 // Columns [c_lo, c_hi) of one accumulator (thread = its TMEM lane), 32 at a time; the next
 // tcgen05.ld is in flight while the current 32 values are reduced.  nv = valid codewords in
 // this tile, tcol0 = codeword index of the tile's column 0.
+template <bool FILTER>
 __device__ __forceinline__ void epi_tile(uint32_t taddr, int c_lo, int c_hi, int tcol0, int nv,
-                                         EpiState &est, const TcParams &p, long row) {
+                                         EpiState &est, const TcParams &p, long row, float thr = 0.f,
+                                         FilterState *fs = nullptr) {
     if (p.exp & 4) return;
     const int nv32 = (nv + 31) & ~31;
     const int c_end = nv32 < c_hi ? nv32 : c_hi;
@@ -364,7 +445,8 @@ __device__ __forceinline__ void epi_tile(uint32_t taddr, int c_lo, int c_hi, int
             _Pragma("unroll") for (int j = 0; j < 32; j++)                                \
                 if (c + j < nv) p.dump[row * p.dump_ld + tcol0 + c + j] = __uint_as_float(R[j]); \
         }                                                                                 \
-        epi_step32(R, tcol0 + c, nv - c, est, p.exp);                                     \
+        if (FILTER) epi_filter32(R, tcol0 + c, nv - c, thr, *fs);                         \
+        else epi_step32(R, tcol0 + c, nv - c, est, p.exp);                                \
     }
     while (c < c_end) {
         tmem_ld_wait();
@@ -587,7 +669,7 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
                 mbar_wait(&sm->tmem_full[acc], (tc >> 1) & 1);
                 tc_fence_after();
                 const int nv = K - t * BN < BN ? K - t * BN : BN;   // valid codewords in this tile
-                epi_tile(lane_addr + acc * 256, c_lo * 16, c_hi * 16, t * BN, nv, est, p, row);
+                epi_tile<false>(lane_addr + acc * 256, c_lo * 16, c_hi * 16, t * BN, nv, est, p, row);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm->tmem_empty[acc]);
@@ -664,7 +746,7 @@ struct Tc2Smem {
 };
 }  // namespace
 
-template <int KS>
+template <int KS, bool FILTER>
 __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) {
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     Tc2Smem *sm = reinterpret_cast<Tc2Smem *>(smem_raw);
@@ -861,15 +943,23 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             const long row = base + r < total ? (p.list ? (long) p.list[base + r] : base + r) : -1;
             EpiState est;
             est.init();
+            float thr = -INFINITY;
+            FilterState fst;
+            fst.init();
+            if (FILTER && row >= 0) thr = p.flag_ub[base + r];
             for (int t = 0; t < n_wtiles; t++, u++) {
                 const uint32_t buf = u & 1;
                 mbar_wait(&sm->acc_full[2 * buf + h], (u >> 1) & 1);
                 tc_fence_after();
                 const int nv = K - t * BN < BN ? K - t * BN : BN;
-                epi_tile(lane_addr + (2 * buf + h) * 128, 0, BN, t * BN, nv, est, p, row);
+                epi_tile<FILTER>(lane_addr + (2 * buf + h) * 128, 0, BN, t * BN, nv, est, p, row, thr, &fst);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm->acc_empty[2 * buf + h]);
+            }
+            if (FILTER) {
+                epi_filter_flush(fst, (int) (base + r), row, p);
+                continue;
             }
             float best = est.best, second;
             int bidx;
@@ -1023,14 +1113,20 @@ static size_t tc2_smem_bytes(int D, int BN) {
     return 5120 + raw_stride + 2 * (2 * KC * kBM * 16) + (size_t) kB2Stages * 2 * KC * BN * 16;
 }
 
-template <int KS>
-static void launch_tc2_inst(const TcParams &p, long grid, cudaStream_t s) {
+template <int KS, bool FILTER>
+static void launch_tc2_inst2(const TcParams &p, long grid, cudaStream_t s) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(vq_assign_tc2<KS>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
+        cudaFuncSetAttribute(vq_assign_tc2<KS, FILTER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             227 * 1024);
         attr_set = true;
     }
-    vq_assign_tc2<KS><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN), s>>>(p);
+    vq_assign_tc2<KS, FILTER><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN), s>>>(p);
+}
+template <int KS>
+static void launch_tc2_inst(const TcParams &p, long grid, cudaStream_t s) {
+    if (p.cand != nullptr) launch_tc2_inst2<KS, true>(p, grid, s);
+    else launch_tc2_inst2<KS, false>(p, grid, s);
 }
 
 void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
@@ -1096,6 +1192,31 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
         return;
     }
     vq_assign_tc<<<(unsigned) grid, kThreads, smem, s>>>(p);
+}
+
+
+bool filter_tc_supported() { return tc_variant() == 2; }
+
+void launch_filter_tc(const float *x32, long n_cap, int D, const float *wtc, int K,
+                      const SearchScratch &sc, float err_scale, int num_sms, cudaStream_t s) {
+    if (n_cap <= 0) return;
+    TcParams p{};
+    p.x = x32; p.n_frames = n_cap; p.D = D; p.ksteps = tc_ksteps(D);
+    p.list = sc.flag_list; p.list_count = sc.counters + 0;
+    p.wtc = wtc; p.K = K; p.BN = tc_tile_cols(K);
+    p.err_scale = err_scale; p.flag_ub = sc.flag_ub;
+    p.cand = sc.cand; p.cand_count = sc.counters + 1; p.cand_cap = (int) sc.cand_cap;
+    p.exact_list = sc.exact_list; p.exact_count = sc.counters + 2;
+    // device-side count: persistent grid sized for the worst case
+    long tiles = (n_cap + 2 * kBM - 1) / (2 * kBM);
+    long grid = tiles < num_sms ? tiles : num_sms;
+    switch (p.ksteps) {
+        case 1: launch_tc2_inst<1>(p, grid, s); break;
+        case 2: launch_tc2_inst<2>(p, grid, s); break;
+        case 3: launch_tc2_inst<3>(p, grid, s); break;
+        case 4: launch_tc2_inst<4>(p, grid, s); break;
+        default: launch_tc2_inst<5>(p, grid, s); break;
+    }
 }
 
 }  // namespace vqb200
