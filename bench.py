@@ -177,7 +177,7 @@ def run_reference_arm(args):
     from oracle import refbuild
     K = args.codebook or (2048 if args.gpus == 1 else 4096)
     if not refbuild.available(K):
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref not built (no /root/reference at build time)"}))
+        emit_line({"impl": "reference", "unavailable": "oracle/_ref not built (no /root/reference at build time)"})
         return
     n_sample = args.ref_sample
     log(f"[reference] generating {n_sample} sample frames (numpy) ...")
@@ -200,7 +200,7 @@ def run_reference_arm(args):
     times, threads = reference_sample_run(sample, base_refl, K, n_passes)
     timed = times[args.warmup:]
     if not timed:
-        print(json.dumps({"impl": "reference", "unavailable": "reference vq.learn produced no pass timings"}))
+        emit_line({"impl": "reference", "unavailable": "reference vq.learn produced no pass timings"})
         return
     total = sum(timed)
     # the reference prints 2 decimals: guard against a zero reading
@@ -220,7 +220,30 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": "evals/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit_line(line)
+
+
+_REAL_STDOUT = None
+
+
+def capture_stdout():
+    """Everything libraries print on stdout (e.g. the 'NCCL version' banner) goes to stderr;
+    the ONE JSON line is written to the real stdout by emit_line()."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit_line(obj):
+    data = (json.dumps(obj) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        sys.stdout.flush()
+        os.write(_REAL_STDOUT, data)
 
 
 def measured_peaks():
@@ -466,7 +489,7 @@ def run_b200_arm(args):
             "learn_stage_ms": {str(s["M"]): s["stage_seconds"] * 1e3 for s in stages},
             "learn_evals_per_s": learn_ctr["evals"] * world / learn_wall,
         }
-        print(json.dumps(line))
+        emit_line(line)
     eng.close()
     if world > 1:
         dist.destroy_process_group()
@@ -475,7 +498,7 @@ def run_b200_arm(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=40)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--frames", type=int, default=N_FRAMES)
@@ -486,6 +509,7 @@ def main():
     ap.add_argument("--mode", default="tf32x3", choices=["tf32x3", "fp32"],
                     help="search arithmetic of the b200 arm (both end in the FP64 re-evaluation)")
     args = ap.parse_args()
+    capture_stdout()
     if args.warmup < 3 and args.impl == "b200":
         log("note: timing rules ask for >= 3 warm-up steps")
     if args.impl == "reference":
