@@ -148,8 +148,13 @@ int Engine::set_kappa(double kappa) {
     return ECOZ2B200_OK;
 }
 int Engine::set_kappa_tc(double kappa) {
-    if (!(kappa >= 0)) return ECOZ2B200_ERR_ARG;
+    if (!(kappa > 0)) return ECOZ2B200_ERR_ARG;
     kappa_tc_ = kappa;
+    if (K_ > 0 && tc_path()) {   // the staged bound weights depend on it (FP16 operand format)
+        int rc = stage_codebook();
+        if (rc) return rc;
+        return sync_all();
+    }
     return ECOZ2B200_OK;
 }
 
@@ -365,7 +370,8 @@ int Engine::stage_codebook() {
         launch_prepare_codebook(s.raas, K_, D_, s.w32, s.w64, s.w1, s.w1max, s.stream);
         ctr_.kernel_launches++;
         if (tc_path()) {
-            launch_prepare_codebook_tc(s.raas, K_, D_, s.wtc, s.stream);
+            launch_prepare_codebook_tc(s.raas, K_, D_, s.wtc, s.w1max,
+                                       (float) (kappa_tc_ * ldexp(1.0, -24)), s.stream);
             ctr_.kernel_launches++;
         }
     }
@@ -654,7 +660,8 @@ int Engine::kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_ou
         launch_prepare_codebook(s.raas, K_, D_, s.w32, s.w64, s.w1, s.w1max, s.stream);
         ctr_.kernel_launches += 2;
         if (tc_path()) {
-            launch_prepare_codebook_tc(s.raas, K_, D_, s.wtc, s.stream);
+            launch_prepare_codebook_tc(s.raas, K_, D_, s.wtc, s.w1max,
+                                       (float) (kappa_tc_ * ldexp(1.0, -24)), s.stream);
             ctr_.kernel_launches++;
         }
         CUDA_TRY(cudaEventRecord(s.ev[4], s.stream));

@@ -96,7 +96,8 @@ void launch_filter_tc(const float *x32, long n_cap, int D, const float *wtc, int
                       const SearchScratch &sc, float err_scale, int num_sms, cudaStream_t s);
 int tc_tile_cols(int K);
 size_t tc_codebook_floats(int K, int D);
-void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, cudaStream_t s);
+void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, const float *w1max,
+                                float err_scale, cudaStream_t s);
 void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
                       const int32_t *list, const int32_t *list_count, const SearchScratch &sc,
                       bool flag, const float *w1, const float *w1max, float err_scale, int32_t *idx,

@@ -29,6 +29,7 @@
 // first index among equal values wins.
 #include "vq_kernels.cuh"
 
+#include <cuda_fp16.h>
 #include <cfloat>
 #include <cmath>
 #include <cstdlib>
@@ -81,6 +82,19 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
     while (!mbar_try_wait(bar, parity)) {
     }
 }
+// wait of a warp that is far ahead of its consumer (producers, frame loaders): sleeping
+// between polls leaves the issue slots of its SM sub-partition to the epilogue warps
+__device__ __forceinline__ void mbar_wait_relaxed(uint64_t *bar, uint32_t parity) {
+    while (!mbar_try_wait(bar, parity)) __nanosleep(200);
+}
+template <int REGS>
+__device__ __forceinline__ void setmaxnreg_inc() {
+    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS));
+}
+template <int REGS>
+__device__ __forceinline__ void setmaxnreg_dec() {
+    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS));
+}
 __device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes,
                                          uint64_t *bar) {
     asm volatile(
@@ -120,6 +134,18 @@ __device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint6
         ".reg .pred p;\n"
         "setp.ne.b32 p, %4, 0;\n"
         "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(d_tmem),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+// D[tmem] (+)= A[smem] * B[smem], FP16 inputs (K = 16 per instruction), FP32 accumulate
+__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
+                                         uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
         "}\n" ::"r"(d_tmem),
         "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
         : "memory");
@@ -201,6 +227,10 @@ __host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
     return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t) (N >> 3) << 17) |
            ((uint32_t) (M >> 4) << 24);
 }
+// same for kind::f16 with A = B = FP16 (format code 0)
+__host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N) {
+    return (1u << 4) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (M >> 4) << 24);
+}
 
 }  // namespace
 
@@ -216,6 +246,7 @@ struct TcParams {
     int BN;                     // codewords per tile (UMMA N): 64, 128 or 256
     const float *w1;            // sum_n |w_i[n]| per codeword
     const float *w1max;         // max_i w1[i]
+    const float *wscale;        // FP16 format: the codebook's power-of-two scale G (device scalar)
     float err_scale;            // kappa * 2^-24
     int32_t *idx_out;
     int32_t *flag_list;
@@ -428,12 +459,14 @@ __device__ __forceinline__ void epi_filter_flush(const FilterState &fs, int pos,
 
 // Columns [c_lo, c_hi) of one accumulator (thread = its TMEM lane), 32 at a time; the next
 // tcgen05.ld is in flight while the current 32 values are reduced.  nv = valid codewords in
-// this tile, tcol0 = codeword index of the tile's column 0.
-template <bool FILTER>
+// this tile, tcol0 = codeword index of the tile's column 0.  Generic path: ragged tiles,
+// filter mode, and (DBG) the distortion dump / experiment switches.
+template <bool FILTER, bool DBG>
 __device__ __forceinline__ void epi_tile(uint32_t taddr, int c_lo, int c_hi, int tcol0, int nv,
                                          EpiState &est, const TcParams &p, long row, float thr = 0.f,
-                                         FilterState *fs = nullptr) {
-    if (p.exp & 4) return;
+                                         FilterState *fs = nullptr, float dump_mul = 1.f) {
+    const int exp = DBG ? p.exp : 0;
+    if (exp & 4) return;
     const int nv32 = (nv + 31) & ~31;
     const int c_end = nv32 < c_hi ? nv32 : c_hi;
     uint32_t ra[32], rb[32];
@@ -441,12 +474,12 @@ __device__ __forceinline__ void epi_tile(uint32_t taddr, int c_lo, int c_hi, int
     if (c < c_end) tmem_ld32(taddr + c, ra);
 #define VQ_TC_STEP(R)                                                                     \
     {                                                                                     \
-        if (p.dump != nullptr && row >= 0) {                                              \
+        if (DBG && p.dump != nullptr && row >= 0) {                                       \
             _Pragma("unroll") for (int j = 0; j < 32; j++)                                \
-                if (c + j < nv) p.dump[row * p.dump_ld + tcol0 + c + j] = __uint_as_float(R[j]); \
+                if (c + j < nv) p.dump[row * p.dump_ld + tcol0 + c + j] = dump_mul * __uint_as_float(R[j]); \
         }                                                                                 \
         if (FILTER) epi_filter32(R, tcol0 + c, nv - c, thr, *fs);                         \
-        else epi_step32(R, tcol0 + c, nv - c, est, p.exp);                                \
+        else epi_step32(R, tcol0 + c, nv - c, est, exp);                                  \
     }
     while (c < c_end) {
         tmem_ld_wait();
@@ -460,6 +493,40 @@ __device__ __forceinline__ void epi_tile(uint32_t taddr, int c_lo, int c_hi, int
         c += 32;
     }
 #undef VQ_TC_STEP
+}
+
+// Full tile of NCOLS codewords, search mode: fully unrolled (constant TMEM offsets, no
+// per-step checks).  The accumulator is handed back to the MMA warp (release_bar) as soon as
+// its last columns are in registers, before they are reduced.
+template <int NCOLS>
+__device__ __forceinline__ void epi_tile_full(uint32_t taddr, int tcol0, EpiState &est,
+                                              uint64_t *release_bar) {
+    constexpr int NS = NCOLS / 32;
+    uint32_t ra[32], rb[32];
+    tmem_ld32(taddr, ra);
+#pragma unroll
+    for (int s = 0; s < NS; s += 2) {
+        tmem_ld_wait();
+        if (s + 1 < NS) {
+            tmem_ld32(taddr + 32 * (s + 1), rb);
+        } else {
+            tc_fence_before();
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) mbar_arrive(release_bar);
+        }
+        epi_step32(ra, tcol0 + 32 * s, 32, est, 0);
+        if (s + 1 < NS) {
+            tmem_ld_wait();
+            if (s + 2 < NS) {
+                tmem_ld32(taddr + 32 * (s + 2), ra);
+            } else {
+                tc_fence_before();
+                __syncwarp();
+                if ((threadIdx.x & 31) == 0) mbar_arrive(release_bar);
+            }
+            epi_step32(rb, tcol0 + 32 * (s + 1), 32, est, 0);
+        }
+    }
 }
 
 __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
@@ -669,7 +736,7 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
                 mbar_wait(&sm->tmem_full[acc], (tc >> 1) & 1);
                 tc_fence_after();
                 const int nv = K - t * BN < BN ? K - t * BN : BN;   // valid codewords in this tile
-                epi_tile<false>(lane_addr + acc * 256, c_lo * 16, c_hi * 16, t * BN, nv, est, p, row);
+                epi_tile<false, true>(lane_addr + acc * 256, c_lo * 16, c_hi * 16, t * BN, nv, est, p, row);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm->tmem_empty[acc]);
@@ -734,7 +801,8 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
 // Global codeword layout (vq_prepare_codebook_tc2): [tile][hi, lo][k-chunk][row][4 floats].
 // =====================================================================================
 namespace {
-constexpr int k2Threads = 480;
+constexpr int k2Threads = 512;      // 4 warpgroups (setmaxnreg is per warpgroup); warp 15 idles
+constexpr int kEpiRegs = 168, kLoaderRegs = 96, kRoleRegs = 80;   // 256*168 + 128*96 + 128*80 = 65536
 constexpr int kB2Stages = 3;
 
 struct Tc2Smem {
@@ -746,20 +814,25 @@ struct Tc2Smem {
 };
 }  // namespace
 
-template <int KS, bool FILTER>
+template <int KS, bool FILTER, bool DBG, bool H16>
 __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) {
+    const int exp = DBG ? p.exp : 0;
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     Tc2Smem *sm = reinterpret_cast<Tc2Smem *>(smem_raw);
     float *s_x0 = reinterpret_cast<float *>(smem_raw + 1024);      // [4 slots][2 halves][128]
     const int D = p.D;
     const int BN = p.BN;
-    constexpr int KC = 2 * KS;
+    constexpr int KC = 2 * KS;                                       // 16-byte k-chunks per row
+    constexpr int EPC = H16 ? 8 : 4;                                 // elements per chunk
+    constexpr int NE = KC * EPC;                                     // padded row length
+    constexpr uint32_t hdr_bytes = H16 ? 9216 : 5120;                // + per-frame scales (FP16 format)
+    float *s_scale = reinterpret_cast<float *>(smem_raw + 5120);     // [4 slots][2 halves][128], H16 only
     constexpr uint32_t a_part_bytes = (uint32_t) KC * kBM * 16;      // hi or lo of one half
     constexpr uint32_t a_half_bytes = 2 * a_part_bytes;
     const uint32_t raw_bytes = (uint32_t) kBM * D * 4;               // 128 rows
     const uint32_t raw_stride = (raw_bytes + 127u) & ~127u;
-    float *raw_base = reinterpret_cast<float *>(smem_raw + 5120);
-    unsigned char *a_base = smem_raw + 5120 + raw_stride;
+    float *raw_base = reinterpret_cast<float *>(smem_raw + hdr_bytes);
+    unsigned char *a_base = smem_raw + hdr_bytes + raw_stride;
     const uint32_t tile_bytes = (uint32_t) 2 * KC * BN * 16;
     unsigned char *b_base = a_base + 2 * a_half_bytes;
 
@@ -793,6 +866,11 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
     tc_fence_after();
     const uint32_t tmem_base = sm->tmem_slot;
 
+    // register budget by role (warpgroups of 4 warps): the epilogue holds two 32-column
+    // TMEM loads, the snapshot chunk and its state in registers
+    if (warp >= 12) {
+        setmaxnreg_dec<kRoleRegs>();
+    }
     if (warp == 12) {
         // ===== codeword tile producer =====
         if (lane == 0) {
@@ -800,8 +878,8 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x) {
                 const unsigned char *src = reinterpret_cast<const unsigned char *>(p.wtc);
                 for (int t = 0; t < n_wtiles; t++) {
-                    mbar_wait(&sm->b_empty[st], ph ^ 1);
-                    if (p.exp & 32) {
+                    mbar_wait_relaxed(&sm->b_empty[st], ph ^ 1);
+                    if (exp & 32) {
                         mbar_arrive(&sm->b_full[st]);
                     } else {
                         mbar_expect_tx(&sm->b_full[st], tile_bytes);
@@ -814,13 +892,13 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         }
     } else if (warp == 14) {
         // ===== raw frame producer (full, contiguous halves only) =====
-        if (lane == 0 && p.list == nullptr && !(p.exp & 64)) {
+        if (lane == 0 && p.list == nullptr && !(exp & 64)) {
             uint32_t rs = 0;   // staged halves so far
             for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x) {
                 for (int h = 0; h < 2; h++) {
                     const long base = ft * (2 * kBM) + h * kBM;
                     if (base + kBM > total) continue;
-                    mbar_wait(&sm->raw_empty, (rs & 1) ^ 1);
+                    mbar_wait_relaxed(&sm->raw_empty, (rs & 1) ^ 1);
                     mbar_expect_tx(&sm->raw_full, raw_bytes);
                     bulk_g2s(raw_base, p.x + base * D, raw_bytes, &sm->raw_full);
                     rs++;
@@ -831,7 +909,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         // ===== MMA issuer =====
         // The whole warp runs the loop (uniform control flow keeps descriptors in uniform
         // registers); one elected lane issues the MMAs and their commits.
-        const uint32_t idesc = umma_idesc_tf32(kBM, BN);
+        const uint32_t idesc = H16 ? umma_idesc_f16(kBM, BN) : umma_idesc_tf32(kBM, BN);
         // descriptor of (half 0, hi, k-step 0) / (stage 0, hi, k-step 0); the start-address
         // field counts 16-byte units, so other operands are reached by adding bytes >> 4
         const uint64_t dA0 = umma_desc(s32(a_base), kBM * 16, 128);
@@ -854,16 +932,22 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                     const uint32_t d_tmem = tmem_base + (2 * buf + h) * 128;
                     if (elect_one()) {
                         // small cross terms first, the dominant hi*hi products last
-                        if (!(p.exp & 8)) {
+                        if (!(exp & 8)) {
+#define VQ_UMMA(D_, A_, B_, ACC_)                                  \
+    do {                                                           \
+        if (H16) umma_f16(D_, A_, B_, idesc, ACC_);                \
+        else umma_tf32(D_, A_, B_, idesc, ACC_);                   \
+    } while (0)
 #pragma unroll
                             for (int s = 0; s < KS; s++)
-                                umma_tf32(d_tmem, dal + s * a_k16, dbh + s * b_k16, idesc, s > 0);
+                                VQ_UMMA(d_tmem, dal + s * a_k16, dbh + s * b_k16, s > 0);
 #pragma unroll
                             for (int s = 0; s < KS; s++)
-                                umma_tf32(d_tmem, dah + s * a_k16, dbl + s * b_k16, idesc, 1);
+                                VQ_UMMA(d_tmem, dah + s * a_k16, dbl + s * b_k16, 1);
 #pragma unroll
                             for (int s = 0; s < KS; s++)
-                                umma_tf32(d_tmem, dah + s * a_k16, dbh + s * b_k16, idesc, 1);
+                                VQ_UMMA(d_tmem, dah + s * a_k16, dbh + s * b_k16, 1);
+#undef VQ_UMMA
                         }
                         umma_commit(&sm->acc_full[2 * buf + h]);
                         if (t == n_wtiles - 1) umma_commit(&sm->a_free[h]);
@@ -876,25 +960,26 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         }
     } else if (warp < 4) {
         // ===== frame loaders: thread = frame row =====
+        setmaxnreg_dec<kLoaderRegs>();
         const int r = warp * 32 + lane;
         uint32_t it = 0, rs = 0;
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
             for (int h = 0; h < 2; h++) {
                 const long base = ft * (2 * kBM) + h * kBM;
-                const bool staged = p.list == nullptr && base + kBM <= total && !(p.exp & 64);
-                float v[8 * KS];
+                const bool staged = p.list == nullptr && base + kBM <= total && !(exp & 64);
+                float v[NE];
                 if (staged) {
-                    mbar_wait(&sm->raw_full, rs & 1);
+                    mbar_wait_relaxed(&sm->raw_full, rs & 1);
                     rs++;
                     const float *src = raw_base + r * D;
 #pragma unroll
-                    for (int k = 0; k < 8 * KS; k++) v[k] = k < D ? src[k] : 0.f;
+                    for (int k = 0; k < NE; k++) v[k] = k < D ? src[k] : 0.f;
                     // the staging buffer may be overwritten as soon as raw_empty completes: the
                     // arrive must not be issued before every lane's loads have RETURNED, so it is
                     // made data dependent on all of them (a vote over a value built from them)
                     uint32_t dep = 0;
 #pragma unroll
-                    for (int k = 0; k < 8 * KS; k++) dep ^= __float_as_uint(v[k]);
+                    for (int k = 0; k < NE; k++) dep ^= __float_as_uint(v[k]);
                     fence_proxy_async();   // generic reads before the async-proxy overwrite
                     const uint32_t all_in = __all_sync(0xffffffffu, dep != 0x7fc12345u);
                     if (lane == 0) mbar_arrive_dep(&sm->raw_empty, all_in);
@@ -903,26 +988,62 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                     const long row = valid ? (p.list ? (long) p.list[base + r] : base + r) : 0;
                     const float *src = p.x + row * D;
 #pragma unroll
-                    for (int k = 0; k < 8 * KS; k++) v[k] = (valid && k < D) ? __ldg(src + k) : 0.f;
+                    for (int k = 0; k < NE; k++) v[k] = (valid && k < D) ? __ldg(src + k) : 0.f;
                 }
-                const float x0 = fabsf(v[0]);
-                // slot D carries -e |x0|; with W1_j in the codeword's slot D the accumulator
-                // becomes the lower bound d~_ij - e |x0| W1_j
+                // reference magnitude of the error bound: |rx[0]| (TF32 format, values unscaled),
+                // or max_k |x[k]| after the frame was scaled by a power of two into [2^14, 2^15)
+                // (FP16 format: both split parts then stay inside the FP16 range, and the
+                // argmin of a frame does not depend on its own positive scale)
+                float x0 = fabsf(v[0]);
+                if (H16) {
+                    float xm = 0.f;
 #pragma unroll
-                for (int k = 0; k < 8 * KS; k++)
+                    for (int k = 0; k < NE; k++) xm = fmaxf(xm, fabsf(v[k]));
+                    uint32_t ef = (__float_as_uint(xm) >> 23) & 0xffu;
+                    ef = ef < 16u ? 16u : ef;
+                    const float scale = __uint_as_float((268u - ef) << 23);   // 2^(14 - floor(log2 xm))
+#pragma unroll
+                    for (int k = 0; k < NE; k++) v[k] *= scale;
+                    x0 = xm * scale;
+                    if (DBG) s_scale[((it & 3) * 2 + h) * kBM + r] = scale;
+                }
+                // slot D carries -e x0; with W1_j in the codeword's slot D the accumulator
+                // becomes the lower bound d~_ij - e x0 W1_j
+#pragma unroll
+                for (int k = 0; k < NE; k++)
                     if (k == D) v[k] = -1.001f * p.err_scale * x0;
-                mbar_wait(&sm->a_free[h], (it & 1) ^ 1);
+                mbar_wait_relaxed(&sm->a_free[h], (it & 1) ^ 1);
                 unsigned char *hi = a_base + (size_t) h * a_half_bytes;
                 unsigned char *lo = hi + a_part_bytes;
+                if (H16) {
 #pragma unroll
-                for (int c = 0; c < KC; c++) {
-                    float4 hv, lv;
-                    hv.x = tf32_rna(v[4 * c + 0]); hv.y = tf32_rna(v[4 * c + 1]);
-                    hv.z = tf32_rna(v[4 * c + 2]); hv.w = tf32_rna(v[4 * c + 3]);
-                    lv.x = tf32_rna(v[4 * c + 0] - hv.x); lv.y = tf32_rna(v[4 * c + 1] - hv.y);
-                    lv.z = tf32_rna(v[4 * c + 2] - hv.z); lv.w = tf32_rna(v[4 * c + 3] - hv.w);
-                    *reinterpret_cast<float4 *>(hi + ((size_t) c * kBM + r) * 16) = hv;
-                    *reinterpret_cast<float4 *>(lo + ((size_t) c * kBM + r) * 16) = lv;
+                    for (int c = 0; c < KC; c++) {
+                        uint32_t hw[4], lw[4];
+#pragma unroll
+                        for (int e = 0; e < 4; e++) {
+                            const float a = v[8 * c + 2 * e], b2 = v[8 * c + 2 * e + 1];
+                            const __half2 hh = __floats2half2_rn(a, b2);
+                            const float2 hf = __half22float2(hh);
+                            const __half2 ll = __floats2half2_rn(a - hf.x, b2 - hf.y);
+                            hw[e] = *reinterpret_cast<const uint32_t *>(&hh);
+                            lw[e] = *reinterpret_cast<const uint32_t *>(&ll);
+                        }
+                        *reinterpret_cast<uint4 *>(hi + ((size_t) c * kBM + r) * 16) =
+                            make_uint4(hw[0], hw[1], hw[2], hw[3]);
+                        *reinterpret_cast<uint4 *>(lo + ((size_t) c * kBM + r) * 16) =
+                            make_uint4(lw[0], lw[1], lw[2], lw[3]);
+                    }
+                } else {
+#pragma unroll
+                    for (int c = 0; c < KC; c++) {
+                        float4 hv, lv;
+                        hv.x = tf32_rna(v[4 * c + 0]); hv.y = tf32_rna(v[4 * c + 1]);
+                        hv.z = tf32_rna(v[4 * c + 2]); hv.w = tf32_rna(v[4 * c + 3]);
+                        lv.x = tf32_rna(v[4 * c + 0] - hv.x); lv.y = tf32_rna(v[4 * c + 1] - hv.y);
+                        lv.z = tf32_rna(v[4 * c + 2] - hv.z); lv.w = tf32_rna(v[4 * c + 3] - hv.w);
+                        *reinterpret_cast<float4 *>(hi + ((size_t) c * kBM + r) * 16) = hv;
+                        *reinterpret_cast<float4 *>(lo + ((size_t) c * kBM + r) * 16) = lv;
+                    }
                 }
                 s_x0[((it & 3) * 2 + h) * kBM + r] = x0;
                 fence_proxy_async();
@@ -932,6 +1053,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         }
     } else if (warp < 12) {
         // ===== epilogue: thread = frame (TMEM lane), registers = codewords =====
+        setmaxnreg_inc<kEpiRegs>();
         const int q = warp & 3;
         const int h = (warp - 4) >> 2;
         const int r = q * 32 + lane;
@@ -952,10 +1074,19 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 mbar_wait(&sm->acc_full[2 * buf + h], (u >> 1) & 1);
                 tc_fence_after();
                 const int nv = K - t * BN < BN ? K - t * BN : BN;
-                epi_tile<FILTER>(lane_addr + (2 * buf + h) * 128, 0, BN, t * BN, nv, est, p, row, thr, &fst);
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&sm->acc_empty[2 * buf + h]);
+                const uint32_t taddr = lane_addr + (2 * buf + h) * 128;
+                if (!FILTER && !DBG && nv == 128) {
+                    epi_tile_full<128>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
+                } else if (!FILTER && !DBG && nv == 64) {
+                    epi_tile_full<64>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
+                } else {
+                    float dump_mul = 1.f;   // debug dump in the caller's units
+                    if (DBG && H16) dump_mul = 1.f / (s_scale[((it & 3) * 2 + h) * kBM + r] * *p.wscale);
+                    epi_tile<FILTER, DBG>(taddr, 0, BN, t * BN, nv, est, p, row, thr, &fst, dump_mul);
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&sm->acc_empty[2 * buf + h]);
+                }
             }
             if (FILTER) {
                 epi_filter_flush(fst, (int) (base + r), row, p);
@@ -964,9 +1095,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             float best = est.best, second;
             int bidx;
             epi_finish(est, second, bidx);
+            if (DBG && exp) bidx = (unsigned) bidx < (unsigned) K ? bidx : 0;   // experiments leave it undefined
             if (row >= 0) {
                 p.idx_out[row] = bidx;
-                if (p.flag_list != nullptr) {
+                if (p.flag_list != nullptr && !(exp & 128)) {
                     // accumulator = lower bound L_ij = d~_ij - e |x0| W1_j of the true distortion;
                     // bidx is certainly the true argmin when every other lower bound exceeds its
                     // upper bound L + 2 e |x0| W1.  NaN-safe.
@@ -1027,6 +1159,62 @@ __global__ void vq_prepare_codebook_tc2(const double *__restrict__ raas, int K, 
     }
 }
 
+// FP16 format: raas f64 [K][D] -> tiles [tile][hi, lo][k-chunk][row][8 halves] of the codebook
+// scaled by G = 2^g, g chosen from *w1max so that every scaled W1_j is below 2^14 (both split
+// parts of every element then stay inside the FP16 range).  Slot D and w1h[j] carry
+//     W1'_j = G W1_j + D 2^-25 / err_scale
+// -- the second term covers the absolute error 2^-25 of a scaled codeword element whose low
+// part is an FP16 subnormal (sum over k of |x_k| 2^-25 <= x_ref D 2^-25 = err_scale x_ref times
+// that term).  w1h[n_wtiles BN] = G (debug dump, to return values in the caller's units).
+__global__ void vq_prepare_codebook_tc2h(const double *__restrict__ raas, int K, int D, int BN,
+                                         int ksteps, const float *__restrict__ w1max,
+                                         float err_scale, float *__restrict__ wtc,
+                                         float *__restrict__ w1h) {
+    const int KC = 2 * ksteps;
+    const int n_wtiles = (K + BN - 1) / BN;
+    const long items = (long) n_wtiles * KC * BN;   // (t, c, r)
+    uint32_t ef = (__float_as_uint(*w1max) >> 23) & 0xffu;
+    ef = ef < 14u ? 14u : (ef > 253u ? 253u : ef);
+    const double G = (double) __uint_as_float((267u - ef) << 23);   // G w1max in [2^13, 2^14)
+    const double extra = (double) D * 2.98023223876953125e-8 / (double) err_scale;
+    if (blockIdx.x == 0 && threadIdx.x == 0) w1h[(long) n_wtiles * BN] = (float) G;
+    for (long it = (long) blockIdx.x * blockDim.x + threadIdx.x; it < items;
+         it += (long) gridDim.x * blockDim.x) {
+        const int r = (int) (it % BN);
+        const int c = (int) ((it / BN) % KC);
+        const int t = (int) (it / ((long) BN * KC));
+        const int cw = t * BN + r;
+        __half hp[8], lp[8];
+#pragma unroll
+        for (int e = 0; e < 8; e++) { hp[e] = __float2half_rn(0.f); lp[e] = hp[e]; }
+        if (cw < K) {
+#pragma unroll
+            for (int e = 0; e < 8; e++) {
+                const int k = 8 * c + e;
+                if (k <= D) {
+                    double w;
+                    if (k < D) {
+                        w = G * (k > 0 ? 2.0 * raas[(long) cw * D + k] : raas[(long) cw * D]);
+                    } else {   // slot D: W1'
+                        w = fabs(raas[(long) cw * D]);
+                        for (int n = 1; n < D; n++) w += 2.0 * fabs(raas[(long) cw * D + n]);
+                        w = (G * w + extra) * (1.0 + 1e-6);
+                        if (c == D / 8) w1h[cw] = (float) (w * (1.0 + 1e-6));
+                    }
+                    const __half hi = __float2half_rn((float) w);
+                    hp[e] = hi;
+                    lp[e] = __float2half_rn((float) (w - (double) __half2float(hi)));
+                }
+            }
+        } else if (c == D / 8) {
+            w1h[cw] = 0.f;
+        }
+        unsigned char *tile = reinterpret_cast<unsigned char *>(wtc) + (size_t) t * (2 * KC * BN * 16);
+        *reinterpret_cast<uint4 *>(tile + ((size_t) c * BN + r) * 16) = *reinterpret_cast<const uint4 *>(hp);
+        *reinterpret_cast<uint4 *>(tile + ((size_t) (KC + c) * BN + r) * 16) = *reinterpret_cast<const uint4 *>(lp);
+    }
+}
+
 // raas f64 [K][D] -> stages [tile][k-step][hi, lo][k-chunk][row][4]  (zero padded)
 __global__ void vq_prepare_codebook_tc(const double *__restrict__ raas, int K, int D, int BN,
                                        int ksteps, float *__restrict__ wtc) {
@@ -1066,8 +1254,6 @@ __global__ void vq_prepare_codebook_tc(const double *__restrict__ raas, int K, i
     }
 }
 
-static int tc_ksteps(int D) { return (D + 8) / 8; }   // D elements + the bound slot
-
 // ECOZ2_VQ_TC_VARIANT=1: both operands from shared memory (first version, kept for A/B runs);
 // default 2: frame operand in tensor memory.
 static int tc_variant() {
@@ -1079,24 +1265,62 @@ static int tc_variant() {
     return v;
 }
 
+// Operand format of variant 2 (ECOZ2_VQ_TC_FMT=tf32 | f16, default f16): the same 22-bit
+// two-way split either as TF32 parts (8 elements per MMA) or as FP16 parts of power-of-two
+// scaled operands (16 elements per MMA at the same shared-memory bytes: fewer MMAs per tile).
+static bool tc_f16() {
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("ECOZ2_VQ_TC_FMT");
+        v = (tc_variant() == 2 && !(e && e[0] == 't')) ? 1 : 0;
+    }
+    return v == 1;
+}
+// k-steps (MMAs per product term): D elements + the bound slot
+static int tc_ksteps(int D) { return tc_f16() ? (D + 16) / 16 : (D + 8) / 8; }
+static int tc_max_ksteps() { return tc_f16() ? 3 : kMaxKSteps; }
+
+// smallest codebook the tensor-core search takes (ECOZ2_VQ_TC_MIN_K, default 2: a 64-column
+// tile that is mostly padding still beats the FP64 sweep of vq_pass_small)
+static int tc_min_k() {
+    static int v = 0;
+    if (v == 0) {
+        const char *e = getenv("ECOZ2_VQ_TC_MIN_K");
+        v = e ? atoi(e) : 2;
+        if (v < 1) v = 1;
+    }
+    return v;
+}
+
 int tc_tile_cols(int K) {
     if (tc_variant() == 2) return K >= 128 ? 128 : 64;
     return K >= 256 ? 256 : (K > 64 ? 128 : 64);
 }
 
-bool assign_tc_supported(int K, int D) { return K >= 64 && tc_ksteps(D) <= kMaxKSteps; }
+bool assign_tc_supported(int K, int D) { return K >= tc_min_k() && tc_ksteps(D) <= tc_max_ksteps(); }
 
-size_t tc_codebook_floats(int K, int D) {
+// floats of the tiles themselves: n_wtiles x [hi, lo] x (2 ksteps chunks) x BN rows x 16 bytes
+static size_t tc_tiles_floats(int K, int D) {
     const int BN = tc_tile_cols(K);
     const int n_wtiles = (K + BN - 1) / BN;
     return (size_t) n_wtiles * tc_ksteps(D) * 4 * BN * 4;
 }
+// + (FP16 format) the scaled bound weights W1'_j per padded codeword and the scale G
+size_t tc_codebook_floats(int K, int D) {
+    const int BN = tc_tile_cols(K);
+    const int n_wtiles = (K + BN - 1) / BN;
+    return tc_tiles_floats(K, D) + (size_t) n_wtiles * BN + 4;
+}
 
-void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, cudaStream_t s) {
+void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, const float *w1max,
+                                float err_scale, cudaStream_t s) {
     const int BN = tc_tile_cols(K), ksteps = tc_ksteps(D);
     const long items = (long) ((K + BN - 1) / BN) * ksteps * 2 * BN;
     const int blocks = (int) ((items + 255) / 256);
-    if (tc_variant() == 2)
+    if (tc_f16())
+        vq_prepare_codebook_tc2h<<<blocks, 256, 0, s>>>(raas, K, D, BN, ksteps, w1max, err_scale, wtc,
+                                                       wtc + tc_tiles_floats(K, D));
+    else if (tc_variant() == 2)
         vq_prepare_codebook_tc2<<<blocks, 256, 0, s>>>(raas, K, D, BN, ksteps, wtc);
     else
         vq_prepare_codebook_tc<<<blocks, 256, 0, s>>>(raas, K, D, BN, ksteps, wtc);
@@ -1110,23 +1334,47 @@ static size_t tc_smem_bytes(int D, int BN) {
 static size_t tc2_smem_bytes(int D, int BN) {
     const size_t raw_stride = ((size_t) kBM * D * 4 + 127) & ~(size_t) 127;
     const size_t KC = 2 * (size_t) tc_ksteps(D);
-    return 5120 + raw_stride + 2 * (2 * KC * kBM * 16) + (size_t) kB2Stages * 2 * KC * BN * 16;
+    return (tc_f16() ? 9216 : 5120) + raw_stride + 2 * (2 * KC * kBM * 16) +
+           (size_t) kB2Stages * 2 * KC * BN * 16;
 }
 
-template <int KS, bool FILTER>
+template <int KS, bool FILTER, bool DBG, bool H16>
 static void launch_tc2_inst2(const TcParams &p, long grid, cudaStream_t s) {
     static bool attr_set = false;
     if (!attr_set) {
-        cudaFuncSetAttribute(vq_assign_tc2<KS, FILTER>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                             227 * 1024);
+        cudaFuncSetAttribute(vq_assign_tc2<KS, FILTER, DBG, H16>,
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         attr_set = true;
     }
-    vq_assign_tc2<KS, FILTER><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN), s>>>(p);
+    vq_assign_tc2<KS, FILTER, DBG, H16><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN), s>>>(p);
 }
-template <int KS>
+template <int KS, bool H16>
 static void launch_tc2_inst(const TcParams &p, long grid, cudaStream_t s) {
-    if (p.cand != nullptr) launch_tc2_inst2<KS, true>(p, grid, s);
-    else launch_tc2_inst2<KS, false>(p, grid, s);
+    if (p.cand != nullptr) launch_tc2_inst2<KS, true, false, H16>(p, grid, s);
+    else if (p.exp != 0 || p.dump != nullptr) launch_tc2_inst2<KS, false, true, H16>(p, grid, s);
+    else launch_tc2_inst2<KS, false, false, H16>(p, grid, s);
+}
+// variant 2, any supported (format, k-steps)
+static void launch_tc2(TcParams &p, long grid, cudaStream_t s) {
+    if (tc_f16()) {
+        // the bound weights and the scale live behind the tiles (vq_prepare_codebook_tc2h)
+        const float *w1h = p.wtc + tc_tiles_floats(p.K, p.D);
+        p.w1 = w1h;
+        p.wscale = w1h + (size_t) ((p.K + p.BN - 1) / p.BN) * p.BN;
+        switch (p.ksteps) {
+            case 1: launch_tc2_inst<1, true>(p, grid, s); break;
+            case 2: launch_tc2_inst<2, true>(p, grid, s); break;
+            default: launch_tc2_inst<3, true>(p, grid, s); break;
+        }
+        return;
+    }
+    switch (p.ksteps) {
+        case 1: launch_tc2_inst<1, false>(p, grid, s); break;
+        case 2: launch_tc2_inst<2, false>(p, grid, s); break;
+        case 3: launch_tc2_inst<3, false>(p, grid, s); break;
+        case 4: launch_tc2_inst<4, false>(p, grid, s); break;
+        default: launch_tc2_inst<5, false>(p, grid, s); break;
+    }
 }
 
 void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
@@ -1152,13 +1400,7 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
     if (tc_variant() == 2) {
         long tiles = (n + 2 * kBM - 1) / (2 * kBM);
         long grid = tiles < num_sms ? tiles : num_sms;
-        switch (p.ksteps) {
-            case 1: launch_tc2_inst<1>(p, grid, s); break;
-            case 2: launch_tc2_inst<2>(p, grid, s); break;
-            case 3: launch_tc2_inst<3>(p, grid, s); break;
-            case 4: launch_tc2_inst<4>(p, grid, s); break;
-            default: launch_tc2_inst<5>(p, grid, s); break;
-        }
+        launch_tc2(p, grid, s);
         return;
     }
     const size_t smem = tc_smem_bytes(D, p.BN);
@@ -1210,13 +1452,7 @@ void launch_filter_tc(const float *x32, long n_cap, int D, const float *wtc, int
     // device-side count: persistent grid sized for the worst case
     long tiles = (n_cap + 2 * kBM - 1) / (2 * kBM);
     long grid = tiles < num_sms ? tiles : num_sms;
-    switch (p.ksteps) {
-        case 1: launch_tc2_inst<1>(p, grid, s); break;
-        case 2: launch_tc2_inst<2>(p, grid, s); break;
-        case 3: launch_tc2_inst<3>(p, grid, s); break;
-        case 4: launch_tc2_inst<4>(p, grid, s); break;
-        default: launch_tc2_inst<5>(p, grid, s); break;
-    }
+    launch_tc2(p, grid, s);
 }
 
 }  // namespace vqb200
