@@ -808,7 +808,7 @@ constexpr int kB2Stages = 3;
 struct Tc2Smem {
     uint64_t b_full[kB2Stages], b_empty[kB2Stages];
     uint64_t raw_full, raw_empty;
-    uint64_t a_full[2], a_free[2];
+    uint64_t a_full[4], a_free[4];        // [2 * frame-tile buffer + half]
     uint64_t acc_full[4], acc_empty[4];   // [2 * buffer + half]
     uint32_t tmem_slot;
 };
@@ -822,7 +822,14 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
     float *s_x0 = reinterpret_cast<float *>(smem_raw + 1024);      // [4 slots][2 halves][128]
     const int D = p.D;
     const int BN = p.BN;
-    constexpr int KC = 2 * KS;                                       // 16-byte k-chunks per row
+    // KS = MMAs per product term (TF32 format, 8 elements each) or 8-element chunks per split
+    // part (FP16 format); either way a part of a row is KC 16-byte chunks
+    constexpr int KC = H16 ? KS : 2 * KS;
+    // FP16 format: a row is [hi: KC chunks][lo: KC chunks], a codeword row [lo][hi][zero chunk if
+    // KC is odd].  The two cross terms are ONE product over the concatenated 2 KC chunks
+    // ([xh|xl] . [wl|wh]), the main term pairs chunks (2s, 2s+1) of [xh|xl..] with [wh|0]:
+    // KC + ceil(KC/2) MMAs of 16 elements instead of 3 ceil(KC/2).
+    constexpr int BC = H16 ? 2 * KC + (KC & 1) : 2 * KC;             // chunks per codeword row
     constexpr int EPC = H16 ? 8 : 4;                                 // elements per chunk
     constexpr int NE = KC * EPC;                                     // padded row length
     constexpr uint32_t hdr_bytes = H16 ? 9216 : 5120;                // + per-frame scales (FP16 format)
@@ -833,8 +840,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
     const uint32_t raw_stride = (raw_bytes + 127u) & ~127u;
     float *raw_base = reinterpret_cast<float *>(smem_raw + hdr_bytes);
     unsigned char *a_base = smem_raw + hdr_bytes + raw_stride;
-    const uint32_t tile_bytes = (uint32_t) 2 * KC * BN * 16;
-    unsigned char *b_base = a_base + 2 * a_half_bytes;
+    const uint32_t tile_bytes = (uint32_t) BC * BN * 16;
+    // the FP16 format leaves room for two frame tiles: the loaders run a whole tile ahead
+    constexpr int ABUF = H16 ? 2 : 1;
+    unsigned char *b_base = a_base + ABUF * 2 * a_half_bytes;
 
     const int tid = threadIdx.x;
     const int warp = tid >> 5, lane = tid & 31;
@@ -850,7 +859,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         }
         mbar_init(&sm->raw_full, 1);
         mbar_init(&sm->raw_empty, 4);
-        for (int i = 0; i < 2; i++) {
+        for (int i = 0; i < 4; i++) {
             mbar_init(&sm->a_full[i], 4);
             mbar_init(&sm->a_free[i], 1);
         }
@@ -923,11 +932,12 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             for (int t = 0; t < n_wtiles; t++, u++) {
                 const uint32_t buf = u & 1;
                 for (int h = 0; h < 2; h++) {
-                    if (t == 0) mbar_wait(&sm->a_full[h], it & 1);
+                    const uint32_t ab = ABUF == 2 ? (it & 1) : 0, aph = ABUF == 2 ? (it >> 1) & 1 : it & 1;
+                    if (t == 0) mbar_wait(&sm->a_full[2 * ab + h], aph);
                     mbar_wait(&sm->acc_empty[2 * buf + h], ((u >> 1) & 1) ^ 1);
                     if (h == 0) mbar_wait(&sm->b_full[st], ph);
                     tc_fence_after();
-                    const uint64_t dah = dA0 + (uint32_t) h * a_half16, dal = dah + a_part16;
+                    const uint64_t dah = dA0 + (uint32_t) (2 * ab + h) * a_half16, dal = dah + a_part16;
                     const uint64_t dbh = dB0 + st * b_tile16, dbl = dbh + b_part16;
                     const uint32_t d_tmem = tmem_base + (2 * buf + h) * 128;
                     if (elect_one()) {
@@ -938,19 +948,29 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         if (H16) umma_f16(D_, A_, B_, idesc, ACC_);                \
         else umma_tf32(D_, A_, B_, idesc, ACC_);                   \
     } while (0)
+                            if (H16) {
+                                // dah = [xh|xl] of this half, dbh = [wl|wh|0] of this tile
 #pragma unroll
-                            for (int s = 0; s < KS; s++)
-                                VQ_UMMA(d_tmem, dal + s * a_k16, dbh + s * b_k16, s > 0);
+                                for (int s = 0; s < KC; s++)
+                                    VQ_UMMA(d_tmem, dah + s * a_k16, dbh + s * b_k16, s > 0);
 #pragma unroll
-                            for (int s = 0; s < KS; s++)
-                                VQ_UMMA(d_tmem, dah + s * a_k16, dbl + s * b_k16, 1);
+                                for (int s = 0; s < (KC + 1) / 2; s++)
+                                    VQ_UMMA(d_tmem, dah + s * a_k16, dbl + s * b_k16, 1);
+                            } else {
 #pragma unroll
-                            for (int s = 0; s < KS; s++)
-                                VQ_UMMA(d_tmem, dah + s * a_k16, dbh + s * b_k16, 1);
+                                for (int s = 0; s < KS; s++)
+                                    VQ_UMMA(d_tmem, dal + s * a_k16, dbh + s * b_k16, s > 0);
+#pragma unroll
+                                for (int s = 0; s < KS; s++)
+                                    VQ_UMMA(d_tmem, dah + s * a_k16, dbl + s * b_k16, 1);
+#pragma unroll
+                                for (int s = 0; s < KS; s++)
+                                    VQ_UMMA(d_tmem, dah + s * a_k16, dbh + s * b_k16, 1);
+                            }
 #undef VQ_UMMA
                         }
                         umma_commit(&sm->acc_full[2 * buf + h]);
-                        if (t == n_wtiles - 1) umma_commit(&sm->a_free[h]);
+                        if (t == n_wtiles - 1) umma_commit(&sm->a_free[2 * ab + h]);
                         if (h == 1) umma_commit(&sm->b_empty[st]);
                     }
                     __syncwarp();
@@ -1012,8 +1032,9 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
 #pragma unroll
                 for (int k = 0; k < NE; k++)
                     if (k == D) v[k] = -1.001f * p.err_scale * x0;
-                mbar_wait_relaxed(&sm->a_free[h], (it & 1) ^ 1);
-                unsigned char *hi = a_base + (size_t) h * a_half_bytes;
+                const uint32_t ab = ABUF == 2 ? (it & 1) : 0, aph = ABUF == 2 ? (it >> 1) & 1 : it & 1;
+                mbar_wait_relaxed(&sm->a_free[2 * ab + h], aph ^ 1);
+                unsigned char *hi = a_base + (size_t) (2 * ab + h) * a_half_bytes;
                 unsigned char *lo = hi + a_part_bytes;
                 if (H16) {
 #pragma unroll
@@ -1048,7 +1069,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 s_x0[((it & 3) * 2 + h) * kBM + r] = x0;
                 fence_proxy_async();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&sm->a_full[h]);
+                if (lane == 0) mbar_arrive(&sm->a_full[2 * ab + h]);
             }
         }
     } else if (warp < 12) {
@@ -1075,9 +1096,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 tc_fence_after();
                 const int nv = K - t * BN < BN ? K - t * BN : BN;
                 const uint32_t taddr = lane_addr + (2 * buf + h) * 128;
-                if (!FILTER && !DBG && nv == 128) {
+                const bool fast = !FILTER && (!DBG || (!(exp & 7) && p.dump == nullptr));
+                if (fast && nv == 128) {
                     epi_tile_full<128>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
-                } else if (!FILTER && !DBG && nv == 64) {
+                } else if (fast && nv == 64) {
                     epi_tile_full<64>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
                 } else {
                     float dump_mul = 1.f;   // debug dump in the caller's units
@@ -1159,7 +1181,8 @@ __global__ void vq_prepare_codebook_tc2(const double *__restrict__ raas, int K, 
     }
 }
 
-// FP16 format: raas f64 [K][D] -> tiles [tile][hi, lo][k-chunk][row][8 halves] of the codebook
+// FP16 format: raas f64 [K][D] -> tiles [tile][lo: KC chunks | hi: KC chunks | zero chunk if KC
+// is odd][row][8 halves] (KC = `ksteps` = 8-element chunks per split part) of the codebook
 // scaled by G = 2^g, g chosen from *w1max so that every scaled W1_j is below 2^14 (both split
 // parts of every element then stay inside the FP16 range).  Slot D and w1h[j] carry
 //     W1'_j = G W1_j + D 2^-25 / err_scale
@@ -1170,7 +1193,8 @@ __global__ void vq_prepare_codebook_tc2h(const double *__restrict__ raas, int K,
                                          int ksteps, const float *__restrict__ w1max,
                                          float err_scale, float *__restrict__ wtc,
                                          float *__restrict__ w1h) {
-    const int KC = 2 * ksteps;
+    const int KC = ksteps;
+    const int BC = 2 * KC + (KC & 1);
     const int n_wtiles = (K + BN - 1) / BN;
     const long items = (long) n_wtiles * KC * BN;   // (t, c, r)
     uint32_t ef = (__float_as_uint(*w1max) >> 23) & 0xffu;
@@ -1209,9 +1233,11 @@ __global__ void vq_prepare_codebook_tc2h(const double *__restrict__ raas, int K,
         } else if (c == D / 8) {
             w1h[cw] = 0.f;
         }
-        unsigned char *tile = reinterpret_cast<unsigned char *>(wtc) + (size_t) t * (2 * KC * BN * 16);
-        *reinterpret_cast<uint4 *>(tile + ((size_t) c * BN + r) * 16) = *reinterpret_cast<const uint4 *>(hp);
-        *reinterpret_cast<uint4 *>(tile + ((size_t) (KC + c) * BN + r) * 16) = *reinterpret_cast<const uint4 *>(lp);
+        unsigned char *tile = reinterpret_cast<unsigned char *>(wtc) + (size_t) t * (BC * BN * 16);
+        *reinterpret_cast<uint4 *>(tile + ((size_t) c * BN + r) * 16) = *reinterpret_cast<const uint4 *>(lp);
+        *reinterpret_cast<uint4 *>(tile + ((size_t) (KC + c) * BN + r) * 16) = *reinterpret_cast<const uint4 *>(hp);
+        if ((KC & 1) && c == 0)
+            *reinterpret_cast<uint4 *>(tile + ((size_t) (2 * KC) * BN + r) * 16) = make_uint4(0u, 0u, 0u, 0u);
     }
 }
 
@@ -1276,9 +1302,15 @@ static bool tc_f16() {
     }
     return v == 1;
 }
-// k-steps (MMAs per product term): D elements + the bound slot
-static int tc_ksteps(int D) { return tc_f16() ? (D + 16) / 16 : (D + 8) / 8; }
-static int tc_max_ksteps() { return tc_f16() ? 3 : kMaxKSteps; }
+// D elements + the bound slot in groups of 8: MMAs per product term (TF32 format) or 16-byte
+// chunks per split part (FP16 format)
+static int tc_ksteps(int D) { return (D + 8) / 8; }
+static int tc_max_ksteps() { return tc_f16() ? 6 : kMaxKSteps; }
+// 16-byte chunks of one codeword row in a tile
+static int tc_row_chunks(int D) {
+    const int ks = tc_ksteps(D);
+    return tc_f16() ? 2 * ks + (ks & 1) : 4 * ks;
+}
 
 // smallest codebook the tensor-core search takes (ECOZ2_VQ_TC_MIN_K, default 2: a 64-column
 // tile that is mostly padding still beats the FP64 sweep of vq_pass_small)
@@ -1303,7 +1335,7 @@ bool assign_tc_supported(int K, int D) { return K >= tc_min_k() && tc_ksteps(D) 
 static size_t tc_tiles_floats(int K, int D) {
     const int BN = tc_tile_cols(K);
     const int n_wtiles = (K + BN - 1) / BN;
-    return (size_t) n_wtiles * tc_ksteps(D) * 4 * BN * 4;
+    return (size_t) n_wtiles * tc_row_chunks(D) * BN * 4;
 }
 // + (FP16 format) the scaled bound weights W1'_j per padded codeword and the scale G
 size_t tc_codebook_floats(int K, int D) {
@@ -1333,9 +1365,9 @@ static size_t tc_smem_bytes(int D, int BN) {
 }
 static size_t tc2_smem_bytes(int D, int BN) {
     const size_t raw_stride = ((size_t) kBM * D * 4 + 127) & ~(size_t) 127;
-    const size_t KC = 2 * (size_t) tc_ksteps(D);
-    return (tc_f16() ? 9216 : 5120) + raw_stride + 2 * (2 * KC * kBM * 16) +
-           (size_t) kB2Stages * 2 * KC * BN * 16;
+    const size_t KC = (tc_f16() ? 1 : 2) * (size_t) tc_ksteps(D);   // chunks per split part
+    return (tc_f16() ? 9216 : 5120) + raw_stride + (tc_f16() ? 2 : 1) * 2 * (2 * KC * kBM * 16) +
+           (size_t) kB2Stages * tc_row_chunks(D) * BN * 16;
 }
 
 template <int KS, bool FILTER, bool DBG, bool H16>
@@ -1364,7 +1396,10 @@ static void launch_tc2(TcParams &p, long grid, cudaStream_t s) {
         switch (p.ksteps) {
             case 1: launch_tc2_inst<1, true>(p, grid, s); break;
             case 2: launch_tc2_inst<2, true>(p, grid, s); break;
-            default: launch_tc2_inst<3, true>(p, grid, s); break;
+            case 3: launch_tc2_inst<3, true>(p, grid, s); break;
+            case 4: launch_tc2_inst<4, true>(p, grid, s); break;
+            case 5: launch_tc2_inst<5, true>(p, grid, s); break;
+            default: launch_tc2_inst<6, true>(p, grid, s); break;
         }
         return;
     }

@@ -56,7 +56,7 @@ def test_tc_values_within_bound(built_lib, frames36, oracle_run36, K):
 @pytest.mark.parametrize("P,K,N", [
     (36, 2, 3000), (36, 5, 1000), (36, 33, 2000), (12, 8, 4000),
     (36, 64, 127), (36, 64, 256), (36, 100, 1000), (36, 129, 4097), (36, 300, 777),
-    (36, 1000, 20000), (36, 2048, 9000), (12, 64, 5000), (12, 1024, 30000), (20, 200, 3000),
+    (36, 1000, 20000), (36, 2048, 9000), (12, 64, 5000), (12, 1024, 30000), (20, 200, 3000), (28, 300, 3000), (44, 500, 5000),
 ], ids=lambda v: str(v))
 def test_tc_assign_matches_oracle(built_lib, frames36, frames12, P, K, N):
     from ecoz2rs_b200 import vq
