@@ -405,22 +405,28 @@ def run_b200_arm(args):
         "fp32_ffma_peak_measured": ffma_peak,
     }
     if tc_mode:
-        # Split-TF32: every algorithmic FMA is 3 TF32 tensor FMAs (xl.wh + xh.wl + xh.wh) and the
-        # inner dimension is padded 37 -> 40.  Denominator = measured tensor peak / 3;
-        # MEASURED_PEAKS.json holds the cuBLAS bf16 figure, TF32 runs at half the bf16 rate.
+        # Two-way split operands: every algorithmic FMA is 3 tensor FMAs (xl.wh + xh.wl + xh.wh).
+        # Denominator = measured dense tensor peak of the operand type / 3;
+        # MEASURED_PEAKS.json holds the cuBLAS bf16 figure: FP16 parts run at that rate, TF32
+        # parts at half of it.  The padding of the inner dimension (37 + bound slot -> MMA
+        # granularity) is NOT credited: it shows in tensor_tflops_issued.
         peaks, src = measured_peaks()
+        issued_per_eval, fmt = vq.tc_issued_flops_per_eval(P)
+        rate = 1.0 if fmt == "f16" else 0.5
         bf16_sus = peaks.get("bf16_tflops_sustained", peaks["bf16_tflops"])
-        peak = bf16_sus / 2.0 / 3.0
-        peak_burst = peaks["bf16_tflops"] / 2.0 / 3.0
-        issued = float(n_local) * K * 2 * 8 * ((D + 8) // 8) * 3
+        peak = bf16_sus * rate / 3.0
+        peak_burst = peaks["bf16_tflops"] * rate / 3.0
+        issued = float(n_local) * K * issued_per_eval
         roofline = {
-            "bound": "tensor", "kernel": "vq_assign_tc2 (tcgen05 split-TF32 distortion + fused argmin)",
+            "bound": "tensor",
+            "kernel": f"vq_assign_tc2 (tcgen05 kind::{fmt} two-way split distortion + fused argmin)",
             "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-            "peak_source": f"{src}: cuBLAS bf16 sustained {bf16_sus:.1f} TFLOP/s / 2 (TF32 rate) / 3 "
-                           "(three TF32 MMAs per product); the kernel is timed inside a long step",
+            "peak_source": f"{src}: cuBLAS bf16 sustained {bf16_sus:.1f} TFLOP/s x {rate} ({fmt} rate) / 3 "
+                           "(three tensor MMAs per product); the kernel is timed inside a long step",
             "peak_burst": peak_burst, "frac_of_burst": achieved / peak_burst,
+            "operand_format": fmt, "tensor_flops_issued_per_eval": issued_per_eval,
             "tensor_tflops_issued": issued / (main_ms * 1e-3) / 1e12 if main_ms > 0 else 0.0,
-            "tensor_frac_of_tf32_sustained": (issued / (main_ms * 1e-3) / 1e12) / (bf16_sus / 2.0) if main_ms > 0 else None,
+            "tensor_frac_of_sustained": (issued / (main_ms * 1e-3) / 1e12) / (bf16_sus * rate) if main_ms > 0 else None,
             **common,
         }
     else:
@@ -466,7 +472,7 @@ def run_b200_arm(args):
             "metric": "frame x codeword evals/sec per k-means pass", "value": value, "unit": "evals/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": wall / args.steps * 1e3, "higher_is_better": True, "scaling": "strong",
-            "vs_baseline": None, "dtype": "tf32x3" if tc_mode else "f32", "data": "synthetic",
+            "vs_baseline": None, "dtype": (vq.tc_issued_flops_per_eval(P)[1] + "x3") if tc_mode else "f32", "data": "synthetic",
             "config": {
                 "workload": (f"vq learn P=36, k-means pass at K={K} on {n_total} synthetic ar_mix frames"
                              + (" (configs[1], 1 B200)" if world == 1 else

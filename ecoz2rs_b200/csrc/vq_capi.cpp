@@ -362,6 +362,10 @@ int ecoz2b200_debug_tc_distortions(ecoz2b200_engine *e, float *out, long n_rows)
     return eng.debug_tc_distortions(out, n_rows);
 }
 
+int ecoz2b200_tc_issued_flops_per_eval(int P, int *is_f16) {
+    return vqb200::tc_issued_flops_per_eval(P + 1, is_f16);
+}
+
 int ecoz2b200_nccl_unique_id(unsigned char id_out[128]) {
     const vqb200::NcclApi *api = vqb200::nccl_api();
     if (!api) return ECOZ2B200_ERR_NCCL;

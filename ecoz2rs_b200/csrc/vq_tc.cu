@@ -1329,6 +1329,14 @@ int tc_tile_cols(int K) {
     return K >= 256 ? 256 : (K > 64 ? 128 : 64);
 }
 
+int tc_issued_flops_per_eval(int D, int *is_f16) {
+    if (is_f16) *is_f16 = tc_f16() ? 1 : 0;
+    const int ks = tc_ksteps(D);
+    if (ks > tc_max_ksteps()) return 0;
+    if (tc_f16()) return 2 * 16 * (ks + (ks + 1) / 2);   // cross product + main product, 16 per MMA
+    return 2 * 8 * 3 * ks;
+}
+
 bool assign_tc_supported(int K, int D) { return K >= tc_min_k() && tc_ksteps(D) <= tc_max_ksteps(); }
 
 // floats of the tiles themselves: n_wtiles x [hi, lo] x (2 ksteps chunks) x BN rows x 16 bytes

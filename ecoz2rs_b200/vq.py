@@ -56,6 +56,7 @@ EXPORTED_SYMBOLS = (
     "ecoz2b200_version", "ecoz2b200_last_error", "ecoz2b200_device_count",
     "ecoz2b200_create", "ecoz2b200_destroy", "ecoz2b200_set_mode", "ecoz2b200_set_recheck_kappa",
     "ecoz2b200_set_recheck_kappa_tc", "ecoz2b200_debug_tc_distortions",
+    "ecoz2b200_tc_issued_flops_per_eval",
     "ecoz2b200_nccl_unique_id", "ecoz2b200_comm_init",
     "ecoz2b200_frames_clear", "ecoz2b200_frames_reserve", "ecoz2b200_frames_append_host",
     "ecoz2b200_frames_append_device", "ecoz2b200_frames_commit", "ecoz2b200_frames_count",
@@ -97,6 +98,7 @@ def lib():
             "ecoz2b200_set_recheck_kappa": (i, [vp, d]),
             "ecoz2b200_set_recheck_kappa_tc": (i, [vp, d]),
             "ecoz2b200_debug_tc_distortions": (i, [vp, vp, l]),
+            "ecoz2b200_tc_issued_flops_per_eval": (i, [i, _ip]),
             "ecoz2b200_nccl_unique_id": (i, [C.c_char_p]),
             "ecoz2b200_comm_init": (i, [vp, C.c_char_p, i, i]),
             "ecoz2b200_frames_clear": (i, [vp]),
@@ -399,6 +401,13 @@ def vq_quantize(nom_raas: str, predictor_filenames: Sequence[str], show_filename
 def ffma_peak_tflops(device: int = 0, millis: float = 20.0) -> float:
     """Measured FP32 FFMA peak of `device` (TFLOP/s): denominator of the FP32 roofline."""
     return lib().ecoz2b200_ffma_peak_tflops(device, millis)
+
+
+def tc_issued_flops_per_eval(P: int):
+    """(tensor-core FLOPs the TF32X3 search issues per frame x codeword pair, operand format)."""
+    f16 = C.c_int32(0)
+    n = lib().ecoz2b200_tc_issued_flops_per_eval(P, C.byref(f16))
+    return n, ("f16" if f16.value else "tf32")
 
 
 def nccl_unique_id() -> bytes:

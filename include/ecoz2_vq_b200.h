@@ -71,10 +71,12 @@ int ecoz2_vq_quantize(const char *nom_raas, const char *predictor_filenames[],
 
 /* Arithmetic mode of the nearest-codeword search (reference
  * ecoz2/src/vq/vq_learn_par.c:62-81, quantize.c:14-30 are FP64).
- *   TF32X3: tcgen05 tensor-core search with split-TF32 operands (FP32 accumulate
- *          in tensor memory) + FP64 re-evaluation of every frame whose best-two
- *          gap is inside the error bound (default; index-exact vs FP64).  Used for
- *          K >= 64 and P <= 38; smaller / wider codebooks take the FP32 path.
+ *   TF32X3: tcgen05 tensor-core search with two-way split operands (22-bit
+ *          products, FP32 accumulate in tensor memory) + FP64 re-evaluation of
+ *          every frame whose best-two gap is inside the error bound (default;
+ *          index-exact vs FP64).  The parts are FP16 values of power-of-two
+ *          scaled operands (ECOZ2_VQ_TC_FMT=f16, default, P <= 46) or TF32 values
+ *          (ECOZ2_VQ_TC_FMT=tf32, P <= 38); wider frames take the FP32 path.
  *   FP32:  FP32 FFMA search + the same FP64 re-evaluation.
  *   FP64:  the whole search in FP64 (verification mode).                      */
 #define ECOZ2B200_MODE_FP32 0
@@ -106,6 +108,11 @@ int ecoz2b200_set_recheck_kappa_tc(ecoz2b200_engine *e, double kappa);
 /* test aid: the raw tensor-core distortion values of the first n_rows resident
  * frames of shard 0 against the current codebook, out[n_rows][K] (TF32X3 mode) */
 int ecoz2b200_debug_tc_distortions(ecoz2b200_engine *e, float *out, long n_rows);
+/* measurement aid: tensor-core FLOPs the TF32X3 search issues per (frame,
+ * codeword) pair at prediction order P (padding and all three product terms
+ * included); 0 if that order takes the FP32 path.  *is_f16 (optional) = 1 when
+ * the operands are FP16 parts, 0 for TF32 parts.                              */
+int ecoz2b200_tc_issued_flops_per_eval(int P, int *is_f16);
 
 /* Multi-process sharding (one process per GPU, e.g. under torchrun): all ranks
  * call comm_init with the same 128-byte id obtained once from

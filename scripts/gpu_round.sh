@@ -18,11 +18,14 @@ echo "bench ref exit $?" >> $O/bench_ref_$TAG.err
 timeout 600 python scripts/perf_probe.py --n 10000000 --ks 2,4,8,16,32,64,128,256,512,1024,2048,4096 > $O/probe_$TAG.log 2>&1
 timeout 600 python scripts/perf_probe.py --n 10000000 --ks 64,256,1024,2048,4096 --mode 0 > $O/probe_fp32_$TAG.log 2>&1
 timeout 600 python scripts/perf_probe.py --n 20000000 --p 12 --ks 2,16,64,256,1024 > $O/probe_p12_$TAG.log 2>&1
-timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -c 600 --csv \
+# launch list of the library's own kernels (the torch synth kernels are filtered out by name)
+timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:"vq_|ffma" -c 1500 --csv \
     --log-file $O/launches_$TAG.csv python bench.py --frames 2000000 --steps 3 --warmup 3 \
     --no-cpu-baseline --e2e-steps 1 > $O/ncu_launches_$TAG.log 2>&1
+# perf_probe --ks 2048: 10 passes at K = 2..1024, then K = 2048; per pass the regex matches
+# search, filter, cell sums -> skip 30 lands on the first K = 2048 pass
 timeout 900 ncu --set full --clock-control none --import-source on \
-    -k regex:"vq_assign_tc2|vq_accumulate" --launch-skip 12 --launch-count 2 \
+    -k regex:"vq_assign_tc2|vq_cell_sums" --launch-skip 30 --launch-count 3 \
     -o $O/search_$TAG -f python scripts/perf_probe.py --n 2000000 --ks 2048 --reps 2 \
     > $O/ncu_full_$TAG.log 2>&1
 ls -la $O
