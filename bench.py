@@ -385,6 +385,32 @@ def run_b200_arm(args):
     h2d = n_local * D * 8 + K * D * 8
     d2h = K * D * 8 + K * 8 * 2 + 16 + 2 * K * D * 8
 
+    # ---- vq quantize of the same frames against the K-codeword codebook: resident
+    # frames -> u16 symbols + average distortion on the host; then host frames in, symbols out
+    quantize_info = None
+    try:
+        eng.set_reflections(refl_K)                         # frames are resident since the e2e steps
+        seq_h = torch.empty(n_local, dtype=torch.int16, pin_memory=True)
+        eng.quantize_resident_ptr(seq_h.data_ptr())         # warm
+        barrier()
+        tq = time.perf_counter()
+        q_reps = 3
+        for _ in range(q_reps):
+            q_avg = eng.quantize_resident_ptr(seq_h.data_ptr())
+        barrier()
+        q_wall = max_over_ranks(time.perf_counter() - tq) / q_reps
+        barrier()
+        tq = time.perf_counter()
+        eng.quantize_ptr(xh.data_ptr(), n_local, seq_h.data_ptr())
+        barrier()
+        q_e2e = max_over_ranks(time.perf_counter() - tq)
+        quantize_info = {"K": K, "frames": n_total, "resident_ms": q_wall * 1e3,
+                         "resident_evals_per_s": n_total * K / q_wall,
+                         "host_to_seq_ms": q_e2e * 1e3, "host_to_seq_evals_per_s": n_total * K / q_e2e,
+                         "avg_distortion": q_avg}
+    except Exception as e:
+        log(f"[quantize] failed: {e!r}")
+
     # ---- roofline of the dominant kernel (the search), measured with CUDA events on the
     # engine's own stream inside the timed region above
     main_ms = ctr["search_main_ms"] / max(1, ctr["search_main_launches"])
@@ -478,7 +504,7 @@ def run_b200_arm(args):
                              + (" (configs[1], 1 B200)" if world == 1 else
                                 f" sharded over {world} B200 with one NCCL allreduce of the packed cell sums per pass (configs[2])")),
                 "P": P, "K": K, "frames": n_total, "frames_per_gpu": n_local, "epsilon": EPS,
-                "search": ("tcgen05 split-TF32 (FP32 accumulate in TMEM) + FP64 re-evaluation of near-ties"
+                "search": ("tcgen05 two-way split operands (FP32 accumulate in TMEM) + FP64 re-evaluation of near-ties"
                            if tc_mode else "FP32 FFMA + FP64 re-evaluation of near-ties"),
                 "l2": "inputs (1.48 GB f32 + 2.96 GB f64 frames per 10M) exceed the 126 MB L2; no flush needed",
             },
@@ -494,6 +520,7 @@ def run_b200_arm(args):
             "learn_wall_s": learn_wall, "learn_passes": len(trace),
             "learn_stage_ms": {str(s["M"]): s["stage_seconds"] * 1e3 for s in stages},
             "learn_evals_per_s": learn_ctr["evals"] * world / learn_wall,
+            "quantize": quantize_info,
         }
         emit_line(line)
     eng.close()

@@ -358,6 +358,12 @@ class VqEngine:
                                                  C.byref(avg)), "quantize_resident")
         return seq, avg.value
 
+    def quantize_resident_ptr(self, seq_ptr: int) -> float:
+        """Resident frames -> u16 symbols at host address seq_ptr (pinned memory for full speed)."""
+        avg = C.c_double(0)
+        _check(lib().ecoz2b200_quantize_resident(self._h, seq_ptr, C.byref(avg)), "quantize_resident")
+        return avg.value
+
     # -- counters
     def counters_reset(self):
         lib().ecoz2b200_counters_reset(self._h)

@@ -126,3 +126,33 @@ def test_tc_matches_fp32_mode_in_learn(built_lib, frames36):
     for sa, sb in zip(a, b):
         assert np.allclose(sa["refl"], sb["refl"], rtol=1e-9, atol=1e-12)
         assert abs(sa["avg_distortion"] - sb["avg_distortion"]) <= 1e-10 * abs(sb["avg_distortion"])
+
+
+def test_tc_extreme_frame_scales(built_lib, frames36):
+    """FP16 operand format: every frame is scaled by its own power of two before the split, so
+    frames of any magnitude (1e-30 .. 1e+30, all-zero rows, non-autocorrelation rows whose largest
+    entry is not rx[0]) are searched with the same relative accuracy; the codebook scale covers
+    codewords of very different size (reflections close to +-1 next to a flat one)."""
+    from ecoz2rs_b200 import vq
+    from oracle import oracle as O
+    rng = np.random.default_rng(99)
+    n = 6000
+    x = frames36[:n].copy()
+    scale = 10.0 ** rng.integers(-30, 31, size=n)
+    x *= scale[:, None]
+    x[17] = 0.0                                   # distortion 0 against every codeword: index 0 wins
+    x[100:200] = rng.normal(size=(100, 37)) * 3   # arbitrary rows: |x[k]| > |x[0]| happens
+    refl = np.zeros((300, 37))
+    refl[:, 1:] = np.clip(rng.normal(size=(300, 36)) * 0.3, -0.9, 0.9)
+    refl[1, 1:] = 0.0                             # flat codeword: W1 = 1
+    refl[2, 1:4] = [0.97, -0.97, 0.97]            # sharp resonances: large W1
+    refl[3, 1:6] = 0.98
+    raas = O.refl_to_raas(refl)
+    idx_ref, dd_ref, d2_ref = O.assign(x, raas)
+    with vq.VqEngine(36, max_M=300, mode=vq.MODE_TF32X3) as eng:
+        eng.set_frames(x)
+        eng.set_raas(raas)
+        idx, dd, nre = eng.assign()
+    bad = allowed_index_mismatches(idx, idx_ref, dd_ref, d2_ref)
+    assert bad.size == 0, f"{bad.size} non-exempt mismatches, first {bad[:5]}: {idx[bad[:5]]} vs {idx_ref[bad[:5]]}"
+    assert idx[17] == 0
