@@ -1,4 +1,4 @@
-// ecoz2_cli.cpp -- `ecoz2 vq learn|quantize` command line on top of the C ABI.
+// ecoz2_cli.cpp -- `ecoz2 vq learn|quantize|classify` command line on top of the C ABI.
 //
 // The reference's CLI is the Rust binary (src/main.rs:95-97 -> src/vq/mod.rs); there
 // is no Rust toolchain in this environment, so this C++ driver keeps the same
@@ -103,6 +103,8 @@ int usage() {
             "                 --predictors <files|dirs|one.csv>...\n"
             "  ecoz2 vq quantize --codebook <cb> --predictors <files|dirs|one.csv>...\n"
             "                 [--predictors-dir-template <t>] [--tt TRAIN|TEST] [--class-name <c>] [-s]\n"
+            "  ecoz2 vq classify [-r] --codebooks <files|dirs>... --tt TRAIN|TEST\n"
+            "                 --predictors <files|dirs|one.csv>...\n"
             "environment: ECOZ2_VQ_GPUS=all|0,1,..  ECOZ2_VQ_MAX_M=<stop size>  ECOZ2_VQ_MIN_DISTS=0|1\n");
     return 2;
 }
@@ -113,7 +115,8 @@ int main(int argc, char **argv) {
     if (argc < 3 || strcmp(argv[1], "vq") != 0) return usage();
     const std::string cmd = argv[2];
     std::string base_cb, class_name, codebook, tt, templ = "data/predictors";
-    bool have_class = false, show = false, have_templ = false;
+    bool have_class = false, show = false, have_templ = false, show_ranked = false;
+    std::vector<std::string> codebooks;
     int P = -1;
     double eps = 0.05;
     std::vector<std::string> predictors;
@@ -130,7 +133,10 @@ int main(int argc, char **argv) {
         else if (a == "--predictors-dir-template") { next(templ); have_templ = true; }
         else if (a == "-s" || a == "--show-filenames") show = true;
         else if (a == "--exp-key") next(v);  // comet logging is out of scope (needs network)
-        else if (a == "--predictors") {
+        else if (a == "-r" || a == "--show-ranked") show_ranked = true;
+        else if (a == "--codebooks") {
+            while (i + 1 < argc && argv[i + 1][0] != '-') codebooks.push_back(argv[++i]);
+        } else if (a == "--predictors") {
             while (i + 1 < argc && argv[i + 1][0] != '-') predictors.push_back(argv[++i]);
         } else return usage();
     }
@@ -169,6 +175,26 @@ int main(int argc, char **argv) {
         std::vector<const char *> ptrs;
         for (auto &f : files) ptrs.push_back(f.c_str());
         return ecoz2_vq_quantize(codebook.c_str(), ptrs.data(), (int) ptrs.size(), show ? 1 : 0);
+    }
+    if (cmd == "classify") {   // reference src/vq/mod.rs:218-246
+        if (codebooks.empty() || predictors.empty() || tt.empty()) return usage();
+        std::vector<std::string> cbs;
+        for (const std::string &g : codebooks) {
+            if (is_dir(g)) walk(g, ".cbook", cbs);
+            else if (is_file(g) && ends_with(g, ".cbook")) cbs.push_back(g);
+        }
+        std::sort(cbs.begin(), cbs.end());
+        if (cbs.empty() || !resolve(predictors, tt, "", "predictors", ".prd", nullptr, files)) {
+            printf("No codebooks or predictors given\n");
+            return 1;
+        }
+        printf("number of codebooks: %zu  number of predictors: %zu\n", cbs.size(), files.size());
+        printf("show_ranked = %s\n", show_ranked ? "true" : "false");
+        std::vector<char *> cb_ptrs, prd_ptrs;
+        for (auto &f : cbs) cb_ptrs.push_back(&f[0]);
+        for (auto &f : files) prd_ptrs.push_back(&f[0]);
+        return ecoz2_vq_classify(cb_ptrs.data(), (int) cb_ptrs.size(), prd_ptrs.data(), (int) prd_ptrs.size(),
+                                 show_ranked ? 1 : 0);
     }
     return usage();
 }

@@ -212,6 +212,10 @@ int learn_files(const double *base_refl, int base_K, int P, double eps, const ch
 
 }  // namespace
 
+// shared with vq_classify.cpp
+void ecoz2b200_apply_mode_env(vqb200::Engine &eng) { apply_mode_env(eng); }
+std::vector<int> ecoz2b200_devices_from_env() { return devices_from_env(); }
+
 // ============================================================================ PART 1
 extern "C" {
 

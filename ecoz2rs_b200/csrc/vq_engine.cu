@@ -563,7 +563,7 @@ int Engine::debug_tc_distortions(float *out, long n_rows) {
     return ECOZ2B200_OK;
 }
 
-int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked) {
+int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked, bool raw) {
     if (!committed_ || K_ < 1) {
         set_last_error("assign: frames not committed or no codebook");
         return ECOZ2B200_ERR_ARG;
@@ -590,7 +590,7 @@ int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked) {
         rechecked += fc;
     }
     CUDA_TRY(cudaGetLastError());
-    if (ddmin_out)
+    if (ddmin_out && raw)
         for (long v = 0; v < n_total_; v++) ddmin_out[v] += 1.0;  // raw distortion (before the -1)
     ctr_.rechecked += rechecked;
     if (num_rechecked) *num_rechecked = rechecked;

@@ -90,7 +90,9 @@ class Engine {
     int codebook_size() const { return K_; }
     int codebook_get(double *refl_out, double *raas_out);
 
-    int assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked);
+    // ddmin_out: the winner's distortion per frame (raw), or distortion - 1 (the reference's
+    // minDist / quantize summand, computed on the device) when raw = false
+    int assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked, bool raw = true);
     int kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_out, double *DD_out);
     int sigma(double avgDistortion, double *sigma_out);
     int inertia(double *inertia_out);

@@ -52,7 +52,7 @@ _PASS_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_doubl
 
 # every symbol include/ecoz2_vq_b200.h declares (tests check the library exports them all)
 EXPORTED_SYMBOLS = (
-    "ecoz2_vq_learn", "ecoz2_vq_learn_using_base_codebook", "ecoz2_vq_quantize",
+    "ecoz2_vq_learn", "ecoz2_vq_learn_using_base_codebook", "ecoz2_vq_quantize", "ecoz2_vq_classify",
     "ecoz2b200_version", "ecoz2b200_last_error", "ecoz2b200_device_count",
     "ecoz2b200_create", "ecoz2b200_destroy", "ecoz2b200_set_mode", "ecoz2b200_set_recheck_kappa",
     "ecoz2b200_set_recheck_kappa_tc", "ecoz2b200_debug_tc_distortions",
@@ -89,6 +89,7 @@ def lib():
             "ecoz2_vq_learn": (i, [i, d, C.c_char_p, cpp, i, vp, VQ_LEARN_CALLBACK]),
             "ecoz2_vq_learn_using_base_codebook": (i, [C.c_char_p, d, cpp, i, vp, VQ_LEARN_CALLBACK]),
             "ecoz2_vq_quantize": (i, [C.c_char_p, cpp, i, i]),
+            "ecoz2_vq_classify": (i, [cpp, i, cpp, i, i]),
             "ecoz2b200_version": (C.c_char_p, []),
             "ecoz2b200_last_error": (C.c_char_p, []),
             "ecoz2b200_device_count": (i, []),
@@ -402,6 +403,14 @@ def vq_quantize(nom_raas: str, predictor_filenames: Sequence[str], show_filename
     """`ecoz2_vq_quantize` (reference src/ecoz2_lib/mod.rs:325-342)."""
     return lib().ecoz2_vq_quantize(os.fsencode(nom_raas), _file_array(predictor_filenames),
                                    len(predictor_filenames), int(show_filenames))
+
+
+def vq_classify(cb_filenames: Sequence[str], predictor_filenames: Sequence[str],
+                show_ranked: bool = False) -> int:
+    """`ecoz2_vq_classify` (reference src/ecoz2_lib/mod.rs:344-360, vq/vq_classify.c:185-327)."""
+    return lib().ecoz2_vq_classify(_file_array(cb_filenames), len(cb_filenames),
+                                   _file_array(predictor_filenames), len(predictor_filenames),
+                                   int(show_ranked))
 
 
 def ffma_peak_tflops(device: int = 0, millis: float = 20.0) -> float:

@@ -60,6 +60,16 @@ int ecoz2_vq_learn_using_base_codebook(char *base_codebook, double epsilon,
 int ecoz2_vq_quantize(const char *nom_raas, const char *predictor_filenames[],
                       int num_predictors, int show_filenames);
 
+/* `ecoz2 vq classify`: replaces ecoz2_vq_classify, reference
+ * ecoz2/src/include/ecoz2.h:95-101 -> vq_classify, ecoz2/src/vq/vq_classify.c:185-327.
+ * Every predictor is quantized against every codebook (all of one size); stdout gets the
+ * reference's model list, optional ranking of misclassified files, confusion matrix and
+ * candidate-order table; stderr one green '*' / red '!' per file.  Returns 0, or 1 on a
+ * codebook load / conformity error.  All frames stay resident in HBM: one search pass per
+ * model over all files.                                                                  */
+int ecoz2_vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenames,
+                      int num_predictors, int show_ranked);
+
 /* ===================================================================== PART 2
  * In-memory API.                                                            */
 

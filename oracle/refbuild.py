@@ -244,3 +244,10 @@ def run_vq_quantize(codebook, prd_files, cwd):
     exe = os.path.join(arch_dir(), "vq.quantize")
     rc, out = _run([exe, codebook] + list(prd_files), cwd, 1)
     return dict(returncode=rc, stdout=out)
+
+
+def run_vq_classify(codebooks, prd_files, cwd, show_ranked=True):
+    """The reference's vq.classify executable; stdout and stderr (the '*' / '!' marks) merged."""
+    exe = os.path.join(arch_dir(), "vq.classify")
+    rc, out = _run([exe] + (["-r"] if show_ranked else []) + list(codebooks) + list(prd_files), cwd, 1)
+    return dict(returncode=rc, stdout=out)

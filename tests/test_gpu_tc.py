@@ -75,7 +75,8 @@ def test_tc_assign_matches_oracle(built_lib, frames36, frames12, P, K, N):
     bad = allowed_index_mismatches(idx, idx_ref, dd_ref, d2_ref)
     assert bad.size == 0, f"{bad.size} non-exempt mismatches, first {bad[:5]}"
     same = idx == idx_ref
-    assert np.allclose(dd[same], dd_ref[same], rtol=1e-12, atol=0)
+    # FP64 sums in a different order than the oracle's: rounding times the conditioning of x.w
+    assert np.allclose(dd[same], dd_ref[same], rtol=1e-10, atol=0)
     assert nre < 0.25 * N
 
 
