@@ -389,7 +389,7 @@ __device__ __forceinline__ void epi_finish(const EpiState &st, float &second, in
 // filter mode (see TcParams::cand): a frame's candidates are collected in registers (a
 // flagged frame typically has 2-3) and published once per frame tile with one atomic per
 // warp; a frame with more than kFilterSlots candidates goes to the all-FP64 search instead.
-constexpr int kFilterSlots = 6;
+constexpr int kFilterSlots = 12;
 struct FilterState {
     int cnt;
     int c[kFilterSlots];
