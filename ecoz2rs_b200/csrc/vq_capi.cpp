@@ -106,14 +106,19 @@ void on_stage(void *c, const ecoz2b200_stage_info *info) {
         ctx->callback(ctx->target, info->M, info->avgDistortion, info->sigma, info->inertia);
     std::vector<int32_t> cw;
     std::vector<double> md;
+    const double t_rep0 = wall_s();
     if (ctx->min_dists) {
         cw.resize((size_t) ctx->tot_vecs);
         md.resize((size_t) ctx->tot_vecs);
         if (ctx->eng->last_assignment(cw.data(), md.data())) ctx->rc = ECOZ2B200_ERR_CUDA;
     }
+    const double t_rep1 = wall_s();
     ctx->report->cbook(ctx->cb_filename, info->passes, info->avgDistortion, info->sigma,
                        info->inertia, info->M, info->cardd, info->discel,
                        ctx->min_dists ? cw.data() : nullptr, ctx->min_dists ? md.data() : nullptr);
+    if (getenv("ECOZ2_VQ_TIMING"))
+        fprintf(stderr, "[timing] M=%d read-back %.1f ms, report files %.1f ms\n", info->M,
+                (t_rep1 - t_rep0) * 1e3, (wall_s() - t_rep1) * 1e3);
     printf("\n");
     // name of the next size (vq_learn_par.c:152-154)
     char buf[64];
@@ -364,6 +369,12 @@ int ecoz2b200_set_recheck_kappa_tc(ecoz2b200_engine *e, double k) { ENG(e); retu
 int ecoz2b200_debug_tc_distortions(ecoz2b200_engine *e, float *out, long n_rows) {
     ENG(e);
     return eng.debug_tc_distortions(out, n_rows);
+}
+
+int ecoz2b200_write_min_dists_csv(const char *path, const int32_t *codeword, const double *min_dist,
+                                  long n) {
+    if (!path || n < 0 || (n > 0 && (!codeword || !min_dist))) return ECOZ2B200_ERR_ARG;
+    return vqb200::write_min_dists_csv(path, codeword, min_dist, n) ? ECOZ2B200_OK : ECOZ2B200_ERR_IO;
 }
 
 int ecoz2b200_tc_issued_flops_per_eval(int P, int *is_f16) {

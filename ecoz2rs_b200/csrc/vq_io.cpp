@@ -7,7 +7,12 @@
 #include <string.h>
 #include <sys/stat.h>
 
+#include <math.h>
+#include <stdint.h>
+
 #include <memory>
+#include <thread>
+#include <vector>
 
 namespace vqb200 {
 
@@ -240,17 +245,98 @@ void Report::cbook(const std::string &cb_filename, int num_pas, double DDprm, do
     }
     if (codeword && min_dist) {
         const std::string name = cb_filename + ".min_dists.csv";
-        FILE *f = fopen(name.c_str(), "w");
-        if (!f) {
+        if (!write_min_dists_csv(name.c_str(), codeword, min_dist, tot_vecs_))
             printf("error creating %s\n", name.c_str());
-        } else {
-            static char big[1 << 20];
-            setvbuf(f, big, _IOFBF, sizeof big);
-            fprintf(f, "%s\n", "codeword,minDistortion");
-            for (long v = 0; v < tot_vecs_; v++) fprintf(f, "%d,%f\n", codeword[v], min_dist[v]);
-            fclose(f);
-        }
     }
+}
+
+// ---- "<cbook>.min_dists.csv" (report.c:109-123): N lines "%d,%f\n" per stage.  With passes of
+// milliseconds, 10M glibc fprintf calls per stage (2 s) would BE the run time of `vq learn`
+// (SURVEY.md 8f-2), so the lines are formatted by all host threads into per-thread buffers with an
+// exact integer "%f" (below) and written in order.
+
+// decimal digits of v, returns the end
+static inline char *fmt_u64(char *p, uint64_t v) {
+    char tmp[24];
+    int n = 0;
+    do { tmp[n++] = (char) ('0' + v % 10); v /= 10; } while (v);
+    while (n) *p++ = tmp[--n];
+    return p;
+}
+
+// printf("%f") of a finite |x| < 2^63: x = m 2^e exactly, so round(x 10^6) is an exact integer
+// computation (m 10^6 < 2^73 in 128 bits, shifted by -e with round-half-to-even on the exact
+// remainder -- what glibc does in the default rounding mode).  Anything else: snprintf.
+char *format_f6(char *p, double x) {
+    uint64_t bits;
+    memcpy(&bits, &x, sizeof bits);
+    const int ef = (int) ((bits >> 52) & 0x7ff);
+    uint64_t m = bits & ((1ull << 52) - 1);
+    if (ef == 0x7ff || ef >= 1023 + 62) return p + sprintf(p, "%f", x);   // inf / nan / huge
+    if (bits >> 63) *p++ = '-';
+    int e;
+    if (ef == 0) e = -1074;            // subnormal (or zero)
+    else { m |= 1ull << 52; e = ef - 1075; }
+    unsigned __int128 v = (unsigned __int128) m * 1000000u;   // x 10^6 = v 2^e
+    if (e >= 0) {
+        v <<= e;                       // ef < 1023 + 62 keeps this below 2^(73+9)... guarded: e <= 9
+    } else if (-e >= 127) {
+        v = 0;                         // below 2^-54: rounds to 0.000000
+    } else {
+        const int sh = -e;
+        const unsigned __int128 q = v >> sh, r = v - (q << sh), half = (unsigned __int128) 1 << (sh - 1);
+        v = q + ((r > half || (r == half && (q & 1))) ? 1 : 0);
+    }
+    const uint64_t ip = (uint64_t) (v / 1000000u), fp = (uint64_t) (v % 1000000u);
+    p = fmt_u64(p, ip);
+    *p++ = '.';
+    for (int k = 5, f = (int) fp; k >= 0; k--, f /= 10) p[k] = (char) ('0' + f % 10);
+    return p + 6;
+}
+
+static inline char *format_i32(char *p, int32_t v) {
+    if (v < 0) { *p++ = '-'; return fmt_u64(p, (uint64_t) (-(int64_t) v)); }
+    return fmt_u64(p, (uint64_t) v);
+}
+
+bool write_min_dists_csv(const char *name, const int32_t *codeword, const double *min_dist, long n) {
+    FILE *f = fopen(name, "w");
+    if (!f) return false;
+    fputs("codeword,minDistortion\n", f);
+    unsigned hw = std::thread::hardware_concurrency();
+    const int T = (int) (hw == 0 ? 1 : (hw > 32 ? 32 : hw));
+    const long kLines = 1L << 17;                 // lines per thread and round; a line is < 64 chars
+    std::vector<std::vector<char>> bufs((size_t) T);
+    std::vector<size_t> used((size_t) T, 0);
+    bool ok = true;
+    for (long base = 0; base < n && ok; base += (long) T * kLines) {
+        auto work = [&](int t) {
+            const long lo = base + (long) t * kLines;
+            long hi = lo + kLines;
+            if (hi > n) hi = n;
+            used[(size_t) t] = 0;
+            if (lo >= hi) return;
+            std::vector<char> &b = bufs[(size_t) t];
+            if (b.size() < (size_t) kLines * 64) b.resize((size_t) kLines * 64);
+            char *p = b.data();
+            for (long v = lo; v < hi; v++) {
+                p = format_i32(p, codeword[v]);
+                *p++ = ',';
+                p = format_f6(p, min_dist[v]);
+                *p++ = '\n';
+            }
+            used[(size_t) t] = (size_t) (p - b.data());
+        };
+        const long left = n - base;
+        const int active = (int) ((left + kLines - 1) / kLines < T ? (left + kLines - 1) / kLines : T);
+        std::vector<std::thread> th;
+        for (int t = 1; t < active; t++) th.emplace_back(work, t);
+        work(0);
+        for (auto &x : th) x.join();
+        for (int t = 0; t < active && ok; t++)
+            if (used[(size_t) t]) ok = fwrite(bufs[(size_t) t].data(), 1, used[(size_t) t], f) == used[(size_t) t];
+    }
+    return fclose(f) == 0 && ok;
 }
 
 void Report::close() {

@@ -29,6 +29,11 @@ extern int cb_errnum_last;  // reference cb_errnum (vq.c:20)
 int seq_save(const char *path, const char *class_name, const uint16_t *seq, int T, int M);
 
 // reference ecoz2/src/utl/fileutil.c:14-119
+// "%f" of x appended at p (exact integer arithmetic, identical to printf); returns the end
+char *format_f6(char *p, double x);
+// "<cbook>.min_dists.csv" (report.c:109-123), formatted by all host threads
+bool write_min_dists_csv(const char *name, const int32_t *codeword, const double *min_dist, long n);
+
 std::string get_class_name(const std::string &path);
 int mk_dirs(const std::string &path);
 // data/<base_dir>/<class>/<stem><ext>; creates the directory

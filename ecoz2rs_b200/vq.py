@@ -56,7 +56,7 @@ EXPORTED_SYMBOLS = (
     "ecoz2b200_version", "ecoz2b200_last_error", "ecoz2b200_device_count",
     "ecoz2b200_create", "ecoz2b200_destroy", "ecoz2b200_set_mode", "ecoz2b200_set_recheck_kappa",
     "ecoz2b200_set_recheck_kappa_tc", "ecoz2b200_debug_tc_distortions",
-    "ecoz2b200_tc_issued_flops_per_eval",
+    "ecoz2b200_tc_issued_flops_per_eval", "ecoz2b200_write_min_dists_csv",
     "ecoz2b200_nccl_unique_id", "ecoz2b200_comm_init",
     "ecoz2b200_frames_clear", "ecoz2b200_frames_reserve", "ecoz2b200_frames_append_host",
     "ecoz2b200_frames_append_device", "ecoz2b200_frames_commit", "ecoz2b200_frames_count",
@@ -100,6 +100,7 @@ def lib():
             "ecoz2b200_set_recheck_kappa_tc": (i, [vp, d]),
             "ecoz2b200_debug_tc_distortions": (i, [vp, vp, l]),
             "ecoz2b200_tc_issued_flops_per_eval": (i, [i, _ip]),
+            "ecoz2b200_write_min_dists_csv": (i, [C.c_char_p, _ip, vp, l]),
             "ecoz2b200_nccl_unique_id": (i, [C.c_char_p]),
             "ecoz2b200_comm_init": (i, [vp, C.c_char_p, i, i]),
             "ecoz2b200_frames_clear": (i, [vp]),
@@ -423,6 +424,15 @@ def tc_issued_flops_per_eval(P: int):
     f16 = C.c_int32(0)
     n = lib().ecoz2b200_tc_issued_flops_per_eval(P, C.byref(f16))
     return n, ("f16" if f16.value else "tf32")
+
+
+def write_min_dists_csv(path: str, codeword: np.ndarray, min_dist: np.ndarray) -> None:
+    """The learn report's `<cbook>.min_dists.csv` writer (host threads, exact "%f")."""
+    cw = np.ascontiguousarray(codeword, dtype=np.int32)
+    md = np.ascontiguousarray(min_dist, dtype=np.float64)
+    assert cw.shape == md.shape and cw.ndim == 1
+    _check(lib().ecoz2b200_write_min_dists_csv(os.fsencode(path), cw.ctypes.data_as(_ip), md.ctypes.data,
+                                               cw.shape[0]), "write_min_dists_csv")
 
 
 def nccl_unique_id() -> bytes:

@@ -123,6 +123,11 @@ int ecoz2b200_debug_tc_distortions(ecoz2b200_engine *e, float *out, long n_rows)
  * included); 0 if that order takes the FP32 path.  *is_f16 (optional) = 1 when
  * the operands are FP16 parts, 0 for TF32 parts.                              */
 int ecoz2b200_tc_issued_flops_per_eval(int P, int *is_f16);
+/* test aid (host only, no device needed): the "<cbook>.min_dists.csv" writer of the learn report
+ * (reference report.c:109-123: N lines "%d,%f"), formatted by all host threads with an exact
+ * integer "%f".  Returns 0, or ECOZ2B200_ERR_IO.                                          */
+int ecoz2b200_write_min_dists_csv(const char *path, const int32_t *codeword, const double *min_dist,
+                                  long n);
 
 /* Multi-process sharding (one process per GPU, e.g. under torchrun): all ranks
  * call comm_init with the same 128-byte id obtained once from

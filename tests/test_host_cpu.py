@@ -113,3 +113,30 @@ def test_class_name_header_padding(tmp_path):
     assert raw[16:16 + 96] == b"ab\0" + b"_" * 93
     assert raw[112:120] == np.array([2, 1], "<i4").tobytes()
     assert len(raw) == 120 + 3 * 8
+
+
+def test_min_dists_csv_writer_matches_printf(built_lib, tmp_path):
+    """The parallel "<cbook>.min_dists.csv" writer reproduces fprintf("%d,%f\\n")
+    of reference report.c:118-120 byte for byte: random magnitudes, exact ties of the 6th decimal
+    (k/128, k/2^20: round-half-to-even), negatives, subnormals, huge values, inf and nan."""
+    import struct
+    from ecoz2rs_b200 import vq
+    rng = np.random.default_rng(7)
+    n = 300_000
+    md = np.concatenate([
+        rng.random(n) * 10.0 ** rng.integers(-9, 6, size=n),
+        rng.integers(0, 2 ** 24, size=5000) / 128.0,          # x 10^6 ends in .5 or .0: ties
+        rng.integers(0, 2 ** 30, size=5000) / 2.0 ** 20,
+        -rng.random(2000),
+        np.array([0.0, -0.0, 5e-324, 1e-310, 0.5e-6, 1.5e-6, 2.5e-6, 0.9999995, 0.99999949999,
+                  1e15, 123456789012345.678, 9.2e18, 1e19, 1e300, np.inf, -np.inf, np.nan]),
+    ])
+    cw = rng.integers(0, 65536, size=md.shape[0]).astype(np.int32)
+    cw[:3] = [0, -1, 2 ** 31 - 1]
+    path = tmp_path / "x.min_dists.csv"
+    vq.write_min_dists_csv(str(path), cw, md)
+    got = path.read_text().split("\n")
+    assert got[0] == "codeword,minDistortion" and got[-1] == "" and len(got) == md.shape[0] + 2
+    want = ["%d,%f" % (int(c), float(x)) for c, x in zip(cw, md)]
+    bad = [i for i, (a, b) in enumerate(zip(got[1:-1], want)) if a != b]
+    assert not bad, f"{len(bad)} lines differ, first: {got[1 + bad[0]]!r} vs {want[bad[0]]!r} ({md[bad[0]]!r})"
