@@ -375,9 +375,14 @@ def run_b200_arm(args):
     barrier()
     t0 = time.perf_counter()
     for _ in range(e2e_steps):
-        eng.set_frames_ptr(xh.data_ptr(), n_local)         # H2D of the step's frames (+ f32 staging)
         eng.set_reflections(refl_now)                      # H2D codebook
-        out = eng.kmeans_pass(want_cells=True)             # D2H cells, counts, distortions, DD
+        if world == 1:
+            # H2D of the step's frames in chunks, each searched while the next one uploads;
+            # D2H cells, counts, distortions, DD
+            out = eng.kmeans_pass_host_ptr(xh.data_ptr(), n_local, want_cells=True)
+        else:
+            eng.set_frames_ptr(xh.data_ptr(), n_local)     # H2D of the step's frames (+ f32 staging)
+            out = eng.kmeans_pass(want_cells=True)         # D2H cells, counts, distortions, DD
         new_refl, new_raas = eng.codebook()                # D2H updated codebook
     barrier()
     e2e_wall = max_over_ranks(time.perf_counter() - t0)

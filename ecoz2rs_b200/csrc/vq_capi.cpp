@@ -436,6 +436,11 @@ int ecoz2b200_kmeans_pass(ecoz2b200_engine *e, double *cells, int32_t *cardd, do
     ENG(e);
     return eng.kmeans_pass(cells, cardd, discel, DD);
 }
+int ecoz2b200_kmeans_pass_host(ecoz2b200_engine *e, const double *x, long n, double *cells,
+                               int32_t *cardd, double *discel, double *DD) {
+    ENG(e);
+    return eng.kmeans_pass_host(x, n, cells, cardd, discel, DD);
+}
 int ecoz2b200_sigma(ecoz2b200_engine *e, double avg, double *out) { ENG(e); return eng.sigma(avg, out); }
 int ecoz2b200_inertia(ecoz2b200_engine *e, double *out) { ENG(e); return eng.inertia(out); }
 int ecoz2b200_last_assignment(ecoz2b200_engine *e, int32_t *idx, double *md) {

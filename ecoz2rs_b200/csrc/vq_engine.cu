@@ -60,7 +60,7 @@ Engine::Engine(const int *devices, int num_devices, int P, int max_M)
         return;
     }
     shards_.resize(num_devices);
-    qbuf_.resize(num_devices);
+    qbuf_.resize(2 * (size_t) num_devices);   // two chunk buffers per device (quantize_host)
     const PackedLayout L{max_M_, D_};
     const size_t cb = sizeof(double) * (size_t) max_M_ * D_;
     const int K32 = (max_M_ + kTileF32 - 1) / kTileF32 * kTileF32;
@@ -121,11 +121,18 @@ Engine::~Engine() {
         cudaFree(s.refl); cudaFree(s.raas); cudaFree(s.w32); cudaFree(s.w64); cudaFree(s.w1max); cudaFree(s.w1);
         cudaFree(s.wtc); cudaFree(s.cs_mem); cudaFree(s.packed_scratch); cudaFree(s.raas_prev);
         cudaFree(s.packed); cudaFree(s.scalars);
-        QBuf &q = qbuf_[i];
-        cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
+        for (int b = 0; b < 2; b++) {
+            QBuf &q = qbuf_[2 * i + b];
+            cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
+        }
         for (auto &e : s.ev)
             if (e) cudaEventDestroy(e);
         if (s.stream) cudaStreamDestroy(s.stream);
+        if (s.copy_stream) cudaStreamDestroy(s.copy_stream);
+        for (cudaEvent_t e : s.ev_chunk)
+            if (e) cudaEventDestroy(e);
+        for (cudaEvent_t e : s.ev_qfree)
+            if (e) cudaEventDestroy(e);
     }
 }
 
@@ -631,7 +638,6 @@ int Engine::kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_ou
         return ECOZ2B200_ERR_ARG;
     }
     const PackedLayout L{K_, D_};
-    const bool reduce = shards_.size() > 1 || multi_process_;
     for (Shard &s : shards_) {
         CUDA_TRY(cudaSetDevice(s.device));
         CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
@@ -639,6 +645,100 @@ int Engine::kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_ou
         pass_kernels(s, s.x64, s.x32, s.n, s.idx, s.sc, s.mindist, nullptr, true);
         CUDA_TRY(cudaEventRecord(s.ev[2], s.stream));
     }
+    return pass_tail(cells_out, cardd_out, discel_out, DD_out);
+}
+
+int Engine::kmeans_pass_host(const double *x, long n, double *cells_out, int32_t *cardd_out,
+                             double *discel_out, double *DD_out) {
+    if (K_ < 1 || n <= 0 || !x) {
+        set_last_error("kmeans_pass_host: no codebook or no frames");
+        return ECOZ2B200_ERR_ARG;
+    }
+    if (multi_process_) {
+        set_last_error("kmeans_pass_host: one process per engine only (use frames_* + kmeans_pass)");
+        return ECOZ2B200_ERR_ARG;
+    }
+    const bool pipelined = !small_path() && use_cell_sort_ && cell_sort_supported(K_);
+    if (!pipelined) {   // plain sequence: upload, commit, pass
+        int rc = frames_clear();
+        if (!rc) rc = frames_reserve(n);
+        if (!rc) rc = frames_append_host(x, n);
+        if (!rc) rc = frames_commit();
+        if (rc) return rc;
+        return kmeans_pass(cells_out, cardd_out, discel_out, DD_out);
+    }
+    const PackedLayout L{K_, D_};
+    const long S = (long) shards_.size();
+    frames_clear();
+    reserved_ = n;
+    per_shard_ = (n + S - 1) / S;
+    const long chunk = 1L << 20;   // frames per upload chunk (310 MB of FP64 at P = 36)
+    for (long i = 0; i < S; i++) {
+        Shard &s = shards_[i];
+        s.frame_offset = i * per_shard_;
+        long mine = n - s.frame_offset;
+        if (mine > per_shard_) mine = per_shard_;
+        if (mine < 0) mine = 0;
+        int rc = ensure_capacity(s, mine > 0 ? mine : 1);
+        if (rc) return rc;
+        s.n = mine;
+        CUDA_TRY(cudaSetDevice(s.device));
+        if (!s.copy_stream) {
+            CUDA_TRY(cudaStreamCreateWithFlags(&s.copy_stream, cudaStreamNonBlocking));
+            for (int k = 0; k < 2; k++) CUDA_TRY(cudaEventCreateWithFlags(&s.ev_chunk[k], cudaEventDisableTiming));
+        }
+        // the copy stream must not overwrite frames an earlier pass on s.stream still reads
+        CUDA_TRY(cudaEventRecord(s.ev_chunk[0], s.stream));
+        CUDA_TRY(cudaStreamWaitEvent(s.copy_stream, s.ev_chunk[0], 0));
+        CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
+        CUDA_TRY(cudaMemsetAsync(s.packed, 0, sizeof(double) * L.size(), s.stream));
+    }
+    // chunks of all shards interleaved: every device's copy engine and SMs stay busy
+    long max_chunks = (per_shard_ + chunk - 1) / chunk;
+    for (long c = 0; c < max_chunks; c++) {
+        for (Shard &s : shards_) {
+            const long off = c * chunk;
+            if (off >= s.n) continue;
+            const long m = s.n - off < chunk ? s.n - off : chunk;
+            CUDA_TRY(cudaSetDevice(s.device));
+            CUDA_TRY(cudaMemcpyAsync(s.x64 + (size_t) off * D_, x + (size_t) (s.frame_offset + off) * D_,
+                                     sizeof(double) * (size_t) m * D_, cudaMemcpyHostToDevice, s.copy_stream));
+            CUDA_TRY(cudaEventRecord(s.ev_chunk[c & 1], s.copy_stream));
+            // the copy stream carries nothing but copies (a kernel queued there would wait for
+            // the persistent search kernel to leave the SMs and hold the next copy back)
+            CUDA_TRY(cudaStreamWaitEvent(s.stream, s.ev_chunk[c & 1], 0));
+            launch_convert_frames(s.x64 + (size_t) off * D_, s.x32 + (size_t) off * D_, m, D_, s.stream);
+            search(s, s.x64 + (size_t) off * D_, s.x32 + (size_t) off * D_, m, s.idx + off, s.sc);
+            ctr_.kernel_launches++;
+        }
+    }
+    appended_ = n;
+    n_total_ = n_global_ = n;
+    if (S > 1) {
+        int rc = ensure_local_comms();
+        if (rc) return rc;
+    }
+    committed_ = true;
+    for (Shard &s : shards_) {
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaEventRecord(s.ev[1], s.stream));
+        if (s.n > 0) {
+            cudaMemcpyAsync(s.raas_prev, s.raas, sizeof(double) * (size_t) K_ * D_, cudaMemcpyDeviceToDevice,
+                            s.stream);
+            launch_cell_sums(s.x64, s.idx, s.n, D_, s.raas, K_, s.packed, nullptr, s.cs, s.num_sms, s.stream);
+            ctr_.kernel_launches += 5;
+        }
+        CUDA_TRY(cudaEventRecord(s.ev[2], s.stream));
+    }
+    K_prev_ = K_;
+    mindist_valid_ = false;
+    return pass_tail(cells_out, cardd_out, discel_out, DD_out);
+}
+
+// allreduce of the packed sums, read-back, centroid update and re-staging of the codebook
+int Engine::pass_tail(double *cells_out, int32_t *cardd_out, double *discel_out, double *DD_out) {
+    const PackedLayout L{K_, D_};
+    const bool reduce = shards_.size() > 1 || multi_process_;
     int rc = allreduce_range(shards_, 0, L.size(), reduce);
     if (rc) return rc;
     h_packed_.resize((size_t) L.size());
@@ -857,36 +957,51 @@ int Engine::quantize_host(const double *x, long T, uint16_t *seq_out, double *av
     const PackedLayout L{K_, D_};
     const long S = (long) shards_.size();
     const long chunk_cap = 1L << 20;  // frames per device chunk
+    const long want = T < chunk_cap ? (T > 0 ? T : 1) : chunk_cap;
     for (long i = 0; i < S; i++) {
         Shard &s = shards_[i];
-        QBuf &q = qbuf_[i];
         CUDA_TRY(cudaSetDevice(s.device));
-        const long want = T < chunk_cap ? (T > 0 ? T : 1) : chunk_cap;
-        if (q.cap < want) {
-            CUDA_TRY(cudaStreamSynchronize(s.stream));
-            cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
-            q = QBuf();
-            CUDA_TRY(cudaMalloc(&q.x64, sizeof(double) * (size_t) want * D_));
-            CUDA_TRY(cudaMalloc(&q.x32, sizeof(float) * (size_t) want * D_));
-            CUDA_TRY(cudaMalloc(&q.idx, sizeof(int32_t) * (size_t) want));
-            CUDA_TRY(cudaMalloc(&q.sc_mem, scratch_bytes(want)));
-            scratch_carve(q.sc_mem, want, &q.sc);
-            CUDA_TRY(cudaMalloc(&q.seq, sizeof(uint16_t) * (size_t) want));
-            q.cap = want;
+        if (!s.copy_stream) {
+            CUDA_TRY(cudaStreamCreateWithFlags(&s.copy_stream, cudaStreamNonBlocking));
+            for (int k = 0; k < 2; k++) CUDA_TRY(cudaEventCreateWithFlags(&s.ev_chunk[k], cudaEventDisableTiming));
+        }
+        for (int b = 0; b < 2; b++) {
+            if (!s.ev_qfree[b]) CUDA_TRY(cudaEventCreateWithFlags(&s.ev_qfree[b], cudaEventDisableTiming));
+            QBuf &q = qbuf_[2 * i + b];
+            if (q.cap < want) {
+                CUDA_TRY(cudaStreamSynchronize(s.stream));
+                cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
+                q = QBuf();
+                CUDA_TRY(cudaMalloc(&q.x64, sizeof(double) * (size_t) want * D_));
+                CUDA_TRY(cudaMalloc(&q.x32, sizeof(float) * (size_t) want * D_));
+                CUDA_TRY(cudaMalloc(&q.idx, sizeof(int32_t) * (size_t) want));
+                CUDA_TRY(cudaMalloc(&q.sc_mem, scratch_bytes(want)));
+                scratch_carve(q.sc_mem, want, &q.sc);
+                CUDA_TRY(cudaMalloc(&q.seq, sizeof(uint16_t) * (size_t) want));
+                q.cap = want;
+            }
+            // whatever s.stream still does with the buffer (an earlier call) comes first
+            CUDA_TRY(cudaEventRecord(s.ev_qfree[b], s.stream));
         }
         CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
     }
-    // contiguous chunks dealt round-robin to the devices; every chunk is
-    // H2D -> f32 copy -> search -> FP64 distortion + symbols -> D2H on its stream
+    // contiguous chunks dealt round-robin to the devices; a chunk is uploaded on the device's
+    // copy stream into one of its two buffers while the previous chunk is searched:
+    // H2D | f32 copy -> search -> FP64 distortion + symbols -> D2H
     long pos = 0;
     int turn = 0;
+    std::vector<int> used((size_t) S, 0);
     while (pos < T) {
         Shard &s = shards_[turn];
-        QBuf &q = qbuf_[turn];
+        const int b = used[(size_t) turn]++ & 1;
+        QBuf &q = qbuf_[2 * (size_t) turn + b];
         const long n = T - pos < q.cap ? T - pos : q.cap;
         CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaStreamWaitEvent(s.copy_stream, s.ev_qfree[b], 0));
         CUDA_TRY(cudaMemcpyAsync(q.x64, x + (size_t) pos * D_, sizeof(double) * (size_t) n * D_,
-                                 cudaMemcpyHostToDevice, s.stream));
+                                 cudaMemcpyHostToDevice, s.copy_stream));
+        CUDA_TRY(cudaEventRecord(s.ev_chunk[b], s.copy_stream));
+        CUDA_TRY(cudaStreamWaitEvent(s.stream, s.ev_chunk[b], 0));
         if (!small_path()) {
             launch_convert_frames(q.x64, q.x32, n, D_, s.stream);
             ctr_.kernel_launches++;
@@ -895,6 +1010,7 @@ int Engine::quantize_host(const double *x, long T, uint16_t *seq_out, double *av
         if (seq_out)
             CUDA_TRY(cudaMemcpyAsync(seq_out + pos, q.seq, sizeof(uint16_t) * (size_t) n,
                                      cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaEventRecord(s.ev_qfree[b], s.stream));
         pos += n;
         turn = (turn + 1) % (int) S;
     }

@@ -22,6 +22,9 @@ struct Shard {
     int device = 0;
     int num_sms = 148;
     cudaStream_t stream = nullptr;
+    cudaStream_t copy_stream = nullptr;   // uploads that overlap the search (kmeans_pass_host)
+    cudaEvent_t ev_chunk[2] = {};
+    cudaEvent_t ev_qfree[2] = {};         // quantize_host: chunk buffer b may be overwritten
     cudaEvent_t ev[8] = {};   // phase boundaries of the current pass (ev[6], ev[7]: FP32 search)
     void *comm = nullptr;     // ncclComm_t
 
@@ -94,6 +97,12 @@ class Engine {
     // minDist / quantize summand, computed on the device) when raw = false
     int assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked, bool raw = true);
     int kmeans_pass(double *cells_out, int32_t *cardd_out, double *discel_out, double *DD_out);
+    // the same pass over n frames that are still in HOST memory (pinned for full speed): they
+    // replace the resident frame set, uploaded in chunks on a copy stream while the search of
+    // the previous chunk runs; cell sums, allreduce and update follow as in kmeans_pass.
+    // Single-process engines only (one or several local devices).
+    int kmeans_pass_host(const double *x, long n, double *cells_out, int32_t *cardd_out,
+                         double *discel_out, double *DD_out);
     int sigma(double avgDistortion, double *sigma_out);
     int inertia(double *inertia_out);
     int last_assignment(int32_t *idx_out, double *mindist_out);
@@ -121,6 +130,7 @@ class Engine {
     void pass_kernels(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
                       const SearchScratch &sc, double *mindist, uint16_t *seq, bool with_cells);
     int stage_codebook();  // raas -> search operands on every shard
+    int pass_tail(double *cells_out, int32_t *cardd_out, double *discel_out, double *DD_out);
     int sync_all();
     void harvest_times(bool with_cells);
 

@@ -63,7 +63,8 @@ EXPORTED_SYMBOLS = (
     "ecoz2b200_codebook_initial", "ecoz2b200_codebook_set_reflections",
     "ecoz2b200_codebook_set_raas", "ecoz2b200_codebook_grow", "ecoz2b200_codebook_size",
     "ecoz2b200_codebook_get",
-    "ecoz2b200_assign", "ecoz2b200_kmeans_pass", "ecoz2b200_sigma", "ecoz2b200_inertia",
+    "ecoz2b200_assign", "ecoz2b200_kmeans_pass", "ecoz2b200_kmeans_pass_host", "ecoz2b200_sigma",
+    "ecoz2b200_inertia",
     "ecoz2b200_last_assignment", "ecoz2b200_learn",
     "ecoz2b200_quantize_host", "ecoz2b200_quantize_resident",
     "ecoz2b200_counters_reset", "ecoz2b200_counters_get", "ecoz2b200_ffma_peak_tflops",
@@ -117,6 +118,7 @@ def lib():
             "ecoz2b200_codebook_get": (i, [vp, _dp, _dp]),
             "ecoz2b200_assign": (i, [vp, _ip, _dp, C.POINTER(l)]),
             "ecoz2b200_kmeans_pass": (i, [vp, _dp, _ip, _dp, _dp]),
+            "ecoz2b200_kmeans_pass_host": (i, [vp, vp, l, _dp, _ip, _dp, _dp]),
             "ecoz2b200_sigma": (i, [vp, d, _dp]),
             "ecoz2b200_inertia": (i, [vp, _dp]),
             "ecoz2b200_last_assignment": (i, [vp, _ip, _dp]),
@@ -291,6 +293,24 @@ class VqEngine:
                                            cardd.ctypes.data_as(_ip), _d(discel), C.byref(DD)),
                "kmeans_pass")
         return dict(cells=cells, cardd=cardd, discel=discel, DD=DD.value)
+
+    def kmeans_pass_host_ptr(self, host_ptr: int, n: int, want_cells: bool = True):
+        """One pass over n frames at host address host_ptr (pinned memory for full speed): the upload
+        overlaps the search chunk by chunk; the frames replace the resident set."""
+        K = self.K
+        cells = np.empty((K, self.D)) if want_cells else None
+        cardd = np.empty(K, np.int32)
+        discel = np.empty(K)
+        DD = C.c_double(0)
+        _check(lib().ecoz2b200_kmeans_pass_host(self._h, host_ptr, n, _d(cells) if want_cells else None,
+                                                cardd.ctypes.data_as(_ip), _d(discel), C.byref(DD)),
+               "kmeans_pass_host")
+        return dict(cells=cells, cardd=cardd, discel=discel, DD=DD.value)
+
+    def kmeans_pass_host(self, x: np.ndarray, want_cells: bool = True):
+        x = _f64(x)
+        assert x.ndim == 2 and x.shape[1] == self.D
+        return self.kmeans_pass_host_ptr(x.ctypes.data, x.shape[0], want_cells)
 
     def sigma(self, avg_distortion: float) -> float:
         out = C.c_double(0)

@@ -190,6 +190,14 @@ int ecoz2b200_assign(ecoz2b200_engine *e, int32_t *idx_out, double *ddmin_out,
 int ecoz2b200_kmeans_pass(ecoz2b200_engine *e, double *cells_out,
                           int32_t *cardd_out, double *discel_out,
                           double *DD_out);
+/* The same pass over n frames x[n][P+1] that are still in HOST memory (pinned memory for
+ * full speed): they replace the resident frame set and are uploaded in chunks on a copy
+ * stream while the search of the previous chunk runs, so the pass costs the PCIe transfer
+ * and little else.  Equivalent to frames_clear + frames_reserve + frames_append_host +
+ * frames_commit + kmeans_pass (same results; the frames stay resident afterwards).
+ * Single-process engines only.                                                     */
+int ecoz2b200_kmeans_pass_host(ecoz2b200_engine *e, const double *x, long n, double *cells_out,
+                               int32_t *cardd_out, double *discel_out, double *DD_out);
 
 /* reference calculateSigma, ecoz2/src/vq/sigma.c:12-29, on the engine's current
  * codebook and normalised cells (i.e. right after kmeans_pass). */

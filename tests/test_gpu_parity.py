@@ -294,3 +294,37 @@ def test_counters_and_launches(built_lib, frames36, oracle_run36):
     assert c["kernel_launches"] >= 4
     assert c["evals"] == len(frames36) * 128
     assert c["assign_ms"] > 0 and c["accumulate_ms"] > 0
+
+
+@pytest.mark.parametrize("K", [8, 300], ids=["K8", "K300"])
+def test_kmeans_pass_host_equals_resident_pass(built_lib, K):
+    """ecoz2b200_kmeans_pass_host (chunked upload overlapped with the search) gives the results of
+    frames_* + kmeans_pass: same cells, counts, distortions and updated codebook; the frames stay
+    resident (a following resident pass continues from the same state).  2.5M frames = 3 chunks."""
+    from ecoz2rs_b200 import vq
+    from ecoz2rs_b200.synth import ar_mix
+    from oracle import oracle as O
+    x = ar_mix(2_500_000, 12, seed=77)
+    rng = np.random.default_rng(K)
+    refl = np.zeros((K, 13))
+    refl[:, 1:] = np.clip(rng.normal(size=(K, 12)) * 0.3, -0.9, 0.9)
+    outs = []
+    for host in (False, True):
+        with vq.VqEngine(12, max_M=max(K, 2)) as eng:
+            eng.set_reflections(refl)
+            if host:
+                a = eng.kmeans_pass_host(x)
+            else:
+                eng.set_frames(x)
+                a = eng.kmeans_pass()
+            r1, _ = eng.codebook()
+            b = eng.kmeans_pass()            # resident frames of either path
+            assert eng.num_frames == x.shape[0]
+            outs.append((a, r1, b))
+    (a0, r0, b0), (a1, r1, b1) = outs
+    assert np.array_equal(a0["cardd"], a1["cardd"]) and np.array_equal(b0["cardd"], b1["cardd"])
+    assert np.allclose(a0["cells"], a1["cells"], rtol=1e-12, atol=1e-9)
+    assert np.allclose(a0["discel"], a1["discel"], rtol=1e-9, atol=1e-9)
+    assert abs(a0["DD"] - a1["DD"]) <= 1e-10 * abs(a0["DD"])
+    assert np.allclose(r0, r1, rtol=1e-10, atol=1e-13)
+    assert abs(b0["DD"] - b1["DD"]) <= 1e-9 * abs(b0["DD"])
