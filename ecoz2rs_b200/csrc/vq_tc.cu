@@ -32,7 +32,9 @@
 #include <cuda_fp16.h>
 #include <cfloat>
 #include <cmath>
+#include <cstdio>
 #include <cstdlib>
+#include <vector>
 
 namespace vqb200 {
 
@@ -264,6 +266,8 @@ struct TcParams {
     int32_t *exact_list;        // frames whose candidates did not fit: all-FP64 search
     int32_t *exact_count;
     int mc;                     // 1: launched as clusters of 2 CTAs that share the codeword stream
+    int raw_bufs;               // variant 2: staging buffers for raw frame halves (1 or 2)
+    unsigned long long *prof;   // dev (exp bit 256): per CTA {SM clocks, ns} of the kernel
     int exp;                    // dev experiments (ECOZ2_VQ_TC_EXP): bit mask 1 no record path, 2 trivial reduction, 4 no tcgen05.ld, 8 no MMA, 16 no tcgen05.st, 32 no B copy
 };
 
@@ -807,7 +811,7 @@ constexpr int kB2Stages = 3;
 
 struct Tc2Smem {
     uint64_t b_full[kB2Stages], b_empty[kB2Stages];
-    uint64_t raw_full, raw_empty;
+    uint64_t raw_full[2], raw_empty[2];   // raw-frame staging buffers (TcParams::raw_bufs of them)
     uint64_t a_full[4], a_free[4];        // [2 * frame-tile buffer + half]
     uint64_t acc_full[4], acc_empty[4];   // [2 * buffer + half]
     uint32_t tmem_slot;
@@ -817,6 +821,11 @@ struct Tc2Smem {
 template <int KS, bool FILTER, bool DBG, bool H16>
 __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) {
     const int exp = DBG ? p.exp : 0;
+    unsigned long long prof_c0 = 0, prof_t0 = 0;
+    if (DBG && p.prof != nullptr && threadIdx.x == 0) {
+        prof_c0 = clock64();
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(prof_t0));
+    }
     extern __shared__ __align__(1024) unsigned char smem_raw[];
     Tc2Smem *sm = reinterpret_cast<Tc2Smem *>(smem_raw);
     float *s_x0 = reinterpret_cast<float *>(smem_raw + 1024);      // [4 slots][2 halves][128]
@@ -838,8 +847,9 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
     constexpr uint32_t a_half_bytes = 2 * a_part_bytes;
     const uint32_t raw_bytes = (uint32_t) kBM * D * 4;               // 128 rows
     const uint32_t raw_stride = (raw_bytes + 127u) & ~127u;
-    float *raw_base = reinterpret_cast<float *>(smem_raw + hdr_bytes);
-    unsigned char *a_base = smem_raw + hdr_bytes + raw_stride;
+    unsigned char *raw_base = smem_raw + hdr_bytes;
+    const uint32_t RB = (uint32_t) p.raw_bufs;                       // 2 when shared memory allows
+    unsigned char *a_base = smem_raw + hdr_bytes + RB * raw_stride;
     const uint32_t tile_bytes = (uint32_t) BC * BN * 16;
     // the FP16 format leaves room for two frame tiles: the loaders run a whole tile ahead
     constexpr int ABUF = H16 ? 2 : 1;
@@ -857,8 +867,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             mbar_init(&sm->b_full[i], 1);
             mbar_init(&sm->b_empty[i], 1);
         }
-        mbar_init(&sm->raw_full, 1);
-        mbar_init(&sm->raw_empty, 4);
+        for (int i = 0; i < 2; i++) {
+            mbar_init(&sm->raw_full[i], 1);
+            mbar_init(&sm->raw_empty[i], 4);
+        }
         for (int i = 0; i < 4; i++) {
             mbar_init(&sm->a_full[i], 4);
             mbar_init(&sm->a_free[i], 1);
@@ -907,9 +919,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 for (int h = 0; h < 2; h++) {
                     const long base = ft * (2 * kBM) + h * kBM;
                     if (base + kBM > total) continue;
-                    mbar_wait_relaxed(&sm->raw_empty, (rs & 1) ^ 1);
-                    mbar_expect_tx(&sm->raw_full, raw_bytes);
-                    bulk_g2s(raw_base, p.x + base * D, raw_bytes, &sm->raw_full);
+                    const uint32_t rb = RB == 2 ? (rs & 1) : 0, rph = RB == 2 ? (rs >> 1) & 1 : rs & 1;
+                    mbar_wait_relaxed(&sm->raw_empty[rb], rph ^ 1);
+                    mbar_expect_tx(&sm->raw_full[rb], raw_bytes);
+                    bulk_g2s(raw_base + rb * raw_stride, p.x + base * D, raw_bytes, &sm->raw_full[rb]);
                     rs++;
                 }
             }
@@ -989,9 +1002,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 const bool staged = p.list == nullptr && base + kBM <= total && !(exp & 64);
                 float v[NE];
                 if (staged) {
-                    mbar_wait_relaxed(&sm->raw_full, rs & 1);
+                    const uint32_t rb = RB == 2 ? (rs & 1) : 0, rph = RB == 2 ? (rs >> 1) & 1 : rs & 1;
+                    mbar_wait_relaxed(&sm->raw_full[rb], rph);
                     rs++;
-                    const float *src = raw_base + r * D;
+                    const float *src = reinterpret_cast<const float *>(raw_base + rb * raw_stride) + r * D;
 #pragma unroll
                     for (int k = 0; k < NE; k++) v[k] = k < D ? src[k] : 0.f;
                     // the staging buffer may be overwritten as soon as raw_empty completes: the
@@ -1002,7 +1016,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                     for (int k = 0; k < NE; k++) dep ^= __float_as_uint(v[k]);
                     fence_proxy_async();   // generic reads before the async-proxy overwrite
                     const uint32_t all_in = __all_sync(0xffffffffu, dep != 0x7fc12345u);
-                    if (lane == 0) mbar_arrive_dep(&sm->raw_empty, all_in);
+                    if (lane == 0) mbar_arrive_dep(&sm->raw_empty[rb], all_in);
                 } else {
                     const bool valid = base + r < total;
                     const long row = valid ? (p.list ? (long) p.list[base + r] : base + r) : 0;
@@ -1140,6 +1154,12 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
     tc_fence_before();
     __syncthreads();
     if (warp == 13) tmem_dealloc(tmem_base, 512);
+    if (DBG && p.prof != nullptr && threadIdx.x == 0) {
+        unsigned long long t1;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t1));
+        p.prof[2 * blockIdx.x] = clock64() - prof_c0;
+        p.prof[2 * blockIdx.x + 1] = t1 - prof_t0;
+    }
 }
 
 // raas f64 [K][D] -> tiles [tile][hi, lo][k-chunk][row][4]  (zero padded; slot D = W1)
@@ -1371,12 +1391,16 @@ static size_t tc_smem_bytes(int D, int BN) {
     return 6144 + (size_t) 2 * 2 * (2 * ksteps) * kBM * 16 + (size_t) kStages * 4 * BN * 16 +
            (((size_t) kBM * D * 4 + 127) & ~(size_t) 127);
 }
-static size_t tc2_smem_bytes(int D, int BN) {
+static size_t tc2_smem_bytes(int D, int BN, int raw_bufs) {
     const size_t raw_stride = ((size_t) kBM * D * 4 + 127) & ~(size_t) 127;
     const size_t KC = (tc_f16() ? 1 : 2) * (size_t) tc_ksteps(D);   // chunks per split part
-    return (tc_f16() ? 9216 : 5120) + raw_stride + (tc_f16() ? 2 : 1) * 2 * (2 * KC * kBM * 16) +
+    return (tc_f16() ? 9216 : 5120) + raw_bufs * raw_stride + (tc_f16() ? 2 : 1) * 2 * (2 * KC * kBM * 16) +
            (size_t) kB2Stages * tc_row_chunks(D) * BN * 16;
 }
+// two staging buffers for the raw frame halves when they fit (the second hides the bulk-copy
+// latency behind the loaders' conversion of the first: it matters for small codebooks, where
+// the loaders are the critical path)
+static int tc2_raw_bufs(int D, int BN) { return tc2_smem_bytes(D, BN, 2) <= 227 * 1024 ? 2 : 1; }
 
 template <int KS, bool FILTER, bool DBG, bool H16>
 static void launch_tc2_inst2(const TcParams &p, long grid, cudaStream_t s) {
@@ -1386,7 +1410,7 @@ static void launch_tc2_inst2(const TcParams &p, long grid, cudaStream_t s) {
                              cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
         attr_set = true;
     }
-    vq_assign_tc2<KS, FILTER, DBG, H16><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN), s>>>(p);
+    vq_assign_tc2<KS, FILTER, DBG, H16><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN, p.raw_bufs), s>>>(p);
 }
 template <int KS, bool H16>
 static void launch_tc2_inst(const TcParams &p, long grid, cudaStream_t s) {
@@ -1396,6 +1420,7 @@ static void launch_tc2_inst(const TcParams &p, long grid, cudaStream_t s) {
 }
 // variant 2, any supported (format, k-steps)
 static void launch_tc2(TcParams &p, long grid, cudaStream_t s) {
+    p.raw_bufs = tc2_raw_bufs(p.D, p.BN);
     if (tc_f16()) {
         // the bound weights and the scale live behind the tiles (vq_prepare_codebook_tc2h)
         const float *w1h = p.wtc + tc_tiles_floats(p.K, p.D);
@@ -1443,6 +1468,20 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
     if (tc_variant() == 2) {
         long tiles = (n + 2 * kBM - 1) / (2 * kBM);
         long grid = tiles < num_sms ? tiles : num_sms;
+        if (p.exp & 256) {   // dev: SM clock seen by the kernel itself (clock64 vs globaltimer)
+            static unsigned long long *prof = nullptr;
+            if (!prof) cudaMalloc(&prof, sizeof(unsigned long long) * 2 * 1024);
+            p.prof = prof;
+            launch_tc2(p, grid, s);
+            std::vector<unsigned long long> h(2 * (size_t) grid);
+            cudaStreamSynchronize(s);
+            cudaMemcpy(h.data(), prof, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost);
+            double clk = 0, ns = 0;
+            for (long i = 0; i < grid; i++) { clk += (double) h[2 * i]; ns += (double) h[2 * i + 1]; }
+            fprintf(stderr, "[tc prof] n=%ld K=%d: %.3f ms per CTA, SM clock %.0f MHz, %.0f clk per CTA\n", n, K,
+                    ns / grid * 1e-6, clk / ns * 1e3, clk / grid);
+            return;
+        }
         launch_tc2(p, grid, s);
         return;
     }
