@@ -28,4 +28,11 @@ timeout 900 ncu --set full --clock-control none --import-source on \
     -k regex:"vq_assign_tc2|vq_cell_sums" --launch-skip 30 --launch-count 3 \
     -o $O/search_$TAG -f python scripts/perf_probe.py --n 2000000 --ks 2048 --reps 2 \
     > $O/ncu_full_$TAG.log 2>&1
+# DRAM traffic of the dominant kernel at the bench size (10M frames, K=2048): one launch
+timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none \
+    -k regex:"vq_assign_tc2" --launch-skip 22 --launch-count 1 --csv --log-file $O/traffic_$TAG.csv \
+    python scripts/perf_probe.py --n 10000000 --ks 2048 --reps 1 > $O/ncu_traffic_$TAG.log 2>&1
+# SM clock seen inside the search kernel (clock64 vs globaltimer), 20 back-to-back passes
+ECOZ2_VQ_TC_EXP=256 timeout 300 python scripts/perf_probe.py --n 10000000 --ks 2048 --reps 20 2>&1 \
+    | grep -E "tc prof|K=" | tail -4 > $O/clock_$TAG.log
 ls -la $O
