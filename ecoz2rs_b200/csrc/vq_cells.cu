@@ -17,6 +17,8 @@
 // distortion-only instance.
 #include "vq_kernels.cuh"
 
+#include <cstdlib>
+
 namespace vqb200 {
 
 namespace {
@@ -181,6 +183,116 @@ vq_cell_sums(const double *__restrict__ x64, const int32_t *__restrict__ perm,
     }
 }
 
+// D <= 16 (P <= 15): a row is at most 128 bytes, so one load instruction of the kernel above
+// would keep 16+ lanes idle.  Here a warp load covers TWO rows (lanes 0-15: row u, lanes 16-31:
+// row u + 1), 8 such loads in flight; the two half-warp sums meet in one shuffle at the end.
+__global__ void __launch_bounds__(256)
+vq_cell_sums_pair(const double *__restrict__ x64, const int32_t *__restrict__ perm,
+                  const int32_t *__restrict__ offsets, const int32_t *__restrict__ item_start, int K,
+                  int D, PackedLayout L, double *__restrict__ packed) {
+    const int lane = threadIdx.x & 31;
+    const int half = lane >> 4, m = lane & 15;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int n_warps = (gridDim.x * blockDim.x) >> 5;
+    const int n_items = item_start[K];
+    for (int item = warp; item < n_items; item += n_warps) {
+        int lo = 0, hi = K;
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (item_start[mid] <= item) lo = mid; else hi = mid;
+        }
+        const int c = lo;
+        const int first = offsets[c] + (item - item_start[c]) * kCellChunk;
+        const int last = min(first + kCellChunk, offsets[c + 1]);
+        double s = 0.0;
+        for (int g = first; g < last; g += 32) {
+            const int mine = g + lane < last ? perm[g + lane] : -1;
+            const int cnt = min(32, last - g);
+            for (int u = 0; u < cnt; u += 16) {
+                double xv[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const int src = u + 2 * k + half;             // this half-warp's row of pair k
+                    const long row = __shfl_sync(0xffffffffu, mine, src & 31);
+                    xv[k] = (src < cnt && m < D) ? x64[row * D + m] : 0.0;
+                }
+#pragma unroll
+                for (int k = 0; k < 8; k++) s += xv[k];
+            }
+        }
+        s += __shfl_down_sync(0xffffffffu, s, 16);
+        if (lane < D) atomicAdd(packed + L.cells() + (long) c * D + lane, s);
+    }
+}
+
+// ---- streaming variant for cell tables that fit in shared memory (K D 8 bytes <= ~200 KB:
+// every stage up to K = 512 at P = 36, every stage of the P = 12 configuration).
+// The frames are read ONCE in natural order, fully coalesced (a warp load = 32 consecutive doubles
+// of the frame array, whatever D is), and added into a shared-memory table [replica][K][D] with
+// FP64 compare-and-swap atomics (ATOMS.CAST.SPIN; shared memory has no native FP64 add); warps are
+// spread over R replicas of the table so that small codebooks do not serialise on a few addresses.
+// Reads 8 D bytes per frame instead of the gather of the sorted variant, whose 104..296-byte rows in
+// cell order cost 1.3-1.6x their size in DRAM atoms; pays ~10 instructions per element for the CAS
+// loop.  Used for short rows (D <= 20), where the gather is at its worst.  Counts go through a
+// shared int table.
+__global__ void __launch_bounds__(1024, 1)
+vq_cell_sums_stream(const double *__restrict__ x64, const int32_t *__restrict__ idx, long n, int K, int D,
+                    int R, PackedLayout L, double *__restrict__ packed, int32_t *__restrict__ hist,
+                    uint16_t *__restrict__ seq) {
+    extern __shared__ __align__(16) unsigned char cs_smem[];
+    double *tab = reinterpret_cast<double *>(cs_smem);                 // [R][K * D]
+    int32_t *cnt = reinterpret_cast<int32_t *>(tab + (size_t) R * K * D);   // [K]
+    const int KD = K * D;
+    for (int i = threadIdx.x; i < R * KD; i += blockDim.x) tab[i] = 0.0;
+    for (int i = threadIdx.x; i < K; i += blockDim.x) cnt[i] = 0;
+    __syncthreads();
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, n_warps = blockDim.x >> 5;
+    double *mytab = tab + (size_t) (warp % R) * KD;
+    // this CTA's contiguous range of frames, split into per-warp rounds of 32 doubles
+    const long per_cta = (n + gridDim.x - 1) / gridDim.x;
+    const long f_lo = (long) blockIdx.x * per_cta;
+    const long f_hi = f_lo + per_cta < n ? f_lo + per_cta : n;
+    if (f_lo < f_hi) {
+        const long e_lo = f_lo * D, e_hi = f_hi * D;                    // element range
+        // element offset -> (frame, component) by multiplication: q = floor(off / D) for every
+        // off with off * D < 2^32 (checked by the launcher)
+        const unsigned magic = (unsigned) ((0x100000000ull + (unsigned) D - 1) / (unsigned) D);
+        constexpr int U = 4;                                            // loads in flight per lane
+        for (long e0 = e_lo + (long) warp * 32 * U; e0 < e_hi; e0 += (long) n_warps * 32 * U) {
+            double v[U];
+            long e[U];
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                e[u] = e0 + u * 32 + lane;
+                v[u] = e[u] < e_hi ? x64[e[u]] : 0.0;
+            }
+#pragma unroll
+            for (int u = 0; u < U; u++) {
+                if (e[u] < e_hi) {
+                    const unsigned off = (unsigned) (e[u] - e_lo);
+                    const unsigned fr = __umulhi(off, magic);
+                    const int m = (int) (off - fr * (unsigned) D);
+                    const long f = f_lo + fr;
+                    const int c = idx[f];
+                    atomicAdd(mytab + c * D + m, v[u]);
+                    if (m == 0) {
+                        atomicAdd(cnt + c, 1);
+                        if (seq) seq[f] = (uint16_t) c;
+                    }
+                }
+            }
+        }
+    }
+    __syncthreads();
+    for (int i = threadIdx.x; i < KD; i += blockDim.x) {
+        double s = tab[i];
+        for (int r = 1; r < R; r++) s += tab[(size_t) r * KD + i];
+        if (s != 0.0) atomicAdd(packed + L.cells() + i, s);
+    }
+    for (int i = threadIdx.x; i < K; i += blockDim.x)
+        if (cnt[i]) atomicAdd(hist + i, cnt[i]);
+}
+
 // counts, per-cell distortion  cellsum . w - count,  DD = sum of them; one warp per cell
 __global__ void __launch_bounds__(256)
 vq_cell_finish(const double *__restrict__ raas, const int32_t *__restrict__ hist, int K, int D,
@@ -233,11 +345,42 @@ void cell_scratch_carve(void *base, long cap, int max_K, CellScratch *out) {
     out->cap = cap;
 }
 
+// shared memory of the streaming variant with R table replicas
+static size_t stream_smem_bytes(int K, int D, int R) {
+    return sizeof(double) * (size_t) R * K * D + sizeof(int32_t) * (size_t) K;
+}
+static bool cell_stream_enabled() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("ECOZ2_VQ_CELL_STREAM"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v == 1;
+}
+
 void launch_cell_sums(const double *x64, const int32_t *idx, long n, int D, const double *raas,
                       int K, double *packed, uint16_t *seq, const CellScratch &cs, int num_sms,
                       cudaStream_t s) {
     const PackedLayout L{K, D};
     cudaMemsetAsync(cs.hist, 0, sizeof(int32_t) * (size_t) (K + 1), s);
+    constexpr size_t kStreamSmemMax = 200 * 1024;
+    const long stream_grid = n > 0 ? ((n + 4095) / 4096 < num_sms ? (n + 4095) / 4096 : num_sms) : 1;
+    const long per_cta = (n + stream_grid - 1) / stream_grid;
+    // measured on B200 (10M x P=36: 0.75 ms either way -- the CAS atomics cost what the gather
+    // loses; 20M x P=12: 0.57-0.67 ms against 0.88-1.02): worth it for short rows only
+    if (n > 0 && cell_stream_enabled() && D <= 20 && stream_smem_bytes(K, D, 1) <= kStreamSmemMax &&
+        (double) per_cta * D * D < 4.0e9) {
+        int R = (int) ((kStreamSmemMax - sizeof(int32_t) * (size_t) K) / (sizeof(double) * (size_t) K * D));
+        if (R > 32) R = 32;
+        static bool attr_set = false;
+        if (!attr_set) {
+            cudaFuncSetAttribute(vq_cell_sums_stream, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                 (int) kStreamSmemMax);
+            attr_set = true;
+        }
+        const long grid = stream_grid;
+        vq_cell_sums_stream<<<(unsigned) grid, 1024, stream_smem_bytes(K, D, R), s>>>(
+            x64, idx, n, K, D, R, L, packed, cs.hist, seq);
+        vq_cell_finish<<<(K * 32 + 255) / 256, 256, 0, s>>>(raas, cs.hist, K, D, L, packed);
+        return;
+    }
     if (n > 0) {
         const size_t smem = sizeof(int32_t) * (size_t) K;
         long blocks = (n + 256 * 32 - 1) / (256 * 32);
@@ -251,7 +394,9 @@ void launch_cell_sums(const double *x64, const int32_t *idx, long n, int D, cons
         if (blocks > (long) num_sms * 4) blocks = (long) num_sms * 4;
         vq_cell_scatter<<<(unsigned) blocks, 256, smem, s>>>(idx, n, K, cs.cursor, cs.perm);
         const int grid = num_sms * 8;
-        switch ((D + 31) / 32) {
+        if (D <= 16) {
+            vq_cell_sums_pair<<<grid, 256, 0, s>>>(x64, cs.perm, cs.offsets, cs.item_start, K, D, L, packed);
+        } else switch ((D + 31) / 32) {
             case 1: vq_cell_sums<1><<<grid, 256, 0, s>>>(x64, cs.perm, cs.offsets, cs.item_start, K, D, L, packed); break;
             case 2: vq_cell_sums<2><<<grid, 256, 0, s>>>(x64, cs.perm, cs.offsets, cs.item_start, K, D, L, packed); break;
             case 3: vq_cell_sums<3><<<grid, 256, 0, s>>>(x64, cs.perm, cs.offsets, cs.item_start, K, D, L, packed); break;
