@@ -346,33 +346,39 @@ __device__ __forceinline__ void epi_step32(const uint32_t (&r)[32], int col0, in
         }
         return;
     }
-    const float a0 = fminf(min3f(F(0), F(1), F(2)), F(3));
-    const float b0 = fminf(min3f(F(16), F(17), F(18)), F(19));
-    const float a1 = fminf(min3f(F(4), F(5), F(6)), F(7));
-    const float b1 = fminf(min3f(F(20), F(21), F(22)), F(23));
-    const float a2 = fminf(min3f(F(8), F(9), F(10)), F(11));
-    const float b2 = fminf(min3f(F(24), F(25), F(26)), F(27));
-    const float a3 = fminf(min3f(F(12), F(13), F(14)), F(15));
-    const float b3 = fminf(min3f(F(28), F(29), F(30)), F(31));
-    const float mA = fminf(min3f(a0, a1, a2), a3);
-    const float mB = fminf(min3f(b0, b1, b2), b3);
+    // minimum of each 16-codeword chunk in 8 three-input ops (16 -> 6 -> 2 -> 1), the two
+    // chunks interleaved: two independent dependency chains
+    const float a0 = min3f(F(0), F(1), F(2)), b0 = min3f(F(16), F(17), F(18));
+    const float a1 = min3f(F(3), F(4), F(5)), b1 = min3f(F(19), F(20), F(21));
+    const float a2 = min3f(F(6), F(7), F(8)), b2 = min3f(F(22), F(23), F(24));
+    const float a3 = min3f(F(9), F(10), F(11)), b3 = min3f(F(25), F(26), F(27));
+    const float a4 = min3f(F(12), F(13), F(14)), b4 = min3f(F(28), F(29), F(30));
+    const float a5 = min3f(a0, a1, F(15)), b5 = min3f(b0, b1, F(31));
+    const float a6 = min3f(a2, a3, a4), b6 = min3f(b2, b3, b4);
+    const float mA = fminf(a5, a6), mB = fminf(b5, b6);
     const float m = fminf(mA, mB);
     const bool rec = m < st.best;
     // contenders for runner-up: the larger chunk minimum always; m itself unless it is the new
     // best, in which case the old best is
     st.second = min3f(st.second, fmaxf(m, st.best), fmaxf(mA, mB));
     st.best = fminf(st.best, m);
-    if (!(exp & 1) && __any_sync(0xffffffffu, rec)) {
+    if (!(exp & 1)) {
+        // snapshot of the record chunk; the two chunks vote separately -- late in the codebook a
+        // step sees records in one or two lanes, i.e. usually in one chunk only
         const bool ra_ = rec && mA <= mB, rb_ = rec && !(mA <= mB);
-        if (ra_) {
+        if (__any_sync(0xffffffffu, ra_)) {
+            if (ra_) {
 #pragma unroll
-            for (int j = 0; j < 16; j++) st.snap[j] = F(j);
-            st.col = col0;
+                for (int j = 0; j < 16; j++) st.snap[j] = F(j);
+                st.col = col0;
+            }
         }
-        if (rb_) {
+        if (__any_sync(0xffffffffu, rb_)) {
+            if (rb_) {
 #pragma unroll
-            for (int j = 0; j < 16; j++) st.snap[j] = F(16 + j);
-            st.col = col0 + 16;
+                for (int j = 0; j < 16; j++) st.snap[j] = F(16 + j);
+                st.col = col0 + 16;
+            }
         }
     }
 #undef F
