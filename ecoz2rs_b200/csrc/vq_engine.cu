@@ -555,7 +555,7 @@ int Engine::debug_tc_distortions(float *out, long n_rows) {
     Shard &s = shards_[0];
     CUDA_TRY(cudaSetDevice(s.device));
     if (n_rows > s.n) n_rows = s.n;
-    const int BN = tc_tile_cols(K_);
+    const int BN = tc_tile_cols(K_, D_);
     const int ld = (K_ + BN - 1) / BN * BN;
     float *dump = nullptr;
     CUDA_TRY(cudaMalloc(&dump, sizeof(float) * (size_t) n_rows * ld));

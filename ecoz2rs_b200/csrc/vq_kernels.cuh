@@ -94,7 +94,7 @@ bool assign_tc_supported(int K, int D);
 bool filter_tc_supported();
 void launch_filter_tc(const float *x32, long n_cap, int D, const float *wtc, int K,
                       const SearchScratch &sc, float err_scale, int num_sms, cudaStream_t s);
-int tc_tile_cols(int K);
+int tc_tile_cols(int K, int D);
 size_t tc_codebook_floats(int K, int D);
 int tc_issued_flops_per_eval(int D, int *is_f16);
 void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, const float *w1max,

@@ -837,6 +837,8 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
     float *s_x0 = reinterpret_cast<float *>(smem_raw + 1024);      // [4 slots][2 halves][128]
     const int D = p.D;
     const int BN = p.BN;
+    const bool wide = BN == 256;                  // UMMA N = 256: see tc_tile_cols
+    const uint32_t n_bstages = wide ? 2 : kB2Stages;
     // KS = MMAs per product term (TF32 format, 8 elements each) or 8-element chunks per split
     // part (FP16 format); either way a part of a row is KC 16-byte chunks
     constexpr int KC = H16 ? KS : 2 * KS;
@@ -913,7 +915,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                         bulk_g2s(b_base + (size_t) st * tile_bytes, src, tile_bytes, &sm->b_full[st]);
                     }
                     src += tile_bytes;
-                    if (++st == kB2Stages) { st = 0; ph ^= 1; }
+                    if (++st == n_bstages) { st = 0; ph ^= 1; }
                 }
             }
         }
@@ -949,16 +951,18 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         uint32_t st = 0, ph = 0, u = 0, it = 0;
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
             for (int t = 0; t < n_wtiles; t++, u++) {
-                const uint32_t buf = u & 1;
+                // 128-column tiles: two accumulators per half (ping-pong); 256-column tiles: one per
+                // half, the halves themselves alternate between the tensor core and the epilogue
+                const uint32_t buf = wide ? 0u : (u & 1), acc_ph = wide ? (u & 1) : ((u >> 1) & 1);
                 for (int h = 0; h < 2; h++) {
                     const uint32_t ab = ABUF == 2 ? (it & 1) : 0, aph = ABUF == 2 ? (it >> 1) & 1 : it & 1;
                     if (t == 0) mbar_wait(&sm->a_full[2 * ab + h], aph);
-                    mbar_wait(&sm->acc_empty[2 * buf + h], ((u >> 1) & 1) ^ 1);
+                    mbar_wait(&sm->acc_empty[2 * buf + h], acc_ph ^ 1);
                     if (h == 0) mbar_wait(&sm->b_full[st], ph);
                     tc_fence_after();
                     const uint64_t dah = dA0 + (uint32_t) (2 * ab + h) * a_half16, dal = dah + a_part16;
                     const uint64_t dbh = dB0 + st * b_tile16, dbl = dbh + b_part16;
-                    const uint32_t d_tmem = tmem_base + (2 * buf + h) * 128;
+                    const uint32_t d_tmem = tmem_base + (wide ? (uint32_t) h * 256u : (2 * buf + h) * 128u);
                     if (elect_one()) {
                         // small cross terms first, the dominant hi*hi products last
                         if (!(exp & 8)) {
@@ -993,7 +997,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                         if (h == 1) umma_commit(&sm->b_empty[st]);
                     }
                     __syncwarp();
-                    if (h == 1 && ++st == kB2Stages) { st = 0; ph ^= 1; }
+                    if (h == 1 && ++st == n_bstages) { st = 0; ph ^= 1; }
                 }
             }
         }
@@ -1111,13 +1115,15 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             fst.init();
             if (FILTER && row >= 0) thr = p.flag_ub[base + r];
             for (int t = 0; t < n_wtiles; t++, u++) {
-                const uint32_t buf = u & 1;
-                mbar_wait(&sm->acc_full[2 * buf + h], (u >> 1) & 1);
+                const uint32_t buf = wide ? 0u : (u & 1), acc_ph = wide ? (u & 1) : ((u >> 1) & 1);
+                mbar_wait(&sm->acc_full[2 * buf + h], acc_ph);
                 tc_fence_after();
                 const int nv = K - t * BN < BN ? K - t * BN : BN;
-                const uint32_t taddr = lane_addr + (2 * buf + h) * 128;
+                const uint32_t taddr = lane_addr + (wide ? (uint32_t) h * 256u : (2 * buf + h) * 128u);
                 const bool fast = !FILTER && (!DBG || (!(exp & 7) && p.dump == nullptr));
-                if (fast && nv == 128) {
+                if (fast && nv == 256) {
+                    epi_tile_full<256>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
+                } else if (fast && nv == 128) {
                     epi_tile_full<128>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
                 } else if (fast && nv == 64) {
                     epi_tile_full<64>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
@@ -1350,8 +1356,24 @@ static int tc_min_k() {
     return v;
 }
 
-int tc_tile_cols(int K) {
-    if (tc_variant() == 2) return K >= 128 ? 128 : 64;
+// Variant 2, FP16 format: 256-column tiles for K >= 256.  A 128x256x16 MMA fetches 96 operand
+// wavefronts in its 128 clocks and runs at the compute floor; a 128x128x16 one fetches 64 in 64
+// and was measured at 73 clk alone, 84 with the epilogue's tcgen05.ld traffic, ~100 in the kernel
+// (scripts/exp/ldtm_bench).  TMEM then holds ONE accumulator per 128-frame half: the two halves
+// alternate between the tensor core and the epilogue.  ECOZ2_VQ_TC_WIDE=0 keeps 128.
+static bool tc_wide() {
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("ECOZ2_VQ_TC_WIDE");
+        v = (tc_variant() == 2 && !(e && e[0] == '0')) ? 1 : 0;
+    }
+    return v == 1;
+}
+
+int tc_tile_cols(int K, int D) {
+    // (wide tiles need 2 x 13 chunks x 4 KB for D + 1 > 40: no room next to the frame tiles)
+    if (tc_variant() == 2)
+        return (K >= 256 && tc_f16() && tc_wide() && tc_ksteps(D) <= 5) ? 256 : (K >= 128 ? 128 : 64);
     return K >= 256 ? 256 : (K > 64 ? 128 : 64);
 }
 
@@ -1367,20 +1389,20 @@ bool assign_tc_supported(int K, int D) { return K >= tc_min_k() && tc_ksteps(D) 
 
 // floats of the tiles themselves: n_wtiles x [hi, lo] x (2 ksteps chunks) x BN rows x 16 bytes
 static size_t tc_tiles_floats(int K, int D) {
-    const int BN = tc_tile_cols(K);
+    const int BN = tc_tile_cols(K, D);
     const int n_wtiles = (K + BN - 1) / BN;
     return (size_t) n_wtiles * tc_row_chunks(D) * BN * 4;
 }
 // + (FP16 format) the scaled bound weights W1'_j per padded codeword and the scale G
 size_t tc_codebook_floats(int K, int D) {
-    const int BN = tc_tile_cols(K);
+    const int BN = tc_tile_cols(K, D);
     const int n_wtiles = (K + BN - 1) / BN;
     return tc_tiles_floats(K, D) + (size_t) n_wtiles * BN + 4;
 }
 
 void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, const float *w1max,
                                 float err_scale, cudaStream_t s) {
-    const int BN = tc_tile_cols(K), ksteps = tc_ksteps(D);
+    const int BN = tc_tile_cols(K, D), ksteps = tc_ksteps(D);
     const long items = (long) ((K + BN - 1) / BN) * ksteps * 2 * BN;
     const int blocks = (int) ((items + 255) / 256);
     if (tc_f16())
@@ -1401,7 +1423,7 @@ static size_t tc2_smem_bytes(int D, int BN, int raw_bufs) {
     const size_t raw_stride = ((size_t) kBM * D * 4 + 127) & ~(size_t) 127;
     const size_t KC = (tc_f16() ? 1 : 2) * (size_t) tc_ksteps(D);   // chunks per split part
     return (tc_f16() ? 9216 : 5120) + raw_bufs * raw_stride + (tc_f16() ? 2 : 1) * 2 * (2 * KC * kBM * 16) +
-           (size_t) kB2Stages * tc_row_chunks(D) * BN * 16;
+           (size_t) (BN == 256 ? 2 : kB2Stages) * tc_row_chunks(D) * BN * 16;
 }
 // two staging buffers for the raw frame halves when they fit (the second hides the bulk-copy
 // latency behind the loaders' conversion of the first: it matters for small codebooks, where
@@ -1459,7 +1481,7 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
     TcParams p{};
     p.x = x32; p.n_frames = n; p.D = D; p.ksteps = tc_ksteps(D);
     p.list = list; p.list_count = list_count;
-    p.wtc = wtc; p.K = K; p.BN = tc_tile_cols(K);
+    p.wtc = wtc; p.K = K; p.BN = tc_tile_cols(K, D);
     p.w1 = w1; p.w1max = w1max; p.err_scale = err_scale; p.idx_out = idx;
     if (flag) {
         p.flag_list = sc.flag_list; p.flag_count = sc.counters + 0; p.flag_ub = sc.flag_ub;
@@ -1533,7 +1555,7 @@ void launch_filter_tc(const float *x32, long n_cap, int D, const float *wtc, int
     TcParams p{};
     p.x = x32; p.n_frames = n_cap; p.D = D; p.ksteps = tc_ksteps(D);
     p.list = sc.flag_list; p.list_count = sc.counters + 0;
-    p.wtc = wtc; p.K = K; p.BN = tc_tile_cols(K);
+    p.wtc = wtc; p.K = K; p.BN = tc_tile_cols(K, D);
     p.err_scale = err_scale; p.flag_ub = sc.flag_ub;
     p.cand = sc.cand; p.cand_count = sc.counters + 1; p.cand_cap = (int) sc.cand_cap;
     p.exact_list = sc.exact_list; p.exact_count = sc.counters + 2;
