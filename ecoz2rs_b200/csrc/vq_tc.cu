@@ -949,6 +949,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         const uint32_t b_tile16 = tile_bytes >> 4, b_part16 = (uint32_t) (KC * BN * 16) >> 4;
         const uint32_t b_k16 = (uint32_t) (2 * BN * 16) >> 4;
         uint32_t st = 0, ph = 0, u = 0, it = 0;
+        long long pw_a = 0, pw_e = 0, pw_b = 0;   // dev (exp bit 256): clocks spent waiting
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
             for (int t = 0; t < n_wtiles; t++, u++) {
                 // 128-column tiles: two accumulators per half (ping-pong); 256-column tiles: one per
@@ -956,9 +957,16 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 const uint32_t buf = wide ? 0u : (u & 1), acc_ph = wide ? (u & 1) : ((u >> 1) & 1);
                 for (int h = 0; h < 2; h++) {
                     const uint32_t ab = ABUF == 2 ? (it & 1) : 0, aph = ABUF == 2 ? (it >> 1) & 1 : it & 1;
+                    const long long pc0 = DBG ? clock64() : 0;
                     if (t == 0) mbar_wait(&sm->a_full[2 * ab + h], aph);
+                    const long long pc1 = DBG ? clock64() : 0;
                     mbar_wait(&sm->acc_empty[2 * buf + h], acc_ph ^ 1);
+                    const long long pc2 = DBG ? clock64() : 0;
                     if (h == 0) mbar_wait(&sm->b_full[st], ph);
+                    if (DBG) {
+                        const long long pc3 = clock64();
+                        pw_a += pc1 - pc0; pw_e += pc2 - pc1; pw_b += pc3 - pc2;
+                    }
                     tc_fence_after();
                     const uint64_t dah = dA0 + (uint32_t) (2 * ab + h) * a_half16, dal = dah + a_part16;
                     const uint64_t dbh = dB0 + st * b_tile16, dbl = dbh + b_part16;
@@ -1000,6 +1008,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                     if (h == 1 && ++st == n_bstages) { st = 0; ph ^= 1; }
                 }
             }
+        }
+        if (DBG && p.prof != nullptr && lane == 0) {
+            unsigned long long *o = p.prof + 2048 + 8 * blockIdx.x;
+            o[0] = pw_a; o[1] = pw_e; o[2] = pw_b;
         }
     } else if (warp < 4) {
         // ===== frame loaders: thread = frame row =====
@@ -1105,6 +1117,8 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         const uint32_t lane_addr = tmem_base + ((uint32_t) (q * 32) << 16);
         const float e2 = 2.f * 1.001f * p.err_scale;
         uint32_t u = 0, it = 0;
+        long long pw_f = 0;   // dev (exp bit 256): clocks spent waiting for accumulators
+        const long long pw_t0 = DBG ? clock64() : 0;
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
             const long base = ft * (2 * kBM) + h * kBM;
             const long row = base + r < total ? (p.list ? (long) p.list[base + r] : base + r) : -1;
@@ -1116,7 +1130,9 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             if (FILTER && row >= 0) thr = p.flag_ub[base + r];
             for (int t = 0; t < n_wtiles; t++, u++) {
                 const uint32_t buf = wide ? 0u : (u & 1), acc_ph = wide ? (u & 1) : ((u >> 1) & 1);
+                const long long pc0 = DBG ? clock64() : 0;
                 mbar_wait(&sm->acc_full[2 * buf + h], acc_ph);
+                if (DBG) pw_f += clock64() - pc0;
                 tc_fence_after();
                 const int nv = K - t * BN < BN ? K - t * BN : BN;
                 const uint32_t taddr = lane_addr + (wide ? (uint32_t) h * 256u : (2 * buf + h) * 128u);
@@ -1160,6 +1176,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                     }
                 }
             }
+        }
+        if (DBG && p.prof != nullptr && lane == 0 && q == 0) {
+            unsigned long long *o = p.prof + 2048 + 8 * blockIdx.x + 3 + 2 * h;
+            o[0] = pw_f; o[1] = clock64() - pw_t0;
         }
     }
 
@@ -1498,16 +1518,25 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
         long grid = tiles < num_sms ? tiles : num_sms;
         if (p.exp & 256) {   // dev: SM clock seen by the kernel itself (clock64 vs globaltimer)
             static unsigned long long *prof = nullptr;
-            if (!prof) cudaMalloc(&prof, sizeof(unsigned long long) * 2 * 1024);
+            if (!prof) cudaMalloc(&prof, sizeof(unsigned long long) * 10 * 1024);
+            cudaMemsetAsync(prof, 0, sizeof(unsigned long long) * 10 * 1024, s);
             p.prof = prof;
             launch_tc2(p, grid, s);
-            std::vector<unsigned long long> h(2 * (size_t) grid);
+            std::vector<unsigned long long> h(10 * 1024);
             cudaStreamSynchronize(s);
             cudaMemcpy(h.data(), prof, sizeof(unsigned long long) * h.size(), cudaMemcpyDeviceToHost);
             double clk = 0, ns = 0;
             for (long i = 0; i < grid; i++) { clk += (double) h[2 * i]; ns += (double) h[2 * i + 1]; }
             fprintf(stderr, "[tc prof] n=%ld K=%d: %.3f ms per CTA, SM clock %.0f MHz, %.0f clk per CTA\n", n, K,
                     ns / grid * 1e-6, clk / ns * 1e3, clk / grid);
+            // where the roles of CTA 0.. wait (clocks, mean over CTAs): MMA issuer for frames /
+            // free accumulator / codeword tile; epilogue of half 0 and 1 for a full accumulator
+            double w[7] = {0, 0, 0, 0, 0, 0, 0};
+            for (long i = 0; i < grid; i++)
+                for (int k = 0; k < 7; k++) w[k] += (double) h[2048 + 8 * i + k] / grid;
+            fprintf(stderr, "[tc prof]   MMA issuer waits: frames %.0f, accumulator %.0f, codewords %.0f | epilogue 0: "
+                            "waits %.0f of %.0f | epilogue 1: waits %.0f of %.0f\n",
+                    w[0], w[1], w[2], w[3], w[4], w[5], w[6]);
             return;
         }
         launch_tc2(p, grid, s);

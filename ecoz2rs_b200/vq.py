@@ -22,7 +22,7 @@ from typing import Callable, Optional, Sequence
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "csrc", "libecoz2_vq_b200.so")
+LIB_PATH = os.environ.get("ECOZ2_VQ_B200_LIB") or os.path.join(_HERE, "csrc", "libecoz2_vq_b200.so")
 
 MODE_FP32, MODE_FP64, MODE_TF32X3 = 0, 1, 2
 
