@@ -1,0 +1,355 @@
+// lpc_front.cu -- the LPC front end of the VQ path on sm_100a:
+// signal -> frames -> mean removal, pre-emphasis, Hamming window -> autocorrelation r[0..P]
+// -> Levinson-Durbin prediction error -> gain-normalised vectors r / errPred, i.e. the
+// content of a `.prd` file, produced in device memory.
+//
+// Reference: ecoz2/src/lpc/lpa_on_signal.c:81-157 (framing :96-101, window pipeline :24-80,
+// normalisation :143-150) and ecoz2/src/lpc/lpca.c:9-59 (autocorrelation :16-21, recursion
+// :27-47).  All arithmetic is FP64 like the reference (sample_t = double, sgn.h:11).
+//
+// Two kernels:
+//   lpc_autocorr<LAGS>   FP64-FMA bound.  A CTA stages the contiguous stretch of signal that
+//       its G overlapping frames cover in shared memory once (a 45 ms window every 15 ms
+//       re-uses each sample three times) together with the Hamming table.  Eight lanes share
+//       a frame: each takes a contiguous eighth of the window and keeps LAGS running sums plus
+//       a sliding register window of the windowed samples, so one new sample costs a few
+//       shared-memory loads against LAGS FMAs with register operands.  Windowed samples are
+//       recomputed on the fly from the raw ones -- no per-frame copy exists anywhere.
+//   lpc_levinson<PMAX>   thread = frame, the recursion fully unrolled in registers, same
+//       operation order as lpca.c; divides the vector by the final prediction error in place.
+#include <cuda_runtime.h>
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+
+#include <string>
+#include <vector>
+
+#include "lpc_front.h"
+
+namespace lpcb200 {
+
+namespace {
+
+constexpr int kLanesPerFrame = 8;
+constexpr int kStep = 8;   // window positions per unrolled block
+
+struct AcParams {
+    const double *signal;   // [num_samples]
+    const double *hamming;  // [win] (windowed mode)
+    double *r;              // [T][ld]
+    long T;
+    int win, off, P, ld;
+    int frames_per_cta;     // G
+    int staged;             // signal stretch + Hamming table in shared memory
+    int windowed;           // 0: plain autocorrelation of each frame (ecoz2_lpca)
+};
+
+// windowed sample n of a frame (0 outside [0, N)): lpa_on_signal.c:42-80
+__device__ __forceinline__ double win_sample(const double *x, const double *h, int n, int N, double mean,
+                                             bool windowed) {
+    if (n >= N) return 0.0;
+    const double d0 = x[n];
+    if (!windowed) return d0;
+    const double c0 = d0 - mean;
+    const double c1 = n > 0 ? x[n - 1] - mean : 0.0;
+    return (c0 - .95 * c1) * h[n];
+}
+
+template <int LAGS>
+__global__ void __launch_bounds__(256, 1) lpc_autocorr(const AcParams p) {
+    extern __shared__ __align__(16) unsigned char lpc_smem[];
+    const int G = p.frames_per_cta;
+    const long t0 = (long) blockIdx.x * G;
+    const int g = threadIdx.x / kLanesPerFrame, j = threadIdx.x % kLanesPerFrame;
+    const int N = p.win;
+    const double *xs;   // samples of frame t0 (shared or global)
+    const double *hs;
+    if (p.staged) {
+        double *s_sig = reinterpret_cast<double *>(lpc_smem);
+        const long n_frames = p.T - t0 < G ? p.T - t0 : G;
+        const int span = (int) (n_frames - 1) * p.off + N;
+        double *s_ham = s_sig + (size_t) (G - 1) * p.off + N;
+        const double *src = p.signal + t0 * p.off;
+        for (int i = threadIdx.x; i < span; i += blockDim.x) s_sig[i] = src[i];
+        if (p.windowed)
+            for (int i = threadIdx.x; i < N; i += blockDim.x) s_ham[i] = p.hamming[i];
+        __syncthreads();
+        xs = s_sig;
+        hs = s_ham;
+    } else {
+        xs = p.signal + t0 * p.off;
+        hs = p.hamming;
+    }
+    const long t = t0 + g;
+    if (g >= G || t >= p.T) return;   // whole 8-lane groups leave together
+    const double *x = xs + (size_t) g * p.off;
+    const unsigned gmask = 0xffu << ((threadIdx.x & 31) & ~7);
+    const bool windowed = p.windowed != 0;
+
+    // this lane's eighth of the window
+    const int L = (N + kLanesPerFrame - 1) / kLanesPerFrame;
+    const int c0 = j * L, c1 = c0 + L < N ? c0 + L : N;
+
+    double mean = 0.0;
+    if (windowed) {
+        double s = 0.0;
+        for (int n = c0; n < c1; n++) s += x[n];
+        s += __shfl_xor_sync(gmask, s, 4);
+        s += __shfl_xor_sync(gmask, s, 2);
+        s += __shfl_xor_sync(gmask, s, 1);
+        mean = s / N;
+    }
+
+    for (int l0 = 0; l0 <= p.P; l0 += LAGS) {
+        double acc[LAGS];
+#pragma unroll
+        for (int i = 0; i < LAGS; i++) acc[i] = 0.0;
+        // wb[q] = y(k + l0 + q), q < LAGS + kStep - 1
+        double wb[LAGS + kStep - 1];
+#pragma unroll
+        for (int q = 0; q < LAGS - 1; q++) wb[q] = win_sample(x, hs, c0 + l0 + q, N, mean, windowed);
+        for (int k = c0; k < c1; k += kStep) {
+            double a[kStep];
+#pragma unroll
+            for (int u = 0; u < kStep; u++) {
+                a[u] = k + u < c1 ? win_sample(x, hs, k + u, N, mean, windowed) : 0.0;
+                wb[LAGS - 1 + u] = win_sample(x, hs, k + l0 + LAGS - 1 + u, N, mean, windowed);
+            }
+#pragma unroll
+            for (int u = 0; u < kStep; u++)
+#pragma unroll
+                for (int i = 0; i < LAGS; i++) acc[i] = fma(a[u], wb[u + i], acc[i]);
+#pragma unroll
+            for (int q = 0; q < LAGS - 1; q++) wb[q] = wb[q + kStep];
+        }
+        double *out = p.r + t * p.ld + l0;
+#pragma unroll
+        for (int i = 0; i < LAGS; i++) {
+            double s = acc[i];
+            s += __shfl_xor_sync(gmask, s, 4);
+            s += __shfl_xor_sync(gmask, s, 2);
+            s += __shfl_xor_sync(gmask, s, 1);
+            if ((i % kLanesPerFrame) == j && l0 + i <= p.P) out[i] = s;
+        }
+    }
+}
+
+struct LvParams {
+    double *r;        // [T][ld], divided by the prediction error in place when normalise != 0
+    long T;
+    int P, ld, normalise;
+    double *rc;       // optional [T][ld]: reflection coefficients (index 1..P)
+    double *a;        // optional [T][ld]: predictor coefficients
+    double *pe;       // optional [T]
+    int *status;      // optional [T]: lpca's return value (0, 1: r0 == 0, 2: error <= 0)
+    int *err_count;   // frames with status != 0
+};
+
+// lpca.c:23-47, the recursion proper (arrays indexed 0..P)
+#define LPC_LEVINSON_BODY(UNROLL_PRAGMA)                                                     \
+    int status = 0;                                                                          \
+    double pe = rr[0];                                                                       \
+    if (rr[0] == 0.0) {                                                                      \
+        status = 1;                                                                          \
+    } else {                                                                                 \
+        a[0] = 1.0;                                                                          \
+        bool live = true;                                                                    \
+        UNROLL_PRAGMA                                                                        \
+        for (int k = 1; k <= KMAX; k++) {                                                    \
+            if (k <= P && live) {                                                            \
+                double sum = 0.0;                                                            \
+                UNROLL_PRAGMA                                                                \
+                for (int i = 1; i <= k; i++) sum -= a[k - i] * rr[i];                        \
+                const double akk = sum / pe;                                                 \
+                if (p.rc) p.rc[t * p.ld + k] = akk;                                          \
+                a[k] = akk;                                                                  \
+                UNROLL_PRAGMA                                                                \
+                for (int i = 1; i <= k >> 1; i++) {                                          \
+                    const double ai = a[i], aj = a[k - i];                                   \
+                    a[i] = ai + akk * aj;                                                    \
+                    a[k - i] = aj + akk * ai;                                                \
+                }                                                                            \
+                pe *= 1.0 - akk * akk;                                                       \
+                if (pe <= 0.0) {                                                             \
+                    status = 2;                                                              \
+                    live = false;                                                            \
+                }                                                                            \
+            }                                                                                \
+        }                                                                                    \
+    }
+
+// thread = frame; everything in registers (loops fully unrolled to PMAX)
+template <int PMAX>
+__global__ void __launch_bounds__(128) lpc_levinson(const LvParams p) {
+    const long t = (long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= p.T) return;
+    const int P = p.P;
+    constexpr int KMAX = PMAX;
+    double rr[PMAX + 1], a[PMAX + 1];
+    double *row = p.r + t * p.ld;
+#pragma unroll
+    for (int i = 0; i <= PMAX; i++) {
+        rr[i] = i <= P ? row[i] : 0.0;
+        a[i] = 0.0;
+    }
+    LPC_LEVINSON_BODY(_Pragma("unroll"))
+    if (p.status) p.status[t] = status;
+    if (status != 0 && p.err_count) atomicAdd(p.err_count, 1);
+    if (p.pe) p.pe[t] = pe;
+#pragma unroll
+    for (int i = 0; i <= PMAX; i++) {
+        if (i <= P) {
+            if (p.a) p.a[t * p.ld + i] = a[i];
+            // lpa_on_signal.c:143-150 (an all-zero frame, status 1, has no defined error: left as is)
+            if (p.normalise && status != 1 && pe != 0.0) row[i] = rr[i] / pe;
+        }
+    }
+}
+
+// any order up to 255: the same recursion with the arrays in local memory
+__global__ void __launch_bounds__(128) lpc_levinson_any(const LvParams p) {
+    const long t = (long) blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= p.T) return;
+    const int P = p.P;
+    const int KMAX = P;
+    double rr[256], a[256];
+    double *row = p.r + t * p.ld;
+    for (int i = 0; i <= P; i++) {
+        rr[i] = row[i];
+        a[i] = 0.0;
+    }
+    LPC_LEVINSON_BODY(_Pragma("unroll 1"))
+    if (p.status) p.status[t] = status;
+    if (status != 0 && p.err_count) atomicAdd(p.err_count, 1);
+    if (p.pe) p.pe[t] = pe;
+    for (int i = 0; i <= P; i++) {
+        if (p.a) p.a[t * p.ld + i] = a[i];
+        if (p.normalise && status != 1 && pe != 0.0) row[i] = rr[i] / pe;
+    }
+}
+#undef LPC_LEVINSON_BODY
+
+__global__ void lpc_hamming(double *h, int win) {
+    const int n = blockIdx.x * blockDim.x + threadIdx.x;
+    if (n < win) h[n] = .54 - .46 * cos((n * 2 * M_PI) / (win - 1));   // lpa_on_signal.c:24-31
+}
+
+thread_local std::string g_err;
+
+bool cuda_ok(cudaError_t e, const char *what) {
+    if (e == cudaSuccess) return true;
+    g_err = std::string(what) + ": " + cudaGetErrorString(e);
+    return false;
+}
+
+template <int LAGS>
+bool launch_autocorr(AcParams p, cudaStream_t s) {
+    // frames per CTA: as many (32, 16, 8, 4) as the staged stretch of signal allows
+    int G = 32;
+    size_t smem = 0;
+    p.staged = 0;
+    for (; G >= 4; G >>= 1) {
+        smem = ((size_t) (G - 1) * p.off + 2 * (size_t) p.win) * sizeof(double);
+        if (smem <= 200 * 1024) {
+            p.staged = 1;
+            break;
+        }
+    }
+    if (!p.staged) {
+        G = 32;
+        smem = 0;
+    }
+    p.frames_per_cta = G;
+    static bool attr_set = false;
+    if (!attr_set) {
+        if (!cuda_ok(cudaFuncSetAttribute(lpc_autocorr<LAGS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          200 * 1024), "cudaFuncSetAttribute(lpc_autocorr)"))
+            return false;
+        attr_set = true;
+    }
+    const long grid = (p.T + G - 1) / G;
+    lpc_autocorr<LAGS><<<(unsigned) grid, G * kLanesPerFrame, smem, s>>>(p);
+    return cuda_ok(cudaGetLastError(), "lpc_autocorr launch");
+}
+
+bool launch_levinson(const LvParams &p, cudaStream_t s) {
+    const unsigned grid = (unsigned) ((p.T + 127) / 128);
+    if (p.P <= 16) lpc_levinson<16><<<grid, 128, 0, s>>>(p);
+    else if (p.P <= 40) lpc_levinson<40><<<grid, 128, 0, s>>>(p);
+    else lpc_levinson_any<<<grid, 128, 0, s>>>(p);
+    return cuda_ok(cudaGetLastError(), "lpc_levinson launch");
+}
+
+}  // namespace
+
+const char *last_error() { return g_err.c_str(); }
+
+long num_frames(long num_samples, double sample_rate, int window_ms, int offset_ms, int *win_out,
+                int *off_out) {
+    // lpa_on_signal.c:84-101 (the sample rate is truncated to an integer there)
+    const long sr = (long) sample_rate;
+    const int win = (int) ((window_ms * sr) / 1000);
+    const int off = (int) ((offset_ms * sr) / 1000);
+    if (win_out) *win_out = win;
+    if (off_out) *off_out = off;
+    if (win <= 0 || off <= 0) {
+        g_err = "lpa_on_signal: window or offset of zero samples";
+        return -1;
+    }
+    if (win > num_samples) {
+        g_err = "lpa_on_signal: signal too short";
+        return -1;
+    }
+    long T = (num_samples - (win - off)) / off;
+    if ((T - 1) * off + win > num_samples) T--;
+    return T;
+}
+
+namespace {
+bool run_autocorr(AcParams ap, cudaStream_t s) {
+    if (ap.P <= 15) return launch_autocorr<16>(ap, s);
+    if (ap.P <= 23) return launch_autocorr<24>(ap, s);
+    return launch_autocorr<40>(ap, s);   // longer orders: several passes of 40 lags
+}
+}  // namespace
+
+bool lpa_device(const double *d_signal, long T, int win, int off, int P, double *d_vectors,
+                double *d_hamming, int *d_err_count, cudaStream_t stream) {
+    if (P < 1 || P > kMaxOrder) {
+        g_err = "lpa_on_signal: prediction order out of range (1..255)";
+        return false;
+    }
+    if (T <= 0) return true;
+    if (win < 2) {
+        g_err = "lpa_on_signal: window shorter than two samples";
+        return false;
+    }
+    lpc_hamming<<<(win + 255) / 256, 256, 0, stream>>>(d_hamming, win);
+    AcParams ap{};
+    ap.signal = d_signal; ap.hamming = d_hamming; ap.r = d_vectors;
+    ap.T = T; ap.win = win; ap.off = off; ap.P = P; ap.ld = P + 1; ap.windowed = 1;
+    if (!run_autocorr(ap, stream)) return false;
+    LvParams lp{};
+    lp.r = d_vectors; lp.T = T; lp.P = P; lp.ld = P + 1; lp.normalise = 1; lp.err_count = d_err_count;
+    return launch_levinson(lp, stream);
+}
+
+bool lpca_device(const double *d_x, long T, int N, long stride, int P, double *d_r, double *d_rc,
+                 double *d_a, double *d_pe, int *d_status, cudaStream_t stream) {
+    if (P < 1 || P > kMaxOrder || N < 1 || stride < 1 || stride > 0x7fffffffL) {
+        g_err = "lpca: arguments out of range";
+        return false;
+    }
+    if (T <= 0) return true;
+    AcParams ap{};
+    ap.signal = d_x; ap.hamming = nullptr; ap.r = d_r;
+    ap.T = T; ap.win = N; ap.off = (int) stride; ap.P = P; ap.ld = P + 1; ap.windowed = 0;
+    if (!run_autocorr(ap, stream)) return false;
+    LvParams lp{};
+    lp.r = d_r; lp.T = T; lp.P = P; lp.ld = P + 1; lp.normalise = 0;
+    lp.rc = d_rc; lp.a = d_a; lp.pe = d_pe; lp.status = d_status;
+    return launch_levinson(lp, stream);
+}
+
+}  // namespace lpcb200

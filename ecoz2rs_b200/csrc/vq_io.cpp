@@ -88,6 +88,19 @@ int prd_read(const char *path, double *out, long capacity_values) {
     return 0;
 }
 
+// reference ecoz2/src/lpc/prd.c:76-115
+int prd_save(const char *path, const char *class_name, const double *vectors, int T, int P) {
+    FilePtr f(fopen(path, "wb"));
+    if (!f) return 1;
+    const int32_t hdr[2] = {P, T};
+    if (!write_ident(f.get(), "<predictor>") || !write_class(f.get(), class_name) ||
+        fwrite(hdr, sizeof(int32_t), 2, f.get()) != 2)
+        return 2;
+    const size_t n = (size_t) T * (P + 1);
+    if (n > 0 && fwrite(vectors, sizeof(double), n, f.get()) != n) return 2;
+    return 0;
+}
+
 // ---- .cbook ------------------------------------------------------------------------
 int cbook_save(const char *path, const char *class_name, const double *refl, int M, int P) {
     FilePtr f(fopen(path, "wb"));

@@ -16,6 +16,7 @@ constexpr int kMaxClassNameLen = 96;  // reference ecoz2/src/include/utl.h (MAX_
 //   "<predictor>" ident | class name | i32 P | i32 T | T x (1+P) f64
 int prd_info(const char *path, int *P, int *T, char class_name[kMaxClassNameLen]);
 int prd_read(const char *path, double *out, long capacity_values);
+int prd_save(const char *path, const char *class_name, const double *vectors, int T, int P);
 
 // `.cbook` (reference ecoz2/src/vq/vq.c:22-116):
 //   "<codebook>" ident | class name | i32 P | i32 M | M x (1+P) f64 reflections

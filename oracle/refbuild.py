@@ -251,3 +251,56 @@ def run_vq_classify(codebooks, prd_files, cwd, show_ranked=True):
     exe = os.path.join(arch_dir(), "vq.classify")
     rc, out = _run([exe] + (["-r"] if show_ranked else []) + list(codebooks) + list(prd_files), cwd, 1)
     return dict(returncode=rc, stdout=out)
+
+
+# ---- LPC front end: the reference's lpa_on_signal / lpca -------------------
+
+class _Sgn(C.Structure):   # ecoz2/src/include/sgn.h:19-23
+    _fields_ = [("samples", _dp), ("numSamples", C.c_int), ("sampleRate", C.c_double)]
+
+
+_lpc_lib = None
+
+
+def lpc_available() -> bool:
+    return os.path.exists(os.path.join(arch_dir(), "libecoz2_ref_lpc.so"))
+
+
+def lpc_lib():
+    global _lpc_lib
+    if _lpc_lib is None:
+        L = C.CDLL(os.path.join(arch_dir(), "libecoz2_ref_lpc.so"))
+        L.lpa_on_signal.restype = C.POINTER(_Predictor)
+        L.lpa_on_signal.argtypes = [C.c_int, C.c_int, C.c_int, C.POINTER(_Sgn), C.c_int]
+        L.prd_destroy.argtypes = [C.POINTER(_Predictor)]
+        L.lpca.restype = C.c_int
+        L.lpca.argtypes = [_dp, C.c_int, C.c_int, _dp, _dp, _dp, _dp]
+        _lpc_lib = L
+    return _lpc_lib
+
+
+def ref_lpa_on_signal(signal, sample_rate, P, window_ms, offset_ms, threads=None):
+    """lpa_on_signal (lpa_on_signal.c:81) -> vectors [T, P+1], or None (signal too short)."""
+    x = _f64(signal)
+    sgn = _Sgn(_d(x), len(x), float(sample_rate))
+    if threads is not None:
+        os.environ["OMP_NUM_THREADS"] = str(threads)
+    p = lpc_lib().lpa_on_signal(P, window_ms, offset_ms, C.byref(sgn), 0)
+    if not p:
+        return None
+    prd = p.contents
+    T = prd.T
+    out = np.empty((T, P + 1))
+    for t in range(T):
+        out[t] = np.ctypeslib.as_array(prd.vectors[t], shape=(P + 1,))
+    lpc_lib().prd_destroy(p)
+    return out
+
+
+def ref_lpca(x, P):
+    """lpca (lpca.c:9) -> (status, r, rc, a, pe)"""
+    x = _f64(x)
+    r = np.zeros(P + 1); rc = np.zeros(P + 1); a = np.zeros(P + 1)
+    pe = C.c_double(0.)
+    st = lpc_lib().lpca(_d(x), len(x), P, _d(r), _d(rc), _d(a), C.byref(pe))
+    return st, r, rc, a, pe.value
