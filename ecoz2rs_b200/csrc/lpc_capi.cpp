@@ -51,6 +51,11 @@ extern "C" {
 
 const char *ecoz2b200_lpc_last_error(void) { return g_lpc_err.c_str(); }
 
+double ecoz2b200_dfma_peak_tflops(int device, double millis) {
+    if (!have_device()) return 0.0;
+    return lpcb200::dfma_peak_tflops(device, millis);
+}
+
 long ecoz2b200_lpa_num_frames(long num_samples, double sample_rate, int window_ms, int offset_ms) {
     const long T = lpcb200::num_frames(num_samples, sample_rate, window_ms, offset_ms, nullptr, nullptr);
     if (T < 0) set_err(lpcb200::last_error());
@@ -65,17 +70,33 @@ long ecoz2b200_lpa_on_signal_device(const double *d_samples, long num_samples, d
     if (T < 0) { set_err(lpcb200::last_error()); return -1; }
     if (T > capacity_frames) { set_err("lpa_on_signal: output buffer too small"); return -1; }
     cudaStream_t s = static_cast<cudaStream_t>(stream);
-    DevBuf ham, err;
-    if (!ham.alloc(sizeof(double) * (size_t) win) || !err.alloc(sizeof(int))) return -1;
-    if (!ck(cudaMemsetAsync(err.p, 0, sizeof(int), s), "cudaMemsetAsync")) return -1;
-    if (!lpcb200::lpa_device(d_samples, T, win, off, P, d_vectors, ham.as<double>(), err.as<int>(), s)) {
-        set_err(lpcb200::last_error());
-        return -1;
+    // scratch (Hamming table + error counter) from the stream-ordered pool: no device-wide
+    // synchronisation per call, the block is recycled by the next call on the stream
+    static thread_local int pool_ready_for = -1;
+    int dev = 0;
+    if (cudaGetDevice(&dev) == cudaSuccess && pool_ready_for != dev) {
+        // keep freed blocks in the pool across synchronisations (the default hands them back)
+        cudaMemPool_t pool;
+        if (cudaDeviceGetDefaultMemPool(&pool, dev) == cudaSuccess) {
+            unsigned long long keep = 64ull << 20;
+            cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep);
+        }
+        pool_ready_for = dev;
     }
+    void *scratch = nullptr;
+    const size_t ham_bytes = (sizeof(double) * (size_t) win + 15) & ~(size_t) 15;
+    if (!ck(cudaMallocAsync(&scratch, ham_bytes + 16, s), "cudaMallocAsync")) return -1;
+    double *d_ham = static_cast<double *>(scratch);
+    int *d_err = reinterpret_cast<int *>(static_cast<char *>(scratch) + ham_bytes);
     int ne = 0;
-    if (!ck(cudaMemcpyAsync(&ne, err.p, sizeof(int), cudaMemcpyDeviceToHost, s), "cudaMemcpyAsync") ||
-        !ck(cudaStreamSynchronize(s), "lpa_on_signal"))
-        return -1;
+    bool ok = ck(cudaMemsetAsync(d_err, 0, sizeof(int), s), "cudaMemsetAsync");
+    if (ok && !lpcb200::lpa_device(d_samples, T, win, off, P, d_vectors, d_ham, d_err, s)) {
+        set_err(lpcb200::last_error());
+        ok = false;
+    }
+    ok = ok && ck(cudaMemcpyAsync(&ne, d_err, sizeof(int), cudaMemcpyDeviceToHost, s), "cudaMemcpyAsync");
+    cudaFreeAsync(scratch, s);
+    if (!ck(cudaStreamSynchronize(s), "lpa_on_signal") || !ok) return -1;
     if (num_errors) *num_errors = ne;
     return T;
 }

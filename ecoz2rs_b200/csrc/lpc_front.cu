@@ -21,7 +21,9 @@
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
+#include <stdlib.h>
 
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -43,6 +45,7 @@ struct AcParams {
     int frames_per_cta;     // G
     int staged;             // signal stretch + Hamming table in shared memory
     int windowed;           // 0: plain autocorrelation of each frame (ecoz2_lpca)
+    int lane_stride;        // fast kernel: samples between the pieces of consecutive lanes (odd)
 };
 
 // windowed sample n of a frame (0 outside [0, N)): lpa_on_signal.c:42-80
@@ -132,6 +135,127 @@ __global__ void __launch_bounds__(256, 1) lpc_autocorr(const AcParams p) {
             s += __shfl_xor_sync(gmask, s, 1);
             if ((i % kLanesPerFrame) == j && l0 + i <= p.P) out[i] = s;
         }
+    }
+}
+
+// ---------------------------------------------------------------------------------------
+// lpc_autocorr_fast<LAGS>: the windowed case with P < LAGS and a stretch of signal that
+// fits shared memory twice per SM -- what lpa_on_signal runs at the usual 45/15 ms framing.
+//
+// Same decomposition as lpc_autocorr (8 lanes share a frame, each owns a contiguous piece
+// of the window and all LAGS running sums) with the inner loop made branch-free:
+//   * the staged signal and the Hamming table are zero-extended by kFastPad entries, so the
+//     sliding window may run past the end of the frame without bounds checks on the loads
+//     (the value is forced to zero by a select, never by arithmetic on what was loaded);
+//   * each windowed sample is produced exactly once per lane (3 FP64 ops: centre, pre-
+//     emphasise with the previous centred sample kept in a register, Hamming) and enters
+//     the LAGS x 8 block of DFMAs both as the "row" and the "column" operand;
+//   * raw samples of the next block are loaded before the 8 x LAGS DFMAs of this one;
+//   * lane pieces start every Ls samples with Ls odd, so the 8 lanes of a frame hit
+//     distinct 8-byte banks; the piece is processed in whole blocks of 8, the rows past
+//     the end of the piece (they belong to the next lane) are masked to zero;
+//   * 16 frames (128 threads) per CTA, two CTAs per SM: one stages its signal with
+//     cp.async while the other keeps the FP64 pipe busy.
+// ---------------------------------------------------------------------------------------
+constexpr int kFastPad = 112;   // >= (odd-Ls slack 15) + (block round-up 7) + LAGS - 1 + 2 * kStep
+
+template <int LAGS>
+__global__ void __launch_bounds__(128, 2) lpc_autocorr_fast(const AcParams p) {
+    extern __shared__ __align__(16) unsigned char lpc_smem[];
+    const int G = p.frames_per_cta;
+    const long t0 = (long) blockIdx.x * G;
+    const int N = p.win;
+    double *s_sig = reinterpret_cast<double *>(lpc_smem);
+    const int sig_cap = (G - 1) * p.off + N + kFastPad;
+    double *s_ham = s_sig + sig_cap;
+    {
+        const long n_frames = p.T - t0 < G ? p.T - t0 : G;
+        const int span = (int) (n_frames - 1) * p.off + N;
+        const double *src = p.signal + t0 * p.off;
+        for (int i = threadIdx.x; i < span; i += blockDim.x) {
+            const unsigned dst = (unsigned) __cvta_generic_to_shared(s_sig + i);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src + i) : "memory");
+        }
+        for (int i = span + threadIdx.x; i < sig_cap; i += blockDim.x) s_sig[i] = 0.0;
+        for (int i = threadIdx.x; i < N; i += blockDim.x) {
+            const unsigned dst = (unsigned) __cvta_generic_to_shared(s_ham + i);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(p.hamming + i) : "memory");
+        }
+        for (int i = N + threadIdx.x; i < N + kFastPad; i += blockDim.x) s_ham[i] = 0.0;
+        asm volatile("cp.async.commit_group;" ::: "memory");
+        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        __syncthreads();
+    }
+    const int g = threadIdx.x / kLanesPerFrame, j = threadIdx.x % kLanesPerFrame;
+    const long t = t0 + g;
+    if (t >= p.T) return;   // whole 8-lane groups leave together
+    const unsigned gmask = 0xffu << ((threadIdx.x & 31) & ~7);
+    const int Ls = p.lane_stride;
+    const int c0 = j * Ls;
+    const int c1 = c0 + Ls < N ? c0 + Ls : N;   // may be <= c0 for tiny windows: nothing to add
+    const double *x = s_sig + (size_t) g * p.off;
+
+    double mean;
+    {
+        double s = 0.0;
+        for (int n = c0; n < c1; n++) s += x[n];
+        s += __shfl_xor_sync(gmask, s, 4);
+        s += __shfl_xor_sync(gmask, s, 2);
+        s += __shfl_xor_sync(gmask, s, 1);
+        mean = s / N;
+    }
+
+    const double *xp = x + c0, *hp = s_ham + c0;
+    // centred sample before the piece (lpa_on_signal.c:52-60: the first sample has no predecessor)
+    double cprev = c0 > 0 ? xp[-1] - mean : 0.0;
+    int lim = N - c0;   // windowed sample m of this piece is zero for m >= lim
+    // y(m) = ((x[m] - mean) - .95 (x[m-1] - mean)) * h[m]
+#define LPC_GEN(dst, xv, hv, m)                                \
+    {                                                          \
+        const double c_ = (xv) - mean;                         \
+        const double v_ = (c_ - .95 * cprev) * (hv);           \
+        cprev = c_;                                            \
+        (dst) = (m) < lim ? v_ : 0.0;                          \
+    }
+    double acc[LAGS];
+#pragma unroll
+    for (int i = 0; i < LAGS; i++) acc[i] = 0.0;
+    double wb[LAGS - 1 + kStep];   // wb[q] = y(k + q) relative to the piece
+#pragma unroll
+    for (int q = 0; q < LAGS - 1; q++) LPC_GEN(wb[q], xp[q], hp[q], q)
+    double xr[kStep], hr[kStep];
+#pragma unroll
+    for (int u = 0; u < kStep; u++) {
+        xr[u] = xp[LAGS - 1 + u];
+        hr[u] = hp[LAGS - 1 + u];
+    }
+    const int rows = c1 - c0;   // rows of this piece that count
+    for (int k = 0; k < Ls; k += kStep) {
+#pragma unroll
+        for (int u = 0; u < kStep; u++) LPC_GEN(wb[LAGS - 1 + u], xr[u], hr[u], k + LAGS - 1 + u)
+#pragma unroll
+        for (int u = 0; u < kStep; u++) {   // next block's raw values, in flight during the DFMAs
+            xr[u] = xp[k + kStep + LAGS - 1 + u];
+            hr[u] = hp[k + kStep + LAGS - 1 + u];
+        }
+#pragma unroll
+        for (int u = 0; u < kStep; u++) {
+            const double a = k + u < rows ? wb[u] : 0.0;
+#pragma unroll
+            for (int i = 0; i < LAGS; i++) acc[i] = fma(a, wb[u + i], acc[i]);
+        }
+#pragma unroll
+        for (int q = 0; q < LAGS - 1; q++) wb[q] = wb[q + kStep];
+    }
+#undef LPC_GEN
+    double *out = p.r + t * p.ld;
+#pragma unroll
+    for (int i = 0; i < LAGS; i++) {
+        double s = acc[i];
+        s += __shfl_xor_sync(gmask, s, 4);
+        s += __shfl_xor_sync(gmask, s, 2);
+        s += __shfl_xor_sync(gmask, s, 1);
+        if ((i % kLanesPerFrame) == j && i <= p.P) out[i] = s;
     }
 }
 
@@ -235,6 +359,22 @@ __global__ void lpc_hamming(double *h, int win) {
     if (n < win) h[n] = .54 - .46 * cos((n * 2 * M_PI) / (win - 1));   // lpa_on_signal.c:24-31
 }
 
+// FP64 DFMA peak probe: 8 independent FMA chains per thread, nothing else -- the measured
+// denominator of lpc_autocorr's roofline on the box the numbers are taken on.
+__global__ void __launch_bounds__(256) lpc_dfma_probe(double *out, int iters, double a, double b) {
+    double c0 = threadIdx.x, c1 = c0 + 1., c2 = c0 + 2., c3 = c0 + 3.;
+    double c4 = c0 + 4., c5 = c0 + 5., c6 = c0 + 6., c7 = c0 + 7.;
+    for (int i = 0; i < iters; i++) {
+#pragma unroll
+        for (int u = 0; u < 16; u++) {
+            c0 = fma(c0, a, b); c1 = fma(c1, a, b); c2 = fma(c2, a, b); c3 = fma(c3, a, b);
+            c4 = fma(c4, a, b); c5 = fma(c5, a, b); c6 = fma(c6, a, b); c7 = fma(c7, a, b);
+        }
+    }
+    const double r = ((c0 + c1) + (c2 + c3)) + ((c4 + c5) + (c6 + c7));
+    if (r == 123.456) out[0] = r;  // keep the chains alive
+}
+
 thread_local std::string g_err;
 
 bool cuda_ok(cudaError_t e, const char *what) {
@@ -243,8 +383,41 @@ bool cuda_ok(cudaError_t e, const char *what) {
     return false;
 }
 
+// fast path when the order fits one pass of LAGS and two CTAs of 16 (8, 4) frames fit an SM
+template <int LAGS>
+bool launch_autocorr_fast(AcParams p, cudaStream_t s, bool *taken) {
+    *taken = false;
+    if (!p.windowed || p.P >= LAGS || std::getenv("ECOZ2_LPC_GENERIC")) return true;
+    int Ls = (p.win + kLanesPerFrame - 1) / kLanesPerFrame;
+    if ((Ls & 1) == 0) Ls++;
+    int G = 16;
+    size_t smem = 0;
+    for (; G >= 4; G >>= 1) {
+        smem = ((size_t) (G - 1) * p.off + 2 * (size_t) p.win + 2 * kFastPad) * sizeof(double);
+        if (smem <= 110 * 1024) break;
+    }
+    if (G < 4) return true;
+    p.frames_per_cta = G;
+    p.lane_stride = Ls;
+    p.staged = 1;
+    static bool attr_set = false;
+    if (!attr_set) {
+        if (!cuda_ok(cudaFuncSetAttribute(lpc_autocorr_fast<LAGS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          110 * 1024), "cudaFuncSetAttribute(lpc_autocorr_fast)"))
+            return false;
+        attr_set = true;
+    }
+    const long grid = (p.T + G - 1) / G;
+    lpc_autocorr_fast<LAGS><<<(unsigned) grid, G * kLanesPerFrame, smem, s>>>(p);
+    *taken = true;
+    return cuda_ok(cudaGetLastError(), "lpc_autocorr_fast launch");
+}
+
 template <int LAGS>
 bool launch_autocorr(AcParams p, cudaStream_t s) {
+    bool taken = false;
+    if (!launch_autocorr_fast<LAGS>(p, s, &taken)) return false;
+    if (taken) return true;
     // frames per CTA: as many (32, 16, 8, 4) as the staged stretch of signal allows
     int G = 32;
     size_t smem = 0;
@@ -285,6 +458,34 @@ bool launch_levinson(const LvParams &p, cudaStream_t s) {
 
 const char *last_error() { return g_err.c_str(); }
 
+double dfma_peak_tflops(int device, double millis) {
+    cudaDeviceProp prop;
+    if (cudaSetDevice(device) != cudaSuccess || cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 0.0;
+    double *out = nullptr;
+    if (cudaMalloc(&out, 16) != cudaSuccess) return 0.0;
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0);
+    cudaEventCreate(&e1);
+    const int blocks = prop.multiProcessorCount * 8;
+    int iters = 500;
+    double best = 0.0;
+    for (int rep = 0; rep < 6; rep++) {
+        cudaEventRecord(e0, 0);
+        lpc_dfma_probe<<<blocks, 256>>>(out, iters, 0.999, 0.001);
+        cudaEventRecord(e1, 0);
+        if (cudaEventSynchronize(e1) != cudaSuccess) break;
+        float ms = 0;
+        cudaEventElapsedTime(&ms, e0, e1);
+        const double tf = 2.0 * 128.0 * iters * 256.0 * blocks / (ms * 1e-3) / 1e12;
+        if (rep > 0 && tf > best) best = tf;
+        if (ms < millis && iters < (1 << 24)) iters = (int) (iters * (millis / (ms > 0.01 ? ms : 0.01)) * 1.05) + 1;
+    }
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    cudaFree(out);
+    return best;
+}
+
 long num_frames(long num_samples, double sample_rate, int window_ms, int offset_ms, int *win_out,
                 int *off_out) {
     // lpa_on_signal.c:84-101 (the sample rate is truncated to an integer there)
@@ -308,8 +509,12 @@ long num_frames(long num_samples, double sample_rate, int window_ms, int offset_
 
 namespace {
 bool run_autocorr(AcParams ap, cudaStream_t s) {
+    // exact widths for the orders ECOZ2 is run with (P = 12, 20, 36): no padded lags
+    if (ap.P == 12) return launch_autocorr<13>(ap, s);
     if (ap.P <= 15) return launch_autocorr<16>(ap, s);
+    if (ap.P == 20) return launch_autocorr<21>(ap, s);
     if (ap.P <= 23) return launch_autocorr<24>(ap, s);
+    if (ap.P == 36) return launch_autocorr<37>(ap, s);
     return launch_autocorr<40>(ap, s);   // longer orders: several passes of 40 lags
 }
 }  // namespace

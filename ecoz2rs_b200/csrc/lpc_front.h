@@ -25,4 +25,7 @@ bool lpa_device(const double *d_signal, long T, int win, int off, int P, double 
 bool lpca_device(const double *d_x, long T, int N, long stride, int P, double *d_r, double *d_rc,
                  double *d_a, double *d_pe, int *d_status, cudaStream_t stream);
 
+// measured FP64 FMA throughput of `device` in TFLOP/s (pure DFMA chains on every SM for ~millis ms)
+double dfma_peak_tflops(int device, double millis);
+
 }  // namespace lpcb200

@@ -18,7 +18,7 @@ from . import vq
 EXPORTED_SYMBOLS = (
     "ecoz2_lpc_signals", "ecoz2_lpca",
     "ecoz2b200_lpa_num_frames", "ecoz2b200_lpa_on_signal", "ecoz2b200_lpa_on_signal_device",
-    "ecoz2b200_lpc_last_error",
+    "ecoz2b200_lpc_last_error", "ecoz2b200_dfma_peak_tflops",
 )
 
 _dp = C.POINTER(C.c_double)
@@ -43,6 +43,8 @@ def _lib():
         L.ecoz2b200_lpa_on_signal_device.argtypes = [C.c_void_p, C.c_long, C.c_double, C.c_int, C.c_int,
                                                      C.c_int, C.c_void_p, C.c_long, C.POINTER(C.c_int),
                                                      C.c_void_p]
+        L.ecoz2b200_dfma_peak_tflops.restype = C.c_double
+        L.ecoz2b200_dfma_peak_tflops.argtypes = [C.c_int, C.c_double]
         L.ecoz2_lpca.restype = C.c_int
         L.ecoz2_lpca.argtypes = [_dp, C.c_int, C.c_int, _dp, _dp, _dp, _dp]
         L.ecoz2_lpc_signals.restype = C.c_int
@@ -54,6 +56,11 @@ def _lib():
 
 def _err() -> str:
     return (_lib().ecoz2b200_lpc_last_error() or b"").decode()
+
+
+def dfma_peak_tflops(device: int = 0, millis: float = 20.0) -> float:
+    """Measured FP64 FMA peak of `device` (TFLOP/s): denominator of lpc_autocorr's roofline."""
+    return float(_lib().ecoz2b200_dfma_peak_tflops(device, millis))
 
 
 def num_frames(num_samples: int, sample_rate: float, window_ms: int, offset_ms: int) -> int:

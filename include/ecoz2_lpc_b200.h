@@ -58,6 +58,10 @@ long ecoz2b200_lpa_on_signal_device(const double *d_samples, long num_samples, d
 
 const char *ecoz2b200_lpc_last_error(void);
 
+/* Measured FP64 FMA throughput of `device` in TFLOP/s (a pure DFMA-chain kernel filling every
+ * SM for ~`millis` ms): the denominator of the autocorrelation kernel's roofline. */
+double ecoz2b200_dfma_peak_tflops(int device, double millis);
+
 #ifdef __cplusplus
 }
 #endif
