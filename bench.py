@@ -416,6 +416,46 @@ def run_b200_arm(args):
     except Exception as e:
         log(f"[quantize] failed: {e!r}")
 
+    # ---- LPC front end (the producer of the frames): one hour of 32 kHz signal resident
+    # in HBM -> gain-normalised vectors in HBM, CUDA events on torch's current stream (the stream the
+    # call is given); rank 0 at N=1 only.  Roofline: FP64 DFMA, measured live.
+    lpc_info = None
+    if world == 1:
+        try:
+            from ecoz2rs_b200 import lpc
+            rate, wms, oms = 32000.0, 45, 15
+            ns = int(3600 * rate)
+            g = torch.Generator(device="cuda").manual_seed(5)
+            sig = torch.randn(ns, device="cuda", dtype=torch.float64, generator=g) * 0.05
+            sig[1:] += 0.8 * sig[:-1].clone()
+            T = lpc.num_frames(ns, rate, wms, oms)
+            vec = torch.empty((T, D), dtype=torch.float64, device="cuda")
+            st = torch.cuda.current_stream().cuda_stream
+            for _ in range(3):
+                lpc.lpa_on_signal_device(sig.data_ptr(), ns, rate, P, wms, oms, vec.data_ptr(), T, st)
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            reps = 10
+            ev0.record()
+            for _ in range(reps):
+                lpc.lpa_on_signal_device(sig.data_ptr(), ns, rate, P, wms, oms, vec.data_ptr(), T, st)
+            ev1.record()
+            torch.cuda.synchronize()
+            lms = ev0.elapsed_time(ev1) / reps
+            win = int(wms * int(rate) // 1000)
+            dpeak = lpc.dfma_peak_tflops(local_rank, 20.0)
+            ach = 2.0 * T * win * D / (lms * 1e-3) / 1e12
+            lpc_info = {"workload": "lpa_on_signal, 3600 s of 32 kHz signal, 45/15 ms frames, P=%d" % P,
+                        "frames": T, "ms": lms, "frames_per_s": T / (lms * 1e-3),
+                        "roofline": {"bound": "fp64_dfma", "achieved": ach, "peak": dpeak, "unit": "TFLOP/s",
+                                     "frac": ach / dpeak if dpeak > 0 else None,
+                                     "peak_source": "measured live: ecoz2b200_dfma_peak_tflops",
+                                     "note": "whole call (Hamming table, autocorrelation, Levinson, "
+                                             "error-count read-back); algorithmic flops = frames x window x "
+                                             "(P+1) x 2"}}
+            del sig, vec
+        except Exception as e:
+            log(f"[lpc] failed: {e!r}")
+
     # ---- roofline of the dominant kernel (the search), measured with CUDA events on the
     # engine's own stream inside the timed region above
     main_ms = ctr["search_main_ms"] / max(1, ctr["search_main_launches"])
@@ -526,6 +566,7 @@ def run_b200_arm(args):
             "learn_stage_ms": {str(s["M"]): s["stage_seconds"] * 1e3 for s in stages},
             "learn_evals_per_s": learn_ctr["evals"] * world / learn_wall,
             "quantize": quantize_info,
+            "lpc_front": lpc_info,
         }
         emit_line(line)
     eng.close()

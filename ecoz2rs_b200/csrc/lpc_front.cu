@@ -46,6 +46,7 @@ struct AcParams {
     int staged;             // signal stretch + Hamming table in shared memory
     int windowed;           // 0: plain autocorrelation of each frame (ecoz2_lpca)
     int lane_stride;        // fast kernel: samples between the pieces of consecutive lanes (odd)
+    int bulk;               // fast kernel: signal and Hamming table 16-byte aligned -> cp.async.bulk staging
 };
 
 // windowed sample n of a frame (0 outside [0, N)): lpa_on_signal.c:42-80
@@ -166,30 +167,70 @@ __global__ void __launch_bounds__(128, 2) lpc_autocorr_fast(const AcParams p) {
     const long t0 = (long) blockIdx.x * G;
     const int N = p.win;
     double *s_sig = reinterpret_cast<double *>(lpc_smem);
-    const int sig_cap = (G - 1) * p.off + N + kFastPad;
+    const int sig_cap = ((G - 1) * p.off + N + kFastPad + 1) & ~1;   // even: s_ham stays 16-byte aligned
     double *s_ham = s_sig + sig_cap;
+    __shared__ uint64_t s_bar;
     {
         const long n_frames = p.T - t0 < G ? p.T - t0 : G;
         const int span = (int) (n_frames - 1) * p.off + N;
         const double *src = p.signal + t0 * p.off;
-        for (int i = threadIdx.x; i < span; i += blockDim.x) {
-            const unsigned dst = (unsigned) __cvta_generic_to_shared(s_sig + i);
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src + i) : "memory");
+        if (p.bulk) {
+            // one elected thread hands the two copies to the TMA engine (16-byte granules; an odd
+            // last element is copied by hand)
+            const uint32_t bar = (uint32_t) __cvta_generic_to_shared(&s_bar);
+            if (threadIdx.x == 0) {
+                asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+                asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+            }
+            __syncthreads();
+            if (threadIdx.x == 0) {
+                const uint32_t b_sig = (uint32_t) (span & ~1) * 8u, b_ham = (uint32_t) (N & ~1) * 8u;
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(b_sig + b_ham)
+                             : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+                                 "r"((uint32_t) __cvta_generic_to_shared(s_sig)), "l"(src), "r"(b_sig), "r"(bar)
+                             : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+                                 "r"((uint32_t) __cvta_generic_to_shared(s_ham)), "l"(p.hamming), "r"(b_ham), "r"(bar)
+                             : "memory");
+            }
+            if (threadIdx.x == 32 && (span & 1)) s_sig[span - 1] = src[span - 1];
+            if (threadIdx.x == 64 && (N & 1)) s_ham[N - 1] = p.hamming[N - 1];
+        } else {
+            for (int i = threadIdx.x; i < span; i += blockDim.x) {
+                const unsigned dst = (unsigned) __cvta_generic_to_shared(s_sig + i);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(src + i) : "memory");
+            }
+            for (int i = threadIdx.x; i < N; i += blockDim.x) {
+                const unsigned dst = (unsigned) __cvta_generic_to_shared(s_ham + i);
+                asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(p.hamming + i) : "memory");
+            }
+            asm volatile("cp.async.commit_group;" ::: "memory");
         }
         for (int i = span + threadIdx.x; i < sig_cap; i += blockDim.x) s_sig[i] = 0.0;
-        for (int i = threadIdx.x; i < N; i += blockDim.x) {
-            const unsigned dst = (unsigned) __cvta_generic_to_shared(s_ham + i);
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 8;" ::"r"(dst), "l"(p.hamming + i) : "memory");
-        }
         for (int i = N + threadIdx.x; i < N + kFastPad; i += blockDim.x) s_ham[i] = 0.0;
-        asm volatile("cp.async.commit_group;" ::: "memory");
-        asm volatile("cp.async.wait_group 0;" ::: "memory");
+        if (p.bulk) {
+            const uint32_t bar = (uint32_t) __cvta_generic_to_shared(&s_bar);
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{\n.reg .pred q;\nmbarrier.try_wait.parity.shared::cta.b64 q, [%1], 0;\n"
+                             "selp.u32 %0, 1, 0, q;\n}\n"
+                             : "=r"(done)
+                             : "r"(bar)
+                             : "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
         __syncthreads();
     }
-    const int g = threadIdx.x / kLanesPerFrame, j = threadIdx.x % kLanesPerFrame;
-    const long t = t0 + g;
-    if (t >= p.T) return;   // whole 8-lane groups leave together
-    const unsigned gmask = 0xffu << ((threadIdx.x & 31) & ~7);
+    // a warp holds 4 frames; warps past the last frame leave, groups past it compute frame t0 again
+    // and store nothing (all 32 lanes stay for the full-mask shuffles)
+    if (t0 + (threadIdx.x >> 5) * (32 / kLanesPerFrame) >= p.T) return;
+    const int j = threadIdx.x % kLanesPerFrame;
+    const long t = t0 + threadIdx.x / kLanesPerFrame;
+    const bool valid = t < p.T;
+    const int g = valid ? threadIdx.x / kLanesPerFrame : 0;
+    constexpr unsigned gmask = 0xffffffffu;
     const int Ls = p.lane_stride;
     const int c0 = j * Ls;
     const int c1 = c0 + Ls < N ? c0 + Ls : N;   // may be <= c0 for tiny windows: nothing to add
@@ -197,8 +238,16 @@ __global__ void __launch_bounds__(128, 2) lpc_autocorr_fast(const AcParams p) {
 
     double mean;
     {
-        double s = 0.0;
-        for (int n = c0; n < c1; n++) s += x[n];
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;   // four chains: the adds are latency bound
+        int n = c0;
+        for (; n + 4 <= c1; n += 4) {
+            s0 += x[n];
+            s1 += x[n + 1];
+            s2 += x[n + 2];
+            s3 += x[n + 3];
+        }
+        for (; n < c1; n++) s0 += x[n];
+        double s = (s0 + s1) + (s2 + s3);
         s += __shfl_xor_sync(gmask, s, 4);
         s += __shfl_xor_sync(gmask, s, 2);
         s += __shfl_xor_sync(gmask, s, 1);
@@ -255,7 +304,7 @@ __global__ void __launch_bounds__(128, 2) lpc_autocorr_fast(const AcParams p) {
         s += __shfl_xor_sync(gmask, s, 4);
         s += __shfl_xor_sync(gmask, s, 2);
         s += __shfl_xor_sync(gmask, s, 1);
-        if ((i % kLanesPerFrame) == j && i <= p.P) out[i] = s;
+        if ((i % kLanesPerFrame) == j && i <= p.P && valid) out[i] = s;
     }
 }
 
@@ -393,13 +442,16 @@ bool launch_autocorr_fast(AcParams p, cudaStream_t s, bool *taken) {
     int G = 16;
     size_t smem = 0;
     for (; G >= 4; G >>= 1) {
-        smem = ((size_t) (G - 1) * p.off + 2 * (size_t) p.win + 2 * kFastPad) * sizeof(double);
+        smem = ((size_t) (G - 1) * p.off + 2 * (size_t) p.win + 2 * kFastPad + 2) * sizeof(double);
         if (smem <= 110 * 1024) break;
     }
     if (G < 4) return true;
     p.frames_per_cta = G;
     p.lane_stride = Ls;
     p.staged = 1;
+    // frame t0 = blockIdx * G starts at an even sample (G is even), so alignment of the bases decides
+    p.bulk = ((reinterpret_cast<uintptr_t>(p.signal) | reinterpret_cast<uintptr_t>(p.hamming)) & 15) == 0 &&
+             !std::getenv("ECOZ2_LPC_NO_BULK");
     static bool attr_set = false;
     if (!attr_set) {
         if (!cuda_ok(cudaFuncSetAttribute(lpc_autocorr_fast<LAGS>, cudaFuncAttributeMaxDynamicSharedMemorySize,

@@ -148,3 +148,20 @@ def test_lpc_signals_writes_prd_files(built_lib, tmp_path):
     assert cls == "whale"
     want = lo.lpa_on_signal((pcm.astype(np.float32) / np.float32(32768.0)).astype(np.float64), 32000., 36, 45, 15)
     assert vec.shape == want.shape and _rel(vec, want) < RTOL
+
+
+def test_device_signal_not_16_byte_aligned(built_lib):
+    """A signal pointer that is only 8-byte aligned takes the cp.async staging instead of the bulk
+    copy; odd window lengths exercise the hand-copied last element.  Same bits either way."""
+    import torch
+    from ecoz2rs_b200 import lpc
+    for rate, P, W, O in ((32000., 36, 45, 15), (22050., 12, 45, 15), (11025., 20, 45, 15)):
+        x = _signal(200001, 41)
+        want = lpc.lpa_on_signal(x, rate, P, W, O)
+        buf = torch.empty(len(x) + 1, dtype=torch.float64, device="cuda")
+        buf[1:].copy_(torch.from_numpy(x))
+        T = lpc.num_frames(len(x), rate, W, O)
+        dv = torch.empty((T, P + 1), dtype=torch.float64, device="cuda")
+        assert (buf.data_ptr() + 8) % 16 == 8
+        assert lpc.lpa_on_signal_device(buf.data_ptr() + 8, len(x), rate, P, W, O, dv.data_ptr(), T) == T
+        assert np.array_equal(dv.cpu().numpy(), want), (rate, P)
