@@ -1,4 +1,4 @@
-// ecoz2_cli.cpp -- `ecoz2 vq learn|quantize|classify` command line on top of the C ABI.
+// ecoz2_cli.cpp -- `ecoz2 vq learn|quantize|classify` and `ecoz2 lpc` command line on top of the C ABI.
 //
 // The reference's CLI is the Rust binary (src/main.rs:95-97 -> src/vq/mod.rs); there
 // is no Rust toolchain in this environment, so this C++ driver keeps the same
@@ -17,6 +17,7 @@
 #include <string>
 #include <vector>
 
+#include "ecoz2_lpc_b200.h"
 #include "ecoz2_vq_b200.h"
 
 namespace {
@@ -105,13 +106,53 @@ int usage() {
             "                 [--predictors-dir-template <t>] [--tt TRAIN|TEST] [--class-name <c>] [-s]\n"
             "  ecoz2 vq classify [-r] --codebooks <files|dirs>... --tt TRAIN|TEST\n"
             "                 --predictors <files|dirs|one.csv>...\n"
+            "  ecoz2 lpc [-P <P>=36] [-W <ms>=45] [-O <ms>=15] [-m <minpc>=0] [-s <split>=0] [-X <secs>=5]\n"
+            "                 [--signals-dir-template <t>] [--tt TRAIN|TEST] [--class <c>] [--verbose]\n"
+            "                 --signals <wav files|dirs|one.csv>...\n"
             "environment: ECOZ2_VQ_GPUS=all|0,1,..  ECOZ2_VQ_MAX_M=<stop size>  ECOZ2_VQ_MIN_DISTS=0|1\n");
     return 2;
+}
+
+
+// `ecoz2 lpc`, reference src/lpc/mod.rs:16-143 (the --zrs / --zrsp Rust-native variants are not
+// part of the C path and are not offered)
+int main_lpc(int argc, char **argv) {
+    int P = 36, W = 45, O = 15, minpc = 0;
+    float split = 0.f, mintrpt = 5.f;
+    bool verbose = false, have_class = false;
+    std::string templ = "data/signals", tt, cls, v;
+    std::vector<std::string> signals, files;
+    for (int i = 2; i < argc; i++) {
+        const std::string a = argv[i];
+        auto next = [&](std::string &dst) { if (i + 1 < argc) dst = argv[++i]; };
+        if (a == "-P" || a == "--prediction-order") { next(v); P = atoi(v.c_str()); }
+        else if (a == "-W" || a == "--window-length-ms") { next(v); W = atoi(v.c_str()); }
+        else if (a == "-O" || a == "--offset-length-ms") { next(v); O = atoi(v.c_str()); }
+        else if (a == "-m" || a == "--minpc") { next(v); minpc = atoi(v.c_str()); }
+        else if (a == "-s" || a == "--split") { next(v); split = (float) atof(v.c_str()); }
+        else if (a == "-X") { next(v); mintrpt = (float) atof(v.c_str()); }
+        else if (a == "--signals-dir-template") next(templ);
+        else if (a == "--tt") next(tt);
+        else if (a == "--class") { next(cls); have_class = true; }
+        else if (a == "--verbose") verbose = true;
+        else if (a == "--signals") {
+            while (i + 1 < argc && argv[i + 1][0] != '-') signals.push_back(argv[++i]);
+        } else return usage();
+    }
+    if (signals.empty()) return usage();
+    if (!resolve(signals, tt, have_class ? cls : "", "", ".wav", &templ, files)) {
+        printf("No signals given\n");
+        return 1;
+    }
+    std::vector<char *> ptrs;
+    for (auto &f : files) ptrs.push_back(&f[0]);
+    return ecoz2_lpc_signals(P, W, O, minpc, split, ptrs.data(), (int) ptrs.size(), mintrpt, verbose ? 1 : 0);
 }
 
 }  // namespace
 
 int main(int argc, char **argv) {
+    if (argc >= 2 && strcmp(argv[1], "lpc") == 0) return main_lpc(argc, argv);
     if (argc < 3 || strcmp(argv[1], "vq") != 0) return usage();
     const std::string cmd = argv[2];
     std::string base_cb, class_name, codebook, tt, templ = "data/predictors";

@@ -165,3 +165,47 @@ def test_device_signal_not_16_byte_aligned(built_lib):
         assert (buf.data_ptr() + 8) % 16 == 8
         assert lpc.lpa_on_signal_device(buf.data_ptr() + 8, len(x), rate, P, W, O, dv.data_ptr(), T) == T
         assert np.array_equal(dv.cpu().numpy(), want), (rate, P)
+
+
+def test_cli_wav_to_symbols(built_lib, tmp_path):
+    """The whole chain with the reference's command lines: `ecoz2 lpc` (wav -> .prd), `ecoz2 vq learn`
+    on those predictors, `ecoz2 vq quantize` -> .seq; the .prd holds what the oracle computes."""
+    import struct
+    import subprocess
+    from ecoz2rs_b200 import formats
+    from oracle import lpc_oracle as lo
+    exe = os.path.join(ROOT, "ecoz2rs_b200", "csrc", "ecoz2")
+    wavs = []
+    for k, cls in enumerate(("A", "A", "Bm")):
+        x = _signal(64000 + 1000 * k, 50 + k)
+        pcm = np.clip(np.round(x * 32768.0), -32768, 32767).astype("<i2")
+        d = tmp_path / "signals" / cls
+        d.mkdir(parents=True, exist_ok=True)
+        w = d / f"s{k}.wav"
+        hdr = b"RIFF" + struct.pack("<I", 36 + pcm.nbytes) + b"WAVEfmt " + struct.pack("<IHHIIHH", 16, 1, 1, 32000, 64000, 2, 16)
+        w.write_bytes(hdr + b"data" + struct.pack("<I", pcm.nbytes) + pcm.tobytes())
+        wavs.append((w, cls, pcm))
+    env = dict(os.environ, ECOZ2_VQ_MAX_M="16", ECOZ2_VQ_MIN_DISTS="0")
+    r = subprocess.run([exe, "lpc", "-P", "20", "-W", "45", "-O", "15", "--signals", str(tmp_path / "signals")],
+                       cwd=tmp_path, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    total = 0
+    for w, cls, pcm in wavs:
+        got_cls, vec = formats.read_prd(str(tmp_path / "data" / "predictors" / cls / (w.stem + ".prd")))
+        want = lo.lpa_on_signal((pcm.astype(np.float32) / np.float32(32768.0)).astype(np.float64), 32000., 20, 45, 15)
+        assert got_cls == cls and vec.shape == want.shape and _rel(vec, want) < RTOL
+        total += len(vec)
+    r = subprocess.run([exe, "vq", "learn", "-P", "20", "--predictors", str(tmp_path / "data" / "predictors")],
+                       cwd=tmp_path, env=env, capture_output=True, text=True, timeout=300)
+    assert r.returncode == 0 and "Ecoz2ObserverRef.step: M=16" in r.stdout, r.stdout + r.stderr
+    cb = tmp_path / "data" / "codebooks" / "_" / "eps_0.05_M_0016.cbook"
+    r = subprocess.run([exe, "vq", "quantize", "--codebook", str(cb), "--predictors",
+                        str(tmp_path / "data" / "predictors")], cwd=tmp_path, env=env, capture_output=True,
+                       text=True, timeout=300)
+    assert r.returncode == 0, r.stdout + r.stderr
+    n = 0
+    for w, cls, _ in wavs:
+        c, M, seq = formats.read_seq(str(tmp_path / "data" / "sequences" / "M16" / cls / (w.stem + ".seq")))
+        assert (c, M) == (cls, 16) and seq.max() < 16
+        n += len(seq)
+    assert n == total
