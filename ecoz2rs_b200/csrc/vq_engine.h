@@ -134,7 +134,9 @@ class Engine {
     int sync_all();
     void harvest_times(bool with_cells);
 
-    bool small_path() const { return use_small_ && pass_small_supported(K_, D_) && !tc_path(); }
+    bool small_path() const {
+        return use_small_ && pass_small_supported(K_, D_) && (!tc_path() || pass_small_fast(K_, D_));
+    }
     bool tc_path() const { return mode_ == ECOZ2B200_MODE_TF32X3 && assign_tc_supported(K_, D_); }
     bool use_small_ = true;   // ECOZ2_VQ_FUSED_SMALL=0 forces the tiled path at every K
     bool use_cell_sort_ = true;  // ECOZ2_VQ_CELL_SORT=0: per-frame atomics (vq_accumulate) instead

@@ -886,7 +886,298 @@ vq_pass_small(const double *__restrict__ x64, long n, const double *__restrict__
     }
 }
 
-bool pass_small_supported(int K, int D) { return K <= 32 && (D == 37 || D == 13); }
+// --------------------------------------------------------------------------------
+// (a+b) fused small-codebook pass, second version: thread = frame.
+// The first version above gives a lane to every codeword, so a frame costs D warp-wide
+// DFMAs whatever K is (2.9 ms per 10M-frame pass, K-independent).  Here
+//   * a CTA of 64 threads takes tiles of 128 consecutive frames: ONE cp.async.bulk of the
+//     contiguous 128 x D doubles (37.9 KB at D = 37) into shared memory; up to 5 CTAs per SM
+//     keep enough bytes in flight without double buffering;
+//   * a thread takes two rows (row stride D is odd: conflict-free 8-byte accesses) and keeps all
+//     2 x KT running distortions in registers; the codebook sits in shared memory as [m][KT]
+//     (factor 2 folded in), read as 16-byte broadcasts: one load feeds four DFMAs.  (With the
+//     codebook in __constant__ memory the kernel ran at a third of the DFMA rate: 5-10 KB cycled
+//     once per frame do not stay in the constant cache);
+//   * argmin with strict '<' in index order (vq_learn_par.c:66-75, quantize.c:14-30);
+//   * cell sums live in REGISTERS for the whole kernel: lane m of a warp owns components m and
+//     m + 32 of all KT cells; the warp walks its 64 rows (cell index by shuffle, 8 rows per step)
+//     and every cell's accumulator takes the row under a predicate.  KT predicated adds per row
+//     cost issue slots but there is no dependent load-add-store chain (per-warp shared-memory
+//     tables, tried first, spent 70 cycles per row in that chain and limited the CTAs per SM);
+//     counts through match_any + one shared int atomic per distinct cell and warp;
+//   * per-cell distortion and DD come from the sums (vq_small_finish: cellsum . w - count),
+//     like the sorted path of vq_cells.cu; the inertia pass (CELLS = false) adds DD and
+//     sum ddmin^2 directly.
+// FP64 throughout: K x D DFMAs per frame under the HBM time of the 8 D bytes per frame.
+// --------------------------------------------------------------------------------
+constexpr int kSmallMaxK = 16, kSmallTile = 128, kSmallThreads = 64;
+constexpr int kSmallRows = kSmallTile / kSmallThreads;   // frames per thread
+
+template <int DT, int KT, bool CELLS>
+__global__ void __launch_bounds__(kSmallThreads, 5)
+vq_pass_small2(const double *__restrict__ x64, long n, const double *__restrict__ raas, int K, PackedLayout L,
+               double *__restrict__ packed, int32_t *__restrict__ idx_out, double *__restrict__ mindist,
+               uint16_t *__restrict__ seq, int bulk_ok) {
+    constexpr int D = DT, R = kSmallRows, NW = kSmallThreads / 32;
+    constexpr bool HI = D > 32;   // components 32.. exist
+    extern __shared__ __align__(16) unsigned char smem_small2[];
+    double *tile = reinterpret_cast<double *>(smem_small2);                       // [128][D]
+    double *wsm = tile + kSmallTile * D;                                          // [D][KT] weights
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    __shared__ uint64_t s_bar;
+    __shared__ int s_cnt[kSmallMaxK];
+    __shared__ double s_dd[NW], s_in[NW];
+    const uint32_t bar = smem_u32(&s_bar);
+    for (int e = threadIdx.x; e < D * KT; e += kSmallThreads) {
+        const int m = e / KT, c = e % KT;
+        const double v = c < K ? raas[(long) c * D + m] : 0.0;
+        wsm[e] = m > 0 ? 2.0 * v : v;   // exact doubling: distortion = r0 a0 + 2 sum r_m a_m (distortion.c:6-13)
+    }
+    if (CELLS && threadIdx.x < kSmallMaxK) s_cnt[threadIdx.x] = 0;
+    if (threadIdx.x == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(bar));
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
+
+    double sum_lo[CELLS ? KT : 1], sum_hi[CELLS && HI ? KT : 1];   // cell sums, components lane / lane + 32
+#pragma unroll
+    for (int c = 0; c < (CELLS ? KT : 1); c++) sum_lo[c] = 0.0;
+#pragma unroll
+    for (int c = 0; c < (CELLS && HI ? KT : 1); c++) sum_hi[c] = 0.0;
+    double dd_sum = 0.0, in_sum = 0.0;
+    uint32_t phase = 0;
+    const long n_tiles = (n + kSmallTile - 1) / kSmallTile;
+    for (long t = blockIdx.x; t < n_tiles; t += gridDim.x) {
+        const long v0 = t * kSmallTile;
+        const int rows = (int) (n - v0 < kSmallTile ? n - v0 : kSmallTile);
+        if (bulk_ok && rows == kSmallTile) {
+            if (threadIdx.x == 0) {
+                constexpr uint32_t bytes = kSmallTile * D * 8;
+                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // the tile's readers are done
+                asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+                asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
+                                 "r"(smem_u32(tile)), "l"(x64 + v0 * D), "r"(bytes), "r"(bar)
+                             : "memory");
+            }
+            uint32_t done = 0;
+            while (!done)
+                asm volatile("{\n.reg .pred q;\nmbarrier.try_wait.parity.shared::cta.b64 q, [%1], %2;\n"
+                             "selp.u32 %0, 1, 0, q;\n}\n"
+                             : "=r"(done)
+                             : "r"(bar), "r"(phase)
+                             : "memory");
+            phase ^= 1;
+        } else {
+            for (int e = threadIdx.x; e < rows * D; e += kSmallThreads) tile[e] = x64[v0 * D + e];
+            __syncthreads();
+        }
+        // rows threadIdx.x and threadIdx.x + 64 (rows past the end of a partial tile read stale
+        // shared memory and are discarded)
+        int best[R];
+        {
+            const double *xr = tile + threadIdx.x * D;
+            double acc[R][KT];
+#pragma unroll
+            for (int m = 0; m < D; m++) {
+                double xv[R];
+#pragma unroll
+                for (int q = 0; q < R; q++) xv[q] = xr[q * kSmallThreads * D + m];
+#pragma unroll
+                for (int c = 0; c < KT; c += 2) {
+                    const double2 wv = *reinterpret_cast<const double2 *>(wsm + m * KT + c);
+#pragma unroll
+                    for (int q = 0; q < R; q++) {
+                        acc[q][c] = m == 0 ? xv[q] * wv.x : fma(xv[q], wv.x, acc[q][c]);
+                        acc[q][c + 1] = m == 0 ? xv[q] * wv.y : fma(xv[q], wv.y, acc[q][c + 1]);
+                    }
+                }
+            }
+#pragma unroll
+            for (int q = 0; q < R; q++) {
+                double bv = acc[q][0];
+                best[q] = 0;
+#pragma unroll
+                for (int c = 1; c < KT; c++)
+                    if (c < K && acc[q][c] < bv) {
+                        bv = acc[q][c];
+                        best[q] = c;
+                    }
+                const int r = threadIdx.x + q * kSmallThreads;
+                if (r < rows) {
+                    const double md = bv - 1.0;
+                    dd_sum += md;
+                    in_sum += bv * bv;
+                    idx_out[v0 + r] = best[q];
+                    if (mindist) mindist[v0 + r] = md;
+                    if (seq) seq[v0 + r] = (uint16_t) best[q];
+                } else {
+                    best[q] = -1;   // matches no cell below
+                }
+            }
+        }
+        if (CELLS) {
+#pragma unroll
+            for (int q = 0; q < R; q++) {
+                const int first = q * kSmallThreads + w * 32;   // first row of this warp's group
+                if (first < rows) {
+                    if (best[q] >= 0) {
+                        const unsigned same = __match_any_sync(__activemask(), best[q]);
+                        if (lane == __ffs(same) - 1) atomicAdd(&s_cnt[best[q]], __popc(same));
+                    }
+                    const double *wt = tile + (size_t) first * D;
+#pragma unroll 1
+                    for (int u = 0; u < 32; u += 8) {
+                        int cu[8];
+                        double xa[8], xb[8];
+#pragma unroll
+                        for (int k = 0; k < 8; k++) {
+                            cu[k] = __shfl_sync(0xffffffffu, best[q], u + k);
+                            xa[k] = lane < D ? wt[(u + k) * D + lane] : 0.0;
+                            xb[k] = HI && lane + 32 < D ? wt[(u + k) * D + lane + 32] : 0.0;
+                        }
+#pragma unroll
+                        for (int k = 0; k < 8; k++)
+#pragma unroll
+                            for (int c = 0; c < KT; c++) {
+                                // explicitly predicated adds: written as `if (cu == c) sum[c] += x` the
+                                // compiler turns the chain into a dynamically indexed local-memory array
+                                if (HI)
+                                    asm("{\n.reg .pred p;\nsetp.eq.s32 p, %3, %4;\n@p add.rn.f64 %0, %0, %2;\n"
+                                        "@p add.rn.f64 %1, %1, %5;\n}"
+                                        : "+d"(sum_lo[c]), "+d"(sum_hi[HI ? c : 0])
+                                        : "d"(xa[k]), "r"(cu[k]), "r"(c), "d"(xb[k]));
+                                else
+                                    asm("{\n.reg .pred p;\nsetp.eq.s32 p, %2, %3;\n@p add.rn.f64 %0, %0, %1;\n}"
+                                        : "+d"(sum_lo[c])
+                                        : "d"(xa[k]), "r"(cu[k]), "r"(c));
+                            }
+                    }
+                }
+            }
+        }
+        __syncthreads();   // the tile is free for the next copy
+    }
+
+    // ---- flush: register cell sums and partial sums -> global packed buffer
+#pragma unroll
+    for (int off = 16; off >= 1; off >>= 1) {
+        dd_sum += __shfl_xor_sync(0xffffffffu, dd_sum, off);
+        in_sum += __shfl_xor_sync(0xffffffffu, in_sum, off);
+    }
+    if (lane == 0) {
+        s_dd[w] = dd_sum;
+        s_in[w] = in_sum;
+    }
+    __syncthreads();
+    if (CELLS) {
+#pragma unroll
+        for (int c = 0; c < KT; c++) {
+            if (c < K) {
+                if (lane < D && sum_lo[c] != 0.0) atomicAdd(packed + L.cells() + (long) c * D + lane, sum_lo[c]);
+                if (HI && lane + 32 < D && sum_hi[c] != 0.0)
+                    atomicAdd(packed + L.cells() + (long) c * D + lane + 32, sum_hi[c]);
+            }
+        }
+        if (threadIdx.x < K && s_cnt[threadIdx.x] > 0)
+            atomicAdd(packed + L.counts() + threadIdx.x, (double) s_cnt[threadIdx.x]);
+    }
+    if (threadIdx.x == 0) {
+        double a = 0.0, b2 = 0.0;
+#pragma unroll
+        for (int ww = 0; ww < NW; ww++) {
+            a += s_dd[ww];
+            b2 += s_in[ww];
+        }
+        if (!CELLS) atomicAdd(packed + L.dd(), a);
+        atomicAdd(packed + L.inertia(), b2);
+    }
+}
+
+// per-cell distortion = cellsum . w - count, DD = their sum (same identity as vq_cell_finish)
+__global__ void __launch_bounds__(256) vq_small_finish(const double *__restrict__ raas, PackedLayout L,
+                                                       double *__restrict__ packed) {
+    const int K = L.K, D = L.D;
+    const int lane = threadIdx.x & 31, c = threadIdx.x >> 5;   // one CTA, warp c handles cells c, c + 8, ..
+    double dd = 0.0;
+    for (int cc = c; cc < K; cc += 8) {
+        double part = 0.0;
+        for (int m = lane; m < D; m += 32) {
+            const double wv = m > 0 ? 2.0 * raas[(long) cc * D + m] : raas[(long) cc * D];
+            part = fma(packed[L.cells() + (long) cc * D + m], wv, part);
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) part += __shfl_xor_sync(0xffffffffu, part, off);
+        const double cnt = packed[L.counts() + cc];
+        const double dis = cnt > 0.0 ? part - cnt : 0.0;
+        if (lane == 0) packed[L.discel() + cc] = dis;
+        dd += dis;
+    }
+    __shared__ double s_part[8];
+    if (lane == 0) s_part[c] = dd;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0;
+        for (int i = 0; i < 8; i++) a += s_part[i];
+        packed[L.dd()] += a;
+    }
+}
+
+static bool small2_enabled() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("ECOZ2_VQ_SMALL2"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v == 1;
+}
+
+template <int DT, int KT>
+static void launch_pass_small2_k(const double *x64, long n, const double *raas, int K, double *packed,
+                                 int32_t *idx, double *mindist, uint16_t *seq, bool with_cells, int num_sms,
+                                 cudaStream_t s) {
+    PackedLayout L{K, DT};
+    const size_t smem = sizeof(double) * ((size_t) kSmallTile * DT + (size_t) DT * KT);
+    const int bulk_ok = (reinterpret_cast<uintptr_t>(x64) & 15) == 0;
+    long blocks = (long) num_sms * 5;
+    const long tiles = (n + kSmallTile - 1) / kSmallTile;
+    if (blocks > tiles) blocks = tiles;
+    if (with_cells) {
+        cudaFuncSetAttribute(vq_pass_small2<DT, KT, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        vq_pass_small2<DT, KT, true><<<(unsigned) blocks, kSmallThreads, smem, s>>>(x64, n, raas, K, L, packed, idx,
+                                                                                  mindist, seq, bulk_ok);
+        vq_small_finish<<<1, 256, 0, s>>>(raas, L, packed);
+    } else {
+        cudaFuncSetAttribute(vq_pass_small2<DT, KT, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) smem);
+        vq_pass_small2<DT, KT, false><<<(unsigned) blocks, kSmallThreads, smem, s>>>(x64, n, raas, K, L, packed, idx,
+                                                                                   mindist, seq, bulk_ok);
+    }
+}
+template <int DT>
+static void launch_pass_small2_d(const double *x64, long n, const double *raas, int K, double *packed,
+                                 int32_t *idx, double *mindist, uint16_t *seq, bool with_cells, int num_sms,
+                                 cudaStream_t s) {
+    if (K <= 2) launch_pass_small2_k<DT, 2>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
+    else if (K <= 4) launch_pass_small2_k<DT, 4>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
+    else if (K <= 8) launch_pass_small2_k<DT, 8>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
+    else launch_pass_small2_k<DT, 16>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
+}
+
+// largest codebook the thread-per-frame kernel takes (ECOZ2_VQ_SMALL2_MAXK, up to 16).  Measured on
+// B200, 10M frames, P = 36, ms per pass against 1.47-1.50 of tensor-core search + sorted cell sums:
+// K = 2: 0.54, 4: 0.79, 8: 1.42, 16: 2.85 -- ptxas turns the predicated adds into add + select, so
+// the register cell sums cost K adds per row and component; the default stops at 4.
+static int small2_max_k() {
+    static int v = -1;
+    if (v < 0) {
+        const char *e = getenv("ECOZ2_VQ_SMALL2_MAXK");
+        v = e ? atoi(e) : 4;
+        if (v > kSmallMaxK) v = kSmallMaxK;
+        if (v < 0) v = 0;
+    }
+    return v;
+}
+static bool small2_takes(int K, int D) { return small2_enabled() && K <= small2_max_k() && (D == 37 || D == 21 || D == 13); }
+
+bool pass_small_fast(int K, int D) { return small2_takes(K, D); }
+bool pass_small_supported(int K, int D) { return (K <= 32 && (D == 37 || D == 13)) || small2_takes(K, D); }
 
 template <int DT>
 static void launch_pass_small_d(const double *x64, long n, const double *raas, int K, double *packed,
@@ -914,6 +1205,12 @@ void launch_pass_small(const double *x64, long n, int D, const double *raas, int
                        int32_t *idx, double *mindist, uint16_t *seq, bool with_cells, int num_sms,
                        cudaStream_t s) {
     if (n <= 0) return;
+    if (small2_takes(K, D)) {
+        if (D == 37) launch_pass_small2_d<37>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
+        else if (D == 21) launch_pass_small2_d<21>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
+        else launch_pass_small2_d<13>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
+        return;
+    }
     if (D == 37) launch_pass_small_d<37>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
     else launch_pass_small_d<13>(x64, n, raas, K, packed, idx, mindist, seq, with_cells, num_sms, s);
 }

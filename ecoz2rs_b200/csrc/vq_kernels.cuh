@@ -137,6 +137,9 @@ void launch_cell_sums(const double *x64, const int32_t *idx, long n, int D, cons
 // One sweep over the FP64 frames: exact argmin (first index on ties), idx / mindist / seq
 // outputs, and (with_cells) the packed cell sums, counts, distortions; DD and inertia always.
 bool pass_small_supported(int K, int D);
+// the thread-per-frame version (vq_pass_small2) takes this codebook: faster than search + cell sums,
+// so the tensor-core mode uses it too (ECOZ2_VQ_SMALL2=0: first version, FP32/FP64 modes only)
+bool pass_small_fast(int K, int D);
 void launch_pass_small(const double *x64, long n, int D, const double *raas, int K, double *packed,
                        int32_t *idx, double *mindist, uint16_t *seq, bool with_cells, int num_sms,
                        cudaStream_t s);
