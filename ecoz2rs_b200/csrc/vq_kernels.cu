@@ -1021,8 +1021,9 @@ vq_pass_small2(const double *__restrict__ x64, long n, const double *__restrict_
             for (int q = 0; q < R; q++) {
                 const int first = q * kSmallThreads + w * 32;   // first row of this warp's group
                 if (first < rows) {
+                    const unsigned live = __ballot_sync(0xffffffffu, best[q] >= 0);
                     if (best[q] >= 0) {
-                        const unsigned same = __match_any_sync(__activemask(), best[q]);
+                        const unsigned same = __match_any_sync(live, best[q]);
                         if (lane == __ffs(same) - 1) atomicAdd(&s_cnt[best[q]], __popc(same));
                     }
                     const double *wt = tile + (size_t) first * D;
