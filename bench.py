@@ -64,8 +64,34 @@ class ClockSampler:
         self.device = device
         self.proc = None
         self.path = None
+        self.thread = None
+        self.rows = []      # NVML samples: (sm MHz, power W, reasons bitmask)
+        self.nvml_max = None
+        self._stop = False
+
+    def _nvml_loop(self, nv, h):
+        while not self._stop:
+            try:
+                self.rows.append((float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)),
+                                  nv.nvmlDeviceGetPowerUsage(h) / 1000.0,
+                                  int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))))
+            except Exception:
+                break
+            time.sleep(0.002)
 
     def start(self):
+        # NVML in a thread (a sample every ~2 ms: the timed region of a multi-GPU run lasts tens of
+        # milliseconds); nvidia-smi -lms 100 runs beside it as the recipe's own clocks line
+        try:
+            import threading
+            import pynvml as nv
+            nv.nvmlInit()
+            h = nv.nvmlDeviceGetHandleByIndex(self.device)
+            self.nvml_max = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
+            self.thread = threading.Thread(target=self._nvml_loop, args=(nv, h), daemon=True)
+            self.thread.start()
+        except Exception:
+            self.thread = None
         try:
             fd, self.path = tempfile.mkstemp(suffix=".csv")
             self.proc = subprocess.Popen(
@@ -77,13 +103,12 @@ class ClockSampler:
 
     def stop(self) -> dict:
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
-        if not self.proc:
-            return out
-        self.proc.terminate()
-        try:
-            self.proc.wait(timeout=5)
-        except subprocess.TimeoutExpired:
-            self.proc.kill()
+        if self.proc:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
         sm, reasons, mx, pw = [], set(), None, []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         try:
@@ -102,11 +127,25 @@ class ClockSampler:
                         if v.lower().startswith("active"):
                             reasons.add(n)
             os.unlink(self.path)
-        except OSError:
+        except (OSError, TypeError):
             pass
         if sm:
             out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": mx, "reasons": sorted(reasons),
-                   "samples": len(sm), "power_w_max": max(pw) if pw else None}
+                   "samples": len(sm), "power_w_max": max(pw) if pw else None, "source": "nvidia-smi -lms 100"}
+        if self.thread is not None:
+            self._stop = True
+            self.thread.join(timeout=2)
+            if len(self.rows) > len(sm):
+                bits = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
+                        0x4: "sw_power_cap"}
+                rs = set(reasons)
+                for _, _, m in self.rows:
+                    for b, n in bits.items():
+                        if m & b:
+                            rs.add(n)
+                out = {"sm_mhz": float(np.median([r[0] for r in self.rows])), "sm_max_mhz": self.nvml_max or mx,
+                       "reasons": sorted(rs), "samples": len(self.rows),
+                       "power_w_max": max(r[1] for r in self.rows), "source": "NVML, 2 ms period"}
         return out
 
 

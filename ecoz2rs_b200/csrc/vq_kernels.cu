@@ -913,6 +913,29 @@ vq_pass_small(const double *__restrict__ x64, long n, const double *__restrict__
 constexpr int kSmallMaxK = 16, kSmallTile = 128, kSmallThreads = 64;
 constexpr int kSmallRows = kSmallTile / kSmallThreads;   // frames per thread
 
+// sum[cu] += x with the accumulators in registers: a warp-uniform switch whose cases add into
+// statically named registers.  The adds are asm volatile on purpose: written as plain C++
+// (`if (cu == c) sum[c] += x`) the compiler turns the chain into a dynamically indexed local-memory
+// array, and explicitly predicated adds become add + select (K adds per row).
+template <int KT, bool HI, int NLO, int NHI>
+__device__ __forceinline__ void small_add_to_cell(double (&lo)[NLO], double (&hi)[NHI], int cu, double xa, double xb) {
+#define ECOZ2_SMALL_CASE(c)                                                              \
+    case c:                                                                              \
+        if constexpr (c < KT && c < NLO) {                                               \
+            asm volatile("add.rn.f64 %0, %0, %1;" : "+d"(lo[c]) : "d"(xa));              \
+            if constexpr (HI && c < NHI) asm volatile("add.rn.f64 %0, %0, %1;" : "+d"(hi[c]) : "d"(xb)); \
+        }                                                                                \
+        break;
+    switch (cu) {
+        ECOZ2_SMALL_CASE(0) ECOZ2_SMALL_CASE(1) ECOZ2_SMALL_CASE(2) ECOZ2_SMALL_CASE(3)
+        ECOZ2_SMALL_CASE(4) ECOZ2_SMALL_CASE(5) ECOZ2_SMALL_CASE(6) ECOZ2_SMALL_CASE(7)
+        ECOZ2_SMALL_CASE(8) ECOZ2_SMALL_CASE(9) ECOZ2_SMALL_CASE(10) ECOZ2_SMALL_CASE(11)
+        ECOZ2_SMALL_CASE(12) ECOZ2_SMALL_CASE(13) ECOZ2_SMALL_CASE(14) ECOZ2_SMALL_CASE(15)
+        default: break;
+    }
+#undef ECOZ2_SMALL_CASE
+}
+
 template <int DT, int KT, bool CELLS>
 __global__ void __launch_bounds__(kSmallThreads, 5)
 vq_pass_small2(const double *__restrict__ x64, long n, const double *__restrict__ raas, int K, PackedLayout L,
@@ -1039,16 +1062,12 @@ vq_pass_small2(const double *__restrict__ x64, long n, const double *__restrict_
                         }
 #pragma unroll
                         for (int k = 0; k < 8; k++)
+                            if constexpr (HI) {
+                                small_add_to_cell<KT, HI>(sum_lo, sum_hi, cu[k], xa[k], xb[k]);
+                            } else {
+                                // short rows (D <= 32): K add + select pairs are cheaper than the jump
 #pragma unroll
-                            for (int c = 0; c < KT; c++) {
-                                // explicitly predicated adds: written as `if (cu == c) sum[c] += x` the
-                                // compiler turns the chain into a dynamically indexed local-memory array
-                                if (HI)
-                                    asm("{\n.reg .pred p;\nsetp.eq.s32 p, %3, %4;\n@p add.rn.f64 %0, %0, %2;\n"
-                                        "@p add.rn.f64 %1, %1, %5;\n}"
-                                        : "+d"(sum_lo[c]), "+d"(sum_hi[HI ? c : 0])
-                                        : "d"(xa[k]), "r"(cu[k]), "r"(c), "d"(xb[k]));
-                                else
+                                for (int c = 0; c < KT; c++)
                                     asm("{\n.reg .pred p;\nsetp.eq.s32 p, %2, %3;\n@p add.rn.f64 %0, %0, %1;\n}"
                                         : "+d"(sum_lo[c])
                                         : "d"(xa[k]), "r"(cu[k]), "r"(c));
@@ -1162,20 +1181,21 @@ static void launch_pass_small2_d(const double *x64, long n, const double *raas, 
 }
 
 // largest codebook the thread-per-frame kernel takes (ECOZ2_VQ_SMALL2_MAXK, up to 16).  Measured on
-// B200, 10M frames, P = 36, ms per pass against 1.47-1.50 of tensor-core search + sorted cell sums:
-// K = 2: 0.54, 4: 0.79, 8: 1.42, 16: 2.85 -- ptxas turns the predicated adds into add + select, so
-// the register cell sums cost K adds per row and component; the default stops at 4.
-static int small2_max_k() {
-    static int v = -1;
-    if (v < 0) {
+// B200, ms per pass.  10M frames, P = 36, against 1.47-1.50 of tensor-core search + sorted cell sums:
+// K = 2: 0.56, 4: 0.75, 8: 1.01, 16: 1.58 (jump per row; with add + select: 0.54, 0.79, 1.42, 2.85).
+// 20M frames, P = 12, against 1.31-1.42: add + select 0.70, 0.99, 1.64, 2.91 (jump: 0.87, 1.25, 1.65,
+// 2.20).  Defaults: K <= 8 for rows longer than 32, K <= 4 for short rows.
+static int small2_max_k(int D) {
+    static int v = -2;
+    if (v == -2) {
         const char *e = getenv("ECOZ2_VQ_SMALL2_MAXK");
-        v = e ? atoi(e) : 4;
+        v = e ? atoi(e) : -1;
         if (v > kSmallMaxK) v = kSmallMaxK;
-        if (v < 0) v = 0;
     }
-    return v;
+    if (v >= 0) return v;
+    return D > 32 ? 8 : 4;
 }
-static bool small2_takes(int K, int D) { return small2_enabled() && K <= small2_max_k() && (D == 37 || D == 21 || D == 13); }
+static bool small2_takes(int K, int D) { return small2_enabled() && K <= small2_max_k(D) && (D == 37 || D == 21 || D == 13); }
 
 bool pass_small_fast(int K, int D) { return small2_takes(K, D); }
 bool pass_small_supported(int K, int D) { return (K <= 32 && (D == 37 || D == 13)) || small2_takes(K, D); }

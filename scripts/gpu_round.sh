@@ -36,3 +36,10 @@ timeout 900 ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_d
 ECOZ2_VQ_TC_EXP=256 timeout 300 python scripts/perf_probe.py --n 10000000 --ks 2048 --reps 20 2>&1 \
     | grep -E "tc prof|K=" | tail -4 > $O/clock_$TAG.log
 ls -la $O
+# fused small-codebook pass (K = 2) and the LPC front end: ncu --set full of one launch each
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:"vq_pass_small2" --launch-skip 4 --launch-count 1 \
+    -o $O/small2_$TAG -f python scripts/perf_probe.py --n 10000000 --ks 2 --reps 2 > $O/ncu_small2_$TAG.log 2>&1
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:"lpc_autocorr" --launch-skip 2 --launch-count 1 \
+    -o $O/lpc_$TAG -f python scripts/lpc_probe.py --seconds 3600 --reps 2 > $O/ncu_lpc_full_$TAG.log 2>&1
+timeout 300 python scripts/lpc_probe.py --seconds 3600 > $O/lpc_probe_$TAG.log 2>&1
+ls -la $O

@@ -328,3 +328,45 @@ def test_kmeans_pass_host_equals_resident_pass(built_lib, K):
     assert abs(a0["DD"] - a1["DD"]) <= 1e-10 * abs(a0["DD"])
     assert np.allclose(r0, r1, rtol=1e-10, atol=1e-13)
     assert abs(b0["DD"] - b1["DD"]) <= 1e-9 * abs(b0["DD"])
+
+
+@pytest.mark.parametrize("P", [36, 12, 20])
+def test_fused_small_codebook_pass_edges(built_lib, P):
+    """vq_pass_small2 (K <= 4, every mode): partial and single tiles, K = 1 / 3 (not a power of two),
+    an FP64 frame pointer that is only 8-byte aligned (chunked host pass), cells / counts / DD /
+    indices / symbols / inertia against the oracle."""
+    from ecoz2rs_b200.synth import ar_mix
+    from oracle import oracle as O
+    rng = np.random.default_rng(11 + P)
+    xall = ar_mix(5000, P, seed=77 + P)
+    for K, N in [(1, 1), (2, 127), (2, 128), (3, 129), (4, 1000), (2, 5000), (4, 4999)]:
+        refl = np.zeros((K, P + 1))
+        refl[:, 1:] = np.clip(rng.normal(size=(K, P)) * 0.3, -0.9, 0.9)
+        raas = O.refl_to_raas(refl)
+        x = xall[:N]
+        ref = O.kmeans_pass(x, refl, raas)
+        for mode in (2, 0):
+            with _engine(P, max_M=64, mode=mode) as eng:
+                eng.set_frames(x)
+                eng.set_reflections(refl)
+                idx, dd, nre = eng.assign()
+                bad = allowed_index_mismatches(idx, ref["idx"], ref["ddmin"], ref["second"])
+                assert bad.size == 0, (K, N, mode)
+                assert np.allclose(dd, ref["ddmin"], rtol=1e-12, atol=0)
+                out = eng.kmeans_pass()
+                assert np.array_equal(out["cardd"], ref["cardd"]), (K, N, mode)
+                assert np.allclose(out["cells"], ref["cells"], rtol=REL_TIGHT, atol=1e-9)
+                assert abs(out["DD"] - ref["DD"]) <= REL_TIGHT * max(1.0, abs(ref["DD"]))
+                assert np.allclose(out["discel"], ref["discel"], rtol=1e-7, atol=1e-9)
+                eng.set_reflections(refl)
+                inert = eng.inertia()
+                assert abs(inert - O.inertia(x, raas)) <= 1e-9 * abs(inert)
+                seq, avg = eng.quantize(x)        # chunk pipeline: frames at arbitrary row offsets
+                oseq, oavg = O.quantize(raas, x)
+                assert np.array_equal(seq, oseq) and abs(avg - oavg) <= 1e-9 * max(1.0, abs(oavg))
+                if N > 3:
+                    # host pass over a view that starts at an odd row: 8-byte aligned rows when P+1 is odd
+                    out2 = eng.kmeans_pass_host(np.ascontiguousarray(x[1:]))
+                    ref2 = O.kmeans_pass(x[1:], refl, raas)
+                    assert np.array_equal(out2["cardd"], ref2["cardd"])
+                    assert np.allclose(out2["cells"], ref2["cells"], rtol=REL_TIGHT, atol=1e-9)
