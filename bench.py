@@ -493,6 +493,26 @@ def run_b200_arm(args):
                                      "note": "whole call (Hamming table, autocorrelation, Levinson, "
                                              "error-count read-back); algorithmic flops = frames x window x "
                                              "(P+1) x 2"}}
+            # cpu_baseline leg: the reference's own lpa_on_signal (oracle/_ref, OpenMP over frames) on the
+            # first 10 minutes of the same signal, all host threads; the GPU vectors are checked against it
+            if not args.no_cpu_baseline:
+                try:
+                    from oracle import refbuild
+                    if refbuild.lpc_available():
+                        n_s = int(600 * rate)
+                        xs = sig[:n_s].cpu().numpy()
+                        tm = {}
+                        refbuild.ref_lpa_on_signal(xs[:int(30 * rate)], rate, P, wms, oms)   # warm (thread pool)
+                        want = refbuild.ref_lpa_on_signal(xs, rate, P, wms, oms, timing=tm)
+                        got = vec[:len(want)].cpu().numpy()
+                        rel = float(np.max(np.abs(got - want) / np.maximum(np.abs(want), 1e-300)))
+                        lpc_info["cpu_baseline"] = {"value": len(want) / tm["seconds"], "unit": "frames/s",
+                                                    "cores": os.cpu_count(), "kind": "reference",
+                                                    "sample": "lpa_on_signal (reference C, OpenMP) on the first "
+                                                              "600 s of the signal, %d frames" % len(want),
+                                                    "max_rel_diff_vs_gpu": rel}
+                except Exception as e:
+                    log(f"[lpc] reference baseline failed: {e!r}")
             del sig, vec
         except Exception as e:
             log(f"[lpc] failed: {e!r}")

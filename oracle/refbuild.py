@@ -279,13 +279,19 @@ def lpc_lib():
     return _lpc_lib
 
 
-def ref_lpa_on_signal(signal, sample_rate, P, window_ms, offset_ms, threads=None):
-    """lpa_on_signal (lpa_on_signal.c:81) -> vectors [T, P+1], or None (signal too short)."""
+def ref_lpa_on_signal(signal, sample_rate, P, window_ms, offset_ms, threads=None, timing=None):
+    """lpa_on_signal (lpa_on_signal.c:81) -> vectors [T, P+1], or None (signal too short).
+    timing (optional dict): receives "seconds" = duration of the C call alone."""
+    import time
     x = _f64(signal)
     sgn = _Sgn(_d(x), len(x), float(sample_rate))
     if threads is not None:
         os.environ["OMP_NUM_THREADS"] = str(threads)
-    p = lpc_lib().lpa_on_signal(P, window_ms, offset_ms, C.byref(sgn), 0)
+    L = lpc_lib()
+    t0 = time.perf_counter()
+    p = L.lpa_on_signal(P, window_ms, offset_ms, C.byref(sgn), 0)
+    if timing is not None:
+        timing["seconds"] = time.perf_counter() - t0
     if not p:
         return None
     prd = p.contents

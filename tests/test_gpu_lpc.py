@@ -209,3 +209,33 @@ def test_cli_wav_to_symbols(built_lib, tmp_path):
         assert (c, M) == (cls, 16) and seq.max() < 16
         n += len(seq)
     assert n == total
+
+
+def test_signal_to_symbols_without_leaving_hbm(built_lib):
+    """the vectors of lpa_on_signal_device are handed to the VQ engine with
+    frames_append_device; codebook learning and the symbols equal the route through host arrays."""
+    import torch
+    from ecoz2rs_b200 import lpc, vq
+    P, W, O = 20, 45, 15
+    x = _signal(32000 * 120, 17)
+    host_vec = lpc.lpa_on_signal(x, 32000., P, W, O)
+    dx = torch.from_numpy(x).cuda()
+    T = lpc.num_frames(len(x), 32000., W, O)
+    dv = torch.empty((T, P + 1), dtype=torch.float64, device="cuda")
+    assert lpc.lpa_on_signal_device(dx.data_ptr(), len(x), 32000., P, W, O, dv.data_ptr(), T) == T
+    with vq.VqEngine(P, max_M=64) as a, vq.VqEngine(P, max_M=64) as b:
+        a.set_frames_device(dv.data_ptr(), T)
+        b.set_frames(host_vec)
+        for e in (a, b):
+            e.codebook_initial()
+        sa, _ = a.learn(eps=0.05, stop_M=64)
+        sb, _ = b.learn(eps=0.05, stop_M=64)
+        assert [s["passes"] for s in sa] == [s["passes"] for s in sb]
+        # the cell sums meet in FP64 atomics: equal to rounding, not bit for bit, between two runs
+        assert np.allclose(sa[-1]["refl"], sb[-1]["refl"], rtol=1e-9, atol=1e-12)
+        for e in (a, b):
+            e.set_reflections(sa[-1]["refl"])
+        seq_a, avg_a = a.quantize_resident()
+        seq_b, avg_b = b.quantize(host_vec)
+        assert np.array_equal(seq_a, seq_b) and abs(avg_a - avg_b) <= 1e-12 * abs(avg_b)
+        assert len(np.unique(seq_a)) > 32
