@@ -155,8 +155,11 @@ __global__ void __launch_bounds__(256, 1) lpc_autocorr(const AcParams p) {
 //   * lane pieces start every Ls samples with Ls odd, so the 8 lanes of a frame hit
 //     distinct 8-byte banks; the piece is processed in whole blocks of 8, the rows past
 //     the end of the piece (they belong to the next lane) are masked to zero;
-//   * 16 frames (128 threads) per CTA, two CTAs per SM: one stages its signal with
-//     cp.async while the other keeps the FP64 pipe busy.
+//   * 16 frames (128 threads) per CTA, two CTAs per SM: one stages its signal (one
+//     cp.async.bulk issued by thread 0 when the pointers are 16-byte aligned, 8-byte cp.async
+//     per thread otherwise) while the other keeps the FP64 pipe busy;
+//   * all 32 lanes of a warp stay to the end (groups past the last frame recompute frame t0
+//     and store nothing): full-mask shuffles, no reconvergence code around them.
 // ---------------------------------------------------------------------------------------
 constexpr int kFastPad = 112;   // >= (odd-Ls slack 15) + (block round-up 7) + LAGS - 1 + 2 * kStep
 
