@@ -5,7 +5,7 @@ O=gpurun_out
 mkdir -p $O
 timeout 600 python -m pytest tests/test_gpu_lpc.py -x -q > $O/pytest_lpc_$TAG.log 2>&1
 echo "pytest exit $?" >> $O/pytest_lpc_$TAG.log
-timeout 300 python scripts/lpc_probe.py --seconds 3600 --cpu > $O/lpc_probe_$TAG.log 2>&1
+timeout 300 python scripts/lpc_probe.py --seconds 3600 > $O/lpc_probe_$TAG.log 2>&1
 timeout 300 python scripts/lpc_probe.py --seconds 3600 --p 12 >> $O/lpc_probe_$TAG.log 2>&1
 timeout 300 python scripts/lpc_probe.py --seconds 3600 --p 20 --win 20 --off 5 >> $O/lpc_probe_$TAG.log 2>&1
 ECOZ2_LPC_GENERIC=1 timeout 300 python scripts/lpc_probe.py --seconds 3600 >> $O/lpc_probe_$TAG.log 2>&1

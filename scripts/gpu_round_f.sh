@@ -14,7 +14,7 @@ timeout 900 python bench.py > $O/bench_$TAG.json 2> $O/bench_$TAG.err
 echo "bench exit $?" >> $O/bench_$TAG.err
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref_$TAG.json 2> $O/bench_ref_$TAG.err
 echo "bench ref exit $?" >> $O/bench_ref_$TAG.err
-timeout 300 python scripts/lpc_probe.py --seconds 3600 --cpu > $O/lpc_probe_$TAG.log 2>&1
+timeout 300 python scripts/lpc_probe.py --seconds 3600 > $O/lpc_probe_$TAG.log 2>&1
 timeout 300 python scripts/lpc_probe.py --seconds 3600 --p 12 >> $O/lpc_probe_$TAG.log 2>&1
 timeout 300 python scripts/lpc_probe.py --seconds 3600 --p 20 --win 20 --off 5 >> $O/lpc_probe_$TAG.log 2>&1
 timeout 600 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none \

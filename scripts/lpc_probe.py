@@ -2,13 +2,12 @@
 gain-normalised vectors in HBM, CUDA events around ecoz2b200_lpa_on_signal_device.
 Reports frames/s, the FP64 FMA rate of the autocorrelation (frames x win x (P+1) FMAs) and
 the bytes moved (signal read once + vectors written once).
+(The CPU baseline of this path is timed by bench.py: lpc_front.cpu_baseline.)
 usage: python scripts/lpc_probe.py [--seconds 3600] [--rate 32000] [--p 36] [--win 45] [--off 15]"""
 import argparse
 import os
 import sys
-import time
 
-import numpy as np
 
 sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 
@@ -21,7 +20,6 @@ def main():
     ap.add_argument("--win", type=int, default=45)
     ap.add_argument("--off", type=int, default=15)
     ap.add_argument("--reps", type=int, default=10)
-    ap.add_argument("--cpu", action="store_true", help="also time the numpy oracle on a 60 s sample")
     a = ap.parse_args()
     import torch
     from ecoz2rs_b200 import lpc
@@ -51,15 +49,6 @@ def main():
     print(f"lpc P={a.p} win={win} off={int(a.off * int(a.rate) // 1000)} samples={n} frames={T}: "
           f"{ms:.3f} ms  {T / ms / 1e3:.2f} M frames/s  {2 * fma / ms / 1e9:.2f} TFLOP/s fp64  "
           f"{byts / ms / 1e6:.1f} GB/s algorithmic  ({a.seconds / (ms / 1e3):.0f}x real time)")
-    if a.cpu:
-        from oracle import lpc_oracle as lo
-        ns = int(60 * a.rate)
-        xs = x[:ns].cpu().numpy()
-        t0 = time.perf_counter()
-        w = lo.lpa_on_signal(xs, a.rate, a.p, a.win, a.off)
-        dt = time.perf_counter() - t0
-        print(f"numpy oracle: 60 s of signal, {len(w)} frames in {dt:.2f} s = {len(w) / dt / 1e3:.1f} K frames/s")
-        assert np.allclose(v[:len(w)].cpu().numpy(), w, rtol=1e-9, atol=0)
 
 
 if __name__ == "__main__":

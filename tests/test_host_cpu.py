@@ -57,6 +57,12 @@ def test_product_never_imports_oracle():
                     src = f.read()
                 assert "import oracle" not in src and "from oracle" not in src, fn
                 assert "vq_oracle" not in src and "oracle/_ref" not in src, fn
+    # the dev / measurement scripts do not use it either (checkers that need it live in tests/tools/)
+    for fn in os.listdir(os.path.join(ROOT, "scripts")):
+        if fn.endswith((".py", ".sh")):
+            with open(os.path.join(ROOT, "scripts", fn), errors="ignore") as f:
+                src = f.read()
+            assert "import oracle" not in src and "from oracle" not in src and "oracle/" not in src, fn
 
 
 def test_formats_roundtrip_and_reference_bytes(built_lib, tmp_path):

@@ -1,14 +1,14 @@
 """Repeatability stress of the two kernels added last in round 1 (compute-sanitizer is not available on
 the GPU pool): the fused small-codebook pass must give identical counts / indices and cell sums equal
 to rounding on every repetition, the LPC front end bit-identical vectors; sizes chosen to exercise
-partial tiles and the last CTA.  usage: python scripts/stress_small_lpc.py [--reps 40]"""
+partial tiles and the last CTA.  usage: python tests/tools/stress_small_lpc.py [--reps 40]"""
 import argparse
 import os
 import sys
 
 import numpy as np
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 import torch  # noqa: E402
 
 from ecoz2rs_b200 import lpc, vq  # noqa: E402
