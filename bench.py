@@ -55,7 +55,28 @@ def log(*a):
 
 # ------------------------------------------------------------------------------------
 # clocks during the timed region (B200_PROFILING.md recipe)
+_NVML_SAMPLER = r"""
+import sys, time
+import pynvml as nv
+nv.nvmlInit()
+h = nv.nvmlDeviceGetHandleByIndex(int(sys.argv[1]))
+mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
+out = open(sys.argv[2], "w", buffering=1)
+out.write("ready %d\n" % mx)
+while True:
+    out.write("%.6f %d %.1f %d\n" % (time.time(), nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM),
+                                     nv.nvmlDeviceGetPowerUsage(h) / 1000.0,
+                                     nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)))
+    time.sleep(0.002)
+"""
+
+
 class ClockSampler:
+    """SM clock, power and throttle reasons of one GPU during the timed region.  A child process
+    polls NVML every ~2 ms (the timed region of a multi-GPU run lasts tens of milliseconds, and a
+    sampling thread in THIS process would contend for the interpreter lock with the timed loop);
+    it is started before the warm-up, and only samples between begin() and end() count.  The
+    recipe's `nvidia-smi -lms 100` line is the fallback when NVML is not importable."""
     Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
@@ -64,45 +85,46 @@ class ClockSampler:
         self.device = device
         self.proc = None
         self.path = None
-        self.thread = None
-        self.rows = []      # NVML samples: (sm MHz, power W, reasons bitmask)
-        self.nvml_max = None
-        self._stop = False
-
-    def _nvml_loop(self, nv, h):
-        while not self._stop:
-            try:
-                self.rows.append((float(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)),
-                                  nv.nvmlDeviceGetPowerUsage(h) / 1000.0,
-                                  int(nv.nvmlDeviceGetCurrentClocksThrottleReasons(h))))
-            except Exception:
-                break
-            time.sleep(0.002)
+        self.nvml = False
+        self.t_begin = self.t_end = None
 
     def start(self):
-        # NVML in a thread (a sample every ~2 ms: the timed region of a multi-GPU run lasts tens of
-        # milliseconds); nvidia-smi -lms 100 runs beside it as the recipe's own clocks line
         try:
-            import threading
-            import pynvml as nv
-            nv.nvmlInit()
-            h = nv.nvmlDeviceGetHandleByIndex(self.device)
-            self.nvml_max = float(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))
-            self.thread = threading.Thread(target=self._nvml_loop, args=(nv, h), daemon=True)
-            self.thread.start()
-        except Exception:
-            self.thread = None
-        try:
-            fd, self.path = tempfile.mkstemp(suffix=".csv")
-            self.proc = subprocess.Popen(
-                ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
-                 "-lms", "100", "-i", str(self.device)], stdout=fd, stderr=subprocess.DEVNULL)
+            fd, self.path = tempfile.mkstemp(suffix=".clk")
             os.close(fd)
-        except OSError:
-            self.proc = None
+            self.proc = subprocess.Popen([sys.executable, "-c", _NVML_SAMPLER, str(self.device), self.path],
+                                         stdout=subprocess.DEVNULL, stderr=subprocess.DEVNULL)
+            t_wait = time.time() + 5.0
+            while time.time() < t_wait and self.proc.poll() is None:
+                with open(self.path) as f:
+                    if f.readline().startswith("ready"):
+                        self.nvml = True
+                        break
+                time.sleep(0.02)
+            if not self.nvml:
+                if self.proc.poll() is None:
+                    self.proc.kill()
+                raise OSError("NVML sampler did not start")
+        except Exception:
+            try:
+                fd = os.open(self.path, os.O_WRONLY | os.O_TRUNC)
+                self.proc = subprocess.Popen(
+                    ["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits",
+                     "-lms", "100", "-i", str(self.device)], stdout=fd, stderr=subprocess.DEVNULL)
+                os.close(fd)
+            except (OSError, TypeError):
+                self.proc = None
+
+    def begin(self):
+        self.t_begin = time.time()
+
+    def end(self):
+        self.t_end = time.time()
 
     def stop(self) -> dict:
         out = {"sm_mhz": None, "sm_max_mhz": None, "reasons": []}
+        if self.t_end is None:
+            self.end()
         if self.proc:
             self.proc.terminate()
             try:
@@ -111,9 +133,26 @@ class ClockSampler:
                 self.proc.kill()
         sm, reasons, mx, pw = [], set(), None, []
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        bits = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap"}
         try:
             with open(self.path) as f:
                 for line in f:
+                    if self.nvml:
+                        p = line.split()
+                        if p and p[0] == "ready":
+                            mx = float(p[1])
+                            continue
+                        if len(p) < 4:
+                            continue
+                        t = float(p[0])
+                        if self.t_begin is not None and not (self.t_begin <= t <= self.t_end):
+                            continue
+                        sm.append(float(p[1]))
+                        pw.append(float(p[2]))
+                        for b, n in bits.items():
+                            if int(p[3]) & b:
+                                reasons.add(n)
+                        continue
                     p = [t.strip() for t in line.split(",")]
                     if len(p) < 7:
                         continue
@@ -127,25 +166,12 @@ class ClockSampler:
                         if v.lower().startswith("active"):
                             reasons.add(n)
             os.unlink(self.path)
-        except (OSError, TypeError):
+        except (OSError, TypeError, ValueError):
             pass
         if sm:
             out = {"sm_mhz": float(np.median(sm)), "sm_max_mhz": mx, "reasons": sorted(reasons),
-                   "samples": len(sm), "power_w_max": max(pw) if pw else None, "source": "nvidia-smi -lms 100"}
-        if self.thread is not None:
-            self._stop = True
-            self.thread.join(timeout=2)
-            if len(self.rows) > len(sm):
-                bits = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown",
-                        0x4: "sw_power_cap"}
-                rs = set(reasons)
-                for _, _, m in self.rows:
-                    for b, n in bits.items():
-                        if m & b:
-                            rs.add(n)
-                out = {"sm_mhz": float(np.median([r[0] for r in self.rows])), "sm_max_mhz": self.nvml_max or mx,
-                       "reasons": sorted(rs), "samples": len(self.rows),
-                       "power_w_max": max(r[1] for r in self.rows), "source": "NVML, 2 ms period"}
+                   "samples": len(sm), "power_w_max": max(pw) if pw else None,
+                   "source": "NVML polled every 2 ms by a child process" if self.nvml else "nvidia-smi -lms 100"}
         return out
 
 
@@ -390,18 +416,22 @@ def run_b200_arm(args):
         else:
             eng.set_reflections(refl_K)
     reset_codebook()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()                                    # child process; ready before the warm-up ends
     for _ in range(args.warmup):
         eng.kmeans_pass(want_cells=False)
-    sampler = ClockSampler(local_rank)
     barrier()
     if rank == 0:
-        sampler.start()
+        sampler.begin()
     eng.counters_reset()
     t0 = time.perf_counter()
     for _ in range(args.steps):
         eng.kmeans_pass(want_cells=False)     # synchronises its own stream before returning
     barrier()
     wall = time.perf_counter() - t0
+    if rank == 0:
+        sampler.end()
     clocks = sampler.stop() if rank == 0 else None
     wall = max_over_ranks(wall)
     ctr = eng.counters()
