@@ -455,13 +455,10 @@ bool launch_autocorr_fast(AcParams p, cudaStream_t s, bool *taken) {
     // frame t0 = blockIdx * G starts at an even sample (G is even), so alignment of the bases decides
     p.bulk = ((reinterpret_cast<uintptr_t>(p.signal) | reinterpret_cast<uintptr_t>(p.hamming)) & 15) == 0 &&
              !std::getenv("ECOZ2_LPC_NO_BULK");
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (!cuda_ok(cudaFuncSetAttribute(lpc_autocorr_fast<LAGS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          110 * 1024), "cudaFuncSetAttribute(lpc_autocorr_fast)"))
-            return false;
-        attr_set = true;
-    }
+    // per device (function attributes belong to the context): set on every launch, ~1 us
+    if (!cuda_ok(cudaFuncSetAttribute(lpc_autocorr_fast<LAGS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      110 * 1024), "cudaFuncSetAttribute(lpc_autocorr_fast)"))
+        return false;
     const long grid = (p.T + G - 1) / G;
     lpc_autocorr_fast<LAGS><<<(unsigned) grid, G * kLanesPerFrame, smem, s>>>(p);
     *taken = true;
@@ -489,13 +486,10 @@ bool launch_autocorr(AcParams p, cudaStream_t s) {
         smem = 0;
     }
     p.frames_per_cta = G;
-    static bool attr_set = false;
-    if (!attr_set) {
-        if (!cuda_ok(cudaFuncSetAttribute(lpc_autocorr<LAGS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                          200 * 1024), "cudaFuncSetAttribute(lpc_autocorr)"))
-            return false;
-        attr_set = true;
-    }
+    // per device (function attributes belong to the context): set on every launch, ~1 us
+    if (!cuda_ok(cudaFuncSetAttribute(lpc_autocorr<LAGS>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                      200 * 1024), "cudaFuncSetAttribute(lpc_autocorr)"))
+        return false;
     const long grid = (p.T + G - 1) / G;
     lpc_autocorr<LAGS><<<(unsigned) grid, G * kLanesPerFrame, smem, s>>>(p);
     return cuda_ok(cudaGetLastError(), "lpc_autocorr launch");

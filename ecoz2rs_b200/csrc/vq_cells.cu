@@ -369,12 +369,9 @@ void launch_cell_sums(const double *x64, const int32_t *idx, long n, int D, cons
         (double) per_cta * D * D < 4.0e9) {
         int R = (int) ((kStreamSmemMax - sizeof(int32_t) * (size_t) K) / (sizeof(double) * (size_t) K * D));
         if (R > 32) R = 32;
-        static bool attr_set = false;
-        if (!attr_set) {
-            cudaFuncSetAttribute(vq_cell_sums_stream, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                 (int) kStreamSmemMax);
-            attr_set = true;
-        }
+        // per device (function attributes belong to the context): set on every launch, ~1 us
+        cudaFuncSetAttribute(vq_cell_sums_stream, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                             (int) kStreamSmemMax);
         const long grid = stream_grid;
         vq_cell_sums_stream<<<(unsigned) grid, 1024, stream_smem_bytes(K, D, R), s>>>(
             x64, idx, n, K, D, R, L, packed, cs.hist, seq);

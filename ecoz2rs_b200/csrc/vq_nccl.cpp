@@ -3,6 +3,8 @@
 
 #include <dlfcn.h>
 
+#include <cstdlib>
+
 #include <mutex>
 #include <string>
 
@@ -18,8 +20,15 @@ const NcclApi *nccl_api() {
     std::lock_guard<std::mutex> lock(g_mu);
     if (g_loaded) return &g_api;
     if (g_failed) return nullptr;
-    // RTLD_NOLOAD first: reuse the NCCL torch already loaded in this process
+    // RTLD_NOLOAD first: reuse the NCCL torch already loaded in this process.  The loader keeps ONE
+    // library per soname: if a process imports torch AFTER this point, torch gets the NCCL loaded
+    // here, so ECOZ2_VQ_NCCL_LIB can name the one to load (the ctypes mirror pre-loads torch's
+    // bundled copy, ecoz2rs_b200/vq.py).
     void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+    if (!h) {
+        const char *path = std::getenv("ECOZ2_VQ_NCCL_LIB");
+        if (path && *path) h = dlopen(path, RTLD_NOW | RTLD_GLOBAL);
+    }
     if (!h) h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
     if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
     if (!h) {

@@ -1452,12 +1452,9 @@ static int tc2_raw_bufs(int D, int BN) { return tc2_smem_bytes(D, BN, 2) <= 227 
 
 template <int KS, bool FILTER, bool DBG, bool H16>
 static void launch_tc2_inst2(const TcParams &p, long grid, cudaStream_t s) {
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(vq_assign_tc2<KS, FILTER, DBG, H16>,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-        attr_set = true;
-    }
+    // per device (function attributes belong to the context): set on every launch, ~1 us
+    cudaFuncSetAttribute(vq_assign_tc2<KS, FILTER, DBG, H16>,
+                         cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
     vq_assign_tc2<KS, FILTER, DBG, H16><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN, p.raw_bufs), s>>>(p);
 }
 template <int KS, bool H16>
@@ -1543,11 +1540,8 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
         return;
     }
     const size_t smem = tc_smem_bytes(D, p.BN);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(vq_assign_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
-        attr_set = true;
-    }
+    // per device (function attributes belong to the context): set on every launch, ~1 us
+    cudaFuncSetAttribute(vq_assign_tc, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
     long tiles = (n + kBM - 1) / kBM;
     long grid = tiles < num_sms ? tiles : num_sms;
     if (grid < 1) grid = 1;

@@ -164,11 +164,37 @@ def _check(rc: int, what: str):
         raise VqError(f"{what} failed (code {rc}): {lib().ecoz2b200_last_error().decode()}")
 
 
+_nccl_preloaded = False
+
+
+def _preload_bundled_nccl():
+    """The library binds NCCL with dlopen("libnccl.so.2") and the dynamic loader keeps one library
+    per soname: if that were the system copy and torch is imported later in the same process, torch
+    would be handed an NCCL older than the one it was built against.  Load the copy bundled with
+    torch's wheels first (when there is one), so both use the same."""
+    global _nccl_preloaded
+    if _nccl_preloaded:
+        return
+    _nccl_preloaded = True
+    try:
+        import glob
+        import importlib.util
+        spec = importlib.util.find_spec("nvidia.nccl")
+        for d in (spec.submodule_search_locations if spec else ()):
+            for f in sorted(glob.glob(os.path.join(d, "lib", "libnccl.so*"))):
+                C.CDLL(f, mode=C.RTLD_GLOBAL)
+                return
+    except Exception:
+        pass
+
+
 class VqEngine:
     """Frames of this process on one or more local B200s + the replicated codebook."""
 
     def __init__(self, P: int, max_M: int = 4096, devices: Sequence[int] = (0,), mode: Optional[int] = None):
         L = lib()
+        if len(devices) > 1:
+            _preload_bundled_nccl()
         devs = (C.c_int32 * len(devices))(*devices)
         self._h = L.ecoz2b200_create(devs, len(devices), P, max_M)
         if not self._h:
@@ -210,6 +236,7 @@ class VqEngine:
 
     def comm_init(self, unique_id: bytes, rank: int, world_size: int):
         assert len(unique_id) == 128
+        _preload_bundled_nccl()
         _check(lib().ecoz2b200_comm_init(self._h, unique_id, rank, world_size), "comm_init")
 
     # -- frames
@@ -456,6 +483,7 @@ def write_min_dists_csv(path: str, codeword: np.ndarray, min_dist: np.ndarray) -
 
 
 def nccl_unique_id() -> bytes:
+    _preload_bundled_nccl()
     buf = C.create_string_buffer(128)
     _check(lib().ecoz2b200_nccl_unique_id(buf), "nccl_unique_id")
     return buf.raw
