@@ -1,0 +1,38 @@
+"""One process driving several GPUs (ECOZ2_VQ_GPUS=all / devices=(0, 1)) and work on a non-zero device:
+the LBG run, the symbols and the LPC vectors do not depend on where they were computed.  Needs two
+GPUs (skipped on a single-GPU box; run with `gpurun --gpus 2`).  torch is imported AFTER the first
+multi-GPU call on purpose: the NCCL bound by the library must be one torch can live with."""
+import numpy as np
+import pytest
+
+pytestmark = pytest.mark.gpu
+
+
+def test_engines_on_several_devices_agree(built_lib):
+    from ecoz2rs_b200 import vq
+    from ecoz2rs_b200.synth import ar_mix
+    if vq.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    x = ar_mix(300_001, 36, seed=3)
+    res = []
+    for devs in ((0,), (0, 1), (1,)):
+        with vq.VqEngine(36, max_M=512, devices=devs) as eng:
+            eng.set_frames(x)
+            eng.codebook_initial()
+            st, _ = eng.learn(eps=0.05, stop_M=512)
+            seq, avg = eng.quantize(x[:50_001])
+            res.append(([(s["M"], s["passes"]) for s in st], st[-1]["avg_distortion"], st[-1]["refl"], seq, avg))
+    for r in res[1:]:
+        assert r[0] == res[0][0] and abs(r[1] - res[0][1]) <= 1e-9 * res[0][1]
+        assert np.allclose(r[2], res[0][2], rtol=1e-7, atol=1e-10) and (r[3] != res[0][3]).mean() < 1e-4
+    # LPC front end on device 1
+    import torch
+    from ecoz2rs_b200 import lpc
+    sig = np.random.default_rng(0).standard_normal(32000 * 30) * 0.1
+    want = lpc.lpa_on_signal(sig, 32000., 36, 45, 15)
+    with torch.cuda.device(1):
+        d = torch.from_numpy(sig).cuda()
+        T = lpc.num_frames(len(sig), 32000., 45, 15)
+        v = torch.empty((T, 37), dtype=torch.float64, device="cuda")
+        assert lpc.lpa_on_signal_device(d.data_ptr(), len(sig), 32000., 36, 45, 15, v.data_ptr(), T) == T
+        assert np.array_equal(v.cpu().numpy(), want)
