@@ -37,7 +37,7 @@ static void apply_mode_env(vqb200::Engine &eng) {
     if (!m) return;
     if (strcmp(m, "fp64") == 0) eng.set_mode(ECOZ2B200_MODE_FP64);
     else if (strcmp(m, "fp32") == 0) eng.set_mode(ECOZ2B200_MODE_FP32);
-    else if (strcmp(m, "tf32x3") == 0) eng.set_mode(ECOZ2B200_MODE_TF32X3);
+    else if (strcmp(m, "tf32x3") == 0) eng.set_mode(ECOZ2B200_MODE_TENSOR);
 }
 
 // ECOZ2_VQ_GPUS: unset/"" -> device 0; "all" -> every visible device; else "0,2,3"
@@ -381,6 +381,19 @@ int ecoz2b200_tc_issued_flops_per_eval(int P, int *is_f16) {
     return vqb200::tc_issued_flops_per_eval(P + 1, is_f16);
 }
 
+int ecoz2b200_shard_range(long total, int rank, int world_size, long *lo, long *hi) {
+    if (total < 0 || world_size < 1 || rank < 0 || rank >= world_size || !lo || !hi) return ECOZ2B200_ERR_ARG;
+    vqb200::shard_range(total, rank, world_size, lo, hi);
+    return ECOZ2B200_OK;
+}
+int ecoz2b200_packed_layout(int K, int P, long offsets[6]) {
+    if (K < 1 || P < 1 || !offsets) return ECOZ2B200_ERR_ARG;
+    const vqb200::PackedLayout L{K, P + 1};
+    offsets[0] = L.cells(); offsets[1] = L.counts(); offsets[2] = L.discel();
+    offsets[3] = L.dd(); offsets[4] = L.inertia(); offsets[5] = L.size();
+    return ECOZ2B200_OK;
+}
+
 int ecoz2b200_nccl_unique_id(unsigned char id_out[128]) {
     const vqb200::NcclApi *api = vqb200::nccl_api();
     if (!api) return ECOZ2B200_ERR_NCCL;
@@ -476,6 +489,9 @@ int ecoz2b200_counters_get(ecoz2b200_engine *e, ecoz2b200_counters *out) {
     out->rechecked = c.rechecked;
     out->search_main_ms = c.search_main_ms;
     out->search_main_launches = c.search_main_launches;
+    out->audited = c.audited;
+    out->audit_idx_diff = c.audit_idx_diff;
+    out->audit_mismatches = c.audit_mismatches;
     return ECOZ2B200_OK;
 }
 

@@ -99,6 +99,8 @@ Engine::Engine(const int *devices, int num_devices, int P, int max_M)
         if (!chk(cudaMalloc(&s.packed_scratch, sizeof(double) * L.size()), "cudaMalloc packed_scratch")) return;
         if (!chk(cudaMalloc(&s.raas_prev, cb), "cudaMalloc raas_prev")) return;
         if (!chk(cudaMalloc(&s.scalars, sizeof(double) * 8), "cudaMalloc scalars")) return;
+        if (!chk(cudaMalloc(&s.dstat, sizeof(unsigned long long) * 8), "cudaMalloc dstat")) return;
+        cudaMemset(s.dstat, 0, sizeof(unsigned long long) * 8);
         cudaMemset(s.refl, 0, cb);
         cudaMemset(s.raas, 0, cb);
     }
@@ -106,6 +108,8 @@ Engine::Engine(const int *devices, int num_devices, int P, int max_M)
     if (fs && fs[0] == '0') use_small_ = false;
     const char *csort = getenv("ECOZ2_VQ_CELL_SORT");
     if (csort && csort[0] == '0') use_cell_sort_ = false;
+    const char *au = getenv("ECOZ2_VQ_AUDIT");
+    if (au && atoi(au) > 0) audit_every_ = atoi(au);
     ok_ = true;
 }
 
@@ -120,7 +124,7 @@ Engine::~Engine() {
         cudaFree(s.mindist); cudaFree(s.sc_mem);
         cudaFree(s.refl); cudaFree(s.raas); cudaFree(s.w32); cudaFree(s.w64); cudaFree(s.w1max); cudaFree(s.w1);
         cudaFree(s.wtc); cudaFree(s.cs_mem); cudaFree(s.packed_scratch); cudaFree(s.raas_prev);
-        cudaFree(s.packed); cudaFree(s.scalars);
+        cudaFree(s.packed); cudaFree(s.scalars); cudaFree(s.dstat);
         for (int b = 0; b < 2; b++) {
             QBuf &q = qbuf_[2 * i + b];
             cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
@@ -137,7 +141,7 @@ Engine::~Engine() {
 }
 
 int Engine::set_mode(int mode) {
-    if (mode != ECOZ2B200_MODE_FP32 && mode != ECOZ2B200_MODE_FP64 && mode != ECOZ2B200_MODE_TF32X3) {
+    if (mode != ECOZ2B200_MODE_FP32 && mode != ECOZ2B200_MODE_FP64 && mode != ECOZ2B200_MODE_TENSOR) {
         set_last_error("set_mode: mode not available in this build");
         return ECOZ2B200_ERR_ARG;
     }
@@ -270,7 +274,7 @@ int Engine::frames_reserve(long total) {
     }
     const long S = (long) shards_.size();
     reserved_ = total;
-    per_shard_ = (total + S - 1) / S;
+    per_shard_ = shard_block(total, (int) S);
     for (long i = 0; i < S; i++) {
         shards_[i].frame_offset = i * per_shard_;
         int rc = ensure_capacity(shards_[i], per_shard_ > 0 ? per_shard_ : 1);
@@ -463,6 +467,35 @@ static void debug_poison(const Shard &s) {
     vq_debug_poison_smem<<<s.num_sms, 256, 200 * 1024, s.stream>>>();
 }
 
+// dstat[3] += *flag_count (frames the search handed to the FP64 re-evaluation)
+__global__ void vq_stat_add(const int32_t *__restrict__ counter, unsigned long long *__restrict__ stat) {
+    if (threadIdx.x == 0 && blockIdx.x == 0) *stat += (unsigned long long) *counter;
+}
+
+void Engine::counters_reset() {
+    ctr_ = Counters();
+    for (Shard &s : shards_) {
+        cudaSetDevice(s.device);
+        cudaMemsetAsync(s.dstat, 0, sizeof(unsigned long long) * 8, s.stream);
+    }
+}
+
+const Counters &Engine::counters() {
+    long st[4] = {0, 0, 0, 0};
+    for (Shard &s : shards_) {
+        unsigned long long h[4] = {0, 0, 0, 0};
+        cudaSetDevice(s.device);
+        cudaMemcpyAsync(h, s.dstat, sizeof h, cudaMemcpyDeviceToHost, s.stream);
+        cudaStreamSynchronize(s.stream);
+        for (int i = 0; i < 4; i++) st[i] += (long) h[i];
+    }
+    ctr_.audited = st[0];
+    ctr_.audit_idx_diff = st[1];
+    ctr_.audit_mismatches = st[2];
+    ctr_.rechecked = st[3];
+    return ctr_;
+}
+
 // ---------------------------------------------------------------------------------
 // (a) the search on one shard: FP32 main pass + FP64 re-evaluation of the frames
 // inside the FP32 ambiguity bound, or the all-FP64 verification mode.
@@ -485,7 +518,8 @@ void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32
         cudaEventRecord(s.ev[7], s.stream);
         launch_recheck(x32, x64, n, D_, s.w32, s.w64, s.w1, s.w1max, s.raas, K_, 2.f * err_scale, sc,
                        idx, s.num_sms, s.stream, s.wtc, err_tc);
-        ctr_.kernel_launches += 5;
+        vq_stat_add<<<1, 32, 0, s.stream>>>(sc.counters, s.dstat + 3);
+        ctr_.kernel_launches += 6;
     } else {
         // |error| of one FP32 distortion <= kappa * 2^-24 * |rx[0]| * sum_n |w[n]|.
         // Main pass: flag when the best-two gap is below twice that bound taken with the
@@ -497,7 +531,12 @@ void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32
         cudaEventRecord(s.ev[7], s.stream);
         launch_recheck(x32, x64, n, D_, s.w32, s.w64, s.w1, s.w1max, s.raas, K_, 2.f * err_scale, sc,
                        idx, s.num_sms, s.stream);
-        ctr_.kernel_launches += 5;
+        vq_stat_add<<<1, 32, 0, s.stream>>>(sc.counters, s.dstat + 3);
+        ctr_.kernel_launches += 6;
+    }
+    if (audit_every_ > 0 && mode_ != ECOZ2B200_MODE_FP64) {
+        launch_audit(x64, n, D_, s.raas, K_, idx, audit_every_, s.dstat, s.num_sms, s.stream);
+        ctr_.kernel_launches++;
     }
     ctr_.evals += (double) n * K_;
 }
@@ -527,6 +566,16 @@ void Engine::pass_kernels(Shard &s, const double *x64, const float *x32, long n,
         K_prev_ = K_;
         mindist_valid_ = false;
         ctr_.kernel_launches += n > 0 ? 5 : 2;
+        return;
+    }
+    if (inertia_exact_ && !with_cells) {
+        // inertia.c:21-25 as written: frames whose minimum distortion is negative (impossible for
+        // gain-normalised input) are listed and scanned exactly for min_i dd_i^2
+        cudaMemsetAsync(sc.counters + 3, 0, sizeof(int32_t), s.stream);
+        launch_accumulate(x64, idx, n, D_, s.raas, K_, s.packed, mindist, seq, false, s.num_sms, s.stream,
+                          sc.exact_list, sc.counters + 3);
+        launch_inertia_neg(x64, D_, s.raas, K_, sc.exact_list, sc.counters + 3, s.packed, s.num_sms, s.stream);
+        ctr_.kernel_launches += 2 * (n > 0);
         return;
     }
     launch_accumulate(x64, idx, n, D_, s.raas, K_, s.packed, mindist, seq, with_cells, s.num_sms,
@@ -599,7 +648,6 @@ int Engine::assign(int32_t *idx_out, double *ddmin_out, long *num_rechecked, boo
     CUDA_TRY(cudaGetLastError());
     if (ddmin_out && raw)
         for (long v = 0; v < n_total_; v++) ddmin_out[v] += 1.0;  // raw distortion (before the -1)
-    ctr_.rechecked += rechecked;
     if (num_rechecked) *num_rechecked = rechecked;
     return ECOZ2B200_OK;
 }
@@ -654,10 +702,6 @@ int Engine::kmeans_pass_host(const double *x, long n, double *cells_out, int32_t
         set_last_error("kmeans_pass_host: no codebook or no frames");
         return ECOZ2B200_ERR_ARG;
     }
-    if (multi_process_) {
-        set_last_error("kmeans_pass_host: one process per engine only (use frames_* + kmeans_pass)");
-        return ECOZ2B200_ERR_ARG;
-    }
     const bool pipelined = !small_path() && use_cell_sort_ && cell_sort_supported(K_);
     if (!pipelined) {   // plain sequence: upload, commit, pass
         int rc = frames_clear();
@@ -671,7 +715,7 @@ int Engine::kmeans_pass_host(const double *x, long n, double *cells_out, int32_t
     const long S = (long) shards_.size();
     frames_clear();
     reserved_ = n;
-    per_shard_ = (n + S - 1) / S;
+    per_shard_ = shard_block(n, (int) S);
     const long chunk = 1L << 20;   // frames per upload chunk (310 MB of FP64 at P = 36)
     for (long i = 0; i < S; i++) {
         Shard &s = shards_[i];
@@ -718,6 +762,17 @@ int Engine::kmeans_pass_host(const double *x, long n, double *cells_out, int32_t
         int rc = ensure_local_comms();
         if (rc) return rc;
     }
+    h_count_ = (double) n;   // member: the asynchronous read-back must not outlive its target
+    if (multi_process_) {
+        // frames of all ranks (the divisor of the average distortion): a one-double allreduce queued
+        // behind the chunks, read back with the pass results
+        Shard &s = shards_[0];
+        const NcclApi *api = nccl_api();
+        if (!api) return ECOZ2B200_ERR_NCCL;
+        CUDA_TRY(cudaMemcpyAsync(s.scalars + 4, &h_count_, sizeof(double), cudaMemcpyHostToDevice, s.stream));
+        NCCL_TRY(api, api->AllReduce(s.scalars + 4, s.scalars + 4, 1, kNcclFloat64, kNcclSum, s.comm, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(&h_count_, s.scalars + 4, sizeof(double), cudaMemcpyDeviceToHost, s.stream));
+    }
     committed_ = true;
     for (Shard &s : shards_) {
         CUDA_TRY(cudaSetDevice(s.device));
@@ -732,7 +787,9 @@ int Engine::kmeans_pass_host(const double *x, long n, double *cells_out, int32_t
     }
     K_prev_ = K_;
     mindist_valid_ = false;
-    return pass_tail(cells_out, cardd_out, discel_out, DD_out);
+    const int rc = pass_tail(cells_out, cardd_out, discel_out, DD_out);   // synchronises the streams
+    n_global_ = (long) (h_count_ + 0.5);
+    return rc;
 }
 
 // allreduce of the packed sums, read-back, centroid update and re-staging of the codebook
@@ -770,14 +827,6 @@ int Engine::pass_tail(double *cells_out, int32_t *cardd_out, double *discel_out,
     if (rc) return rc;
     CUDA_TRY(cudaGetLastError());
     harvest_times(true);
-    if (mode_ != ECOZ2B200_MODE_FP64 && !small_path()) {
-        for (Shard &s : shards_) {
-            int32_t fc = 0;
-            cudaSetDevice(s.device);
-            cudaMemcpy(&fc, s.sc.counters, sizeof(int32_t), cudaMemcpyDeviceToHost);
-            ctr_.rechecked += fc;
-        }
-    }
     if (cardd_out)
         for (int i = 0; i < K_; i++) cardd_out[i] = (int32_t) (h_packed_[L.counts() + i] + 0.5);
     if (discel_out) memcpy(discel_out, h_packed_.data() + L.discel(), sizeof(double) * K_);
@@ -803,14 +852,17 @@ int Engine::sigma(double avgDistortion, double *sigma_out) {
 
 int Engine::inertia(double *inertia_out) {
     // inertia.c:10-31: sum_v min_i distortion^2 with the current (post-update) codebook.
-    // min of dd^2 == (min dd)^2 because dd >= 0 for gain-normalised frames.
+    // min_i dd_i^2 == (min_i dd_i)^2 whenever the minimum is >= 0 (every gain-normalised frame);
+    // the other frames take the exact scan (pass_kernels, vq_pass_small*).
     const PackedLayout L{K_, D_};
     const bool reduce = shards_.size() > 1 || multi_process_;
     for (Shard &s : shards_) {
         CUDA_TRY(cudaSetDevice(s.device));
         CUDA_TRY(cudaEventRecord(s.ev[0], s.stream));
         CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
+        inertia_exact_ = true;
         pass_kernels(s, s.x64, s.x32, s.n, s.idx_tmp, s.sc, nullptr, nullptr, false);
+        inertia_exact_ = false;
         CUDA_TRY(cudaEventRecord(s.ev[2], s.stream));
     }
     int rc = allreduce_range(shards_, L.dd(), 2, reduce);

@@ -17,6 +17,21 @@ const char *get_last_error();
 
 struct NcclApi;  // dlopen'ed libnccl (vq_nccl.cpp)
 
+// The sharding rule of the path: `total` frames in append order are split into
+// `parts` contiguous blocks of ceil(total / parts) frames; the last blocks may be shorter or empty.
+// Used for the devices of one engine (frames_reserve) and, by the callers, for the ranks of a
+// multi-process run (ecoz2b200_shard_range).
+inline long shard_block(long total, int parts) { return parts > 0 ? (total + parts - 1) / parts : total; }
+inline void shard_range(long total, int part, int parts, long *lo, long *hi) {
+    const long per = shard_block(total, parts);
+    long a = (long) part * per;
+    if (a > total) a = total;
+    long b = a + per;
+    if (b > total) b = total;
+    *lo = a;
+    *hi = b;
+}
+
 // One GPU's share of the frames + a replica of the codebook state.
 struct Shard {
     int device = 0;
@@ -54,6 +69,10 @@ struct Shard {
     double *packed_scratch = nullptr;  // same size: sink of the on-demand minDist pass
     double *raas_prev = nullptr;       // [max_M][D] codebook the last assignment was made against
     double *scalars = nullptr;  // [8] misc device scalars (sigma sum, ...)
+    // device-side statistics, read only when the counters are asked for (no per-pass host sync):
+    // [0] frames audited, [1] audit: index differs, [2] audit: real mis-assignment, [3] frames
+    // re-evaluated in FP64
+    unsigned long long *dstat = nullptr;
 };
 
 struct Counters {
@@ -63,6 +82,7 @@ struct Counters {
     long kernel_launches = 0;
     double evals = 0;
     long rechecked = 0;
+    long audited = 0, audit_idx_diff = 0, audit_mismatches = 0;
 };
 
 class Engine {
@@ -100,7 +120,6 @@ class Engine {
     // the same pass over n frames that are still in HOST memory (pinned for full speed): they
     // replace the resident frame set, uploaded in chunks on a copy stream while the search of
     // the previous chunk runs; cell sums, allreduce and update follow as in kmeans_pass.
-    // Single-process engines only (one or several local devices).
     int kmeans_pass_host(const double *x, long n, double *cells_out, int32_t *cardd_out,
                          double *discel_out, double *DD_out);
     int sigma(double avgDistortion, double *sigma_out);
@@ -111,8 +130,8 @@ class Engine {
     int quantize_host(const double *x, long T, uint16_t *seq_out, double *avg);
     int quantize_resident(uint16_t *seq_out, double *avg);
 
-    void counters_reset() { ctr_ = Counters(); }
-    const Counters &counters() const { return ctr_; }
+    void counters_reset();
+    const Counters &counters();   // fetches the device-side statistics (synchronises the streams)
 
     int P() const { return P_; }
     int D() const { return D_; }
@@ -137,16 +156,18 @@ class Engine {
     bool small_path() const {
         return use_small_ && pass_small_supported(K_, D_) && (!tc_path() || pass_small_fast(K_, D_));
     }
-    bool tc_path() const { return mode_ == ECOZ2B200_MODE_TF32X3 && assign_tc_supported(K_, D_); }
+    bool tc_path() const { return mode_ == ECOZ2B200_MODE_TENSOR && assign_tc_supported(K_, D_); }
     bool use_small_ = true;   // ECOZ2_VQ_FUSED_SMALL=0 forces the tiled path at every K
     bool use_cell_sort_ = true;  // ECOZ2_VQ_CELL_SORT=0: per-frame atomics (vq_accumulate) instead
     bool mindist_valid_ = true;  // s.mindist holds the last pass's values (else: compute on demand)
+    bool inertia_exact_ = false; // inside inertia(): frames with a negative minimum take the exact scan
+    int audit_every_ = 0;        // ECOZ2_VQ_AUDIT=n: all-FP64 search of every n-th frame after each search
     int K_prev_ = 0;             // rows of raas_prev
     int ensure_mindist();
     bool ok_ = false;
     int P_, D_, max_M_;
     int K_ = 0;
-    int mode_ = ECOZ2B200_MODE_TF32X3;   // falls back to the FFMA search where unsupported
+    int mode_ = ECOZ2B200_MODE_TENSOR;   // falls back to the FFMA search where unsupported
     double kappa_ = 8.0;
     double kappa_tc_ = 40.0;
     std::vector<Shard> shards_;
@@ -166,6 +187,7 @@ class Engine {
     bool local_comms_ready_ = false;
     Counters ctr_;
     std::vector<double> h_packed_;  // host mirror of the packed buffer tail / cells
+    double h_count_ = 0;            // kmeans_pass_host: frames of all ranks (read back with the pass)
 };
 
 }  // namespace vqb200

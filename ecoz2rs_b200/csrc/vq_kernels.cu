@@ -165,8 +165,10 @@ vq_assign_tiled(const AssignParams<T> p) {
     T *Ws0 = reinterpret_cast<T *>(smem_raw + 128);
     T *Ws1 = Ws0 + (size_t) D * BN;
     T *Xs = Ws1 + (size_t) D * BN;
+    // row D of Xs: the frame's norm max_k |x[k]| the error bound scales with (for an autocorrelation
+    // that is |rx[0]|, but frames_append accepts arbitrary rows)
     // kModeFilter only: [Xs][int2 cbuf[kCandBuf]][int s_count, s_base]
-    int2 *cbuf = reinterpret_cast<int2 *>(Xs + (size_t) D * XS);
+    int2 *cbuf = reinterpret_cast<int2 *>(Xs + (size_t) (D + 1) * XS);
     int *s_ctl = reinterpret_cast<int *>(cbuf + kCandBuf);
 
     const int tid = threadIdx.x;
@@ -218,6 +220,14 @@ vq_assign_tiled(const AssignParams<T> p) {
             }
         }
         __syncthreads();
+        if (TRACK2 || FILTER) {
+            for (int f = tid; f < BM; f += 256) {
+                T m = (T) 0;
+                for (int n = 0; n < D; n++) m = max(m, (T) fabs((double) Xs[n * XS + f]));
+                Xs[D * XS + f] = m;
+            }
+            __syncthreads();
+        }
 
         R best[TM];
         T second[TRACK2 ? TM : 1];
@@ -230,7 +240,7 @@ vq_assign_tiled(const AssignParams<T> p) {
             bidx[i] = 0;
             if (FILTER) {
                 const int f = (i >> 2) * (BM / RM) + ty * 4 + (i & 3);
-                const float c = p.err_scale * fabsf((float) Xs[f]);
+                const float c = p.err_scale * (float) Xs[D * XS + f];
                 cand_c[i] = c;
                 // frames beyond the list never produce a candidate
                 cand_b[i] = f < nvalid ? p.flag_ub[base + f] : -INFINITY;
@@ -360,7 +370,7 @@ vq_assign_tiled(const AssignParams<T> p) {
                     const long row = list ? (long) list[base + f] : base + f;
                     p.idx_out[row] = bidx[i];
                     if (TRACK2) {
-                        const float x0 = fabsf((float) Xs[f]);
+                        const float x0 = (float) Xs[D * XS + f];
                         // NaN-safe: "not clearly separated" => re-evaluate
                         if (!((float) (second[i] - (T) best[i]) >= bound * x0)) {
                             const int pos = atomicAdd(p.flag_count, 1);
@@ -379,7 +389,7 @@ vq_assign_tiled(const AssignParams<T> p) {
 template <typename T, int RM, int RN>
 static size_t assign_smem_bytes(int D, bool filter) {
     constexpr int BM = 64 * RM, BN = 64 * RN;
-    return 128 + sizeof(T) * ((size_t) 2 * D * BN + (size_t) D * (BM + 4)) +
+    return 128 + sizeof(T) * ((size_t) 2 * D * BN + (size_t) (D + 1) * (BM + 4)) +
            (filter ? sizeof(int2) * kCandBuf + 16 : 0);
 }
 
@@ -608,7 +618,8 @@ template <int NR, bool CELLS>
 __global__ void __launch_bounds__(256)
 vq_accumulate(const double *__restrict__ x64, const int32_t *__restrict__ idx, long n, int D,
               const double *__restrict__ raas, PackedLayout L, double *__restrict__ packed,
-              double *__restrict__ mindist, uint16_t *__restrict__ seq) {
+              double *__restrict__ mindist, uint16_t *__restrict__ seq, int32_t *__restrict__ neg_list,
+              int32_t *__restrict__ neg_count) {
     const int lane = threadIdx.x & 31;
     const long warp = ((long) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const long n_warps = ((long) gridDim.x * blockDim.x) >> 5;
@@ -667,7 +678,14 @@ vq_accumulate(const double *__restrict__ x64, const int32_t *__restrict__ idx, l
             const double dd = warp_sum(part);
             const double md = dd - 1.0;
             dd_sum += md;
-            in_sum += dd * dd;
+            // inertia.c:21-25 takes min_i (dd_i^2): equal to (min_i dd_i)^2 only when the minimum is
+            // >= 0 (every gain-normalised frame).  A frame whose minimum is negative is listed for
+            // the exact scan (vq_inertia_neg) instead.
+            if (neg_list != nullptr && dd < 0.0) {
+                if (lane == 0) neg_list[atomicAdd(neg_count, 1)] = (int32_t) (v0 + u);
+            } else {
+                in_sum += dd * dd;
+            }
             if (lane == 0) {
                 if (mindist) mindist[v0 + u] = md;
                 if (seq) seq[v0 + u] = (uint16_t) ci[u];
@@ -705,7 +723,8 @@ vq_accumulate(const double *__restrict__ x64, const int32_t *__restrict__ idx, l
 template <int NR>
 static void launch_accumulate_nr(const double *x64, const int32_t *idx, long n, int D,
                                  const double *raas, int K, double *packed, double *mindist,
-                                 uint16_t *seq, bool with_cells, int num_sms, cudaStream_t s) {
+                                 uint16_t *seq, bool with_cells, int num_sms, cudaStream_t s,
+                                 int32_t *neg_list, int32_t *neg_count) {
     PackedLayout L{K, D};
     long warps_wanted = (n + 31) / 32;  // >= 32 frames per warp
     long blocks = (warps_wanted + 7) / 8;
@@ -713,22 +732,114 @@ static void launch_accumulate_nr(const double *x64, const int32_t *idx, long n, 
     if (blocks > cap) blocks = cap;
     if (blocks < 1) blocks = 1;
     if (with_cells)
-        vq_accumulate<NR, true><<<(unsigned) blocks, 256, 0, s>>>(x64, idx, n, D, raas, L, packed, mindist, seq);
+        vq_accumulate<NR, true><<<(unsigned) blocks, 256, 0, s>>>(x64, idx, n, D, raas, L, packed, mindist, seq,
+                                                                  neg_list, neg_count);
     else
-        vq_accumulate<NR, false><<<(unsigned) blocks, 256, 0, s>>>(x64, idx, n, D, raas, L, packed, mindist, seq);
+        vq_accumulate<NR, false><<<(unsigned) blocks, 256, 0, s>>>(x64, idx, n, D, raas, L, packed, mindist, seq,
+                                                                   neg_list, neg_count);
+}
+
+// inertia.c:15-28 for the frames whose minimum distortion is negative (never for gain-normalised
+// input): min_i (dd_i^2) by an exact scan of all K codewords; one warp per listed frame, lanes over
+// codewords.
+__global__ void __launch_bounds__(256)
+vq_inertia_neg(const double *__restrict__ x64, int D, const double *__restrict__ raas, PackedLayout L,
+               const int32_t *__restrict__ neg_list, const int32_t *__restrict__ neg_count,
+               double *__restrict__ packed) {
+    const int lane = threadIdx.x & 31;
+    const long warp = ((long) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long n_warps = ((long) gridDim.x * blockDim.x) >> 5;
+    const long total = *neg_count;
+    double acc = 0.0;
+    for (long k = warp; k < total; k += n_warps) {
+        const double *xr = x64 + (long) neg_list[k] * D;
+        double best = (double) INFINITY;
+        for (int c = lane; c < L.K; c += 32) {
+            const double *rr = raas + (long) c * D;
+            double dd = xr[0] * rr[0];
+            for (int m = 1; m < D; m++) dd = fma(xr[m], 2.0 * rr[m], dd);
+            best = fmin(best, dd * dd);
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, off));
+        acc += best;
+    }
+    if (lane == 0 && acc != 0.0) atomicAdd(packed + L.inertia(), acc);
+}
+void launch_inertia_neg(const double *x64, int D, const double *raas, int K, const int32_t *neg_list,
+                        const int32_t *neg_count, double *packed, int num_sms, cudaStream_t s) {
+    PackedLayout L{K, D};
+    vq_inertia_neg<<<num_sms * 2, 256, 0, s>>>(x64, D, raas, L, neg_list, neg_count, packed);
+}
+
+// ECOZ2_VQ_AUDIT=n: every n-th frame is searched again over ALL codewords in FP64 (one warp per
+// audited frame, lanes over codewords, strict '<' in index order like quantize.c:19-26) and compared
+// with the index the search + re-evaluation produced.
+//   out[0] += frames audited
+//   out[1] += frames whose index differs from the FP64 scan's
+//   out[2] += of those, frames whose chosen codeword is worse than the FP64 minimum by more than
+//             1e-6 relative (north_star's exemption does not cover them: a real mis-assignment)
+__global__ void __launch_bounds__(256)
+vq_audit(const double *__restrict__ x64, long n, int D, const double *__restrict__ raas, int K,
+         const int32_t *__restrict__ idx, int every, unsigned long long *__restrict__ out) {
+    const int lane = threadIdx.x & 31;
+    const long warp = ((long) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long n_warps = ((long) gridDim.x * blockDim.x) >> 5;
+    const long n_audit = (n + every - 1) / every;
+    unsigned long long audited = 0, differ = 0, wrong = 0;
+    for (long a = warp; a < n_audit; a += n_warps) {
+        const long v = a * every;
+        const double *xr = x64 + v * D;
+        double best = (double) INFINITY;
+        int bi = 0x7fffffff;
+        const int chosen = idx[v];
+        double d_chosen = 0.0;
+        for (int c = lane; c < K; c += 32) {
+            const double *rr = raas + (long) c * D;
+            double dd = xr[0] * rr[0];
+            for (int m = 1; m < D; m++) dd = fma(xr[m], 2.0 * rr[m], dd);
+            if (dd < best) { best = dd; bi = c; }
+        }
+        {   // the chosen codeword by the same summation order (all lanes: no divergence in the shuffles)
+            const double *rr = raas + (long) (chosen >= 0 && chosen < K ? chosen : 0) * D;
+            d_chosen = xr[0] * rr[0];
+            for (int m = 1; m < D; m++) d_chosen = fma(xr[m], 2.0 * rr[m], d_chosen);
+        }
+#pragma unroll
+        for (int off = 16; off >= 1; off >>= 1) {
+            const double ob = __shfl_xor_sync(0xffffffffu, best, off);
+            const int oi = __shfl_xor_sync(0xffffffffu, bi, off);
+            if (ob < best || (ob == best && oi < bi)) { best = ob; bi = oi; }
+        }
+        audited++;
+        if (bi != chosen && bi != 0x7fffffff) {     // (a NaN frame keeps index 0 everywhere)
+            differ++;
+            if (!(d_chosen - best <= 1e-6 * fabs(best))) wrong++;
+        }
+    }
+    if (lane == 0 && audited) {
+        atomicAdd(out + 0, audited);
+        if (differ) atomicAdd(out + 1, differ);
+        if (wrong) atomicAdd(out + 2, wrong);
+    }
+}
+void launch_audit(const double *x64, long n, int D, const double *raas, int K, const int32_t *idx,
+                  int every, unsigned long long *out, int num_sms, cudaStream_t s) {
+    if (n <= 0 || every < 1) return;
+    vq_audit<<<num_sms * 4, 256, 0, s>>>(x64, n, D, raas, K, idx, every, out);
 }
 
 void launch_accumulate(const double *x64, const int32_t *idx, long n, int D, const double *raas,
                        int K, double *packed, double *mindist, uint16_t *seq, bool with_cells,
-                       int num_sms, cudaStream_t s) {
+                       int num_sms, cudaStream_t s, int32_t *neg_list, int32_t *neg_count) {
     if (n <= 0) return;
     const int nr = (D + 31) / 32;
     switch (nr) {
-        case 1: launch_accumulate_nr<1>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s); break;
-        case 2: launch_accumulate_nr<2>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s); break;
-        case 3: launch_accumulate_nr<3>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s); break;
-        case 4: launch_accumulate_nr<4>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s); break;
-        default: launch_accumulate_nr<7>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s); break;
+        case 1: launch_accumulate_nr<1>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s, neg_list, neg_count); break;
+        case 2: launch_accumulate_nr<2>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s, neg_list, neg_count); break;
+        case 3: launch_accumulate_nr<3>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s, neg_list, neg_count); break;
+        case 4: launch_accumulate_nr<4>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s, neg_list, neg_count); break;
+        default: launch_accumulate_nr<7>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s, neg_list, neg_count); break;
     }
 }
 
@@ -844,7 +955,13 @@ vq_pass_small(const double *__restrict__ x64, long n, const double *__restrict__
             const int ci = hit ? __ffs(hit) - 1 : 0;    // NaN frame: reference quantize keeps 0
             const double md = mn - 1.0;
             dd_sum += md;
-            in_sum += mn * mn;
+            double m2 = mn * mn;
+            if (mn < 0.0) {   // inertia.c:21-25 as written: min_i (dd_i^2), not (min_i dd_i)^2
+                m2 = owner ? mine * mine : (double) INFINITY;
+#pragma unroll
+                for (int off = 16; off >= 1; off >>= 1) m2 = fmin(m2, __shfl_xor_sync(0xffffffffu, m2, off));
+            }
+            in_sum += m2;
             if (lane == 0) {
                 idx_out[v0 + u] = ci;
                 if (mindist) mindist[v0 + u] = md;
@@ -1030,7 +1147,13 @@ vq_pass_small2(const double *__restrict__ x64, long n, const double *__restrict_
                 if (r < rows) {
                     const double md = bv - 1.0;
                     dd_sum += md;
-                    in_sum += bv * bv;
+                    double m2 = bv * bv;
+                    if (bv < 0.0) {   // inertia.c:21-25 as written: min_i (dd_i^2), not (min_i dd_i)^2
+#pragma unroll
+                        for (int c = 0; c < KT; c++)
+                            if (c < K) m2 = fmin(m2, acc[q][c] * acc[q][c]);
+                    }
+                    in_sum += m2;
                     idx_out[v0 + r] = best[q];
                     if (mindist) mindist[v0 + r] = md;
                     if (seq) seq[v0 + r] = (uint16_t) best[q];

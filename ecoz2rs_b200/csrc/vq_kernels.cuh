@@ -109,9 +109,19 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
 //   mindist[v] = dd - 1 (if mindist != nullptr); seq[v] = (u16) idx (if seq != nullptr)
 //   with_cells: packed.cells[idx] += rx, counts[idx] += 1, discel[idx] += dd - 1
 //   packed.dd += dd - 1 ; packed.inertia += dd * dd
+//   neg_list / neg_count (optional): frames whose winner distortion is NEGATIVE are appended there
+//   instead of adding dd * dd (inertia.c:21-25 wants min_i dd_i^2: launch_inertia_neg scans them)
 void launch_accumulate(const double *x64, const int32_t *idx, long n, int D,
                        const double *raas, int K, double *packed, double *mindist,
-                       uint16_t *seq, bool with_cells, int num_sms, cudaStream_t s);
+                       uint16_t *seq, bool with_cells, int num_sms, cudaStream_t s,
+                       int32_t *neg_list = nullptr, int32_t *neg_count = nullptr);
+// packed.inertia += min_i distortion(x_v, raas_i)^2 for the listed frames (exact FP64 scan)
+void launch_inertia_neg(const double *x64, int D, const double *raas, int K, const int32_t *neg_list,
+                        const int32_t *neg_count, double *packed, int num_sms, cudaStream_t s);
+// run-time audit of the search (ECOZ2_VQ_AUDIT=n): all-FP64 scan of every n-th frame against idx;
+// out[3] += {audited, index differs, chosen codeword worse than the minimum by > 1e-6 relative}
+void launch_audit(const double *x64, long n, int D, const double *raas, int K, const int32_t *idx,
+                  int every, unsigned long long *out, int num_sms, cudaStream_t s);
 
 // ---- (b') cell accumulation by counting sort + gather (vq_cells.cu) ---------------------
 // Same packed outputs as launch_accumulate(with_cells = true) -- cell sums, counts, cell

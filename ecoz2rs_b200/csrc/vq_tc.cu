@@ -686,7 +686,10 @@ __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
                     src = p.x + row * D;
                 }
                 const bool valid = f < nvalid;
-                const float x0 = valid ? fabsf(src[0]) : 0.f;
+                // norm of the error bound: max_k |x[k]| (= |rx[0]| for an autocorrelation row)
+                float x0 = 0.f;
+                if (valid)
+                    for (int k = 0; k < D; k++) x0 = fmaxf(x0, fabsf(src[k]));
                 for (int c = 0; c < KC; c++) {
                     float v[4];
 #pragma unroll
@@ -1046,15 +1049,15 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
 #pragma unroll
                     for (int k = 0; k < NE; k++) v[k] = (valid && k < D) ? __ldg(src + k) : 0.f;
                 }
-                // reference magnitude of the error bound: |rx[0]| (TF32 format, values unscaled),
-                // or max_k |x[k]| after the frame was scaled by a power of two into [2^14, 2^15)
+                // reference magnitude of the error bound: max_k |x[k]| (TF32 format, values unscaled),
+                // or the same after the frame was scaled by a power of two into [2^14, 2^15)
                 // (FP16 format: both split parts then stay inside the FP16 range, and the
                 // argmin of a frame does not depend on its own positive scale)
-                float x0 = fabsf(v[0]);
-                if (H16) {
-                    float xm = 0.f;
+                float xm = 0.f;
 #pragma unroll
-                    for (int k = 0; k < NE; k++) xm = fmaxf(xm, fabsf(v[k]));
+                for (int k = 0; k < NE; k++) xm = fmaxf(xm, fabsf(v[k]));
+                float x0 = xm;
+                if (H16) {
                     uint32_t ef = (__float_as_uint(xm) >> 23) & 0xffu;
                     ef = ef < 16u ? 16u : ef;
                     const float scale = __uint_as_float((268u - ef) << 23);   // 2^(14 - floor(log2 xm))

@@ -24,7 +24,8 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("ECOZ2_VQ_B200_LIB") or os.path.join(_HERE, "csrc", "libecoz2_vq_b200.so")
 
-MODE_FP32, MODE_FP64, MODE_TF32X3 = 0, 1, 2
+MODE_FP32, MODE_FP64, MODE_TENSOR = 0, 1, 2
+MODE_TF32X3 = MODE_TENSOR   # first name of the mode, kept as an alias
 
 _dp = C.POINTER(C.c_double)
 _ip = C.POINTER(C.c_int32)
@@ -44,7 +45,8 @@ class Counters(C.Structure):
     _fields_ = [("assign_ms", C.c_double), ("accumulate_ms", C.c_double),
                 ("update_ms", C.c_double), ("allreduce_ms", C.c_double),
                 ("kernel_launches", C.c_long), ("evals", C.c_double), ("rechecked", C.c_long),
-                ("search_main_ms", C.c_double), ("search_main_launches", C.c_long)]
+                ("search_main_ms", C.c_double), ("search_main_launches", C.c_long),
+                ("audited", C.c_long), ("audit_idx_diff", C.c_long), ("audit_mismatches", C.c_long)]
 
 
 _STAGE_CB = C.CFUNCTYPE(None, C.c_void_p, C.POINTER(StageInfo))
@@ -57,7 +59,7 @@ EXPORTED_SYMBOLS = (
     "ecoz2b200_create", "ecoz2b200_destroy", "ecoz2b200_set_mode", "ecoz2b200_set_recheck_kappa",
     "ecoz2b200_set_recheck_kappa_tc", "ecoz2b200_debug_tc_distortions",
     "ecoz2b200_tc_issued_flops_per_eval", "ecoz2b200_write_min_dists_csv",
-    "ecoz2b200_nccl_unique_id", "ecoz2b200_comm_init",
+    "ecoz2b200_nccl_unique_id", "ecoz2b200_comm_init", "ecoz2b200_shard_range", "ecoz2b200_packed_layout",
     "ecoz2b200_frames_clear", "ecoz2b200_frames_reserve", "ecoz2b200_frames_append_host",
     "ecoz2b200_frames_append_device", "ecoz2b200_frames_commit", "ecoz2b200_frames_count",
     "ecoz2b200_codebook_initial", "ecoz2b200_codebook_set_reflections",
@@ -104,6 +106,8 @@ def lib():
             "ecoz2b200_write_min_dists_csv": (i, [C.c_char_p, _ip, vp, l]),
             "ecoz2b200_nccl_unique_id": (i, [C.c_char_p]),
             "ecoz2b200_comm_init": (i, [vp, C.c_char_p, i, i]),
+            "ecoz2b200_shard_range": (i, [l, i, i, C.POINTER(l), C.POINTER(l)]),
+            "ecoz2b200_packed_layout": (i, [i, i, C.POINTER(l)]),
             "ecoz2b200_frames_clear": (i, [vp]),
             "ecoz2b200_frames_reserve": (i, [vp, l]),
             "ecoz2b200_frames_append_host": (i, [vp, vp, l]),

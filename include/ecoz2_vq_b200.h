@@ -81,7 +81,7 @@ int ecoz2_vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenam
 
 /* Arithmetic mode of the nearest-codeword search (reference
  * ecoz2/src/vq/vq_learn_par.c:62-81, quantize.c:14-30 are FP64).
- *   TF32X3: tcgen05 tensor-core search with two-way split operands (22-bit
+ *   TENSOR: tcgen05 tensor-core search with two-way split operands (22-bit
  *          products, FP32 accumulate in tensor memory) + FP64 re-evaluation of
  *          every frame whose best-two gap is inside the error bound (default;
  *          index-exact vs FP64).  The parts are FP16 values of power-of-two
@@ -91,7 +91,8 @@ int ecoz2_vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenam
  *   FP64:  the whole search in FP64 (verification mode).                      */
 #define ECOZ2B200_MODE_FP32 0
 #define ECOZ2B200_MODE_FP64 1
-#define ECOZ2B200_MODE_TF32X3 2
+#define ECOZ2B200_MODE_TENSOR 2
+#define ECOZ2B200_MODE_TF32X3 ECOZ2B200_MODE_TENSOR /* first name of the mode (round 1), kept as an alias */
 
 typedef struct ecoz2b200_engine ecoz2b200_engine;
 
@@ -136,6 +137,14 @@ int ecoz2b200_write_min_dists_csv(const char *path, const int32_t *codeword, con
  * K cell distortions | DD] buffer.  Engines with several local devices and no
  * comm_init use ncclCommInitAll internally.                                   */
 int ecoz2b200_nccl_unique_id(unsigned char id_out[128]);
+/* The sharding rule (host only, no device needed): rank `rank` of `world_size` owns the frames
+ * [*lo, *hi) of `total` in append order -- contiguous blocks of ceil(total / world_size), the
+ * reference's thread partition vq_learn_par.c:62 made contiguous.  The same function splits an
+ * engine's frames over its local devices.                                                  */
+int ecoz2b200_shard_range(long total, int rank, int world_size, long *lo, long *hi);
+/* Offsets (in doubles) of the packed per-pass buffer the allreduce sums:
+ * offsets = {cell sums [K][P+1], counts [K], cell distortions [K], DD, inertia, total size} */
+int ecoz2b200_packed_layout(int K, int P, long offsets[6]);
 int ecoz2b200_comm_init(ecoz2b200_engine *e, const unsigned char id[128],
                         int rank, int world_size);
 
@@ -194,8 +203,8 @@ int ecoz2b200_kmeans_pass(ecoz2b200_engine *e, double *cells_out,
  * full speed): they replace the resident frame set and are uploaded in chunks on a copy
  * stream while the search of the previous chunk runs, so the pass costs the PCIe transfer
  * and little else.  Equivalent to frames_clear + frames_reserve + frames_append_host +
- * frames_commit + kmeans_pass (same results; the frames stay resident afterwards).
- * Single-process engines only.                                                     */
+ * frames_commit + kmeans_pass (same results; the frames stay resident afterwards).  With
+ * comm_init every rank passes ITS frames and gets the global sums.                     */
 int ecoz2b200_kmeans_pass_host(ecoz2b200_engine *e, const double *x, long n, double *cells_out,
                                int32_t *cardd_out, double *discel_out, double *DD_out);
 
@@ -264,6 +273,13 @@ typedef struct {
     double search_main_ms; /* the dominant kernel alone: the full search over all frames
                               (FP32 pass in FP32 mode), CUDA events on its stream */
     long search_main_launches;
+    /* run-time audit (environment ECOZ2_VQ_AUDIT=n): after every search every n-th frame is searched
+     * again over ALL codewords in FP64 on the device and compared with the index the tensor-core /
+     * FP32 search + FP64 re-evaluation produced                                                 */
+    long audited;          /* frames audited since reset */
+    long audit_idx_diff;   /* of those: index differs from the all-FP64 scan (includes FP64-level ties) */
+    long audit_mismatches; /* of those: the chosen codeword is worse than the FP64 minimum by more than
+                              1e-6 relative, i.e. outside north_star's exemption: must stay 0 */
 } ecoz2b200_counters;
 int ecoz2b200_counters_reset(ecoz2b200_engine *e);
 int ecoz2b200_counters_get(ecoz2b200_engine *e, ecoz2b200_counters *out);

@@ -370,3 +370,48 @@ def test_fused_small_codebook_pass_edges(built_lib, P):
                     ref2 = O.kmeans_pass(x[1:], refl, raas)
                     assert np.array_equal(out2["cardd"], ref2["cardd"])
                     assert np.allclose(out2["cells"], ref2["cells"], rtol=REL_TIGHT, atol=1e-9)
+
+
+@pytest.mark.parametrize("K", [4, 16, 200], ids=["K4", "K16", "K200"])
+def test_inertia_as_written_with_negative_distortions(built_lib, K):
+    """inertia.c:21-25 takes min_i (dd_i^2), which is NOT (min_i dd_i)^2 when a frame has negative
+    distortions (rows that are not gain-normalised autocorrelations).  Half of these frames are
+    arbitrary rows with negative minima."""
+    from ecoz2rs_b200.synth import ar_mix
+    from oracle import oracle as O
+    rng = np.random.default_rng(K)
+    x = ar_mix(6000, 36, seed=3)
+    x[::2] = rng.normal(size=(3000, 37))
+    refl = np.zeros((K, 37))
+    refl[:, 1:] = np.clip(rng.normal(size=(K, 36)) * 0.3, -0.9, 0.9)
+    raas = O.refl_to_raas(refl)
+    _, dd, _ = O.assign(x, raas)
+    assert (dd < 0).sum() > 100, "fixture should contain negative minima"
+    want = O.inertia(x, raas)
+    naive = float((dd * dd).sum())
+    assert abs(naive - want) > 1e-3 * abs(want), "fixture should separate the two definitions"
+    for mode in (2, 0, 1):
+        with _engine(36, max_M=max(K, 2), mode=mode) as eng:
+            eng.set_frames(x)
+            eng.set_raas(raas)
+            got = eng.inertia()
+        assert abs(got - want) <= 1e-9 * abs(want), (mode, got, want, naive)
+
+
+def test_runtime_audit_counts(built_lib, frames36, oracle_run36, monkeypatch):
+    """ECOZ2_VQ_AUDIT=n: every n-th frame is searched again in FP64 over all codewords on the device;
+    the counters report how many were audited and that none was mis-assigned."""
+    from ecoz2rs_b200 import vq
+    monkeypatch.setenv("ECOZ2_VQ_AUDIT", "7")
+    stages, _ = oracle_run36
+    with vq.VqEngine(36, max_M=256) as eng:
+        eng.set_frames(frames36)
+        eng.set_reflections(stages[7]["refl"])
+        eng.counters_reset()
+        eng.kmeans_pass(want_cells=False)
+        eng.assign()
+        c = eng.counters()
+    per = (len(frames36) + 6) // 7
+    assert c["audited"] == 2 * per
+    assert c["audit_mismatches"] == 0 and c["audit_idx_diff"] <= 2
+    assert c["rechecked"] > 0
