@@ -217,6 +217,9 @@ int learn_files(const double *base_refl, int base_K, int P, double eps, const ch
 
 }  // namespace
 
+int ecoz2b200_classify_entry(char **cb_filenames, int num_codebooks, char **prd_filenames,
+                             int num_predictors, int show_ranked);   // vq_classify.cpp
+
 // shared with vq_classify.cpp
 void ecoz2b200_apply_mode_env(vqb200::Engine &eng) { apply_mode_env(eng); }
 std::vector<int> ecoz2b200_devices_from_env() { return devices_from_env(); }
@@ -224,9 +227,12 @@ std::vector<int> ecoz2b200_devices_from_env() { return devices_from_env(); }
 // ============================================================================ PART 1
 extern "C" {
 
-int ecoz2_vq_learn(int prediction_order, double epsilon, const char *codebook_class_name,
-                   const char *predictor_filenames[], int num_predictors, void *callback_target,
-                   vq_learn_callback_t callback) {
+// The exported names below forward to these internal bodies: when the library is linked next to the
+// reference's own ecoz2.c (integration/build.rs.patch), ecoz2_vq_learn resolves to THAT file's forward,
+// which calls vq_learn -- which must not call ecoz2_vq_learn back through the dynamic symbol table.
+static int learn_entry(int prediction_order, double epsilon, const char *codebook_class_name,
+                       const char *predictor_filenames[], int num_predictors, void *callback_target,
+                       vq_learn_callback_t callback) {
     // vq_learn.c:17-19
     printf("\nCodebook generation:\n\n");
     printf("prediction_order=%d class='%s'  epsilon=%g\n\n", prediction_order, codebook_class_name,
@@ -235,9 +241,15 @@ int ecoz2_vq_learn(int prediction_order, double epsilon, const char *codebook_cl
                        predictor_filenames, num_predictors, callback_target, callback);
 }
 
-int ecoz2_vq_learn_using_base_codebook(char *base_codebook, double epsilon,
-                                       const char *predictor_filenames[], int num_predictors,
-                                       void *callback_target, vq_learn_callback_t callback) {
+int ecoz2_vq_learn(int prediction_order, double epsilon, const char *codebook_class_name,
+                   const char *predictor_filenames[], int num_predictors, void *callback_target,
+                   vq_learn_callback_t callback) {
+    return learn_entry(prediction_order, epsilon, codebook_class_name, predictor_filenames, num_predictors,
+                       callback_target, callback);
+}
+
+static int learn_base_entry(char *base_codebook, double epsilon, const char *predictor_filenames[],
+                            int num_predictors, void *callback_target, vq_learn_callback_t callback) {
     // vq_learn.c:44-60
     int P = 0, M = 0;
     char cls[vqb200::kMaxClassNameLen];
@@ -257,8 +269,15 @@ int ecoz2_vq_learn_using_base_codebook(char *base_codebook, double epsilon,
                        callback_target, callback);
 }
 
-int ecoz2_vq_quantize(const char *nom_raas, const char *predictor_filenames[], int num_predictors,
-                      int show_filenames) {
+int ecoz2_vq_learn_using_base_codebook(char *base_codebook, double epsilon,
+                                       const char *predictor_filenames[], int num_predictors,
+                                       void *callback_target, vq_learn_callback_t callback) {
+    return learn_base_entry(base_codebook, epsilon, predictor_filenames, num_predictors, callback_target,
+                            callback);
+}
+
+static int quantize_entry(const char *nom_raas, const char *predictor_filenames[], int num_predictors,
+                          int show_filenames) {
     // vq_quantize.c:13-111
     int P = 0, M = 0;
     char cb_class[vqb200::kMaxClassNameLen];
@@ -334,6 +353,44 @@ int ecoz2_vq_quantize(const char *nom_raas, const char *predictor_filenames[], i
         printf("\ntotal: %d sequences; total  average distortion = %f\n", num_seqs,
                ddprm_total / num_seqs);
     return 0;
+}
+
+// ---- the inner C API of the reference (ecoz2/src/include/vq.h:82-117), i.e. what its public
+// forwards (ecoz2/src/ecoz2/ecoz2.c:109-193) and its C mains (x/vq.learn.c:107-128,
+// x/vq.quantize.c:41, x/vq.classify.c) call.  Exporting these as well lets ecoz2.c and the mains
+// link against this library UNMODIFIED once vq/vq_learn.c, vq_quantize.c, vq_classify.c (+ report.c,
+// sigma.c, inertia.c) are dropped from the build.  `use_par` selects between the reference's
+// serial and OpenMP loops; both are the one CUDA path here.
+int ecoz2_vq_quantize(const char *nom_raas, const char *predictor_filenames[], int num_predictors,
+                      int show_filenames) {
+    return quantize_entry(nom_raas, predictor_filenames, num_predictors, show_filenames);
+}
+
+int vq_learn(int prediction_order, double epsilon, const char *codebook_class_name,
+             const char *predictor_filenames[], int num_predictors, int use_par, void *callback_target,
+             vq_learn_callback_t callback) {
+    (void) use_par;
+    return learn_entry(prediction_order, epsilon, codebook_class_name, predictor_filenames,
+                       num_predictors, callback_target, callback);
+}
+int vq_learn_using_base_codebook(char *base_codebook, double epsilon, const char *predictor_filenames[],
+                                 int num_predictors, int use_par, void *callback_target,
+                                 vq_learn_callback_t callback) {
+    (void) use_par;
+    return learn_base_entry(base_codebook, epsilon, predictor_filenames, num_predictors, callback_target,
+                            callback);
+}
+int vq_quantize(const char *nom_raas, const char *predictor_filenames[], int num_predictors,
+                int show_filenames) {
+    return quantize_entry(nom_raas, predictor_filenames, num_predictors, show_filenames);
+}
+int ecoz2_vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenames, int num_predictors,
+                      int show_ranked) {
+    return ecoz2b200_classify_entry(cb_filenames, num_codebooks, prd_filenames, num_predictors, show_ranked);
+}
+int vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenames, int num_predictors,
+                int show_ranked) {
+    return ecoz2b200_classify_entry(cb_filenames, num_codebooks, prd_filenames, num_predictors, show_ranked);
 }
 
 // ============================================================================ PART 2

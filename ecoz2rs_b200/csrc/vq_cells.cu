@@ -345,6 +345,11 @@ void cell_scratch_carve(void *base, long cap, int max_K, CellScratch *out) {
     out->cap = cap;
 }
 
+void launch_cell_finish(const double *raas, const int32_t *hist, int K, int D, double *packed, cudaStream_t s) {
+    const PackedLayout L{K, D};
+    vq_cell_finish<<<(K + 7) / 8, 256, 0, s>>>(raas, hist, K, D, L, packed);
+}
+
 // shared memory of the streaming variant with R table replicas
 static size_t stream_smem_bytes(int K, int D, int R) {
     return sizeof(double) * (size_t) R * K * D + sizeof(int32_t) * (size_t) K;

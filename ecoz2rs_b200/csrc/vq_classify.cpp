@@ -136,7 +136,9 @@ void sort_dists(const std::vector<double> &dists, std::vector<int> &ordp) {
 
 }  // namespace
 
-extern "C" int ecoz2_vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenames,
+// internal body: the exported names ecoz2_vq_classify / vq_classify (vq_capi.cpp) forward here, never
+// to each other through the dynamic symbol table (see learn_entry in vq_capi.cpp)
+int ecoz2b200_classify_entry(char **cb_filenames, int num_codebooks, char **prd_filenames,
                                  int num_predictors, int show_ranked) {
     // the reference asserts num_codebooks < MAX_CB_MODELS (256) but its tables have 127 class rows
     // (vq_classify.c:16-37): more models than that corrupt its memory; here they are refused

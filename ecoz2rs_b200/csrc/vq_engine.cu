@@ -110,6 +110,8 @@ Engine::Engine(const int *devices, int num_devices, int P, int max_M)
     if (csort && csort[0] == '0') use_cell_sort_ = false;
     const char *au = getenv("ECOZ2_VQ_AUDIT");
     if (au && atoi(au) > 0) audit_every_ = atoi(au);
+    const char *fk = getenv("ECOZ2_VQ_TC_CELLS_MINK");
+    if (fk && atoi(fk) > 0) fuse_min_k_ = atoi(fk);
     ok_ = true;
 }
 
@@ -500,7 +502,7 @@ const Counters &Engine::counters() {
 // (a) the search on one shard: FP32 main pass + FP64 re-evaluation of the frames
 // inside the FP32 ambiguity bound, or the all-FP64 verification mode.
 void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
-                    const SearchScratch &sc) {
+                    const SearchScratch &sc, bool fuse_cells) {
     if (n <= 0) return;
     debug_poison(s);
     cudaEventRecord(s.ev[6], s.stream);
@@ -514,12 +516,17 @@ void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32
         const float err_scale = (float) (kappa_ * ldexp(1.0, -24));
         cudaMemsetAsync(sc.counters, 0, 4 * sizeof(int32_t), s.stream);
         launch_assign_tc(x32, n, D_, s.wtc, K_, nullptr, nullptr, sc, true, s.w1, s.w1max, err_tc, idx,
-                         nullptr, 0, s.num_sms, s.stream);
+                         nullptr, 0, s.num_sms, s.stream, x64, fuse_cells ? s.packed : nullptr,
+                         fuse_cells ? s.cs.hist : nullptr);
         cudaEventRecord(s.ev[7], s.stream);
         launch_recheck(x32, x64, n, D_, s.w32, s.w64, s.w1, s.w1max, s.raas, K_, 2.f * err_scale, sc,
                        idx, s.num_sms, s.stream, s.wtc, err_tc);
         vq_stat_add<<<1, 32, 0, s.stream>>>(sc.counters, s.dstat + 3);
         ctr_.kernel_launches += 6;
+        if (fuse_cells) {
+            launch_cell_fixup(x64, idx, D_, sc.flag_list, sc.counters + 0, s.packed, s.cs.hist, s.num_sms, s.stream);
+            ctr_.kernel_launches++;
+        }
     } else {
         // |error| of one FP32 distortion <= kappa * 2^-24 * |rx[0]| * sum_n |w[n]|.
         // Main pass: flag when the best-two gap is below twice that bound taken with the
@@ -541,8 +548,48 @@ void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32
     ctr_.evals += (double) n * K_;
 }
 
+void Engine::mid_pass(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
+                      const SearchScratch &sc, bool first_block) {
+    if (n <= 0) {
+        if (first_block) cudaMemsetAsync(s.cs.hist, 0, sizeof(int32_t) * (size_t) (K_ + 1), s.stream);
+        return;
+    }
+    debug_poison(s);
+    const float err_tc = (float) (kappa_tc_ * ldexp(1.0, -24));
+    const float err_scale = (float) (kappa_ * ldexp(1.0, -24));
+    cudaMemsetAsync(sc.counters, 0, 4 * sizeof(int32_t), s.stream);
+    // (the sorted path's scratch is idle here: perm takes the rows whose cell list was full)
+    launch_pass_mid(x64, n, D_, s.wtc, K_, sc, err_tc, idx, s.packed, s.cs.hist, s.cs.perm, s.cs.cursor,
+                    first_block, s.num_sms, s.stream);
+    cudaEventRecord(s.ev[7], s.stream);
+    launch_recheck(x32, x64, n, D_, s.w32, s.w64, s.w1, s.w1max, s.raas, K_, 2.f * err_scale, sc, idx,
+                   s.num_sms, s.stream, s.wtc, err_tc);
+    vq_stat_add<<<1, 32, 0, s.stream>>>(sc.counters, s.dstat + 3);
+    launch_cell_fixup(x64, idx, D_, sc.flag_list, sc.counters + 0, s.packed, s.cs.hist, s.num_sms, s.stream);
+    launch_cell_fixup(x64, idx, D_, s.cs.perm, s.cs.cursor, s.packed, s.cs.hist, s.num_sms, s.stream);
+    ctr_.kernel_launches += 9;
+    if (audit_every_ > 0) {
+        launch_audit(x64, n, D_, s.raas, K_, idx, audit_every_, s.dstat, s.num_sms, s.stream);
+        ctr_.kernel_launches++;
+    }
+    ctr_.evals += (double) n * K_;
+}
+
 void Engine::pass_kernels(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
                           const SearchScratch &sc, double *mindist, uint16_t *seq, bool with_cells) {
+    if (with_cells && mid_path() && seq == nullptr) {
+        // one sweep over the FP64 frames: search + cell sums (vq_mid.cu)
+        cudaEventRecord(s.ev[6], s.stream);
+        mid_pass(s, x64, x32, n, idx, sc, true);
+        cudaEventRecord(s.ev[1], s.stream);
+        cudaMemcpyAsync(s.raas_prev, s.raas, sizeof(double) * (size_t) K_ * D_, cudaMemcpyDeviceToDevice,
+                        s.stream);
+        launch_cell_finish(s.raas, s.cs.hist, K_, D_, s.packed, s.stream);
+        ctr_.kernel_launches++;
+        K_prev_ = K_;
+        if (idx == s.idx) mindist_valid_ = false;
+        return;
+    }
     if (small_path()) {
         // small codebooks are HBM-bound: one all-FP64 sweep does search + sums
         cudaEventRecord(s.ev[6], s.stream);
@@ -555,8 +602,19 @@ void Engine::pass_kernels(Shard &s, const double *x64, const float *x32, long n,
         if (mindist == s.mindist) mindist_valid_ = true;
         return;
     }
-    search(s, x64, x32, n, idx, sc);
+    const bool fuse = with_cells && seq == nullptr && fuse_path();
+    if (fuse) cudaMemsetAsync(s.cs.hist, 0, sizeof(int32_t) * (size_t) (K_ + 1), s.stream);
+    search(s, x64, x32, n, idx, sc, fuse);
     cudaEventRecord(s.ev[1], s.stream);
+    if (fuse) {
+        cudaMemcpyAsync(s.raas_prev, s.raas, sizeof(double) * (size_t) K_ * D_, cudaMemcpyDeviceToDevice,
+                        s.stream);
+        launch_cell_finish(s.raas, s.cs.hist, K_, D_, s.packed, s.stream);
+        ctr_.kernel_launches++;
+        K_prev_ = K_;
+        if (idx == s.idx) mindist_valid_ = false;
+        return;
+    }
     if (with_cells && use_cell_sort_ && cell_sort_supported(K_) && x64 == s.x64) {
         // grouped accumulation; per-frame minDist values are produced on demand from the
         // codebook this assignment was made against
@@ -752,7 +810,13 @@ int Engine::kmeans_pass_host(const double *x, long n, double *cells_out, int32_t
             // the persistent search kernel to leave the SMs and hold the next copy back)
             CUDA_TRY(cudaStreamWaitEvent(s.stream, s.ev_chunk[c & 1], 0));
             launch_convert_frames(s.x64 + (size_t) off * D_, s.x32 + (size_t) off * D_, m, D_, s.stream);
-            search(s, s.x64 + (size_t) off * D_, s.x32 + (size_t) off * D_, m, s.idx + off, s.sc);
+            if (mid_path()) {
+                mid_pass(s, s.x64 + (size_t) off * D_, s.x32 + (size_t) off * D_, m, s.idx + off, s.sc, c == 0);
+            } else {
+                if (fuse_path() && c == 0)
+                    cudaMemsetAsync(s.cs.hist, 0, sizeof(int32_t) * (size_t) (K_ + 1), s.stream);
+                search(s, s.x64 + (size_t) off * D_, s.x32 + (size_t) off * D_, m, s.idx + off, s.sc, fuse_path());
+            }
             ctr_.kernel_launches++;
         }
     }
@@ -780,8 +844,13 @@ int Engine::kmeans_pass_host(const double *x, long n, double *cells_out, int32_t
         if (s.n > 0) {
             cudaMemcpyAsync(s.raas_prev, s.raas, sizeof(double) * (size_t) K_ * D_, cudaMemcpyDeviceToDevice,
                             s.stream);
-            launch_cell_sums(s.x64, s.idx, s.n, D_, s.raas, K_, s.packed, nullptr, s.cs, s.num_sms, s.stream);
-            ctr_.kernel_launches += 5;
+            if (mid_path() || fuse_path()) {
+                launch_cell_finish(s.raas, s.cs.hist, K_, D_, s.packed, s.stream);
+                ctr_.kernel_launches++;
+            } else {
+                launch_cell_sums(s.x64, s.idx, s.n, D_, s.raas, K_, s.packed, nullptr, s.cs, s.num_sms, s.stream);
+                ctr_.kernel_launches += 5;
+            }
         }
         CUDA_TRY(cudaEventRecord(s.ev[2], s.stream));
     }

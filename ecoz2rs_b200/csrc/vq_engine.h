@@ -142,12 +142,18 @@ class Engine {
   private:
     int ensure_capacity(Shard &s, long n);
     int ensure_local_comms();
+    // fuse_cells: the tensor-core search also adds every frame outside the error bound to the packed
+    // cell sums / s.cs.hist (the flagged ones follow after their re-evaluation)
     void search(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
-                const SearchScratch &sc);
+                const SearchScratch &sc, bool fuse_cells = false);
     // search + winner distortion (+ cell sums) of one block of frames; records ev[1]
     // between the two phases.  K <= 32: one fused FP64 kernel.
     void pass_kernels(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
                       const SearchScratch &sc, double *mindist, uint16_t *seq, bool with_cells);
+    // fused mid-size pass of one block of frames: tensor-core search + cell sums of the frames outside
+    // the error bound (vq_pass_mid), FP64 re-evaluation of the others, their rows added afterwards
+    void mid_pass(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
+                  const SearchScratch &sc, bool first_block);
     int stage_codebook();  // raas -> search operands on every shard
     int pass_tail(double *cells_out, int32_t *cardd_out, double *discel_out, double *DD_out);
     int sync_all();
@@ -157,6 +163,11 @@ class Engine {
         return use_small_ && pass_small_supported(K_, D_) && (!tc_path() || pass_small_fast(K_, D_));
     }
     bool tc_path() const { return mode_ == ECOZ2B200_MODE_TENSOR && assign_tc_supported(K_, D_); }
+    bool mid_path() const { return tc_path() && !small_path() && pass_mid_supported(K_, D_); }
+    bool fuse_path() const {
+        return tc_path() && !small_path() && !mid_path() && K_ >= fuse_min_k_ && assign_tc_fuses_cells(K_, D_);
+    }
+    int fuse_min_k_ = 4096;      // ECOZ2_VQ_TC_CELLS_MINK: smallest codebook whose search carries the cell sums
     bool use_small_ = true;   // ECOZ2_VQ_FUSED_SMALL=0 forces the tiled path at every K
     bool use_cell_sort_ = true;  // ECOZ2_VQ_CELL_SORT=0: per-frame atomics (vq_accumulate) instead
     bool mindist_valid_ = true;  // s.mindist holds the last pass's values (else: compute on demand)

@@ -95,14 +95,22 @@ bool filter_tc_supported();
 void launch_filter_tc(const float *x32, long n_cap, int D, const float *wtc, int K,
                       const SearchScratch &sc, float err_scale, int num_sms, cudaStream_t s);
 int tc_tile_cols(int K, int D);
+bool tc_operands_f16();                                  // FP16 split parts (default) or TF32 parts
+const float *tc_bound_weights(const float *wtc, int K, int D);   // W1'_j behind the tiles (FP16 format)
 size_t tc_codebook_floats(int K, int D);
 int tc_issued_flops_per_eval(int D, int *is_f16);
 void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, const float *w1max,
                                 float err_scale, cudaStream_t s);
+// cells / hist (optional, with x64 = the FP64 originals of x32's rows; needs assign_tc_fuses_cells):
+// the search also adds the FP64 row of every frame OUTSIDE the error bound to packed cell sums and
+// counts (FP64 reductions issued by otherwise idle warps while the tensor core works); the flagged
+// frames follow through launch_cell_fixup after launch_recheck, then launch_cell_finish.
+bool assign_tc_fuses_cells(int K, int D);
 void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
                       const int32_t *list, const int32_t *list_count, const SearchScratch &sc,
                       bool flag, const float *w1, const float *w1max, float err_scale, int32_t *idx,
-                      float *dump, int dump_ld, int num_sms, cudaStream_t s);
+                      float *dump, int dump_ld, int num_sms, cudaStream_t s, const double *x64 = nullptr,
+                      double *cells = nullptr, int32_t *hist = nullptr);
 
 // ---- (b) cell accumulation ----------------------------------------------------
 // For every frame: dd = FP64 distortion against its codeword raas[idx];
@@ -142,6 +150,23 @@ void cell_scratch_carve(void *base, long cap, int max_K, CellScratch *out);
 void launch_cell_sums(const double *x64, const int32_t *idx, long n, int D, const double *raas,
                       int K, double *packed, uint16_t *seq, const CellScratch &cs, int num_sms,
                       cudaStream_t s);
+
+// ---- (a+b) fused pass for codebooks of ONE tensor-core tile (vq_mid.cu), 8 < K <= 128 ------------
+// One sweep over the FP64 frames: tensor-core search (same operands, same error bound and flag
+// protocol as launch_assign_tc) + cell sums of every frame OUTSIDE the bound into packed (cell sums)
+// and hist (counts).  The flagged frames (sc.flag_list) are re-evaluated by launch_recheck as usual;
+// launch_cell_fixup then adds their rows, launch_cell_finish derives counts / distortions / DD.
+// zero_hist = false accumulates into hist across calls (chunked host pass).
+bool pass_mid_supported(int K, int D);
+// late_list [n] / late_count [1]: rows the sweep could not take (a cell's per-tile list was full).
+void launch_pass_mid(const double *x64, long n, int D, const float *wtc, int K, const SearchScratch &sc,
+                     float err_scale, int32_t *idx, double *packed, int32_t *hist, int32_t *late_list,
+                     int32_t *late_count, bool zero_hist, int num_sms, cudaStream_t s);
+// packed cells[idx[row]] += x64[row], hist[idx[row]] += 1 for the rows list[0 .. *count)
+void launch_cell_fixup(const double *x64, const int32_t *idx, int D, const int32_t *list, const int32_t *count,
+                       double *packed, int32_t *hist, int num_sms, cudaStream_t s);
+// counts, per-cell distortion (cellsum . w - count) and DD from the cell sums and hist (vq_cells.cu)
+void launch_cell_finish(const double *raas, const int32_t *hist, int K, int D, double *packed, cudaStream_t s);
 
 // ---- (a+b) fused small-codebook pass (K <= 32, D = 37 or 13), all FP64 ----------
 // One sweep over the FP64 frames: exact argmin (first index on ties), idx / mindist / seq

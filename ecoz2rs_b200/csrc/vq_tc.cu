@@ -36,205 +36,10 @@
 #include <cstdlib>
 #include <vector>
 
+#include "vq_tc_common.cuh"
+
 namespace vqb200 {
 
-namespace {
-
-constexpr int kBM = 128;        // frames per tile = UMMA M = TMEM lanes
-constexpr int kStages = 6;      // B stage ring
-constexpr int kMaxKSteps = 5;   // D <= 40
-constexpr int kThreads = 384;    // 4 role warps + 8 epilogue warps
-constexpr int kLoaderThreads = 64;
-constexpr int kEpiWarp0 = 4;
-constexpr int kEpiWarps = 8;     // two per TMEM lane quarter, each takes half of the columns
-
-// ---- PTX wrappers -----------------------------------------------------------------
-__device__ __forceinline__ uint32_t s32(const void *p) {
-    return (uint32_t) __cvta_generic_to_shared(p);
-}
-__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(s32(bar)), "r"(count));
-}
-__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes) {
-    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(s32(bar)),
-                 "r"(bytes)
-                 : "memory");
-}
-__device__ __forceinline__ void mbar_arrive(uint64_t *bar) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(s32(bar)) : "memory");
-}
-// arrive whose issue depends on `dep` having been computed
-__device__ __forceinline__ void mbar_arrive_dep(uint64_t *bar, uint32_t dep) {
-    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0]; // %1" ::"r"(s32(bar)), "r"(dep) : "memory");
-}
-__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity) {
-    uint32_t ok;
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
-        "selp.u32 %0, 1, 0, p;\n"
-        "}\n"
-        : "=r"(ok)
-        : "r"(s32(bar)), "r"(parity)
-        : "memory");
-    return ok != 0;
-}
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
-    while (!mbar_try_wait(bar, parity)) {
-    }
-}
-// wait of a warp that is far ahead of its consumer (producers, frame loaders): sleeping
-// between polls leaves the issue slots of its SM sub-partition to the epilogue warps
-__device__ __forceinline__ void mbar_wait_relaxed(uint64_t *bar, uint32_t parity) {
-    while (!mbar_try_wait(bar, parity)) __nanosleep(200);
-}
-template <int REGS>
-__device__ __forceinline__ void setmaxnreg_inc() {
-    asm volatile("setmaxnreg.inc.sync.aligned.u32 %0;" ::"n"(REGS));
-}
-template <int REGS>
-__device__ __forceinline__ void setmaxnreg_dec() {
-    asm volatile("setmaxnreg.dec.sync.aligned.u32 %0;" ::"n"(REGS));
-}
-__device__ __forceinline__ void bulk_g2s(void *dst_smem, const void *src_gmem, uint32_t bytes,
-                                         uint64_t *bar) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::
-            "r"(s32(dst_smem)),
-        "l"(src_gmem), "r"(bytes), "r"(s32(bar))
-        : "memory");
-}
-__device__ __forceinline__ void fence_barrier_init() {
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-}
-__device__ __forceinline__ void fence_proxy_async() {
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-}
-__device__ __forceinline__ void tc_fence_before() {
-    asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tc_fence_after() {
-    asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_alloc(uint32_t *slot_smem, uint32_t cols) {
-    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(
-                     s32(slot_smem)),
-                 "r"(cols)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t cols) {
-    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(cols)
-                 : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem], TF32 inputs, FP32 accumulate
-__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
-                                          uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
-        "}\n" ::"r"(d_tmem),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// D[tmem] (+)= A[smem] * B[smem], FP16 inputs (K = 16 per instruction), FP32 accumulate
-__device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t adesc, uint64_t bdesc,
-                                         uint32_t idesc, uint32_t accumulate) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "setp.ne.b32 p, %4, 0;\n"
-        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
-        "}\n" ::"r"(d_tmem),
-        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
-        : "memory");
-}
-// mbarrier arrives when every tcgen05.mma issued so far by this thread has completed
-__device__ __forceinline__ void umma_commit(uint64_t *bar) {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::
-                     "r"(s32(bar))
-                 : "memory");
-}
-// multicast variants (thread-block cluster of 2): the copy lands at the same CTA-relative
-// offset in every CTA of cta_mask and signals each one's mbarrier at that offset
-__device__ __forceinline__ void bulk_g2s_mc(void *dst_smem, const void *src_gmem, uint32_t bytes,
-                                            uint64_t *bar, uint16_t cta_mask) {
-    asm volatile(
-        "cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes.multicast::cluster "
-        "[%0], [%1], %2, [%3], %4;" ::"r"(s32(dst_smem)),
-        "l"(src_gmem), "r"(bytes), "r"(s32(bar)), "h"(cta_mask)
-        : "memory");
-}
-__device__ __forceinline__ void umma_commit_mc(uint64_t *bar, uint16_t cta_mask) {
-    asm volatile(
-        "tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64 "
-        "[%0], %1;" ::"r"(s32(bar)),
-        "h"(cta_mask)
-        : "memory");
-}
-__device__ __forceinline__ void cluster_sync_all() {
-    asm volatile("barrier.cluster.arrive.release.aligned;" ::: "memory");
-    asm volatile("barrier.cluster.wait.acquire.aligned;" ::: "memory");
-}
-__device__ __forceinline__ uint32_t cluster_ctarank() {
-    uint32_t r;
-    asm volatile("mov.u32 %0, %%cluster_ctarank;" : "=r"(r));
-    return r;
-}
-__device__ __forceinline__ void tmem_ld32(uint32_t taddr, uint32_t (&v)[32]) {
-    asm volatile(
-        "tcgen05.ld.sync.aligned.32x32b.x32.b32 "
-        "{%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, "
-        "%16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];"
-        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]),
-          "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]),
-          "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]),
-          "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]),
-          "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
-        : "r"(taddr)
-        : "memory");
-}
-__device__ __forceinline__ bool elect_one() {
-    uint32_t pred;
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "elect.sync _|p, 0xffffffff;\n"
-        "selp.u32 %0, 1, 0, p;\n"
-        "}\n"
-        : "=r"(pred));
-    return pred != 0;
-}
-__device__ __forceinline__ void tmem_ld_wait() {
-    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
-}
-__device__ __forceinline__ float tf32_rna(float v) {
-    uint32_t r;
-    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
-    return __uint_as_float(r);
-}
-
-// UMMA shared-memory matrix descriptor, K-major, no swizzle: core matrix = 8 rows x 16 B
-// stored as 128 contiguous bytes; lbo = byte distance between the two core matrices of a
-// k-step (K direction), sbo = byte distance between 8-row groups (M/N direction).
-__device__ __forceinline__ uint64_t umma_desc(uint32_t saddr, uint32_t lbo, uint32_t sbo) {
-    return (uint64_t) ((saddr >> 4) & 0x3FFFu) | ((uint64_t) ((lbo >> 4) & 0x3FFFu) << 16) |
-           ((uint64_t) ((sbo >> 4) & 0x3FFFu) << 32) | (1ull << 46);
-}
-// instruction descriptor: D = F32, A = B = TF32, both K-major, M x N
-__host__ __device__ constexpr uint32_t umma_idesc_tf32(int M, int N) {
-    return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t) (N >> 3) << 17) |
-           ((uint32_t) (M >> 4) << 24);
-}
-// same for kind::f16 with A = B = FP16 (format code 0)
-__host__ __device__ constexpr uint32_t umma_idesc_f16(int M, int N) {
-    return (1u << 4) | ((uint32_t) (N >> 3) << 17) | ((uint32_t) (M >> 4) << 24);
-}
-
-}  // namespace
 
 struct TcParams {
     const float *x;             // frames [n][D] FP32
@@ -266,7 +71,13 @@ struct TcParams {
     int32_t *exact_list;        // frames whose candidates did not fit: all-FP64 search
     int32_t *exact_count;
     int mc;                     // 1: launched as clusters of 2 CTAs that share the codeword stream
-    int raw_bufs;               // variant 2: staging buffers for raw frame halves (1 or 2)
+    int raw_bufs;               // variant 2: staging buffers for raw frame halves (1 .. 8)
+    // fused cell sums (CELLS instance): the FP64 row of every frame OUTSIDE the error bound is added
+    // to its cell with FP64 reductions (RED) by the loader warps while the tensor core is busy with
+    // later tiles; flagged frames are added after their re-evaluation (vq_cell_fixup)
+    const double *x64;
+    double *cells;              // packed cell sums [K][D]
+    int32_t *hist;              // frames per cell
     unsigned long long *prof;   // dev (exp bit 256): per CTA {SM clocks, ns} of the kernel
     int exp;                    // dev experiments (ECOZ2_VQ_TC_EXP): bit mask 1 no record path, 2 trivial reduction, 4 no tcgen05.ld, 8 no MMA, 16 no tcgen05.st, 32 no B copy
 };
@@ -285,116 +96,6 @@ struct TcSmem {
     uint64_t raw_full;
     uint32_t tmem_slot;
 };
-
-__device__ __forceinline__ float min3f(float a, float b, float c) { return fminf(fminf(a, b), c); }
-
-
-// Running state of one frame (one epilogue thread): minimum, runner-up, and a snapshot of
-// the 16-codeword chunk that holds the minimum.  Only the FINAL minimum's chunk matters for
-// the runner-up inside a chunk (a superseded minimum is itself a smaller-or-equal contender
-// than anything else in its chunk), so the position inside the chunk is resolved once per
-// frame (epi_finish), not per record.
-struct EpiState {
-    float best, second;
-    int col;          // first codeword of the snapshot chunk
-    float snap[16];
-    __device__ __forceinline__ void init() {
-        best = INFINITY; second = INFINITY; col = 0;
-#pragma unroll
-        for (int j = 0; j < 16; j++) snap[j] = INFINITY;
-    }
-};
-
-// One chunk of 16 consecutive codewords: 10 FMNMX(3) for the chunk minimum + 4 ops; when some
-// lane of the warp sees a new minimum those lanes copy the chunk (predicated moves).
-__device__ __forceinline__ void epi_chunk(const float (&v)[16], int col0, EpiState &st, int exp = 0) {
-    if (exp & 2) { st.best = fminf(st.best, v[0]); return; }
-    const float q0 = fminf(min3f(v[0], v[1], v[2]), v[3]);
-    const float q1 = fminf(min3f(v[4], v[5], v[6]), v[7]);
-    const float q2 = fminf(min3f(v[8], v[9], v[10]), v[11]);
-    const float q3 = fminf(min3f(v[12], v[13], v[14]), v[15]);
-    const float m = fminf(min3f(q0, q1, q2), q3);
-    const bool rec = m < st.best;
-    // not a record: every value of the chunk is >= m >= best, so m is the chunk's only
-    // contender for runner-up.  record: the old best is.
-    st.second = fminf(st.second, fmaxf(m, st.best));
-    st.best = fminf(st.best, m);
-    if (!(exp & 1) && __any_sync(0xffffffffu, rec)) {
-        if (rec) {
-#pragma unroll
-            for (int j = 0; j < 16; j++) st.snap[j] = v[j];
-            st.col = col0;
-        }
-    }
-}
-
-// 32 consecutive codewords (two independent 16-chunks -> two min trees in flight).
-// nv_rel = number of valid codewords from col0 on (>= 32 except at the end of the codebook).
-__device__ __forceinline__ void epi_step32(const uint32_t (&r)[32], int col0, int nv_rel,
-                                           EpiState &st, int exp) {
-#define F(i) __uint_as_float(r[i])
-    if (exp & 2) { st.best = fminf(st.best, F(0)); return; }
-    if (nv_rel < 32) {   // ragged end of the codebook: generic path
-        float v[16];
-#pragma unroll
-        for (int j = 0; j < 16; j++) v[j] = j < nv_rel ? F(j) : INFINITY;
-        epi_chunk(v, col0, st, exp);
-        if (nv_rel > 16) {
-#pragma unroll
-            for (int j = 0; j < 16; j++) v[j] = 16 + j < nv_rel ? F(16 + j) : INFINITY;
-            epi_chunk(v, col0 + 16, st, exp);
-        }
-        return;
-    }
-    // minimum of each 16-codeword chunk in 8 three-input ops (16 -> 6 -> 2 -> 1), the two
-    // chunks interleaved: two independent dependency chains
-    const float a0 = min3f(F(0), F(1), F(2)), b0 = min3f(F(16), F(17), F(18));
-    const float a1 = min3f(F(3), F(4), F(5)), b1 = min3f(F(19), F(20), F(21));
-    const float a2 = min3f(F(6), F(7), F(8)), b2 = min3f(F(22), F(23), F(24));
-    const float a3 = min3f(F(9), F(10), F(11)), b3 = min3f(F(25), F(26), F(27));
-    const float a4 = min3f(F(12), F(13), F(14)), b4 = min3f(F(28), F(29), F(30));
-    const float a5 = min3f(a0, a1, F(15)), b5 = min3f(b0, b1, F(31));
-    const float a6 = min3f(a2, a3, a4), b6 = min3f(b2, b3, b4);
-    const float mA = fminf(a5, a6), mB = fminf(b5, b6);
-    const float m = fminf(mA, mB);
-    const bool rec = m < st.best;
-    // contenders for runner-up: the larger chunk minimum always; m itself unless it is the new
-    // best, in which case the old best is
-    st.second = min3f(st.second, fmaxf(m, st.best), fmaxf(mA, mB));
-    st.best = fminf(st.best, m);
-    if (!(exp & 1)) {
-        // snapshot of the record chunk; the two chunks vote separately -- late in the codebook a
-        // step sees records in one or two lanes, i.e. usually in one chunk only
-        const bool ra_ = rec && mA <= mB, rb_ = rec && !(mA <= mB);
-        if (__any_sync(0xffffffffu, ra_)) {
-            if (ra_) {
-#pragma unroll
-                for (int j = 0; j < 16; j++) st.snap[j] = F(j);
-                st.col = col0;
-            }
-        }
-        if (__any_sync(0xffffffffu, rb_)) {
-            if (rb_) {
-#pragma unroll
-                for (int j = 0; j < 16; j++) st.snap[j] = F(16 + j);
-                st.col = col0 + 16;
-            }
-        }
-    }
-#undef F
-}
-
-// -> codeword of the minimum (first position among equal values) and the overall runner-up
-__device__ __forceinline__ void epi_finish(const EpiState &st, float &second, int &bidx) {
-    int jm = 15;
-#pragma unroll
-    for (int j = 14; j >= 0; j--) jm = st.snap[j] == st.best ? j : jm;
-    float s2 = INFINITY;
-#pragma unroll
-    for (int j = 0; j < 16; j++) s2 = fminf(s2, j == jm ? INFINITY : st.snap[j]);
-    second = fminf(st.second, s2);
-    bidx = st.col + jm;
-}
 
 // filter mode (see TcParams::cand): a frame's candidates are collected in registers (a
 // flagged frame typically has 2-3) and published once per frame tile with one atomic per
@@ -503,40 +204,6 @@ __device__ __forceinline__ void epi_tile(uint32_t taddr, int c_lo, int c_hi, int
         c += 32;
     }
 #undef VQ_TC_STEP
-}
-
-// Full tile of NCOLS codewords, search mode: fully unrolled (constant TMEM offsets, no
-// per-step checks).  The accumulator is handed back to the MMA warp (release_bar) as soon as
-// its last columns are in registers, before they are reduced.
-template <int NCOLS>
-__device__ __forceinline__ void epi_tile_full(uint32_t taddr, int tcol0, EpiState &est,
-                                              uint64_t *release_bar) {
-    constexpr int NS = NCOLS / 32;
-    uint32_t ra[32], rb[32];
-    tmem_ld32(taddr, ra);
-#pragma unroll
-    for (int s = 0; s < NS; s += 2) {
-        tmem_ld_wait();
-        if (s + 1 < NS) {
-            tmem_ld32(taddr + 32 * (s + 1), rb);
-        } else {
-            tc_fence_before();
-            __syncwarp();
-            if ((threadIdx.x & 31) == 0) mbar_arrive(release_bar);
-        }
-        epi_step32(ra, tcol0 + 32 * s, 32, est, 0);
-        if (s + 1 < NS) {
-            tmem_ld_wait();
-            if (s + 2 < NS) {
-                tmem_ld32(taddr + 32 * (s + 2), ra);
-            } else {
-                tc_fence_before();
-                __syncwarp();
-                if ((threadIdx.x & 31) == 0) mbar_arrive(release_bar);
-            }
-            epi_step32(rb, tcol0 + 32 * (s + 1), 32, est, 0);
-        }
-    }
 }
 
 __global__ void __launch_bounds__(kThreads, 1) vq_assign_tc(const TcParams p) {
@@ -819,15 +486,16 @@ constexpr int kEpiRegs = 168, kLoaderRegs = 96, kRoleRegs = 80;   // 256*168 + 1
 constexpr int kB2Stages = 3;
 
 struct Tc2Smem {
+    uint64_t cell_full[8];                // [2 * (tile & 3) + half]: the half's cell indices are in s_cell
     uint64_t b_full[kB2Stages], b_empty[kB2Stages];
-    uint64_t raw_full[2], raw_empty[2];   // raw-frame staging buffers (TcParams::raw_bufs of them)
+    uint64_t raw_full[8], raw_empty[8];   // raw-frame staging buffers (TcParams::raw_bufs of them)
     uint64_t a_full[4], a_free[4];        // [2 * frame-tile buffer + half]
     uint64_t acc_full[4], acc_empty[4];   // [2 * buffer + half]
     uint32_t tmem_slot;
 };
 }  // namespace
 
-template <int KS, bool FILTER, bool DBG, bool H16>
+template <int KS, bool FILTER, bool DBG, bool H16, bool CELLS>
 __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) {
     const int exp = DBG ? p.exp : 0;
     unsigned long long prof_c0 = 0, prof_t0 = 0;
@@ -852,8 +520,9 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
     constexpr int BC = H16 ? 2 * KC + (KC & 1) : 2 * KC;             // chunks per codeword row
     constexpr int EPC = H16 ? 8 : 4;                                 // elements per chunk
     constexpr int NE = KC * EPC;                                     // padded row length
-    constexpr uint32_t hdr_bytes = H16 ? 9216 : 5120;                // + per-frame scales (FP16 format)
+    constexpr uint32_t hdr_bytes = H16 ? 13312 : 5120;               // + per-frame scales, cell indices (FP16 format)
     float *s_scale = reinterpret_cast<float *>(smem_raw + 5120);     // [4 slots][2 halves][128], H16 only
+    int32_t *s_cell = reinterpret_cast<int32_t *>(smem_raw + 9216);  // [4 slots][2 halves][128], CELLS only
     constexpr uint32_t a_part_bytes = (uint32_t) KC * kBM * 16;      // hi or lo of one half
     constexpr uint32_t a_half_bytes = 2 * a_part_bytes;
     const uint32_t raw_bytes = (uint32_t) kBM * D * 4;               // 128 rows
@@ -878,7 +547,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             mbar_init(&sm->b_full[i], 1);
             mbar_init(&sm->b_empty[i], 1);
         }
-        for (int i = 0; i < 2; i++) {
+        for (int i = 0; i < 8; i++) {
             mbar_init(&sm->raw_full[i], 1);
             mbar_init(&sm->raw_empty[i], 4);
         }
@@ -890,6 +559,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             mbar_init(&sm->acc_full[i], 1);
             mbar_init(&sm->acc_empty[i], 4);
         }
+        for (int i = 0; i < 8; i++) mbar_init(&sm->cell_full[i], 4);
         fence_barrier_init();
     }
     if (warp == 13) tmem_alloc(&sm->tmem_slot, 512);
@@ -930,7 +600,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 for (int h = 0; h < 2; h++) {
                     const long base = ft * (2 * kBM) + h * kBM;
                     if (base + kBM > total) continue;
-                    const uint32_t rb = RB == 2 ? (rs & 1) : 0, rph = RB == 2 ? (rs >> 1) & 1 : rs & 1;
+                    const uint32_t rb = rs % RB, rph = (rs / RB) & 1;
                     mbar_wait_relaxed(&sm->raw_empty[rb], rph ^ 1);
                     mbar_expect_tx(&sm->raw_full[rb], raw_bytes);
                     bulk_g2s(raw_base + rb * raw_stride, p.x + base * D, raw_bytes, &sm->raw_full[rb]);
@@ -1021,13 +691,57 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         setmaxnreg_dec<kLoaderRegs>();
         const int r = warp * 32 + lane;
         uint32_t it = 0, rs = 0;
+        // CELLS: the rows of tile `t` (this CTA's t-th tile) that fell OUTSIDE the error bound are added
+        // to their cells two tiles later, when the epilogue has long finished with it; warp w takes rows
+        // 32 w .. 32 w + 31 of both halves, lanes = components, 8 rows in flight
+        auto accumulate_tile = [&](uint32_t t) {
+            const long ft = (long) blockIdx.x + (long) t * gridDim.x;
+            for (int h = 0; h < 2; h++) {
+                const uint32_t slot = (t & 3) * 2 + h;
+                mbar_wait_relaxed(&sm->cell_full[slot], (t >> 2) & 1);
+                const int cmine = s_cell[slot * kBM + r];
+                const long row0 = ft * (2 * kBM) + h * kBM + warp * 32;
+                // the rows this warp adds NEXT time (tile t + 1) start their way from HBM to L2 now
+                {
+                    const long nrow0 = row0 + (long) gridDim.x * (2 * kBM);
+                    if (nrow0 + 32 <= total) {
+                        const char *nb = reinterpret_cast<const char *>(p.x64 + nrow0 * D);
+                        for (int o = lane * 128; o < 32 * D * 8; o += 32 * 128)
+                            asm volatile("prefetch.global.L2 [%0];" ::"l"(nb + o));
+                    }
+                }
+                if (__ballot_sync(0xffffffffu, cmine >= 0) == 0u) continue;
+#pragma unroll 1
+                for (int u = 0; u < 32; u += 4) {
+                    int cu[4];
+                    double xa[4], xb[4];
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        cu[k] = __shfl_sync(0xffffffffu, cmine, u + k);
+                        const double *xr = p.x64 + (row0 + u + k) * D;
+                        xa[k] = (cu[k] >= 0 && lane < D) ? xr[lane] : 0.0;
+                        xb[k] = (cu[k] >= 0 && lane + 32 < D) ? xr[lane + 32] : 0.0;
+                    }
+#pragma unroll
+                    for (int k = 0; k < 4; k++) {
+                        if (cu[k] >= 0) {
+                            double *dst = p.cells + (long) cu[k] * D;
+                            if (lane < D) atomicAdd(dst + lane, xa[k]);
+                            if (lane + 32 < D) atomicAdd(dst + lane + 32, xb[k]);
+                        }
+                    }
+                }
+                if (cmine >= 0) atomicAdd(p.hist + cmine, 1);
+            }
+        };
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+            if (CELLS && it >= 2) accumulate_tile(it - 2);
             for (int h = 0; h < 2; h++) {
                 const long base = ft * (2 * kBM) + h * kBM;
                 const bool staged = p.list == nullptr && base + kBM <= total && !(exp & 64);
                 float v[NE];
                 if (staged) {
-                    const uint32_t rb = RB == 2 ? (rs & 1) : 0, rph = RB == 2 ? (rs >> 1) & 1 : rs & 1;
+                    const uint32_t rb = rs % RB, rph = (rs / RB) & 1;
                     mbar_wait_relaxed(&sm->raw_full[rb], rph);
                     rs++;
                     const float *src = reinterpret_cast<const float *>(raw_base + rb * raw_stride) + r * D;
@@ -1111,6 +825,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 if (lane == 0) mbar_arrive(&sm->a_full[2 * ab + h]);
             }
         }
+        if (CELLS) {   // drain: the last two tiles
+            if (it >= 2) accumulate_tile(it - 2);
+            if (it >= 1) accumulate_tile(it - 1);
+        }
     } else if (warp < 12) {
         // ===== epilogue: thread = frame (TMEM lane), registers = codewords =====
         setmaxnreg_inc<kEpiRegs>();
@@ -1163,8 +881,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             int bidx;
             epi_finish(est, second, bidx);
             if (DBG && exp) bidx = (unsigned) bidx < (unsigned) K ? bidx : 0;   // experiments leave it undefined
+            int cell = -1;
             if (row >= 0) {
                 p.idx_out[row] = bidx;
+                cell = bidx;
                 if (p.flag_list != nullptr && !(exp & 128)) {
                     // accumulator = lower bound L_ij = d~_ij - e |x0| W1_j of the true distortion;
                     // bidx is certainly the true argmin when every other lower bound exceeds its
@@ -1176,8 +896,14 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                         p.flag_list[pos] = (int32_t) row;
                         p.flag_ub[pos] = ub;
                         p.min_key[pos] = ~0ull;
+                        cell = -1;   // its row is added after the FP64 re-evaluation (vq_cell_fixup)
                     }
                 }
+            }
+            if (CELLS) {
+                s_cell[((it & 3) * 2 + h) * kBM + r] = cell;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&sm->cell_full[(it & 3) * 2 + h]);
             }
         }
         if (DBG && p.prof != nullptr && lane == 0 && q == 0) {
@@ -1393,6 +1119,8 @@ static bool tc_wide() {
     return v == 1;
 }
 
+bool tc_operands_f16() { return tc_f16(); }
+
 int tc_tile_cols(int K, int D) {
     // (wide tiles need 2 x 13 chunks x 4 KB for D + 1 > 40: no room next to the frame tiles)
     if (tc_variant() == 2)
@@ -1423,6 +1151,8 @@ size_t tc_codebook_floats(int K, int D) {
     return tc_tiles_floats(K, D) + (size_t) n_wtiles * BN + 4;
 }
 
+const float *tc_bound_weights(const float *wtc, int K, int D) { return wtc + tc_tiles_floats(K, D); }
+
 void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, const float *w1max,
                                 float err_scale, cudaStream_t s) {
     const int BN = tc_tile_cols(K, D), ksteps = tc_ksteps(D);
@@ -1445,26 +1175,37 @@ static size_t tc_smem_bytes(int D, int BN) {
 static size_t tc2_smem_bytes(int D, int BN, int raw_bufs) {
     const size_t raw_stride = ((size_t) kBM * D * 4 + 127) & ~(size_t) 127;
     const size_t KC = (tc_f16() ? 1 : 2) * (size_t) tc_ksteps(D);   // chunks per split part
-    return (tc_f16() ? 9216 : 5120) + raw_bufs * raw_stride + (tc_f16() ? 2 : 1) * 2 * (2 * KC * kBM * 16) +
+    return (tc_f16() ? 13312 : 5120) + raw_bufs * raw_stride + (tc_f16() ? 2 : 1) * 2 * (2 * KC * kBM * 16) +
            (size_t) (BN == 256 ? 2 : kB2Stages) * tc_row_chunks(D) * BN * 16;
 }
 // two staging buffers for the raw frame halves when they fit (the second hides the bulk-copy
 // latency behind the loaders' conversion of the first: it matters for small codebooks, where
 // the loaders are the critical path)
-static int tc2_raw_bufs(int D, int BN) { return tc2_smem_bytes(D, BN, 2) <= 227 * 1024 ? 2 : 1; }
+// Small codebooks are bound by the frames in flight, not by the tensor core: a half-tile's bulk copy
+// takes ~4000 clocks from HBM under load, so an SM needs ~100 KB in flight to take its share of the
+// bandwidth (measured on B200: two 19 KB buffers = 2.6 TB/s, 0.56 ms per 10M-frame search whatever K).
+// The narrow-tile configurations leave that much shared memory free: up to 8 staging buffers.
+static int tc2_raw_bufs(int D, int BN) {
+    static int cap = -1;
+    if (cap < 0) { const char *e = getenv("ECOZ2_VQ_TC_RAW"); cap = e ? atoi(e) : 2; if (cap < 1) cap = 1; if (cap > 8) cap = 8; }
+    int n = cap;
+    while (n > 1 && tc2_smem_bytes(D, BN, n) > 227 * 1024) n--;
+    return n;
+}
 
-template <int KS, bool FILTER, bool DBG, bool H16>
+template <int KS, bool FILTER, bool DBG, bool H16, bool CELLS>
 static void launch_tc2_inst2(const TcParams &p, long grid, cudaStream_t s) {
     // per device (function attributes belong to the context): set on every launch, ~1 us
-    cudaFuncSetAttribute(vq_assign_tc2<KS, FILTER, DBG, H16>,
+    cudaFuncSetAttribute(vq_assign_tc2<KS, FILTER, DBG, H16, CELLS>,
                          cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    vq_assign_tc2<KS, FILTER, DBG, H16><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN, p.raw_bufs), s>>>(p);
+    vq_assign_tc2<KS, FILTER, DBG, H16, CELLS><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN, p.raw_bufs), s>>>(p);
 }
 template <int KS, bool H16>
 static void launch_tc2_inst(const TcParams &p, long grid, cudaStream_t s) {
-    if (p.cand != nullptr) launch_tc2_inst2<KS, true, false, H16>(p, grid, s);
-    else if (p.exp != 0 || p.dump != nullptr) launch_tc2_inst2<KS, false, true, H16>(p, grid, s);
-    else launch_tc2_inst2<KS, false, false, H16>(p, grid, s);
+    if (p.cand != nullptr) launch_tc2_inst2<KS, true, false, H16, false>(p, grid, s);
+    else if (p.exp != 0 || p.dump != nullptr) launch_tc2_inst2<KS, false, true, H16, false>(p, grid, s);
+    else if (H16 && p.cells != nullptr) launch_tc2_inst2<KS, false, false, H16, H16>(p, grid, s);
+    else launch_tc2_inst2<KS, false, false, H16, false>(p, grid, s);
 }
 // variant 2, any supported (format, k-steps)
 static void launch_tc2(TcParams &p, long grid, cudaStream_t s) {
@@ -1493,12 +1234,22 @@ static void launch_tc2(TcParams &p, long grid, cudaStream_t s) {
     }
 }
 
+bool assign_tc_fuses_cells(int K, int D) {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("ECOZ2_VQ_TC_CELLS"); on = (e && e[0] == '0') ? 0 : 1; }
+    return on && tc_variant() == 2 && tc_f16() && D <= 64 && assign_tc_supported(K, D);
+}
+
 void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
                       const int32_t *list, const int32_t *list_count, const SearchScratch &sc,
                       bool flag, const float *w1, const float *w1max, float err_scale, int32_t *idx,
-                      float *dump, int dump_ld, int num_sms, cudaStream_t s) {
+                      float *dump, int dump_ld, int num_sms, cudaStream_t s, const double *x64,
+                      double *cells, int32_t *hist) {
     if (n <= 0) return;
     TcParams p{};
+    if (cells != nullptr && list == nullptr && dump == nullptr && flag && assign_tc_fuses_cells(K, D)) {
+        p.x64 = x64; p.cells = cells; p.hist = hist;
+    }
     p.x = x32; p.n_frames = n; p.D = D; p.ksteps = tc_ksteps(D);
     p.list = list; p.list_count = list_count;
     p.wtc = wtc; p.K = K; p.BN = tc_tile_cols(K, D);

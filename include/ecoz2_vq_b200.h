@@ -70,6 +70,23 @@ int ecoz2_vq_quantize(const char *nom_raas, const char *predictor_filenames[],
 int ecoz2_vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenames,
                       int num_predictors, int show_ranked);
 
+/* The reference's INNER C API (ecoz2/src/include/vq.h:82-117) with identical signatures: what its
+ * public forwards (ecoz2/src/ecoz2/ecoz2.c:109-193) and its C mains (ecoz2/src/x/vq.learn.c:107-128,
+ * x/vq.quantize.c:41, x/vq.classify.c) call.  With these exported, ecoz2.c and the mains link against
+ * this library unmodified (integration/build.rs.patch; oracle/Makefile target `dropin` builds the
+ * reference's vq.learn / vq.quantize mains that way).  `use_par` (serial / OpenMP loop of the
+ * reference) is accepted and ignored: both are the CUDA path.                                  */
+int vq_learn(int prediction_order, double epsilon, const char *codebook_class_name,
+             const char *predictor_filenames[], int num_predictors, int use_par,
+             void *callback_target, vq_learn_callback_t callback);
+int vq_learn_using_base_codebook(char *base_codebook, double epsilon,
+                                 const char *predictor_filenames[], int num_predictors, int use_par,
+                                 void *callback_target, vq_learn_callback_t callback);
+int vq_quantize(const char *nom_raas, const char *predictor_filenames[], int num_predictors,
+                int show_filenames);
+int vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenames, int num_predictors,
+                int show_ranked);
+
 /* ===================================================================== PART 2
  * In-memory API.                                                            */
 

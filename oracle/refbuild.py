@@ -44,6 +44,9 @@ def build() -> bool:
     """Build oracle/_ref when the reference sources are present. Returns availability."""
     if os.path.exists(os.path.join(REF_SRC, "vq", "vq_learn.c")):
         subprocess.check_call(["make", "-s", "-j8", "-C", _HERE, "ref"])
+        # the reference's own mains linked against the product library (its exported inner API)
+        if os.path.exists(os.path.join(os.path.dirname(_HERE), "ecoz2rs_b200", "csrc", "libecoz2_vq_b200.so")):
+            subprocess.check_call(["make", "-s", "-j8", "-C", _HERE, "dropin", "linkcheck"])
     return available()
 
 
@@ -226,6 +229,22 @@ def run_vq_learn(prd_files, cwd, P=None, eps=0.05, class_name="_", max_M=256,
     m = _TOTAL_RE.search(out)
     res["total_s"] = float(m.group(1)) if m else None
     return res
+
+
+def dropin_available() -> bool:
+    d = arch_dir()
+    return os.path.exists(os.path.join(d, "dropin.vq.learn")) and os.path.exists(os.path.join(d, "dropin.vq.quantize"))
+
+
+def run_dropin(which, args, cwd, env=None):
+    """The reference's unmodified main (x/vq.learn.c or x/vq.quantize.c) linked against
+    libecoz2_vq_b200.so (which exports vq_learn / vq_quantize).  which: "vq.learn" | "vq.quantize"."""
+    exe = os.path.join(arch_dir(), "dropin." + which)
+    e = dict(os.environ)
+    e.update(env or {})
+    proc = subprocess.run([exe] + list(args), cwd=cwd, env=e, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
+                          text=True)
+    return dict(returncode=proc.returncode, stdout=proc.stdout)
 
 
 def read_rpt_csv(path):

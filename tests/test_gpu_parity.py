@@ -415,3 +415,87 @@ def test_runtime_audit_counts(built_lib, frames36, oracle_run36, monkeypatch):
     assert c["audited"] == 2 * per
     assert c["audit_mismatches"] == 0 and c["audit_idx_diff"] <= 2
     assert c["rechecked"] > 0
+
+
+@pytest.mark.parametrize("P", [36, 12, 20])
+def test_fused_mid_codebook_pass_edges(built_lib, P):
+    """vq_pass_mid (8 < K <= 128: tensor-core search + cell sums in one sweep over the FP64 frames):
+    single / partial / many half-tiles, ragged codebooks, frames inside the error bound (duplicate
+    codewords flag EVERY frame: all rows then arrive through the fix-up), an 8-byte aligned frame
+    pointer (no bulk copies), against the oracle's teacher-forced pass."""
+    from ecoz2rs_b200.synth import ar_mix
+    from oracle import oracle as O
+    rng = np.random.default_rng(5 + P)
+    xall = ar_mix(70_000, P, seed=7 + P)
+    cases = [(16, 1), (16, 127), (32, 128), (20, 129), (64, 255), (64, 256), (100, 257), (128, 1000),
+             (128, 70_000), (16, 69_999), (9, 5000)]
+    for K, N in cases:
+        refl = np.zeros((K, P + 1))
+        refl[:, 1:] = np.clip(rng.normal(size=(K, P)) * 0.3, -0.9, 0.9)
+        if K == 32:
+            refl[16:] = refl[:16]            # exact ties: the whole block goes through the re-evaluation
+        raas = O.refl_to_raas(refl)
+        x = xall[:N]
+        ref = O.kmeans_pass(x, refl, raas)
+        with _engine(P, max_M=128) as eng:
+            eng.set_frames(x)
+            eng.set_reflections(refl)
+            out = eng.kmeans_pass()
+            idx, md = eng.last_assignment()
+            nrefl, _ = eng.codebook()
+            bad = allowed_index_mismatches(idx, ref["idx"], ref["ddmin"], ref["second"])
+            assert bad.size == 0, (K, N, bad[:5])
+            if np.array_equal(idx, ref["idx"]):
+                assert np.array_equal(out["cardd"], ref["cardd"]), (K, N)
+                assert np.allclose(out["cells"], ref["cells"], rtol=REL_TIGHT, atol=1e-9), (K, N)
+                assert abs(out["DD"] - ref["DD"]) <= REL_TIGHT * max(1.0, abs(ref["DD"])), (K, N)
+                assert np.allclose(out["discel"], ref["discel"], rtol=1e-7, atol=1e-8), (K, N)
+                assert np.allclose(md, ref["ddmin"] - 1.0, rtol=0, atol=1e-11)
+                assert np.allclose(nrefl, ref["refl"], rtol=1e-7, atol=1e-10)
+            if N > 300:
+                # host pass over a view that starts at an odd row: 8-byte aligned rows when P + 1 is odd
+                eng.set_reflections(refl)
+                out2 = eng.kmeans_pass_host(np.ascontiguousarray(x[1:]))
+                ref2 = O.kmeans_pass(x[1:], refl, raas)
+                if np.array_equal(eng.last_assignment()[0], ref2["idx"]):
+                    assert np.array_equal(out2["cardd"], ref2["cardd"]), (K, N)
+                    assert np.allclose(out2["cells"], ref2["cells"], rtol=REL_TIGHT, atol=1e-9), (K, N)
+                assert abs(out2["DD"] - ref2["DD"]) <= 1e-7 * max(1.0, abs(ref2["DD"]))
+
+
+def test_fused_mid_pass_equals_two_kernel_pass(built_lib, monkeypatch):
+    """The fused sweep and the search + sorted-cell-sums pass (ECOZ2_VQ_MID_MAXK=0) give the same
+    learn: pass counts, DD trace, codebooks (3M frames, several chunks of the host pass too)."""
+    import importlib
+    import subprocess
+    import sys
+    import os
+    code = r'''
+import sys, numpy as np
+sys.path.insert(0, %r)
+from ecoz2rs_b200 import vq
+from ecoz2rs_b200.synth import ar_mix
+x = ar_mix(600_000, 36, seed=9)
+with vq.VqEngine(36, max_M=128) as eng:
+    eng.set_frames(x)
+    eng.codebook_initial()
+    st, tr = eng.learn(eps=0.05, stop_M=128)
+    eng.set_reflections(st[-2]["refl"]); eng.grow()
+    h = eng.kmeans_pass_host(x)
+np.savez(sys.argv[1], passes=[s["passes"] for s in st], dd=[t[2] for t in tr], refl=st[-1]["refl"],
+         hcells=h["cells"], hcardd=h["cardd"], hDD=h["DD"])
+''' % os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    import tempfile
+    outs = []
+    for maxk in ("128", "0"):
+        with tempfile.TemporaryDirectory() as td:
+            env = dict(os.environ, ECOZ2_VQ_MID_MAXK=maxk)
+            subprocess.run([sys.executable, "-c", code, os.path.join(td, "o.npz")], check=True, env=env)
+            outs.append({k: v.copy() for k, v in np.load(os.path.join(td, "o.npz")).items()})
+    a, b = outs
+    assert np.array_equal(a["passes"], b["passes"])
+    assert np.allclose(a["dd"], b["dd"], rtol=1e-11, atol=0)
+    assert np.allclose(a["refl"], b["refl"], rtol=1e-9, atol=1e-12)
+    assert np.array_equal(a["hcardd"], b["hcardd"])
+    assert np.allclose(a["hcells"], b["hcells"], rtol=1e-11, atol=1e-9)
+    assert abs(float(a["hDD"]) - float(b["hDD"])) <= 1e-11 * abs(float(b["hDD"]))
