@@ -4,7 +4,7 @@ import sys
 
 import numpy as np
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))))
 from ecoz2rs_b200 import vq
 from ecoz2rs_b200.synth import ar_mix
 from oracle import oracle as O
