@@ -7,9 +7,10 @@ Metric: frame x codeword evaluations per second of a k-means pass of `vq learn`
 (search + cell accumulation + allreduce + centroid update), P = 36.
 
   N = 1 : BASELINE.json configs[1]: 10M synthetic frames, codebook at K = 2048.
-  N > 1 : configs[2]: the same 10M frames sharded over N B200s (strong scaling),
-          K = 4096, one NCCL allreduce of the packed cell sums per pass.
-          Launched by torchrun, one rank per GPU.
+  N > 1 : configs[2]: the SAME 10M frames (one global stream, rank r takes the block the library's
+          sharding rule gives it) over N B200s (strong scaling), K = 4096, one NCCL allreduce of the
+          packed cell sums per pass.  Launched by torchrun, one rank per GPU.  After the timed
+          region rank 0 repeats the whole learn on one GPU and reports `multirank_parity`.
 
 A step is ONE k-means pass over all frames.  `value` is measured with the frames
 already resident in HBM; `e2e` is the same pass through the C-ABI with HOST
@@ -180,8 +181,8 @@ class ClockSampler:
 _PASS_RE = re.compile(r"\(pass=(\d+)\) min processing took ([0-9.]+)s")
 
 
-def time_reference_passes(prd_path: str, base_cbook: str, K: int, n_passes: int, cwd: str,
-                          threads: int, timeout_s: float = 900.0):
+def time_reference_passes(prd_paths, base_cbook: str, K: int, n_passes: int, cwd: str,
+                          threads: int, timeout_s: float = 1500.0):
     """Run the reference `vq.learn` (built for stop size K) from a base codebook of
     size K/2 with eps = 0 (never converges) and collect the first `n_passes`
     '(pass=i) min processing took' times of its OpenMP assign loop
@@ -192,7 +193,7 @@ def time_reference_passes(prd_path: str, base_cbook: str, K: int, n_passes: int,
         raise RuntimeError(f"{exe} not built (oracle/_ref)")
     env = dict(os.environ, OMP_NUM_THREADS=str(threads))
     shell = 'ulimit -s unlimited 2>/dev/null || ulimit -s $(ulimit -H -s); exec "$@"'
-    cmd = ["bash", "-c", shell, "bash", exe, "-B", base_cbook, "-e", "0", prd_path]
+    cmd = ["bash", "-c", shell, "bash", exe, "-B", base_cbook, "-e", "0"] + list(prd_paths)
     proc = subprocess.Popen(cmd, cwd=cwd, env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT,
                             text=True, start_new_session=True)
     times, t0 = [], time.time()
@@ -214,18 +215,31 @@ def time_reference_passes(prd_path: str, base_cbook: str, K: int, n_passes: int,
     return times
 
 
-def reference_sample_run(sample: np.ndarray, base_refl: np.ndarray, K: int, n_passes: int):
-    """-> (per-pass seconds, threads used)"""
+REF_SHARD = 1_000_000   # frames per `.prd` file: the reference's new_matrix overflows above ~7M
+
+
+def reference_sample_run(sample, base_refl: np.ndarray, K: int, n_passes: int):
+    """sample: float64 [n, D] frames (numpy, or a torch tensor on any device) -> written as `.prd`
+    shards of at most 1M frames on tmpfs, concatenated by the reference in argument order
+    (vq_learn.i:198-217).  -> (per-pass seconds, threads used)"""
     from ecoz2rs_b200 import formats
-    tmp = tempfile.mkdtemp(prefix="ecoz2ref_")
+    base = "/dev/shm" if os.path.isdir("/dev/shm") else None
+    tmp = tempfile.mkdtemp(prefix="ecoz2ref_", dir=base)
     try:
-        prd = os.path.join(tmp, "TRAIN", "_", "sample.prd")
-        formats.write_prd(prd, sample, "_")
+        paths = []
+        n = len(sample)
+        for k, a in enumerate(range(0, n, REF_SHARD)):
+            part = sample[a:a + REF_SHARD]
+            if not isinstance(part, np.ndarray):
+                part = part.cpu().numpy()
+            prd = os.path.join(tmp, "TRAIN", "_", f"part_{k:05d}.prd")
+            formats.write_prd(prd, part, "_")
+            paths.append(prd)
         cb = os.path.join(tmp, "base.cbook")
         formats.write_cbook(cb, base_refl, "_")
         threads = os.cpu_count() or 1
         while True:
-            times = time_reference_passes(prd, cb, K, n_passes, tmp, threads)
+            times = time_reference_passes(paths, cb, K, n_passes, tmp, threads)
             if times or threads == 1:
                 return times, threads
             threads = max(1, threads // 2)   # per-thread stack arrays did not fit: retry smaller
@@ -233,20 +247,47 @@ def reference_sample_run(sample: np.ndarray, base_refl: np.ndarray, K: int, n_pa
         shutil.rmtree(tmp, ignore_errors=True)
 
 
+def reference_frames(n: int):
+    """The first n frames of the global stream the b200 arm runs on (torch on the GPU when there is
+    one: the same generator, the same data); numpy ar_mix otherwise (same mixture, own stream)."""
+    try:
+        import torch
+        if torch.cuda.is_available():
+            from ecoz2rs_b200.synth import ar_mix_torch_range
+            out = np.empty((n, D), dtype=np.float64)
+            for a in range(0, n, REF_SHARD):
+                b = min(n, a + REF_SHARD)
+                out[a:b] = ar_mix_torch_range(a, b, P, seed=SEED, device="cuda").cpu().numpy()
+            return out, "global stream of the b200 arm (torch generator on the GPU)"
+    except Exception as e:
+        log(f"[reference] torch generator unavailable ({e!r}); numpy ar_mix")
+    from ecoz2rs_b200.synth import ar_mix
+    return ar_mix(n, P, seed=SEED), "numpy ar_mix (same mixture, own random stream)"
+
+
 def run_reference_arm(args):
-    """rank 0 only: the reference's CPU implementation on a bounded sample."""
+    """rank 0 only: the reference's CPU implementation (OpenMP learn_par, all host threads) on the
+    arm's own workload: as many of the 10M frames per step as fit the time budget (all of them at
+    K = 2048 on a 16-thread host)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from ecoz2rs_b200.synth import ar_mix
     from oracle import refbuild
     K = args.codebook or (2048 if args.gpus == 1 else 4096)
     if not refbuild.available(K):
         emit_line({"impl": "reference", "unavailable": "oracle/_ref not built (no /root/reference at build time)"})
         return
-    n_sample = args.ref_sample
-    log(f"[reference] generating {n_sample} sample frames (numpy) ...")
-    sample = ar_mix(n_sample, P, seed=SEED)
+    threads = os.cpu_count() or 1
+    n_passes = args.warmup + args.steps
+    if args.ref_sample > 0:
+        n_sample = min(args.ref_sample, args.frames)
+    else:
+        # ~1.6e8 evals/s per host thread (measured round 1: 2.6e9 on 16 threads); whole run within the budget
+        est_rate = 1.6e8 * threads
+        fit = int(args.ref_budget_s * est_rate / (K * n_passes))
+        n_sample = max(REF_SHARD, min(args.frames, fit // REF_SHARD * REF_SHARD))
+    log(f"[reference] generating {n_sample} frames ...")
+    sample, how = reference_frames(n_sample)
     # base codebook of size K/2: the reference's own LBG on a 100k-frame subset (setup, untimed)
     log("[reference] base codebook: reference LBG 2 -> K/2 on a 100k-frame subset (untimed setup)")
     from ecoz2rs_b200 import formats
@@ -260,7 +301,6 @@ def run_reference_arm(args):
         _, base_refl = formats.read_cbook(os.path.join(tmp, "data", "codebooks", "_", f"eps_{EPS:g}_M_{K // 2:04d}.cbook"))
     finally:
         shutil.rmtree(tmp, ignore_errors=True)
-    n_passes = args.warmup + args.steps
     log(f"[reference] timing {n_passes} passes at K={K} on {n_sample} frames ...")
     times, threads = reference_sample_run(sample, base_refl, K, n_passes)
     timed = times[args.warmup:]
@@ -271,14 +311,17 @@ def run_reference_arm(args):
     # the reference prints 2 decimals: guard against a zero reading
     total = max(total, 0.005 * len(timed))
     value = n_sample * K * len(timed) / total
+    full = n_sample == args.frames
     line = {
         "impl": "reference", "metric": "frame x codeword evals/sec per k-means pass",
         "value": value, "unit": "evals/s", "n_gpus": args.gpus, "steps": len(timed),
         "warmup": args.warmup, "ms_per_step": total / len(timed) * 1e3, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"vq learn P=36 k-means pass at K={K}: reference C learn_par on host cores, "
-                               f"bounded sample of {n_sample} of the 10M synthetic frames per step",
-                   "P": P, "K": K, "frames_per_step": n_sample, "epsilon": 0.0},
+                               + (f"all {n_sample} synthetic frames per step in {REF_SHARD}-frame .prd shards"
+                                  if full else f"bounded sample of {n_sample} of the {args.frames} synthetic frames per step"),
+                   "P": P, "K": K, "frames": args.frames, "frames_per_step": n_sample, "epsilon": 0.0,
+                   "frames_source": how},
         "cpu_baseline": {"value": value, "unit": "evals/s", "cores": threads, "kind": "reference",
                          "sample": f"{len(timed)} passes of vq.learn (OpenMP learn_par assign loop) at K={K} on "
                                    f"{n_sample} frames, times from its own '(pass=i) min processing took' lines"},
@@ -326,12 +369,191 @@ def measured_peaks():
 
 
 # ------------------------------------------------------------------------------------
+# untimed extras of the N = 1 line: the other single-GPU configurations of BASELINE.json at full size
+def _cfg4_quantize(dev, local_rank, refl_2048, n_frames=50_000_000):
+    """configs[3]: vq quantize of 50M frames against a 4096-codeword P=36 codebook -> u16 symbols."""
+    import torch
+    from ecoz2rs_b200 import formats, vq
+    from ecoz2rs_b200.synth import ar_mix_torch_range
+    out = {"workload": f"vq quantize {n_frames} frames, K=4096, P=36 -> u16 symbols (configs[3])"}
+    xd = ar_mix_torch_range(0, n_frames, P, seed=20260104, device=dev)
+    with vq.VqEngine(P, max_M=4096, devices=(local_rank,)) as eng:
+        eng.set_frames_device(xd.data_ptr(), n_frames)
+        # the codebook: split of the converged 2048-codeword codebook, refined on these frames
+        eng.set_reflections(refl_2048)
+        eng.grow()
+        st, _ = eng.learn(eps=EPS, stop_M=4096)
+        refl = st[-1]["refl"]
+        eng.set_reflections(refl)
+        seq_h = torch.empty(n_frames, dtype=torch.int16, pin_memory=True)
+        eng.quantize_resident_ptr(seq_h.data_ptr())
+        torch.cuda.synchronize()
+        eng.counters_reset()
+        t0 = time.perf_counter()
+        reps = 3
+        for _ in range(reps):
+            avg = eng.quantize_resident_ptr(seq_h.data_ptr())
+        torch.cuda.synchronize()
+        dt = (time.perf_counter() - t0) / reps
+        c = eng.counters()
+        out["resident"] = {"ms": dt * 1e3, "evals_per_s": n_frames * 4096 / dt, "avg_distortion": avg,
+                           "search_kernel_ms": c["search_main_ms"] / max(1, c["search_main_launches"]),
+                           "rechecked_frac": c["rechecked"] / (reps * float(n_frames)),
+                           "d2h_bytes": 2 * n_frames}
+        seq_res = seq_h.numpy().copy()
+        # host frames (pinned) -> symbols on the host: 14.8 GB over PCIe inside the timed region
+        try:
+            xh = torch.empty((n_frames, D), dtype=torch.float64, pin_memory=True)
+            xh.copy_(xd)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            avg2 = eng.quantize_ptr(xh.data_ptr(), n_frames, seq_h.data_ptr())
+            dt2 = time.perf_counter() - t0
+            out["host_to_seq"] = {"ms": dt2 * 1e3, "evals_per_s": n_frames * 4096 / dt2,
+                                  "h2d_bytes": n_frames * D * 8, "d2h_bytes": 2 * n_frames,
+                                  "symbols_equal_resident": bool(np.array_equal(seq_h.numpy(), seq_res)),
+                                  "avg_distortion": avg2}
+            sample = xh[:100_000].numpy().copy()
+            del xh
+        except Exception as e:
+            out["host_to_seq"] = {"error": repr(e)}
+            sample = xd[:100_000].cpu().numpy()
+    del xd
+    torch.cuda.empty_cache()
+    # CPU baseline: the reference's single-threaded vq.quantize (quantize.c:14-30) on a 100k-frame shard
+    try:
+        from oracle import refbuild
+        if refbuild.available(4096):
+            tmp = tempfile.mkdtemp(prefix="ecoz2q_")
+            try:
+                prd = os.path.join(tmp, "TRAIN", "_", "q.prd")
+                formats.write_prd(prd, sample, "_")
+                cb = os.path.join(tmp, "q.cbook")
+                formats.write_cbook(cb, refl, "_")
+                t0 = time.perf_counter()
+                r = refbuild.run_vq_quantize(cb, [prd], tmp)
+                dtq = time.perf_counter() - t0
+                if r["returncode"] == 0:
+                    seq_ref = np.frombuffer(open(os.path.join(tmp, "data", "sequences", "TRAIN", "M4096", "_", "q.seq"),
+                                                 "rb").read(), "<u2", offset=120)
+                    out["cpu_baseline"] = {"value": len(sample) * 4096 / dtq, "unit": "evals/s", "cores": 1,
+                                           "kind": "reference",
+                                           "sample": f"reference vq.quantize (serial) on the first {len(sample)} frames, "
+                                                     "wall time of the executable incl. file i/o",
+                                           "symbols_differing_from_gpu": int((seq_ref != seq_res[:len(sample)].view(np.uint16)).sum())}
+            finally:
+                shutil.rmtree(tmp, ignore_errors=True)
+    except Exception as e:
+        out["cpu_baseline"] = {"error": repr(e)}
+    return out
+
+
+def _cfg5_learn_p12(dev, local_rank, n_frames=20_000_000):
+    """configs[4]: vq learn P=12, 2 -> 1024 on 20M frames (the bandwidth-bound case)."""
+    import torch
+    from ecoz2rs_b200 import vq
+    from ecoz2rs_b200.synth import ar_mix_torch_range
+    P5 = 12
+    xd = ar_mix_torch_range(0, n_frames, P5, seed=20260105, device=dev)
+    with vq.VqEngine(P5, max_M=1024, devices=(local_rank,)) as eng:
+        eng.set_frames_device(xd.data_ptr(), n_frames)
+        del xd
+        torch.cuda.empty_cache()
+        eng.codebook_initial()
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        st, tr = eng.learn(eps=EPS, stop_M=1024)
+        wall = time.perf_counter() - t0
+    row_bytes = (P5 + 1) * 8
+    stages = []
+    for s_ in st:
+        ms = s_["stage_seconds"] * 1e3
+        passes = s_["passes"] + 1          # + the inertia sweep of the stage
+        stages.append({"M": s_["M"], "passes": s_["passes"], "stage_ms": ms,
+                       "algorithmic_hbm_gbs": n_frames * row_bytes * passes / (ms * 1e-3) / 1e9})
+    return {"workload": f"vq learn P=12, 2 -> 1024 on {n_frames} frames (configs[4])", "learn_wall_s": wall,
+            "passes": len(tr), "final_avg_distortion": st[-1]["avg_distortion"],
+            "empty_cells_last_stage": int((st[-1]["cardd"] == 0).sum()), "stages": stages,
+            "note": "algorithmic_hbm_gbs = frames x 8 (P+1) bytes x (passes + inertia sweep) / stage wall time; "
+                    "K <= 16 is the HBM-bound regime (SURVEY 8d), hbm_gbs of MEASURED_PEAKS.json is the roofline"}
+
+
+def _dropin_cfg2(dev, n_frames, stop_M):
+    """Wall time of the drop-in entry point `ecoz2_vq_learn` (what the Rust crate calls) on configs[1]:
+    `.prd` shards on tmpfs in, `.cbook` / report files out, with and without `min_dists.csv`."""
+    from ecoz2rs_b200 import formats, vq
+    from ecoz2rs_b200.synth import ar_mix_torch_range
+    base = "/dev/shm" if os.path.isdir("/dev/shm") else None
+    need = n_frames * D * 8 + 14 * n_frames * 20          # shards + ~11 stages of min_dists lines
+    if base and shutil.disk_usage(base).free < 1.3 * need:
+        return {"skipped": f"tmpfs has less than {1.3 * need / 1e9:.1f} GB free"}
+    tmp = tempfile.mkdtemp(prefix="ecoz2dropin_", dir=base)
+    out = {"workload": f"ecoz2_vq_learn P=36, 2 -> {stop_M} on {n_frames} frames from .prd shards on tmpfs (configs[1])"}
+    cwd = os.getcwd()
+    saved = {k: os.environ.get(k) for k in ("ECOZ2_VQ_MAX_M", "ECOZ2_VQ_MIN_DISTS")}
+    try:
+        files = []
+        t0 = time.perf_counter()
+        for k, a in enumerate(range(0, n_frames, REF_SHARD)):
+            b = min(n_frames, a + REF_SHARD)
+            f = os.path.join(tmp, "predictors", "TRAIN", "cfg2", f"part_{k:05d}.prd")
+            formats.write_prd(f, ar_mix_torch_range(a, b, P, seed=SEED, device=dev).cpu().numpy(), "cfg2")
+            files.append(f)
+        out["prd_write_s"] = time.perf_counter() - t0
+        os.environ["ECOZ2_VQ_MAX_M"] = str(stop_M)
+        for label, md in (("with_min_dists", "1"), ("without_min_dists", "0")):
+            wd = os.path.join(tmp, "run_" + label)
+            os.makedirs(wd)
+            os.chdir(wd)
+            os.environ["ECOZ2_VQ_MIN_DISTS"] = md
+            stages = []
+            t0 = time.perf_counter()
+            rc = vq.vq_learn(P, EPS, "cfg2", files, callback=lambda M, a_, s_, i_: stages.append((M, a_)))
+            wall = time.perf_counter() - t0
+            os.chdir(cwd)
+            sizes = sum(os.path.getsize(os.path.join(dp, fn)) for dp, _, fns in os.walk(wd) for fn in fns)
+            out[label] = {"wall_s": wall, "rc": rc, "stages": len(stages), "bytes_written": sizes,
+                          "final_avg_distortion": stages[-1][1] if stages else None}
+            shutil.rmtree(wd, ignore_errors=True)
+        a, b = out["with_min_dists"]["wall_s"], out["without_min_dists"]["wall_s"]
+        out["reports_overhead_ratio"] = a / b if b > 0 else None
+    finally:
+        os.chdir(cwd)
+        for k, v in saved.items():
+            if v is None:
+                os.environ.pop(k, None)
+            else:
+                os.environ[k] = v
+        shutil.rmtree(tmp, ignore_errors=True)
+    return out
+
+
+def measure_extra_configs(args, dev, local_rank, refl_2048, stages):
+    import torch
+    res = {}
+    for name, fn in (("cfg4_quantize_50M_K4096", lambda: _cfg4_quantize(dev, local_rank, refl_2048)),
+                     ("cfg5_learn_P12_20M", lambda: _cfg5_learn_p12(dev, local_rank)),
+                     ("dropin_cfg2", lambda: _dropin_cfg2(dev, args.frames, stages[-1]["M"]))):
+        t0 = time.time()
+        try:
+            log(f"[extras] {name} ...")
+            # file-level entry points print the reference's progress lines on stdout: keep them off the JSON line
+            res[name] = fn()
+        except Exception as e:
+            res[name] = {"error": repr(e)}
+        res[name]["measured_in_s"] = time.time() - t0
+        torch.cuda.empty_cache()
+    return res
+
+
+# ------------------------------------------------------------------------------------
 def run_b200_arm(args):
     import torch
     import torch.distributed as dist
 
     from ecoz2rs_b200 import vq
-    from ecoz2rs_b200.synth import ar_mix_torch
+    from ecoz2rs_b200.sharding import shard_range
+    from ecoz2rs_b200.synth import ar_mix_torch_range
 
     world = int(os.environ.get("WORLD_SIZE", "1"))
     rank = int(os.environ.get("RANK", "0"))
@@ -348,9 +570,8 @@ def run_b200_arm(args):
 
     K = args.codebook or (2048 if world == 1 else 4096)
     n_total = args.frames
-    per = (n_total + world - 1) // world
-    lo = min(rank * per, n_total)
-    n_local = min(per, n_total - lo)
+    lo, hi = shard_range(n_total, rank, world)      # the library's own sharding rule
+    n_local = hi - lo
 
     def barrier():
         torch.cuda.synchronize()
@@ -369,12 +590,12 @@ def run_b200_arm(args):
     log(f"[rank {rank}] measured FP32 FFMA peak {ffma_peak:.1f} TFLOP/s (nominal {NOMINAL_FP32_TFLOPS:.1f})")
 
     t0 = time.time()
-    xd = ar_mix_torch(n_local, P, seed=SEED, device=dev, stream_id=rank)
+    xd = ar_mix_torch_range(lo, hi, P, seed=SEED, device=dev)   # this rank's slice of ONE global stream
     torch.cuda.synchronize()
-    log(f"[rank {rank}] {n_local} synthetic frames generated on device in {time.time() - t0:.1f}s")
+    log(f"[rank {rank}] frames [{lo}, {hi}) of the global stream generated on device in {time.time() - t0:.1f}s")
 
     tc_mode = args.mode == "tf32x3"
-    eng = vq.VqEngine(P, max_M=K, devices=(local_rank,),
+    eng = vq.VqEngine(P, max_M=max(K, 4096) if world == 1 else K, devices=(local_rank,),
                       mode=vq.MODE_TF32X3 if tc_mode else vq.MODE_FP32)
     if world > 1:
         ids = [vq.nccl_unique_id() if rank == 0 else None]
@@ -447,19 +668,73 @@ def run_b200_arm(args):
             barrier()
             t0 = time.perf_counter()
         eng.set_reflections(refl_now)                      # H2D codebook
-        if world == 1:
-            # H2D of the step's frames in chunks, each searched while the next one uploads;
-            # D2H cells, counts, distortions, DD
-            out = eng.kmeans_pass_host_ptr(xh.data_ptr(), n_local, want_cells=True)
-        else:
-            eng.set_frames_ptr(xh.data_ptr(), n_local)     # H2D of the step's frames (+ f32 staging)
-            out = eng.kmeans_pass(want_cells=True)         # D2H cells, counts, distortions, DD
+        # H2D of the step's frames (this rank's block) in chunks, each searched while the next one
+        # uploads; allreduce; D2H cells, counts, distortions, DD
+        out = eng.kmeans_pass_host_ptr(xh.data_ptr(), n_local, want_cells=True)
         new_refl, new_raas = eng.codebook()                # D2H updated codebook
     barrier()
     e2e_wall = max_over_ranks(time.perf_counter() - t0)
     e2e_value = n_total * K * e2e_steps / e2e_wall
     h2d = n_local * D * 8 + K * D * 8
     d2h = K * D * 8 + K * 8 * 2 + 16 + 2 * K * D * 8
+
+    # ---- N = 1: the same pass at K = 4096, the codebook size the N > 1 lines run (configs[2]), so that
+    # a 1 -> N efficiency can be formed from equal work
+    value_k4096 = None
+    if world == 1 and K < 4096 and not args.no_extras:
+        try:
+            # (the frames are resident since the e2e steps) split of the converged K-codeword codebook
+            eng.set_reflections(refl_K)
+            while eng.K < 4096:
+                eng.grow()
+            for _ in range(args.warmup):
+                eng.kmeans_pass(want_cells=False)
+            barrier()
+            t4 = time.perf_counter()
+            for _ in range(args.steps):
+                eng.kmeans_pass(want_cells=False)
+            barrier()
+            w4 = time.perf_counter() - t4
+            value_k4096 = {"K": 4096, "value": n_total * 4096 * args.steps / w4, "unit": "evals/s",
+                           "ms_per_step": w4 / args.steps * 1e3, "steps": args.steps,
+                           "note": "same 10M frames, K = 4096 (the codebook size of the N > 1 lines), 1 GPU"}
+            eng.set_reflections(refl_K)
+        except Exception as e:
+            log(f"[value_k4096] failed: {e!r}")
+
+    # ---- N > 1: does the sharded learn reproduce the single-GPU learn?  Rank 0 repeats the whole LBG
+    # run 2 -> K on ALL frames of the same global stream with a second, single-GPU engine (untimed)
+    multirank_parity = None
+    if world > 1:
+        if rank == 0:
+            try:
+                t1 = time.time()
+                x_all = ar_mix_torch_range(0, n_total, P, seed=SEED, device=dev)
+                with vq.VqEngine(P, max_M=K, devices=(local_rank,),
+                                 mode=vq.MODE_TENSOR if tc_mode else vq.MODE_FP32) as e1:
+                    e1.set_frames_device(x_all.data_ptr(), n_total)
+                    del x_all
+                    torch.cuda.empty_cache()
+                    e1.codebook_initial()
+                    st1, tr1 = e1.learn(eps=EPS, stop_M=K)
+                same = [(s["M"], s["passes"]) for s in st1] == [(s["M"], s["passes"]) for s in stages]
+                dd = max((abs(a[2] - b[2]) / abs(b[2]) for a, b in zip(trace, tr1)), default=0.0) if same else None
+                rf = None
+                if same:
+                    rf = 0.0
+                    for a, b in zip(stages, st1):
+                        sc = np.maximum(np.abs(b["refl"]).max(axis=1, keepdims=True), 1e-300)
+                        rf = max(rf, float(np.max(np.abs(a["refl"] - b["refl"]) / sc)))
+                multirank_parity = {"passes_equal": bool(same), "max_rel_dd_diff": dd, "max_rel_refl_diff": rf,
+                                    "stages": len(st1), "passes": len(tr1),
+                                    "single_gpu_learn_wall_s": time.time() - t1,
+                                    "what": f"LBG 2 -> {K} on the same {n_total} frames: {world} ranks (NCCL allreduce "
+                                            "per pass) against one GPU; per-pass DD and every stage's reflections"}
+                log(f"[multirank_parity] {multirank_parity}")
+            except Exception as e:
+                log(f"[multirank_parity] failed: {e!r}")
+                multirank_parity = {"error": repr(e)}
+        barrier()
 
     # ---- vq quantize of the same frames against the K-codeword codebook: resident
     # frames -> u16 symbols + average distortion on the host; then host frames in, symbols out
@@ -582,10 +857,11 @@ def run_b200_arm(args):
         roofline = {
             "bound": "tensor",
             "kernel": f"vq_assign_tc2 (tcgen05 kind::{fmt} two-way split distortion + fused argmin)",
-            "achieved": achieved, "peak": peak, "unit": "TFLOP/s", "frac": achieved / peak,
-            "peak_source": f"{src}: cuBLAS bf16 sustained {bf16_sus:.1f} TFLOP/s x {rate} ({fmt} rate) / 3 "
-                           "(three tensor MMAs per product); the kernel is timed inside a long step",
-            "peak_burst": peak_burst, "frac_of_burst": achieved / peak_burst,
+            # the timed region lasts ~0.1 s: the BURST figure is the denominator; sustained is secondary
+            "achieved": achieved, "peak": peak_burst, "unit": "TFLOP/s", "frac": achieved / peak_burst,
+            "peak_source": f"{src}: cuBLAS bf16 burst {peaks['bf16_tflops']:.1f} TFLOP/s x {rate} ({fmt} rate) / 3 "
+                           "(three tensor MMAs per product); the timed region is a fraction of a second",
+            "peak_sustained": peak, "frac_of_sustained": achieved / peak,
             "operand_format": fmt, "tensor_flops_issued_per_eval": issued_per_eval,
             "tensor_tflops_issued": issued / (main_ms * 1e-3) / 1e12 if main_ms > 0 else 0.0,
             "tensor_frac_of_sustained": (issued / (main_ms * 1e-3) / 1e12) / (bf16_sus * rate) if main_ms > 0 else None,
@@ -607,7 +883,7 @@ def run_b200_arm(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         try:
             from oracle import refbuild
-            ns = min(args.ref_sample, n_local)
+            ns = min(args.ref_sample if args.ref_sample > 0 else 2_000_000, n_local)
             if refbuild.available(K) and base_refl is not None:
                 times, threads = reference_sample_run(xh[:ns].numpy(), base_refl, K, 3)
                 timed = times[1:] if len(times) > 1 else times
@@ -628,6 +904,14 @@ def run_b200_arm(args):
                                 "sample": f"oracle orc_assign (OpenMP) on {ns} frames at K={K}"}
         except Exception as e:  # the baseline must never take the GPU result down with it
             log(f"[cpu_baseline] failed: {e!r}")
+
+    # ---- untimed extras (N = 1): BASELINE.json configs 4 and 5 at full size, drop-in wall time of config 2
+    extra_configs = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        eng.close()                      # frees the 10M-frame engine (4.5 GB) before the 50M-frame one
+        del xh
+        torch.cuda.empty_cache()
+        extra_configs = measure_extra_configs(args, dev, local_rank, refl_K, stages)
 
     if rank == 0:
         line = {
@@ -658,6 +942,11 @@ def run_b200_arm(args):
             "learn_evals_per_s": learn_ctr["evals"] * world / learn_wall,
             "quantize": quantize_info,
             "lpc_front": lpc_info,
+            "value_k4096": value_k4096,
+            "multirank_parity": multirank_parity,
+            "audit": {"every": int(os.environ.get("ECOZ2_VQ_AUDIT", "0") or 0), "audited": int(ctr["audited"]),
+                      "index_differs": int(ctr["audit_idx_diff"]), "audit_mismatches": int(ctr["audit_mismatches"])},
+            "configs": extra_configs,
         }
         emit_line(line)
     eng.close()
@@ -674,8 +963,12 @@ def main():
     ap.add_argument("--frames", type=int, default=N_FRAMES)
     ap.add_argument("--codebook", type=int, default=0, help="K (default 2048 at 1 GPU, 4096 otherwise)")
     ap.add_argument("--e2e-steps", type=int, default=6)
-    ap.add_argument("--ref-sample", type=int, default=1_000_000)
+    ap.add_argument("--ref-sample", type=int, default=0,
+                    help="frames per step of the reference arm / cpu_baseline (0: as many of --frames as fit --ref-budget-s)")
+    ap.add_argument("--ref-budget-s", type=float, default=240.0)
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true",
+                    help="skip the untimed extra measurements (value_k4096, configs 4 / 5, drop-in wall time)")
     ap.add_argument("--mode", default="tf32x3", choices=["tf32x3", "fp32"],
                     help="search arithmetic of the b200 arm (both end in the FP64 re-evaluation)")
     args = ap.parse_args()

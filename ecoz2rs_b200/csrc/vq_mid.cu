@@ -480,15 +480,11 @@ static int mid_raw_depth(int D, int BN) {
     return n;
 }
 static int mid_max_k() {
-    static int v = -1;
-    if (v < 0) {
-        // experimental, off by default: on B200 the fused sweep does not beat search + sorted cell sums yet
-        // (see DESIGN.md); ECOZ2_VQ_MID_MAXK=128 switches it on for 9 <= K <= 128
-        const char *e = getenv("ECOZ2_VQ_MID_MAXK");
-        v = e ? atoi(e) : 0;
-        if (v > 128) v = 128;
-    }
-    return v;
+    // experimental, off by default: on B200 the fused sweep does not beat search + sorted cell sums yet
+    // (see DESIGN.md); ECOZ2_VQ_MID_MAXK=128 switches it on for 9 <= K <= 128 (read at every pass)
+    const char *e = getenv("ECOZ2_VQ_MID_MAXK");
+    int v = e ? atoi(e) : 0;
+    return v > 128 ? 128 : v;
 }
 
 bool pass_mid_supported(int K, int D) {

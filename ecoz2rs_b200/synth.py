@@ -105,3 +105,31 @@ def ar_mix_torch(N: int, P: int, C: int = DEFAULT_CENTRES, seed: int = 0,
         k = torch.clamp(torch.tanh(g), -0.98, 0.98)
         out[lo:lo + n] = _inverse_levinson(k, torch)
     return out
+
+
+def ar_mix_torch_range(lo: int, hi: int, P: int, C: int = DEFAULT_CENTRES, seed: int = 0, device="cuda",
+                       chunk: int = 1 << 20):
+    """Frames [lo, hi) of ONE global stream (torch back end): the stream is defined chunk by chunk
+    (chunk c = frames [c * chunk, (c + 1) * chunk), its own generator seeded by (seed, c)), so any
+    rank can produce exactly its slice and the union over the ranks of a multi-GPU run is the
+    single-GPU data set.  float64 [hi - lo, P+1] on `device`."""
+    import torch
+
+    rng = np.random.default_rng(seed)
+    sig_np = _sigma(P)
+    centres = torch.from_numpy(rng.normal(size=(C, P)) * sig_np).to(device)
+    sig = torch.from_numpy(sig_np).to(device)
+    out = torch.empty((max(hi - lo, 0), P + 1), dtype=torch.float64, device=device)
+    gen = torch.Generator(device=device)
+    for c in range(lo // chunk, (max(hi, lo + 1) - 1) // chunk + 1):
+        a, b = max(lo, c * chunk), min(hi, (c + 1) * chunk)
+        if a >= b:
+            continue
+        gen.manual_seed(int(seed) * 1000003 + 7919 * c + 1)
+        labels = torch.randint(0, C, (chunk,), generator=gen, device=device)
+        noise = torch.randn((chunk, P), generator=gen, device=device, dtype=torch.float64)
+        sl = slice(a - c * chunk, b - c * chunk)
+        g = centres[labels[sl]] + 0.3 * sig * noise[sl]
+        k = torch.clamp(torch.tanh(g), -0.98, 0.98)
+        out[a - lo:b - lo] = _inverse_levinson(k, torch)
+    return out

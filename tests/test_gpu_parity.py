@@ -418,13 +418,15 @@ def test_runtime_audit_counts(built_lib, frames36, oracle_run36, monkeypatch):
 
 
 @pytest.mark.parametrize("P", [36, 12, 20])
-def test_fused_mid_codebook_pass_edges(built_lib, P):
-    """vq_pass_mid (8 < K <= 128: tensor-core search + cell sums in one sweep over the FP64 frames):
+def test_fused_mid_codebook_pass_edges(built_lib, P, monkeypatch):
+    """vq_pass_mid (experimental, ECOZ2_VQ_MID_MAXK=128; 8 < K <= 128: tensor-core search + cell sums in
+    one sweep over the FP64 frames):
     single / partial / many half-tiles, ragged codebooks, frames inside the error bound (duplicate
     codewords flag EVERY frame: all rows then arrive through the fix-up), an 8-byte aligned frame
     pointer (no bulk copies), against the oracle's teacher-forced pass."""
     from ecoz2rs_b200.synth import ar_mix
     from oracle import oracle as O
+    monkeypatch.setenv("ECOZ2_VQ_MID_MAXK", "128")
     rng = np.random.default_rng(5 + P)
     xall = ar_mix(70_000, P, seed=7 + P)
     cases = [(16, 1), (16, 127), (32, 128), (20, 129), (64, 255), (64, 256), (100, 257), (128, 1000),
