@@ -107,17 +107,30 @@ void on_stage(void *c, const ecoz2b200_stage_info *info) {
     std::vector<int32_t> cw;
     std::vector<double> md;
     const double t_rep0 = wall_s();
+    bool text_done = false;
     if (ctx->min_dists) {
-        cw.resize((size_t) ctx->tot_vecs);
-        md.resize((size_t) ctx->tot_vecs);
-        if (ctx->eng->last_assignment(cw.data(), md.data())) ctx->rc = ECOZ2B200_ERR_CUDA;
+        // "<cbook>.min_dists.csv": formatted on the device (vq_report.cu), written by the report's
+        // writer thread while the next stage runs.  The engine double-buffers the text: before a
+        // new text is produced at most one older file may still be in flight.
+        ctx->report->wait_pending(1);
+        const char *text = nullptr;
+        size_t bytes = 0;
+        if (!getenv("ECOZ2_VQ_REPORT_HOST") && ctx->eng->min_dists_text(&text, &bytes) == ECOZ2B200_OK) {
+            ctx->report->min_dists_submit(ctx->cb_filename, text, bytes);
+            text_done = true;
+        } else {   // values the device formatter does not take (inf / nan): the host formatter
+            cw.resize((size_t) ctx->tot_vecs);
+            md.resize((size_t) ctx->tot_vecs);
+            if (ctx->eng->last_assignment(cw.data(), md.data())) ctx->rc = ECOZ2B200_ERR_CUDA;
+        }
     }
     const double t_rep1 = wall_s();
+    const bool host_lines = ctx->min_dists && !text_done;
     ctx->report->cbook(ctx->cb_filename, info->passes, info->avgDistortion, info->sigma,
                        info->inertia, info->M, info->cardd, info->discel,
-                       ctx->min_dists ? cw.data() : nullptr, ctx->min_dists ? md.data() : nullptr);
+                       host_lines ? cw.data() : nullptr, host_lines ? md.data() : nullptr);
     if (getenv("ECOZ2_VQ_TIMING"))
-        fprintf(stderr, "[timing] M=%d read-back %.1f ms, report files %.1f ms\n", info->M,
+        fprintf(stderr, "[timing] M=%d report text / read-back %.1f ms, report files %.1f ms\n", info->M,
                 (t_rep1 - t_rep0) * 1e3, (wall_s() - t_rep1) * 1e3);
     printf("\n");
     // name of the next size (vq_learn_par.c:152-154)
@@ -432,6 +445,47 @@ int ecoz2b200_write_min_dists_csv(const char *path, const int32_t *codeword, con
                                   long n) {
     if (!path || n < 0 || (n > 0 && (!codeword || !min_dist))) return ECOZ2B200_ERR_ARG;
     return vqb200::write_min_dists_csv(path, codeword, min_dist, n) ? ECOZ2B200_OK : ECOZ2B200_ERR_IO;
+}
+
+int ecoz2b200_debug_format_lines(const int32_t *codeword, const double *min_dist, long n, char *out,
+                                 size_t capacity, size_t *bytes) {
+    if (n < 0 || (n > 0 && (!codeword || !min_dist)) || !bytes) return ECOZ2B200_ERR_ARG;
+    *bytes = 0;
+    if (n == 0) return ECOZ2B200_OK;
+    int32_t *d_cw = nullptr;
+    double *d_md = nullptr;
+    void *d_scr = nullptr;
+    char *d_txt = nullptr;
+    int rc = ECOZ2B200_ERR_CUDA;
+    unsigned long long total = 0;
+    int bad = 0;
+    const unsigned long long *d_total;
+    const int *d_bad;
+    if (cudaMalloc(&d_cw, sizeof(int32_t) * (size_t) n) != cudaSuccess) goto done;
+    if (cudaMalloc(&d_md, sizeof(double) * (size_t) n) != cudaSuccess) goto done;
+    if (cudaMalloc(&d_scr, vqb200::format_scratch_bytes(n)) != cudaSuccess) goto done;
+    if (cudaMalloc(&d_txt, vqb200::format_text_capacity(n)) != cudaSuccess) goto done;
+    cudaMemcpy(d_cw, codeword, sizeof(int32_t) * (size_t) n, cudaMemcpyHostToDevice);
+    cudaMemcpy(d_md, min_dist, sizeof(double) * (size_t) n, cudaMemcpyHostToDevice);
+    vqb200::launch_format_lengths(d_cw, d_md, n, d_scr, 0);
+    vqb200::format_result_ptrs(d_scr, n, &d_total, &d_bad);
+    cudaMemcpy(&total, d_total, sizeof total, cudaMemcpyDeviceToHost);
+    cudaMemcpy(&bad, d_bad, sizeof bad, cudaMemcpyDeviceToHost);
+    if (bad) { rc = ECOZ2B200_ERR_ARG; goto done; }
+    *bytes = (size_t) total;
+    if (total > capacity || !out) { rc = ECOZ2B200_ERR_ARG; goto done; }
+    vqb200::launch_format_write(d_cw, d_md, n, d_scr, d_txt, 0);
+    if (cudaMemcpy(out, d_txt, (size_t) total, cudaMemcpyDeviceToHost) == cudaSuccess &&
+        cudaGetLastError() == cudaSuccess)
+        rc = ECOZ2B200_OK;
+done:
+    cudaFree(d_cw); cudaFree(d_md); cudaFree(d_scr); cudaFree(d_txt);
+    return rc;
+}
+
+int ecoz2b200_min_dists_text(ecoz2b200_engine *e, const char **text, size_t *bytes) {
+    ENG(e);
+    return eng.min_dists_text(text, bytes);
 }
 
 int ecoz2b200_tc_issued_flops_per_eval(int P, int *is_f16) {

@@ -116,6 +116,8 @@ Engine::Engine(const int *devices, int num_devices, int P, int max_M)
 }
 
 Engine::~Engine() {
+    for (char *p : h_text_)
+        if (p) cudaFreeHost(p);
     const NcclApi *api = (local_comms_ready_ || multi_process_) ? nccl_api() : nullptr;
     for (size_t i = 0; i < shards_.size(); i++) {
         Shard &s = shards_[i];
@@ -127,6 +129,7 @@ Engine::~Engine() {
         cudaFree(s.refl); cudaFree(s.raas); cudaFree(s.w32); cudaFree(s.w64); cudaFree(s.w1max); cudaFree(s.w1);
         cudaFree(s.wtc); cudaFree(s.cs_mem); cudaFree(s.packed_scratch); cudaFree(s.raas_prev);
         cudaFree(s.packed); cudaFree(s.scalars); cudaFree(s.dstat);
+        cudaFree(s.fmt_scratch); cudaFree(s.fmt_text);
         for (int b = 0; b < 2; b++) {
             QBuf &q = qbuf_[2 * i + b];
             cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
@@ -963,6 +966,74 @@ int Engine::last_assignment(int32_t *idx_out, double *mindist_out) {
                                      cudaMemcpyDeviceToHost, s.stream));
     }
     return sync_all();
+}
+
+int Engine::min_dists_text(const char **text, size_t *bytes) {
+    if (text) *text = nullptr;
+    if (bytes) *bytes = 0;
+    int rc = ensure_mindist();
+    if (rc) return rc;
+    // pass 1: line lengths and offsets on every shard
+    std::vector<unsigned long long> totals(shards_.size(), 0);
+    size_t all = 0;
+    bool bad_any = false;
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        if (s.n <= 0) continue;
+        CUDA_TRY(cudaSetDevice(s.device));
+        if (s.fmt_cap < s.n) {
+            CUDA_TRY(cudaStreamSynchronize(s.stream));
+            cudaFree(s.fmt_scratch); cudaFree(s.fmt_text);
+            s.fmt_scratch = nullptr; s.fmt_text = nullptr; s.fmt_cap = 0;
+            CUDA_TRY(cudaMalloc(&s.fmt_scratch, format_scratch_bytes(s.n)));
+            CUDA_TRY(cudaMalloc(&s.fmt_text, format_text_capacity(s.n)));
+            s.fmt_cap = s.n;
+        }
+        launch_format_lengths(s.idx, s.mindist, s.n, s.fmt_scratch, s.stream);
+        ctr_.kernel_launches += 2;
+    }
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        if (s.n <= 0) continue;
+        CUDA_TRY(cudaSetDevice(s.device));
+        const unsigned long long *d_total;
+        const int *d_bad;
+        format_result_ptrs(s.fmt_scratch, s.n, &d_total, &d_bad);
+        int bad = 0;
+        CUDA_TRY(cudaMemcpyAsync(&totals[i], d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+        bad_any = bad_any || bad != 0;
+        all += (size_t) totals[i];
+    }
+    if (bad_any) return ECOZ2B200_ERR_ARG;   // caller formats on the host (inf / nan / huge values)
+    // pass 2: the text, straight into a pinned host buffer
+    const int slot = h_text_slot_;
+    h_text_slot_ ^= 1;
+    if (h_text_cap_[slot] < all) {
+        if (h_text_[slot]) cudaFreeHost(h_text_[slot]);
+        h_text_[slot] = nullptr;
+        h_text_cap_[slot] = 0;
+        const size_t want = all + all / 8 + 4096;
+        CUDA_TRY(cudaMallocHost(&h_text_[slot], want));
+        h_text_cap_[slot] = want;
+    }
+    size_t off = 0;
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        if (s.n <= 0) continue;
+        CUDA_TRY(cudaSetDevice(s.device));
+        launch_format_write(s.idx, s.mindist, s.n, s.fmt_scratch, s.fmt_text, s.stream);
+        ctr_.kernel_launches++;
+        CUDA_TRY(cudaMemcpyAsync(h_text_[slot] + off, s.fmt_text, (size_t) totals[i], cudaMemcpyDeviceToHost, s.stream));
+        off += (size_t) totals[i];
+    }
+    rc = sync_all();
+    if (rc) return rc;
+    CUDA_TRY(cudaGetLastError());
+    if (text) *text = h_text_[slot];
+    if (bytes) *bytes = all;
+    return ECOZ2B200_OK;
 }
 
 // ---------------------------------------------------------------------------------

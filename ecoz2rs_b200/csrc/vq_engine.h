@@ -69,6 +69,9 @@ struct Shard {
     double *packed_scratch = nullptr;  // same size: sink of the on-demand minDist pass
     double *raas_prev = nullptr;       // [max_M][D] codebook the last assignment was made against
     double *scalars = nullptr;  // [8] misc device scalars (sigma sum, ...)
+    void *fmt_scratch = nullptr;   // report formatter: line offsets
+    char *fmt_text = nullptr;      // report formatter: text of this shard's frames
+    long fmt_cap = 0;              // frames the two buffers above are sized for
     // device-side statistics, read only when the counters are asked for (no per-pass host sync):
     // [0] frames audited, [1] audit: index differs, [2] audit: real mis-assignment, [3] frames
     // re-evaluated in FP64
@@ -125,6 +128,11 @@ class Engine {
     int sigma(double avgDistortion, double *sigma_out);
     int inertia(double *inertia_out);
     int last_assignment(int32_t *idx_out, double *mindist_out);
+    // the lines "codeword,minDistortion\n" of the last pass's assignment (all local frames in append
+    // order) formatted ON THE DEVICE, byte for byte the reference's "%d,%f\n" (report.c:118-121); the
+    // text lands in one of two pinned host buffers owned by the engine (valid until the call after the
+    // next).  ECOZ2B200_ERR_ARG with *bytes = 0 when a value cannot be formatted there (inf / nan).
+    int min_dists_text(const char **text, size_t *bytes);
     int learn(double eps, int stop_M, ecoz2b200_stage_cb on_stage, ecoz2b200_pass_cb on_pass,
               void *ctx);
     int quantize_host(const double *x, long T, uint16_t *seq_out, double *avg);
@@ -197,6 +205,9 @@ class Engine {
     bool multi_process_ = false;
     bool local_comms_ready_ = false;
     Counters ctr_;
+    char *h_text_[2] = {nullptr, nullptr};   // pinned: report text, double buffered
+    size_t h_text_cap_[2] = {0, 0};
+    int h_text_slot_ = 0;
     std::vector<double> h_packed_;  // host mirror of the packed buffer tail / cells
     double h_count_ = 0;            // kmeans_pass_host: frames of all ranks (read back with the pass)
 };

@@ -3,6 +3,10 @@
 // every function cites the reference code whose bytes it must reproduce.
 #include "vq_io.h"
 
+#include <fcntl.h>
+#include <sys/mman.h>
+#include <unistd.h>
+
 #include <errno.h>
 #include <string.h>
 #include <sys/stat.h>
@@ -352,7 +356,96 @@ bool write_min_dists_csv(const char *name, const int32_t *codeword, const double
     return fclose(f) == 0 && ok;
 }
 
+bool write_text_file(const char *name, const char *header, const char *text, size_t bytes) {
+    const int fd = open(name, O_RDWR | O_CREAT | O_TRUNC, 0644);
+    if (fd < 0) return false;
+    const size_t hl = strlen(header);
+    const size_t total = hl + bytes;
+    bool ok = true;
+    // Large files: the copy into fresh page-cache pages is what costs, and write() / pwrite() to one
+    // file are serialised by its inode lock.  Mapping the file lets several threads fault and fill
+    // disjoint ranges at once.
+    void *map = MAP_FAILED;
+    // (posix_fallocate + MAP_POPULATE first was measured slower on tmpfs: 2.8 s against 1.6 s for the
+    // eleven 120 MB files of configs[1])
+    if (bytes >= (8u << 20) && ftruncate(fd, (off_t) total) == 0)
+        map = mmap(nullptr, total, PROT_READ | PROT_WRITE, MAP_SHARED, fd, 0);
+    if (map != MAP_FAILED) {
+        char *dst = static_cast<char *>(map);
+        memcpy(dst, header, hl);
+        unsigned hw = std::thread::hardware_concurrency();
+        const int T = (int) (hw == 0 ? 1 : (hw > 16 ? 16 : hw));
+        const size_t per = ((bytes + T - 1) / T + 4095) & ~(size_t) 4095;
+        auto work = [&](int t) {
+            const size_t lo = (size_t) t * per;
+            if (lo >= bytes) return;
+            const size_t hi = lo + per < bytes ? lo + per : bytes;
+            memcpy(dst + hl + lo, text + lo, hi - lo);
+        };
+        std::vector<std::thread> th;
+        for (int t = 1; t < T; t++) th.emplace_back(work, t);
+        work(0);
+        for (auto &x : th) x.join();
+        ok = munmap(map, total) == 0;
+    } else {
+        ok = (size_t) write(fd, header, hl) == hl;
+        size_t lo = 0;
+        while (ok && lo < bytes) {
+            const ssize_t w = write(fd, text + lo, bytes - lo);
+            if (w <= 0) ok = false;
+            else lo += (size_t) w;
+        }
+    }
+    return ::close(fd) == 0 && ok;
+}
+
+void Report::writer_loop() {
+    for (;;) {
+        Job job;
+        {
+            std::unique_lock<std::mutex> lk(mu_);
+            cv_.wait(lk, [&] { return stop_ || !jobs_.empty(); });
+            if (jobs_.empty()) return;
+            job = jobs_.front();
+            jobs_.pop_front();
+        }
+        const std::string name = job.name + ".min_dists.csv";
+        if (!write_text_file(name.c_str(), "codeword,minDistortion\n", job.text, job.bytes))
+            printf("error creating %s\n", name.c_str());
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            outstanding_--;
+        }
+        cv_.notify_all();
+    }
+}
+
+void Report::min_dists_submit(const std::string &cb_filename, const char *text, size_t bytes) {
+    {
+        std::lock_guard<std::mutex> lk(mu_);
+        if (!writer_.joinable()) writer_ = std::thread(&Report::writer_loop, this);
+        jobs_.push_back(Job{cb_filename, text, bytes});
+        outstanding_++;
+    }
+    cv_.notify_all();
+}
+
+void Report::wait_pending(size_t max_outstanding) {
+    std::unique_lock<std::mutex> lk(mu_);
+    cv_.wait(lk, [&] { return outstanding_ <= max_outstanding; });
+}
+
 void Report::close() {
+    if (writer_.joinable()) {
+        wait_pending(0);
+        {
+            std::lock_guard<std::mutex> lk(mu_);
+            stop_ = true;
+        }
+        cv_.notify_all();
+        writer_.join();
+        stop_ = false;
+    }
     if (file_) { fclose(file_); file_ = nullptr; }
     if (file_csv_) { fclose(file_csv_); file_csv_ = nullptr; }
 }

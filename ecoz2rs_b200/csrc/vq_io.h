@@ -4,7 +4,11 @@
 #include <stdint.h>
 #include <stdio.h>
 
+#include <condition_variable>
+#include <deque>
+#include <mutex>
 #include <string>
+#include <thread>
 #include <vector>
 
 namespace vqb200 {
@@ -48,13 +52,29 @@ class Report {
     void cbook(const std::string &cb_filename, int num_pas, double DDprm, double sigma,
                double inertia, int M, const int32_t *cardd, const double *discel,
                const int32_t *codeword, const double *min_dist /* both may be null */);
-    void close();
+    // "<cbook>.min_dists.csv" from text that is already formatted (Engine::min_dists_text): handed to
+    // a writer thread, so that the next stage runs while the file is written.  `text` must stay valid
+    // until wait_pending() says at most one LATER job is outstanding (the engine double-buffers it).
+    void min_dists_submit(const std::string &cb_filename, const char *text, size_t bytes);
+    void wait_pending(size_t max_outstanding);
+    void close();   // joins the writer
     ~Report() { close(); }
 
   private:
+    struct Job { std::string name; const char *text; size_t bytes; };
+    void writer_loop();
     long tot_vecs_ = 0;
     FILE *file_ = nullptr;
     FILE *file_csv_ = nullptr;
+    std::thread writer_;
+    std::mutex mu_;
+    std::condition_variable cv_;
+    std::deque<Job> jobs_;
+    size_t outstanding_ = 0;
+    bool stop_ = false;
 };
+
+// header line + `bytes` of ready-made lines -> file, the copy split over several threads (pwrite)
+bool write_text_file(const char *name, const char *header, const char *text, size_t bytes);
 
 }  // namespace vqb200

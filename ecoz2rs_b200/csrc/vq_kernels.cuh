@@ -195,6 +195,18 @@ void launch_refl_to_raas(const double *refl, double *raas, int K, int D, cudaStr
 void launch_sigma_sum(const double *raas, const double *cells, int K, int D, double *out,
                       cudaStream_t s);
 
+// ---- stage report on the device (vq_report.cu): "<cbook>.min_dists.csv", report.c:109-123 -------
+// Lines "%d,%f\n" (codeword, minDistortion) of n frames as text, byte for byte what fprintf prints.
+// launch_format_lengths: line lengths + offsets into `scratch` (format_scratch_bytes(n)); then
+// *total (bytes of text) and *bad (1: a value was inf / nan / >= 2^63 -- format on the host instead)
+// can be read back (format_result_ptrs); launch_format_write writes the text (capacity >= *total).
+size_t format_scratch_bytes(long n);
+size_t format_text_capacity(long n);
+void launch_format_lengths(const int32_t *cw, const double *md, long n, void *scratch, cudaStream_t s);
+void format_result_ptrs(void *scratch, long n, const unsigned long long **total, const int **bad);
+void launch_format_write(const int32_t *cw, const double *md, long n, const void *scratch, char *text,
+                         cudaStream_t s);
+
 // FP32 FFMA probe: blocks x 256 threads x iters x 128 FMAs each
 void launch_ffma_probe(float *out, int blocks, int iters, cudaStream_t s);
 

@@ -59,7 +59,7 @@ EXPORTED_SYMBOLS = (
     "ecoz2b200_version", "ecoz2b200_last_error", "ecoz2b200_device_count",
     "ecoz2b200_create", "ecoz2b200_destroy", "ecoz2b200_set_mode", "ecoz2b200_set_recheck_kappa",
     "ecoz2b200_set_recheck_kappa_tc", "ecoz2b200_debug_tc_distortions",
-    "ecoz2b200_tc_issued_flops_per_eval", "ecoz2b200_write_min_dists_csv",
+    "ecoz2b200_tc_issued_flops_per_eval", "ecoz2b200_write_min_dists_csv", "ecoz2b200_min_dists_text", "ecoz2b200_debug_format_lines",
     "ecoz2b200_nccl_unique_id", "ecoz2b200_comm_init", "ecoz2b200_shard_range", "ecoz2b200_packed_layout",
     "ecoz2b200_frames_clear", "ecoz2b200_frames_reserve", "ecoz2b200_frames_append_host",
     "ecoz2b200_frames_append_device", "ecoz2b200_frames_commit", "ecoz2b200_frames_count",
@@ -105,6 +105,8 @@ def lib():
             "ecoz2b200_debug_tc_distortions": (i, [vp, vp, l]),
             "ecoz2b200_tc_issued_flops_per_eval": (i, [i, _ip]),
             "ecoz2b200_write_min_dists_csv": (i, [C.c_char_p, _ip, vp, l]),
+            "ecoz2b200_min_dists_text": (i, [vp, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+            "ecoz2b200_debug_format_lines": (i, [_ip, vp, l, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
             "ecoz2b200_nccl_unique_id": (i, [C.c_char_p]),
             "ecoz2b200_comm_init": (i, [vp, C.c_char_p, i, i]),
             "ecoz2b200_shard_range": (i, [l, i, i, C.POINTER(l), C.POINTER(l)]),
@@ -361,6 +363,12 @@ class VqEngine:
         _check(lib().ecoz2b200_last_assignment(self._h, idx.ctypes.data_as(_ip), _d(md)), "last_assignment")
         return idx, md
 
+    def min_dists_text(self) -> bytes:
+        """The "codeword,minDistortion" lines of the last pass (report.c:118-121), formatted on the device."""
+        ptr, n = C.c_void_p(0), C.c_size_t(0)
+        _check(lib().ecoz2b200_min_dists_text(self._h, C.byref(ptr), C.byref(n)), "min_dists_text")
+        return C.string_at(ptr.value, n.value)
+
     def learn(self, eps: float = 0.05, stop_M: int = 4096, keep_assignments: bool = False,
               on_stage: Optional[Callable[[dict], None]] = None):
         """Full LBG run from the current codebook. -> (stages, trace) like oracle.learn."""
@@ -485,6 +493,17 @@ def write_min_dists_csv(path: str, codeword: np.ndarray, min_dist: np.ndarray) -
     assert cw.shape == md.shape and cw.ndim == 1
     _check(lib().ecoz2b200_write_min_dists_csv(os.fsencode(path), cw.ctypes.data_as(_ip), md.ctypes.data,
                                                cw.shape[0]), "write_min_dists_csv")
+
+
+def format_lines_on_device(codeword: np.ndarray, min_dist: np.ndarray):
+    """Test aid: the device report formatter on host arrays -> (return code, text bytes)."""
+    cw = np.ascontiguousarray(codeword, dtype=np.int32)
+    md = np.ascontiguousarray(min_dist, dtype=np.float64)
+    buf = C.create_string_buffer(40 * max(1, cw.shape[0]))
+    n = C.c_size_t(0)
+    rc = lib().ecoz2b200_debug_format_lines(cw.ctypes.data_as(_ip), md.ctypes.data, cw.shape[0], buf, len(buf),
+                                            C.byref(n))
+    return rc, buf.raw[:n.value]
 
 
 def nccl_unique_id() -> bytes:

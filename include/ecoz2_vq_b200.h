@@ -20,6 +20,7 @@
 #ifndef ECOZ2_VQ_B200_H
 #define ECOZ2_VQ_B200_H
 
+#include <stddef.h>
 #include <stdint.h>
 
 #ifdef __cplusplus
@@ -136,6 +137,16 @@ int ecoz2b200_set_recheck_kappa_tc(ecoz2b200_engine *e, double kappa);
 /* test aid: the raw tensor-core distortion values of the first n_rows resident
  * frames of shard 0 against the current codebook, out[n_rows][K] (TF32X3 mode) */
 int ecoz2b200_debug_tc_distortions(ecoz2b200_engine *e, float *out, long n_rows);
+/* The lines "<codeword>,<minDistortion>\n" of the LAST pass's assignment of all local frames, in
+ * append order, formatted on the device: byte for byte the "%d,%f\n" lines of the reference's
+ * "<cbook>.min_dists.csv" (ecoz2/src/vq/report.c:118-121).  *text points into a pinned host buffer
+ * owned by the engine, valid until the call after the next.  ECOZ2B200_ERR_ARG when a value is
+ * inf / nan / >= 2^62 (the file writer then formats on the host).                             */
+int ecoz2b200_min_dists_text(ecoz2b200_engine *e, const char **text, size_t *bytes);
+/* test aid: the device formatter alone on host arrays (device 0): n lines into out[capacity];
+ * *bytes = size of the text.  ECOZ2B200_ERR_ARG if a value cannot be formatted or it does not fit. */
+int ecoz2b200_debug_format_lines(const int32_t *codeword, const double *min_dist, long n, char *out,
+                                 size_t capacity, size_t *bytes);
 /* measurement aid: tensor-core FLOPs the TF32X3 search issues per (frame,
  * codeword) pair at prediction order P (padding and all three product terms
  * included); 0 if that order takes the FP32 path.  *is_f16 (optional) = 1 when

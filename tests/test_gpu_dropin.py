@@ -134,3 +134,49 @@ def test_cli_learn_and_quantize(built_lib, in_tmp_cwd):
     assert "number of predictor files: 1" in r.stdout
     cls, M, seq = formats.read_seq(str(in_tmp_cwd / "data" / "sequences" / "TEST" / "M8" / "gold" / "x.seq"))
     assert (cls, M, len(seq)) == ("gold", 8, len(q["x"]))
+
+
+def test_device_report_formatter_matches_printf(built_lib):
+    """vq_report.cu: "%d,%f\\n" lines formatted on the device are byte for byte what the
+    reference's fprintf writes (report.c:118-121): random magnitudes, exact ties of the 6th decimal
+    (round-half-to-even), negatives, -0.0, subnormals, values up to 2^62; inf / nan / >= 2^62 are
+    refused (the file writer then formats on the host)."""
+    from ecoz2rs_b200 import vq
+    rng = np.random.default_rng(7)
+    n = 300_000
+    md = np.concatenate([
+        rng.random(n) * 10.0 ** rng.integers(-9, 6, size=n),
+        rng.integers(0, 2 ** 24, size=5000) / 128.0,
+        rng.integers(0, 2 ** 30, size=5000) / 2.0 ** 20,
+        -rng.random(2000),
+        rng.random(2000) * 10.0 ** rng.integers(6, 18, size=2000),
+        np.array([0.0, -0.0, 5e-324, 1e-310, 0.5e-6, 1.5e-6, 2.5e-6, 0.9999995, 0.99999949999,
+                  1e15, 123456789012345.678, 4.6e18, 2.0 ** 62 * (1 - 2.0 ** -53), 2.0 ** 52 + 1, 2.0 ** 53]),
+    ])
+    cw = rng.integers(0, 65536, size=md.shape[0]).astype(np.int32)
+    cw[:3] = [0, -1, 2 ** 31 - 1]
+    rc, text = vq.format_lines_on_device(cw, md)
+    assert rc == 0
+    got = text.decode().split("\n")
+    assert got[-1] == "" and len(got) == md.shape[0] + 1
+    want = ["%d,%f" % (int(c), float(x)) for c, x in zip(cw, md)]
+    bad = [i for i, (a, b) in enumerate(zip(got[:-1], want)) if a != b]
+    assert not bad, f"{len(bad)} lines differ, first: {got[bad[0]]!r} vs {want[bad[0]]!r} ({md[bad[0]]!r})"
+    for x in (np.inf, -np.inf, np.nan, 2.0 ** 62, 1e19, 1e300):
+        rc, _ = vq.format_lines_on_device(np.array([1], np.int32), np.array([x]))
+        assert rc != 0, x
+
+
+def test_min_dists_text_of_a_pass(built_lib, frames36, oracle_run36):
+    """The engine's report text of a pass == "%d,%f" of its last_assignment."""
+    from ecoz2rs_b200 import vq
+    stages, _ = oracle_run36
+    with vq.VqEngine(36, max_M=256) as eng:
+        eng.set_frames(frames36)
+        eng.set_reflections(stages[6]["refl"])
+        eng.kmeans_pass(want_cells=False)
+        idx, md = eng.last_assignment()
+        t1 = eng.min_dists_text()
+        t2 = eng.min_dists_text()          # second pinned buffer, same bytes
+    want = "".join("%d,%f\n" % (int(c), float(x)) for c, x in zip(idx, md)).encode()
+    assert t1 == want and t2 == want
