@@ -678,6 +678,23 @@ def run_b200_arm(args):
     h2d = n_local * D * 8 + K * D * 8
     d2h = K * D * 8 + K * 8 * 2 + 16 + 2 * K * D * 8
 
+    # ---- run-time audit (untimed): one more pass in which every 64th frame of this rank's shard also
+    # gets the all-FP64 scan; the device counts the frames whose index differs beyond an FP64-level tie
+    audit_info = None
+    try:
+        every = int(os.environ.get("ECOZ2_VQ_AUDIT", "0") or 0) or 64
+        reset_codebook()
+        eng.set_audit(every)
+        eng.counters_reset()
+        eng.kmeans_pass(want_cells=False)
+        ac = eng.counters()
+        eng.set_audit(int(os.environ.get("ECOZ2_VQ_AUDIT", "0") or 0))
+        audit_info = {"every": every, "frames_in_pass": int(n_local), "audited": int(ac["audited"]),
+                      "index_differs": int(ac["audit_idx_diff"]), "audit_mismatches": int(ac["audit_mismatches"]),
+                      "what": f"one untimed pass at K={K} on rank 0's shard after the timed region"}
+    except Exception as e:
+        log(f"[audit] failed: {e!r}")
+
     # ---- N = 1: the same pass at K = 4096, the codebook size the N > 1 lines run (configs[2]), so that
     # a 1 -> N efficiency can be formed from equal work
     value_k4096 = None
@@ -944,8 +961,7 @@ def run_b200_arm(args):
             "lpc_front": lpc_info,
             "value_k4096": value_k4096,
             "multirank_parity": multirank_parity,
-            "audit": {"every": int(os.environ.get("ECOZ2_VQ_AUDIT", "0") or 0), "audited": int(ctr["audited"]),
-                      "index_differs": int(ctr["audit_idx_diff"]), "audit_mismatches": int(ctr["audit_mismatches"])},
+            "audit": audit_info,
             "configs": extra_configs,
         }
         emit_line(line)

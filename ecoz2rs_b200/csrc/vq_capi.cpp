@@ -436,6 +436,7 @@ void ecoz2b200_destroy(ecoz2b200_engine *e) { delete e; }
 int ecoz2b200_set_mode(ecoz2b200_engine *e, int mode) { ENG(e); return eng.set_mode(mode); }
 int ecoz2b200_set_recheck_kappa(ecoz2b200_engine *e, double k) { ENG(e); return eng.set_kappa(k); }
 int ecoz2b200_set_recheck_kappa_tc(ecoz2b200_engine *e, double k) { ENG(e); return eng.set_kappa_tc(k); }
+int ecoz2b200_set_audit(ecoz2b200_engine *e, int every) { ENG(e); return eng.set_audit(every); }
 int ecoz2b200_debug_tc_distortions(ecoz2b200_engine *e, float *out, long n_rows) {
     ENG(e);
     return eng.debug_tc_distortions(out, n_rows);

@@ -97,6 +97,7 @@ class Engine {
     int set_mode(int mode);
     int set_kappa(double kappa);
     int set_kappa_tc(double kappa);
+    int set_audit(int every) { if (every < 0) return ECOZ2B200_ERR_ARG; audit_every_ = every; return ECOZ2B200_OK; }
     // debug: the tensor-core search's raw distortion values of the first n_rows frames of
     // shard 0 against the current codebook, [n_rows][K] floats
     int debug_tc_distortions(float *out, long n_rows);

@@ -58,7 +58,7 @@ EXPORTED_SYMBOLS = (
     "vq_learn", "vq_learn_using_base_codebook", "vq_quantize", "vq_classify",
     "ecoz2b200_version", "ecoz2b200_last_error", "ecoz2b200_device_count",
     "ecoz2b200_create", "ecoz2b200_destroy", "ecoz2b200_set_mode", "ecoz2b200_set_recheck_kappa",
-    "ecoz2b200_set_recheck_kappa_tc", "ecoz2b200_debug_tc_distortions",
+    "ecoz2b200_set_recheck_kappa_tc", "ecoz2b200_set_audit", "ecoz2b200_debug_tc_distortions",
     "ecoz2b200_tc_issued_flops_per_eval", "ecoz2b200_write_min_dists_csv", "ecoz2b200_min_dists_text", "ecoz2b200_debug_format_lines",
     "ecoz2b200_nccl_unique_id", "ecoz2b200_comm_init", "ecoz2b200_shard_range", "ecoz2b200_packed_layout",
     "ecoz2b200_frames_clear", "ecoz2b200_frames_reserve", "ecoz2b200_frames_append_host",
@@ -102,6 +102,7 @@ def lib():
             "ecoz2b200_set_mode": (i, [vp, i]),
             "ecoz2b200_set_recheck_kappa": (i, [vp, d]),
             "ecoz2b200_set_recheck_kappa_tc": (i, [vp, d]),
+            "ecoz2b200_set_audit": (i, [vp, i]),
             "ecoz2b200_debug_tc_distortions": (i, [vp, vp, l]),
             "ecoz2b200_tc_issued_flops_per_eval": (i, [i, _ip]),
             "ecoz2b200_write_min_dists_csv": (i, [C.c_char_p, _ip, vp, l]),
@@ -233,6 +234,10 @@ class VqEngine:
 
     def set_recheck_kappa_tc(self, kappa: float):
         _check(lib().ecoz2b200_set_recheck_kappa_tc(self._h, kappa), "set_recheck_kappa_tc")
+
+    def set_audit(self, every: int):
+        """Every `every`-th frame of every search also gets the all-FP64 scan (0 = off); see counters()."""
+        _check(lib().ecoz2b200_set_audit(self._h, every), "set_audit")
 
     def debug_tc_distortions(self, n_rows: int) -> np.ndarray:
         """Raw tensor-core (split-TF32) distortion values of the first n_rows resident frames."""

@@ -134,6 +134,11 @@ int ecoz2b200_set_mode(ecoz2b200_engine *e, int mode);
 int ecoz2b200_set_recheck_kappa(ecoz2b200_engine *e, double kappa);
 /* same for the TF32X3 tensor-core search (its own error constant)             */
 int ecoz2b200_set_recheck_kappa_tc(ecoz2b200_engine *e, double kappa);
+/* run-time audit of the search (same as ECOZ2_VQ_AUDIT=n at creation): after every search, every
+ * `every`-th frame also gets the all-FP64 scan of vq_learn_par.c:62-81 and the device counts audited
+ * frames, differing indices and differences that are not FP64-level ties (ecoz2b200_counters);
+ * 0 switches it off.                                                                              */
+int ecoz2b200_set_audit(ecoz2b200_engine *e, int every);
 /* test aid: the raw tensor-core distortion values of the first n_rows resident
  * frames of shard 0 against the current codebook, out[n_rows][K] (TF32X3 mode) */
 int ecoz2b200_debug_tc_distortions(ecoz2b200_engine *e, float *out, long n_rows);
