@@ -31,13 +31,13 @@ double wall_s() {
     return duration<double>(steady_clock::now().time_since_epoch()).count();
 }
 
-// ECOZ2_VQ_MODE=fp32|fp64|tf32x3 overrides the search arithmetic (default tf32x3)
+// ECOZ2_VQ_MODE=tensor|fp32|fp64 overrides the search arithmetic (default tensor; "tf32x3" = its old name)
 static void apply_mode_env(vqb200::Engine &eng) {
     const char *m = getenv("ECOZ2_VQ_MODE");
     if (!m) return;
     if (strcmp(m, "fp64") == 0) eng.set_mode(ECOZ2B200_MODE_FP64);
     else if (strcmp(m, "fp32") == 0) eng.set_mode(ECOZ2B200_MODE_FP32);
-    else if (strcmp(m, "tf32x3") == 0) eng.set_mode(ECOZ2B200_MODE_TENSOR);
+    else if (strcmp(m, "tf32x3") == 0 || strcmp(m, "tensor") == 0) eng.set_mode(ECOZ2B200_MODE_TENSOR);
 }
 
 // ECOZ2_VQ_GPUS: unset/"" -> device 0; "all" -> every visible device; else "0,2,3"

@@ -9,30 +9,34 @@
 // per SM streams half-tiles of 128 FP64 frames through a ring of bulk copies and does everything
 // while a half-tile is in shared memory:
 //
-//   warp 12      raw producer: ONE cp.async.bulk per half-tile (128 rows x D doubles, contiguous)
-//   warps 0-3    loaders, thread = frame row: FP64 row -> FP32 -> power-of-two scaling -> FP16
-//                (hi, lo) split -> UMMA canonical K-major operand (same numerics as vq_assign_tc2)
-//   warp 13      MMA issuer: the codebook tile is resident in shared memory for the whole kernel
-//                (loaded once by warp 14); 8 tcgen05.mma per half-tile into a TMEM accumulator
-//   warps 4-11   epilogue + cell sums.  Epilogue (one warpgroup per half, thread = frame):
+//   warp 16      raw producer: ONE cp.async.bulk per half-tile (128 rows x D doubles, contiguous)
+//   warps 0-7    loaders (one warpgroup per half of a tile pair), thread = frame row: FP64 row ->
+//                FP32 -> power-of-two scaling -> FP16 (hi, lo) split -> UMMA canonical K-major
+//                operand (same numerics as vq_assign_tc2)
+//   warp 17      MMA issuer: the codebook tile is resident in shared memory for the whole kernel
+//                (loaded once by warp 18); 8 tcgen05.mma per half-tile into a TMEM accumulator
+//   warps 8-15   epilogue + cell sums.  Epilogue (one warpgroup per half, thread = frame):
 //                tcgen05.ld, (best, runner-up, argbest), error-bound test; writes idx, appends frames
-//                inside the bound to flag_list, publishes the half-tile's cell indices.  Cell sums
-//                (all 8 warps, every half-tile): warp w OWNS the cells c with (c & 7) == w and keeps
-//                their sums in REGISTERS for the whole kernel (lane = component; CPW = K / 8 cells
-//                per warp, statically indexed).  For each of its cells it finds the half-tile's rows
-//                by ballot over the cell indices and adds the FP64 rows -- still in the raw buffer --
-//                with plain loads and DADDs: no atomics, no table in shared memory, no
-//                read-modify-write chain.  The raw buffer returns to the ring when the loaders and
-//                all 8 warps are done with it.
+//                inside the bound to flag_list and every other frame's row number to the list of
+//                its cell (s_list[ring slot][cell][CAP], one shared-memory atomic per frame; a row
+//                that finds its list full goes to late_list).  Cell sums (all 8 warps, every
+//                half-tile): lane = cell, warp = a slice of NCW components kept in REGISTERS for the
+//                whole kernel; a lane walks its cell's row list and adds the FP64 row -- still in
+//                the raw buffer -- with plain loads and DADDs: no atomics on the sums, no table in
+//                shared memory.  The raw buffer returns to the ring when the loaders and all 8
+//                warps are done with it.
 //
 // Frames inside the error bound are NOT accumulated here: they go through the usual FP64
-// re-evaluation (launch_recheck) and vq_cell_fixup adds their rows afterwards with the final index.
-// At the end every warp flushes its registers with one FP64 atomic per (cell, component); counts,
-// per-cell distortions and DD follow from the sums exactly as in vq_cells.cu (vq_cell_finish).
+// re-evaluation (launch_recheck) and vq_cell_fixup adds their rows (and the late_list rows)
+// afterwards with the final index.  At the end every warp flushes its registers with one FP64
+// atomic per (cell, component); counts, per-cell distortions and DD follow from the sums exactly as
+// in vq_cells.cu (launch_cell_finish).
 //
-// (First version, measured on B200: four dedicated warps adding rows into a shared-memory table
-// [K][D] by cell ownership -- 280 clocks per row in the load / add / store chain, 2.5-2.9 ms per
-// 10M-frame pass against 1.5 ms of the two-kernel pass.)
+// STATUS: experimental, OFF by default (ECOZ2_VQ_MID_MAXK=0).  Measured on B200, 10M frames, per pass
+// at K = 16 / 32 / 64 / 128: 2.0 / 2.1 / 1.34 / 2.0 ms against 1.5 ms of search + sorted sums.  Earlier
+// designs: shared-memory cell table by ownership 2.5-2.9 ms; ballots per cell 1.56 / 1.59 / 1.79 /
+// 2.55; register switch 1.8-4.4.  Without the cell-sum loop (ECOZ2_VQ_MID_EXP=1) the sweep takes
+// 1.06-1.10 ms: the loaders' FP64 -> FP16 conversion bounds it.  DESIGN.md 10.3.
 #include "vq_kernels.cuh"
 #include "vq_tc_common.cuh"
 
