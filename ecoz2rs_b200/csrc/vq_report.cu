@@ -12,6 +12,10 @@
 //   vq_fmt_scan      exclusive scan of the block sums (one CTA), total size, "cannot format" flag
 //   vq_fmt_write     the text
 #include "vq_kernels.cuh"
+#include "vq_engine.h"      // set_last_error, the error codes of the public header
+
+#include <cstdio>
+#include <mutex>
 
 namespace vqb200 {
 
@@ -227,3 +231,119 @@ void launch_format_write(const int32_t *cw, const double *md, long n, const void
 }
 
 }  // namespace vqb200
+
+// ---------------------------------------------------------------------------------------------
+// ecoz2b200_format_lines_noalloc -- the same formatter for callers that must not allocate (code
+// under CUDA graph capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in
+// the reference.
+//
+// The scratch of the three kernels (per-block sums, the total, the "cannot format" flag) lives in
+// a file-scope __device__ array: every GPU that loads the library holds these 128.3 KB until the
+// process exits.  In HOST code the array's name is only a stand-in for the symbol -- its device
+// address comes from cudaGetSymbolAddress, looked up once per device with that device current.
+// All calls on one device share the array: calls that overlap on the GPU (different streams, no
+// ordering between them) race on it.  Everything a call reads from the array it has written
+// itself first (block sums, total) or cleared (the flag), so the previous call's contents do not
+// matter.
+namespace {
+constexpr long kNoAllocMaxLines = ECOZ2B200_NOALLOC_MAX_LINES;
+constexpr long kNoAllocMaxBlocks = (kNoAllocMaxLines + vqb200::kFmtBlock - 1) / vqb200::kFmtBlock;
+// (blocks + 1) sums + 16 bytes for the flag, rounded up to the array's alignment
+constexpr size_t kNoAllocScratchBytes = ((size_t) (kNoAllocMaxBlocks + 1) * 8 + 16 + 255) / 256 * 256;
+constexpr int kNoAllocMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNoAllocScratchBytes];
+
+namespace {
+
+std::mutex g_noalloc_mutex;
+void *g_noalloc_ptr[kNoAllocMaxDevices] = {};      // device address of g_noalloc_scratch per device
+
+// *bytes = size of the text, or ~0 when some value could not be formatted
+__global__ void vq_fmt_result(const unsigned long long *__restrict__ total, const int *__restrict__ bad,
+                              unsigned long long *__restrict__ bytes) {
+    *bytes = *bad ? ~0ull : *total;
+}
+
+int noalloc_fail(int code, const char *msg) {
+    vqb200::set_last_error(msg);
+    return code;
+}
+
+// device address of the scratch array on the CURRENT device (looked up once per device)
+int noalloc_scratch(void **ptr) {
+    int dev = -1;
+    if (cudaGetDevice(&dev) != cudaSuccess || dev < 0 || dev >= kNoAllocMaxDevices)
+        return noalloc_fail(ECOZ2B200_ERR_CUDA, "format_lines_noalloc: no current CUDA device");
+    std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+    if (!g_noalloc_ptr[dev]) {
+        void *p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+        if (e != cudaSuccess || !p) {
+            char msg[160];
+            snprintf(msg, sizeof msg, "format_lines_noalloc: cudaGetSymbolAddress failed on device %d: %s", dev,
+                     cudaGetErrorString(e));
+            return noalloc_fail(ECOZ2B200_ERR_CUDA, msg);
+        }
+        g_noalloc_ptr[dev] = p;
+    }
+    *ptr = g_noalloc_ptr[dev];
+    return ECOZ2B200_OK;
+}
+
+// a pointer the kernels can dereference on device `dev`?  (plain host memory cannot be)
+bool noalloc_device_pointer(const void *p, int dev) {
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) { cudaGetLastError(); return false; }
+    if (a.type == cudaMemoryTypeDevice) return a.device == dev;
+    return a.type == cudaMemoryTypeManaged || a.type == cudaMemoryTypeHost;
+}
+
+}  // namespace
+
+extern "C" int ecoz2b200_format_lines_noalloc(const int32_t *d_codeword, const double *d_min_dist, long n,
+                                              char *d_text, size_t text_capacity,
+                                              unsigned long long *d_bytes, void *stream) {
+    char msg[200];
+    if (n < 0 || !d_bytes || (n > 0 && (!d_codeword || !d_min_dist || !d_text)))
+        return noalloc_fail(ECOZ2B200_ERR_ARG, "format_lines_noalloc: null pointer or negative line count");
+    if (n > kNoAllocMaxLines) {
+        snprintf(msg, sizeof msg, "format_lines_noalloc: %ld lines exceed the maximum of %ld per call "
+                 "(ECOZ2B200_NOALLOC_MAX_LINES; the scratch is a fixed device array)", n, kNoAllocMaxLines);
+        return noalloc_fail(ECOZ2B200_ERR_ARG, msg);
+    }
+    if (text_capacity < vqb200::format_text_capacity(n)) {
+        snprintf(msg, sizeof msg, "format_lines_noalloc: text_capacity %zu is below %zu (%d bytes per line)",
+                 text_capacity, vqb200::format_text_capacity(n), vqb200::kFmtMaxLine);
+        return noalloc_fail(ECOZ2B200_ERR_ARG, msg);
+    }
+    void *scratch = nullptr;
+    const int rc = noalloc_scratch(&scratch);
+    if (rc != ECOZ2B200_OK) return rc;
+    int dev = 0;
+    cudaGetDevice(&dev);
+    if (!noalloc_device_pointer(d_bytes, dev) ||
+        (n > 0 && (!noalloc_device_pointer(d_codeword, dev) || !noalloc_device_pointer(d_min_dist, dev) ||
+                   !noalloc_device_pointer(d_text, dev))))
+        return noalloc_fail(ECOZ2B200_ERR_ARG,
+                            "format_lines_noalloc: every buffer must be device-accessible memory of the current device");
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (n == 0) {
+        if (cudaMemsetAsync(d_bytes, 0, sizeof(unsigned long long), s) != cudaSuccess)
+            return noalloc_fail(ECOZ2B200_ERR_CUDA, "format_lines_noalloc: cudaMemsetAsync failed");
+        return ECOZ2B200_OK;
+    }
+    const unsigned long long *d_total;
+    const int *d_bad;
+    vqb200::format_result_ptrs(scratch, n, &d_total, &d_bad);
+    vqb200::launch_format_lengths(d_codeword, d_min_dist, n, scratch, s);   // clears the flag first
+    vq_fmt_result<<<1, 1, 0, s>>>(d_total, d_bad, d_bytes);
+    vqb200::launch_format_write(d_codeword, d_min_dist, n, scratch, d_text, s);
+    const cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) {
+        snprintf(msg, sizeof msg, "format_lines_noalloc: launch failed: %s", cudaGetErrorString(e));
+        return noalloc_fail(ECOZ2B200_ERR_CUDA, msg);
+    }
+    return ECOZ2B200_OK;
+}

@@ -25,6 +25,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.environ.get("ECOZ2_VQ_B200_LIB") or os.path.join(_HERE, "csrc", "libecoz2_vq_b200.so")
 
 MODE_FP32, MODE_FP64, MODE_TENSOR = 0, 1, 2
+OK, ERR_ARG, ERR_IO, ERR_CUDA, ERR_NCCL = 0, 1, 2, 3, 4     # ECOZ2B200_OK / ECOZ2B200_ERR_*
 MODE_TF32X3 = MODE_TENSOR   # first name of the mode, kept as an alias
 
 _dp = C.POINTER(C.c_double)
@@ -59,7 +60,7 @@ EXPORTED_SYMBOLS = (
     "ecoz2b200_version", "ecoz2b200_last_error", "ecoz2b200_device_count",
     "ecoz2b200_create", "ecoz2b200_destroy", "ecoz2b200_set_mode", "ecoz2b200_set_recheck_kappa",
     "ecoz2b200_set_recheck_kappa_tc", "ecoz2b200_set_audit", "ecoz2b200_debug_tc_distortions",
-    "ecoz2b200_tc_issued_flops_per_eval", "ecoz2b200_write_min_dists_csv", "ecoz2b200_min_dists_text", "ecoz2b200_debug_format_lines",
+    "ecoz2b200_tc_issued_flops_per_eval", "ecoz2b200_write_min_dists_csv", "ecoz2b200_min_dists_text", "ecoz2b200_debug_format_lines", "ecoz2b200_format_lines_noalloc",
     "ecoz2b200_nccl_unique_id", "ecoz2b200_comm_init", "ecoz2b200_shard_range", "ecoz2b200_packed_layout",
     "ecoz2b200_frames_clear", "ecoz2b200_frames_reserve", "ecoz2b200_frames_append_host",
     "ecoz2b200_frames_append_device", "ecoz2b200_frames_commit", "ecoz2b200_frames_count",
@@ -108,6 +109,7 @@ def lib():
             "ecoz2b200_write_min_dists_csv": (i, [C.c_char_p, _ip, vp, l]),
             "ecoz2b200_min_dists_text": (i, [vp, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
             "ecoz2b200_debug_format_lines": (i, [_ip, vp, l, C.c_char_p, C.c_size_t, C.POINTER(C.c_size_t)]),
+            "ecoz2b200_format_lines_noalloc": (i, [vp, vp, l, vp, C.c_size_t, vp, vp]),
             "ecoz2b200_nccl_unique_id": (i, [C.c_char_p]),
             "ecoz2b200_comm_init": (i, [vp, C.c_char_p, i, i]),
             "ecoz2b200_shard_range": (i, [l, i, i, C.POINTER(l), C.POINTER(l)]),
@@ -509,6 +511,23 @@ def format_lines_on_device(codeword: np.ndarray, min_dist: np.ndarray):
     rc = lib().ecoz2b200_debug_format_lines(cw.ctypes.data_as(_ip), md.ctypes.data, cw.shape[0], buf, len(buf),
                                             C.byref(n))
     return rc, buf.raw[:n.value]
+
+
+def last_error() -> str:
+    """Message of the last failed call on this thread (ecoz2b200_last_error)."""
+    return lib().ecoz2b200_last_error().decode()
+
+
+NOALLOC_MAX_LINES = 4194304        # ECOZ2B200_NOALLOC_MAX_LINES
+
+
+def format_lines_noalloc(d_codeword: int, d_min_dist: int, n: int, d_text: int, text_capacity: int,
+                         d_bytes: int, stream: int = 0) -> int:
+    """The device report formatter on caller-owned DEVICE buffers (raw addresses), queued on `stream`;
+    allocates nothing (its scratch is a fixed device array of the library).  Returns the C return code;
+    `last_error()` has the message of a failure."""
+    return lib().ecoz2b200_format_lines_noalloc(d_codeword, d_min_dist, n, d_text, text_capacity, d_bytes,
+                                                stream or None)
 
 
 def nccl_unique_id() -> bytes:

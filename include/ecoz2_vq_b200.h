@@ -152,6 +152,22 @@ int ecoz2b200_min_dists_text(ecoz2b200_engine *e, const char **text, size_t *byt
  * *bytes = size of the text.  ECOZ2B200_ERR_ARG if a value cannot be formatted or it does not fit. */
 int ecoz2b200_debug_format_lines(const int32_t *codeword, const double *min_dist, long n, char *out,
                                  size_t capacity, size_t *bytes);
+/* The same device formatter for callers that must NOT allocate (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+ * Calls no cudaMalloc / cudaFree or any allocating
+ * routine: the kernels' scratch (per-block sums, the "cannot format" flag) is a fixed __device__
+ * array of the library, 128.3 KB held by every GPU that loads it until the process exits, which
+ * limits one call to ECOZ2B200_NOALLOC_MAX_LINES lines (more -> ECOZ2B200_ERR_ARG and a message in
+ * ecoz2b200_last_error).  ALL pointers are device-accessible memory of the CURRENT device, owned
+ * by the caller: d_codeword[n], d_min_dist[n] in; d_text[text_capacity] out, text_capacity >=
+ * 40 * n (else ERR_ARG); *d_bytes out = size of the text, or ~0 when a value is inf / nan /
+ * >= 2^62 (d_text is then incomplete).  `stream` is a cudaStream_t or NULL; the work is queued
+ * on it, nothing is synchronised.  Every call on a device shares the one scratch array: calls
+ * whose kernels can overlap on the GPU (different streams without an ordering) race on it.     */
+#define ECOZ2B200_NOALLOC_MAX_LINES 4194304L
+int ecoz2b200_format_lines_noalloc(const int32_t *d_codeword, const double *d_min_dist, long n,
+                                   char *d_text, size_t text_capacity,
+                                   unsigned long long *d_bytes, void *stream);
 /* measurement aid: tensor-core FLOPs the TF32X3 search issues per (frame,
  * codeword) pair at prediction order P (padding and all three product terms
  * included); 0 if that order takes the FP32 path.  *is_f16 (optional) = 1 when
