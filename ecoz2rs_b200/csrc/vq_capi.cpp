@@ -15,6 +15,7 @@
 
 #include "vq_engine.h"
 #include "vq_io.h"
+#include "vq_textwriter.h"
 #include "vq_nccl.h"
 
 using vqb200::Engine;
@@ -72,6 +73,7 @@ struct LearnCtx {
     Engine *eng;
     std::string class_name, prefix, cb_filename;
     vqb200::Report *report;
+    vqb200::DeviceTextWriter *text_writer;
     void *target;
     vq_learn_callback_t callback;
     double DDprv = DBL_MAX;
@@ -109,14 +111,13 @@ void on_stage(void *c, const ecoz2b200_stage_info *info) {
     const double t_rep0 = wall_s();
     bool text_done = false;
     if (ctx->min_dists) {
-        // "<cbook>.min_dists.csv": formatted on the device (vq_report.cu), written by the report's
-        // writer thread while the next stage runs.  The engine double-buffers the text: before a
-        // new text is produced at most one older file may still be in flight.
-        ctx->report->wait_pending(1);
-        const char *text = nullptr;
-        size_t bytes = 0;
-        if (!getenv("ECOZ2_VQ_REPORT_HOST") && ctx->eng->min_dists_text(&text, &bytes) == ECOZ2B200_OK) {
-            ctx->report->min_dists_submit(ctx->cb_filename, text, bytes);
+        // "<cbook>.min_dists.csv": formatted on the device (vq_report.cu); the text stays in HBM and
+        // a pool of writer threads copies it out and writes the file while the next stages run
+        // (vq_textwriter.h: one file does not fill faster with more threads, several files do).
+        std::vector<Engine::TextSegment> segs;
+        if (ctx->text_writer && ctx->eng->min_dists_text_device(segs) == ECOZ2B200_OK) {
+            ctx->text_writer->submit(ctx->cb_filename + ".min_dists.csv", "codeword,minDistortion\n",
+                                     std::move(segs));
             text_done = true;
         } else {   // values the device formatter does not take (inf / nan): the host formatter
             cw.resize((size_t) ctx->tot_vecs);
@@ -209,6 +210,15 @@ int learn_files(const double *base_refl, int base_K, int P, double eps, const ch
     ctx.class_name = class_name;
     ctx.prefix = prefix;
     ctx.report = &report;
+    ctx.min_dists = env_int("ECOZ2_VQ_MIN_DISTS", 1) != 0;
+    // writer threads for the device-formatted min_dists.csv (streams and pinned chunks are set up
+    // here, before the run); ECOZ2_VQ_REPORT_HOST=1 keeps the host formatter
+    std::unique_ptr<vqb200::DeviceTextWriter> text_writer;
+    if (ctx.min_dists && !getenv("ECOZ2_VQ_REPORT_HOST")) {
+        text_writer.reset(new vqb200::DeviceTextWriter(&eng));
+        if (!text_writer->ready()) text_writer.reset();
+    }
+    ctx.text_writer = text_writer.get();
     ctx.target = target;
     ctx.callback = callback;
     ctx.tot_vecs = tot_vecs;
@@ -223,6 +233,11 @@ int learn_files(const double *base_refl, int base_K, int P, double eps, const ch
     ctx.t_stage = t0;
     rc = eng.learn(eps, stop_M, on_stage, on_pass, &ctx);
     printf("\nprocessing took %.2fs\n", wall_s() - t0);
+    const double t_fin = wall_s();
+    if (text_writer) text_writer->finish();   // the last stages' files
+    if (getenv("ECOZ2_VQ_TIMING"))
+        fprintf(stderr, "[timing] waited %.1f ms for the report writers after the last stage\n",
+                (wall_s() - t_fin) * 1e3);
     report.close();
     if (rc) return ECOZ2B200_ERR_CUDA;
     return ctx.rc;

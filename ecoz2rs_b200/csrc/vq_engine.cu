@@ -130,6 +130,10 @@ Engine::~Engine() {
         cudaFree(s.wtc); cudaFree(s.cs_mem); cudaFree(s.packed_scratch); cudaFree(s.raas_prev);
         cudaFree(s.packed); cudaFree(s.scalars); cudaFree(s.dstat);
         cudaFree(s.fmt_scratch); cudaFree(s.fmt_text);
+        for (auto &tb : s.text_pool) {
+            cudaFree(tb.d);
+            if (tb.ready) cudaEventDestroy(tb.ready);
+        }
         for (int b = 0; b < 2; b++) {
             QBuf &q = qbuf_[2 * i + b];
             cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
@@ -981,11 +985,12 @@ int Engine::min_dists_text(const char **text, size_t *bytes) {
         Shard &s = shards_[i];
         if (s.n <= 0) continue;
         CUDA_TRY(cudaSetDevice(s.device));
+        rc = ensure_fmt_scratch(s);
+        if (rc) return rc;
         if (s.fmt_cap < s.n) {
             CUDA_TRY(cudaStreamSynchronize(s.stream));
-            cudaFree(s.fmt_scratch); cudaFree(s.fmt_text);
-            s.fmt_scratch = nullptr; s.fmt_text = nullptr; s.fmt_cap = 0;
-            CUDA_TRY(cudaMalloc(&s.fmt_scratch, format_scratch_bytes(s.n)));
+            cudaFree(s.fmt_text);
+            s.fmt_text = nullptr; s.fmt_cap = 0;
             CUDA_TRY(cudaMalloc(&s.fmt_text, format_text_capacity(s.n)));
             s.fmt_cap = s.n;
         }
@@ -1034,6 +1039,151 @@ int Engine::min_dists_text(const char **text, size_t *bytes) {
     if (text) *text = h_text_[slot];
     if (bytes) *bytes = all;
     return ECOZ2B200_OK;
+}
+
+int Engine::ensure_fmt_scratch(Shard &s) {
+    if (s.fmt_scratch_cap >= s.n) return ECOZ2B200_OK;
+    CUDA_TRY(cudaStreamSynchronize(s.stream));
+    cudaFree(s.fmt_scratch);
+    s.fmt_scratch = nullptr; s.fmt_scratch_cap = 0;
+    CUDA_TRY(cudaMalloc(&s.fmt_scratch, format_scratch_bytes(s.n)));
+    s.fmt_scratch_cap = s.n;
+    return ECOZ2B200_OK;
+}
+
+int Engine::min_dists_text_device(std::vector<TextSegment> &segs) {
+    segs.clear();
+    const int rc = min_dists_text_device_impl(segs);
+    if (rc) {   // hand back what was taken before the failure
+        for (const TextSegment &g : segs) release_text(g);
+        segs.clear();
+    }
+    return rc;
+}
+
+int Engine::min_dists_text_device_impl(std::vector<TextSegment> &segs) {
+    static const bool timing = getenv("ECOZ2_VQ_TIMING") != nullptr;
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    const double t0 = now();
+    int rc = ensure_mindist();
+    if (rc) return rc;
+    if (timing) { sync_all(); fprintf(stderr, "[timing]   text: minDist %.2f ms\n", (now() - t0) * 1e3); }
+    const double t1 = now();
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        if (s.n <= 0) continue;
+        CUDA_TRY(cudaSetDevice(s.device));
+        rc = ensure_fmt_scratch(s);
+        if (rc) return rc;
+        launch_format_lengths(s.idx, s.mindist, s.n, s.fmt_scratch, s.stream);
+        ctr_.kernel_launches += 2;
+    }
+    std::vector<unsigned long long> totals(shards_.size(), 0);
+    bool bad_any = false;
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        if (s.n <= 0) continue;
+        CUDA_TRY(cudaSetDevice(s.device));
+        const unsigned long long *d_total;
+        const int *d_bad;
+        format_result_ptrs(s.fmt_scratch, s.n, &d_total, &d_bad);
+        int bad = 0;
+        CUDA_TRY(cudaMemcpyAsync(&totals[i], d_total, sizeof(unsigned long long), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(&bad, d_bad, sizeof(int), cudaMemcpyDeviceToHost, s.stream));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+        bad_any = bad_any || bad != 0;
+    }
+    if (bad_any) return ECOZ2B200_ERR_ARG;   // caller formats on the host (inf / nan / huge values)
+    if (timing) fprintf(stderr, "[timing]   text: lengths + scan + read-back %.2f ms\n", (now() - t1) * 1e3);
+    const double t2 = now();
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        if (s.n <= 0) continue;
+        CUDA_TRY(cudaSetDevice(s.device));
+        const size_t need = (size_t) totals[i];
+        // First text of a run: allocate the pool for all the stages to come NOW, while no writer
+        // thread is active -- cudaMalloc next to another thread's copies was measured to stall both
+        // for tens to hundreds of milliseconds.  Lines grow from "0,0.123456" to "4095,0.123456":
+        // half as much again covers it (a text that still does not fit takes the slow path below).
+        if (s.text_pool.empty()) {
+            int stages = 1;
+            for (int k = K_ < 1 ? 1 : K_; 2 * k <= max_M_; k *= 2) stages++;
+            if (stages > kTextPoolMax) stages = kTextPoolMax;
+            const size_t cap = need + need / 2 + 4096;
+            size_t free_b = 0, total_b = 0;
+            if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) free_b = 0;
+            while (stages > 2 && (size_t) stages * cap > free_b / 4) stages--;
+            std::lock_guard<std::mutex> lk(text_mu_);
+            for (int b = 0; b < stages; b++) {
+                Shard::TextBuf tb;
+                if (cudaMalloc(&tb.d, cap) != cudaSuccess) { cudaGetLastError(); break; }
+                tb.cap = cap;
+                if (cudaEventCreateWithFlags(&tb.ready, cudaEventDisableTiming) != cudaSuccess) {
+                    cudaFree(tb.d);
+                    break;
+                }
+                s.text_pool.push_back(tb);
+            }
+        }
+        // a free buffer of the pool that is large enough; else a new one; else (pool full or out of
+        // memory) wait for a writer to hand one back
+        int slot = -1;
+        {
+            std::unique_lock<std::mutex> lk(text_mu_);
+            for (;;) {
+                int small_free = -1, busy = 0;
+                for (size_t b = 0; b < s.text_pool.size() && slot < 0; b++) {
+                    Shard::TextBuf &tb = s.text_pool[b];
+                    if (tb.busy) { busy++; continue; }
+                    if (tb.cap >= need) slot = (int) b;
+                    else small_free = (int) b;
+                }
+                if (slot >= 0) break;
+                const size_t want = need + need / 8 + 4096;
+                if (small_free >= 0 || (int) s.text_pool.size() < kTextPoolMax) {
+                    if (small_free < 0) {
+                        s.text_pool.emplace_back();
+                        small_free = (int) s.text_pool.size() - 1;
+                    }
+                    Shard::TextBuf &tb = s.text_pool[small_free];
+                    if (tb.d) { cudaFree(tb.d); tb.d = nullptr; tb.cap = 0; }
+                    if (!tb.ready && cudaEventCreateWithFlags(&tb.ready, cudaEventDisableTiming) != cudaSuccess) {
+                        set_last_error("min_dists_text_device: cudaEventCreate failed");
+                        return ECOZ2B200_ERR_CUDA;
+                    }
+                    if (cudaMalloc(&tb.d, want) == cudaSuccess) {
+                        tb.cap = want;
+                        slot = small_free;
+                        break;
+                    }
+                    cudaGetLastError();   // out of memory: fall through and wait for a busy buffer
+                    tb.d = nullptr;
+                    if (busy == 0) {
+                        set_last_error("min_dists_text_device: out of device memory for the report text");
+                        return ECOZ2B200_ERR_CUDA;
+                    }
+                }
+                text_cv_.wait(lk);
+            }
+            s.text_pool[slot].busy = true;
+        }
+        Shard::TextBuf &tb = s.text_pool[slot];
+        launch_format_write(s.idx, s.mindist, s.n, s.fmt_scratch, tb.d, s.stream);
+        ctr_.kernel_launches++;
+        CUDA_TRY(cudaEventRecord(tb.ready, s.stream));
+        segs.push_back(TextSegment{(int) i, slot, s.device, tb.d, need, tb.ready});
+    }
+    if (timing) fprintf(stderr, "[timing]   text: buffer + write launch %.2f ms\n", (now() - t2) * 1e3);
+    CUDA_TRY(cudaGetLastError());
+    return ECOZ2B200_OK;
+}
+
+void Engine::release_text(const TextSegment &seg) {
+    {
+        std::lock_guard<std::mutex> lk(text_mu_);
+        shards_[seg.shard].text_pool[seg.slot].busy = false;
+    }
+    text_cv_.notify_all();
 }
 
 // ---------------------------------------------------------------------------------

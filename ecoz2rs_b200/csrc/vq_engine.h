@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <condition_variable>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -71,7 +73,11 @@ struct Shard {
     double *scalars = nullptr;  // [8] misc device scalars (sigma sum, ...)
     void *fmt_scratch = nullptr;   // report formatter: line offsets
     char *fmt_text = nullptr;      // report formatter: text of this shard's frames
-    long fmt_cap = 0;              // frames the two buffers above are sized for
+    long fmt_cap = 0;              // frames fmt_text is sized for
+    long fmt_scratch_cap = 0;      // frames fmt_scratch is sized for
+    // report texts that stay in HBM until a writer thread has copied them out (min_dists_text_device)
+    struct TextBuf { char *d = nullptr; size_t cap = 0; cudaEvent_t ready = nullptr; bool busy = false; };
+    std::vector<TextBuf> text_pool;
     // device-side statistics, read only when the counters are asked for (no per-pass host sync):
     // [0] frames audited, [1] audit: index differs, [2] audit: real mis-assignment, [3] frames
     // re-evaluated in FP64
@@ -134,6 +140,21 @@ class Engine {
     // text lands in one of two pinned host buffers owned by the engine (valid until the call after the
     // next).  ECOZ2B200_ERR_ARG with *bytes = 0 when a value cannot be formatted there (inf / nan).
     int min_dists_text(const char **text, size_t *bytes);
+    std::vector<int> devices() const {
+        std::vector<int> d;
+        for (const Shard &s : shards_) d.push_back(s.device);
+        return d;
+    }
+    // Same lines, but the text STAYS ON THE DEVICE: one segment per shard (append order), each in a
+    // buffer of a per-shard pool, complete when `ready` has fired.  The caller (the report's writer
+    // threads, vq_io.cpp) copies the segments out on streams of its own while the next stages run and
+    // hands each one back with release_text (thread-safe).  When all kTextPoolMax buffers of a shard
+    // are with writers the call waits for one to come back.
+    struct TextSegment { int shard; int slot; int device; const char *d_text; size_t bytes; cudaEvent_t ready; };
+    int min_dists_text_device(std::vector<TextSegment> &segs);
+    int min_dists_text_device_impl(std::vector<TextSegment> &segs);
+    int ensure_fmt_scratch(Shard &s);
+    void release_text(const TextSegment &seg);
     int learn(double eps, int stop_M, ecoz2b200_stage_cb on_stage, ecoz2b200_pass_cb on_pass,
               void *ctx);
     int quantize_host(const double *x, long T, uint16_t *seq_out, double *avg);
@@ -209,6 +230,9 @@ class Engine {
     char *h_text_[2] = {nullptr, nullptr};   // pinned: report text, double buffered
     size_t h_text_cap_[2] = {0, 0};
     int h_text_slot_ = 0;
+    static constexpr int kTextPoolMax = 12;   // report texts in flight per shard (one LBG run 2 -> 4096)
+    std::mutex text_mu_;
+    std::condition_variable text_cv_;
     std::vector<double> h_packed_;  // host mirror of the packed buffer tail / cells
     double h_count_ = 0;            // kmeans_pass_host: frames of all ranks (read back with the pass)
 };
