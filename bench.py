@@ -501,8 +501,12 @@ def _dropin_cfg2(dev, n_frames, stop_M):
             files.append(f)
         out["prd_write_s"] = time.perf_counter() - t0
         os.environ["ECOZ2_VQ_MAX_M"] = str(stop_M)
-        for label, md in (("with_min_dists", "1"), ("without_min_dists", "0")):
-            wd = os.path.join(tmp, "run_" + label)
+        # the first call of a process also pays the library's one-time costs (module load, first pinned
+        # allocation, thread start-up): it is reported on its own, then both variants run twice,
+        # alternating, and the faster run of each counts
+        for rep, (label, md) in enumerate((("first_call", "0"), ("with_min_dists", "1"), ("without_min_dists", "0"),
+                                           ("with_min_dists", "1"), ("without_min_dists", "0"))):
+            wd = os.path.join(tmp, f"run_{rep}_{label}")
             os.makedirs(wd)
             os.chdir(wd)
             os.environ["ECOZ2_VQ_MIN_DISTS"] = md
@@ -512,10 +516,17 @@ def _dropin_cfg2(dev, n_frames, stop_M):
             wall = time.perf_counter() - t0
             os.chdir(cwd)
             sizes = sum(os.path.getsize(os.path.join(dp, fn)) for dp, _, fns in os.walk(wd) for fn in fns)
-            out[label] = {"wall_s": wall, "rc": rc, "stages": len(stages), "bytes_written": sizes,
-                          "final_avg_distortion": stages[-1][1] if stages else None}
             shutil.rmtree(wd, ignore_errors=True)
+            if label == "first_call":
+                out["first_call_without_min_dists_s"] = wall
+                continue
+            prev = out.get(label)
+            walls = (prev["walls_s"] if prev else []) + [wall]
+            out[label] = {"wall_s": min(walls), "walls_s": walls, "rc": rc if not prev else (rc or prev["rc"]),
+                          "stages": len(stages), "bytes_written": sizes,
+                          "final_avg_distortion": stages[-1][1] if stages else None}
         a, b = out["with_min_dists"]["wall_s"], out["without_min_dists"]["wall_s"]
+        out["reports_overhead_s"] = a - b
         out["reports_overhead_ratio"] = a / b if b > 0 else None
     finally:
         os.chdir(cwd)

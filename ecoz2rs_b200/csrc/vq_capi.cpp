@@ -15,7 +15,7 @@
 
 #include "vq_engine.h"
 #include "vq_io.h"
-#include "vq_textwriter.h"
+#include "vq_hostio.h"
 #include "vq_nccl.h"
 
 using vqb200::Engine;
@@ -113,7 +113,7 @@ void on_stage(void *c, const ecoz2b200_stage_info *info) {
     if (ctx->min_dists) {
         // "<cbook>.min_dists.csv": formatted on the device (vq_report.cu); the text stays in HBM and
         // a pool of writer threads copies it out and writes the file while the next stages run
-        // (vq_textwriter.h: one file does not fill faster with more threads, several files do).
+        // (vq_hostio.h: one file does not fill faster with more threads, several files do).
         std::vector<Engine::TextSegment> segs;
         if (ctx->text_writer && ctx->eng->min_dists_text_device(segs) == ECOZ2B200_OK) {
             ctx->text_writer->submit(ctx->cb_filename + ".min_dists.csv", "codeword,minDistortion\n",
@@ -144,6 +144,7 @@ void on_stage(void *c, const ecoz2b200_stage_info *info) {
 // vq_learn_ (vq_learn.i:161-247)
 int learn_files(const double *base_refl, int base_K, int P, double eps, const char *class_name,
                 const char *files[], int num_files, void *target, vq_learn_callback_t callback) {
+    const double t_call = wall_s();
     const std::string class_dir = std::string("data/codebooks/") + class_name;
     vqb200::mk_dirs(class_dir);
     char epsbuf[64];
@@ -171,7 +172,23 @@ int learn_files(const double *base_refl, int base_K, int P, double eps, const ch
     apply_mode_env(eng);
     int rc = eng.frames_reserve(tot_vecs);
     if (rc) return ECOZ2B200_ERR_CUDA;
-    {
+    // streams + pinned chunks of the loader threads and, later, of the report writers (vq_hostio.h)
+    // (small inputs: fewer threads, pinning memory costs more than it saves)
+    const size_t total_bytes = (size_t) tot_vecs * (size_t) (P + 1) * sizeof(double);
+    const int small_threads = (int) (total_bytes >> 25) + 1;             // one per 32 MB
+    vqb200::IoLanes lanes(eng.devices(), small_threads < 8 ? small_threads : 0);
+    if (lanes.ready() && tot_vecs > 0 && !getenv("ECOZ2_VQ_LOAD_SERIAL")) {
+        const double t_load = wall_s();
+        const int lr = vqb200::load_prd_frames(eng, lanes, files, Ts.data(), num_files, P);
+        if (lr > 0) {
+            fprintf(stderr, "error loading predictor %s\n", files[lr - 1]);
+            return 2;
+        }
+        if (lr < 0) return ECOZ2B200_ERR_CUDA;
+        if (getenv("ECOZ2_VQ_TIMING"))
+            fprintf(stderr, "[timing] %ld frames of %d file(s) loaded in %.1f ms by %d thread(s)\n", tot_vecs,
+                    num_files, (wall_s() - t_load) * 1e3, lanes.threads());
+    } else {
         std::vector<double> buf;
         for (int i = 0; i < num_files; i++) {
             const size_t vals = (size_t) Ts[i] * (P + 1);
@@ -215,8 +232,7 @@ int learn_files(const double *base_refl, int base_K, int P, double eps, const ch
     // here, before the run); ECOZ2_VQ_REPORT_HOST=1 keeps the host formatter
     std::unique_ptr<vqb200::DeviceTextWriter> text_writer;
     if (ctx.min_dists && !getenv("ECOZ2_VQ_REPORT_HOST")) {
-        text_writer.reset(new vqb200::DeviceTextWriter(&eng));
-        if (!text_writer->ready()) text_writer.reset();
+        if (lanes.ready()) text_writer.reset(new vqb200::DeviceTextWriter(&eng, &lanes));
     }
     ctx.text_writer = text_writer.get();
     ctx.target = target;
@@ -231,6 +247,8 @@ int learn_files(const double *base_refl, int base_K, int P, double eps, const ch
     printf("\n(devices=%d, B200 CUDA path)\n", (int) devs.size());
     const double t0 = wall_s();
     ctx.t_stage = t0;
+    if (getenv("ECOZ2_VQ_TIMING"))
+        fprintf(stderr, "[timing] %.1f ms from entry to the first pass\n", (t0 - t_call) * 1e3);
     rc = eng.learn(eps, stop_M, on_stage, on_pass, &ctx);
     printf("\nprocessing took %.2fs\n", wall_s() - t0);
     const double t_fin = wall_s();
@@ -239,6 +257,13 @@ int learn_files(const double *base_refl, int base_K, int P, double eps, const ch
         fprintf(stderr, "[timing] waited %.1f ms for the report writers after the last stage\n",
                 (wall_s() - t_fin) * 1e3);
     report.close();
+    if (getenv("ECOZ2_VQ_TIMING")) {   // where the rest of the wall time goes: tear-down in the open
+        const double t1 = wall_s();
+        text_writer.reset();
+        h.reset();
+        fprintf(stderr, "[timing] whole call %.1f ms so far; engine tear-down %.1f ms\n", (t1 - t_call) * 1e3,
+                (wall_s() - t1) * 1e3);
+    }
     if (rc) return ECOZ2B200_ERR_CUDA;
     return ctx.rc;
 }

@@ -337,6 +337,50 @@ int Engine::append_block(const double *x, long n, bool device_src) {
     return ECOZ2B200_OK;
 }
 
+int Engine::frames_put_host(long pos, const double *x, long n, const cudaStream_t *stream_by_device) {
+    if (n < 0 || pos < 0 || (n > 0 && !x) || committed_ || reserved_ == 0 || pos + n > reserved_) {
+        set_last_error("frames_put_host: outside the reserved frame set");
+        return ECOZ2B200_ERR_ARG;
+    }
+    long left = n;
+    const double *src = x;
+    cudaStream_t used[2] = {nullptr, nullptr};
+    int used_dev[2] = {-1, -1}, n_used = 0;
+    while (left > 0) {
+        const long si = pos / per_shard_;
+        const Shard &s = shards_[si];
+        const long room = s.frame_offset + per_shard_ - pos;
+        const long take = left < room ? left : room;
+        cudaStream_t st = stream_by_device[s.device];
+        CUDA_TRY(cudaSetDevice(s.device));
+        CUDA_TRY(cudaMemcpyAsync(s.x64 + (size_t) (pos - s.frame_offset) * D_, src,
+                                 sizeof(double) * (size_t) take * D_, cudaMemcpyHostToDevice, st));
+        if (n_used < 2) { used[n_used] = st; used_dev[n_used] = s.device; n_used++; }
+        else CUDA_TRY(cudaStreamSynchronize(st));   // a chunk over more than two shards: rare, just wait
+        pos += take; left -= take; src += (size_t) take * D_;
+    }
+    for (int u = 0; u < n_used; u++) {
+        CUDA_TRY(cudaSetDevice(used_dev[u]));
+        CUDA_TRY(cudaStreamSynchronize(used[u]));
+    }
+    return ECOZ2B200_OK;
+}
+
+int Engine::frames_mark_filled(long total) {
+    if (committed_ || reserved_ == 0 || total < 0 || total > reserved_) {
+        set_last_error("frames_mark_filled: outside the reserved frame set");
+        return ECOZ2B200_ERR_ARG;
+    }
+    for (Shard &s : shards_) {
+        long n = total - s.frame_offset;
+        if (n < 0) n = 0;
+        if (n > per_shard_) n = per_shard_;
+        s.n = n;
+    }
+    appended_ = total;
+    return ECOZ2B200_OK;
+}
+
 int Engine::frames_append_host(const double *x, long n) { return append_block(x, n, false); }
 int Engine::frames_append_device(const double *x_dev, long n) {
     // the source lives on devices[0]; make sure work queued there by the caller's
@@ -1124,6 +1168,9 @@ int Engine::min_dists_text_device_impl(std::vector<TextSegment> &segs) {
                 }
                 s.text_pool.push_back(tb);
             }
+            if (timing)
+                fprintf(stderr, "[timing]   text: pool of %zu x %.0f MB allocated, %.2f ms since the lengths\n",
+                        s.text_pool.size(), cap / 1e6, (now() - t2) * 1e3);
         }
         // a free buffer of the pool that is large enough; else a new one; else (pool full or out of
         // memory) wait for a writer to hand one back

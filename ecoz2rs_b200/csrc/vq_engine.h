@@ -134,6 +134,12 @@ class Engine {
                          double *discel_out, double *DD_out);
     int sigma(double avgDistortion, double *sigma_out);
     int inertia(double *inertia_out);
+    // Random-access fill of a RESERVED frame set, for loaders that read several files / ranges at
+    // once: frames [pos, pos + n) from host memory (pinned for full speed), copied on
+    // stream_by_device[device ordinal of the owning shard] and complete on return.  Thread-safe
+    // (touches no engine state); frames_mark_filled(total) then declares the set complete.
+    int frames_put_host(long pos, const double *x, long n, const cudaStream_t *stream_by_device);
+    int frames_mark_filled(long total);
     int last_assignment(int32_t *idx_out, double *mindist_out);
     // the lines "codeword,minDistortion\n" of the last pass's assignment (all local frames in append
     // order) formatted ON THE DEVICE, byte for byte the reference's "%d,%f\n" (report.c:118-121); the

@@ -18,6 +18,7 @@ constexpr int kMaxClassNameLen = 96;  // reference ecoz2/src/include/utl.h (MAX_
 
 // `.prd`  (reference ecoz2/src/lpc/prd.c:34-115):
 //   "<predictor>" ident | class name | i32 P | i32 T | T x (1+P) f64
+constexpr long kPrdDataOffset = kFileIdentLen + kMaxClassNameLen + 2 * 4;   // ident | class | P | T | data
 int prd_info(const char *path, int *P, int *T, char class_name[kMaxClassNameLen]);
 int prd_read(const char *path, double *out, long capacity_values);
 int prd_save(const char *path, const char *class_name, const double *vectors, int T, int P);

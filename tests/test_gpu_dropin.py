@@ -100,6 +100,58 @@ def test_vq_learn_from_base_codebook_and_errors(built_lib, in_tmp_cwd, monkeypat
     assert vq.vq_quantize(str(in_tmp_cwd / "nope.cbook"), [f1]) == 1
 
 
+def test_parallel_prd_loader_equals_serial(built_lib, in_tmp_cwd, monkeypatch):
+    """The loader threads of ecoz2_vq_learn (vq_hostio.cpp: several files and ranges in flight, chunks
+    placed by their global frame position) against the one-file-at-a-time fread path
+    (prd.c:34-74 order): ragged files, one of a single frame, an empty one; a truncated file is an
+    error, not a short read."""
+    import shutil
+    from ecoz2rs_b200 import formats, vq
+    from ecoz2rs_b200.synth import ar_mix
+    x = ar_mix(200_000, 36, seed=77)
+    cuts = [0, 1, 60_001, 60_001, 131_072, 199_990, 200_000]          # 1 frame, ragged, EMPTY, chunk-sized ...
+    files = []
+    for k in range(len(cuts) - 1):
+        f = str(in_tmp_cwd / "predictors" / "TRAIN" / "par" / f"part{k}.prd")
+        formats.write_prd(f, x[cuts[k]:cuts[k + 1]], "par")
+        files.append(f)
+    monkeypatch.setenv("ECOZ2_VQ_MAX_M", "32")
+    monkeypatch.setenv("ECOZ2_VQ_MIN_DISTS", "1")
+    cdir = in_tmp_cwd / "data" / "codebooks" / "par"
+    outs = {}
+    for mode in ("parallel", "serial"):
+        if mode == "serial":
+            monkeypatch.setenv("ECOZ2_VQ_LOAD_SERIAL", "1")
+        monkeypatch.setenv("ECOZ2_VQ_IO_THREADS", "5")
+        assert vq.vq_learn(36, 0.05, "par", files) == 0
+        outs[mode] = {p_.name: p_.read_bytes() for p_ in sorted(cdir.iterdir())}
+        shutil.rmtree(cdir)
+    assert sorted(outs["parallel"]) == sorted(outs["serial"]) and len(outs["serial"]) >= 5 * 2 + 2
+    # (two runs are not bit-identical: the cell sums end in FP64 atomics whose order varies -- the
+    # codebooks agree to rounding, the per-frame report, which lists the frames in FILE order, to its digits)
+    import io
+    for name, data in outs["serial"].items():
+        other = outs["parallel"][name]
+        if name.endswith(".cbook"):
+            ra = np.frombuffer(data[128:], dtype="<f8")
+            rb = np.frombuffer(other[128:], dtype="<f8")
+            assert data[:128] == other[:128] and np.allclose(ra, rb, rtol=0, atol=1e-11), name
+        elif name.endswith(".min_dists.csv"):
+            ta = np.loadtxt(io.BytesIO(data), delimiter=",", skiprows=1)
+            tb = np.loadtxt(io.BytesIO(other), delimiter=",", skiprows=1)
+            assert ta.shape == tb.shape == (200_000, 2), name
+            assert np.count_nonzero(ta[:, 0] != tb[:, 0]) <= 2, name             # FP64-level ties only
+            assert np.count_nonzero(np.abs(ta[:, 1] - tb[:, 1]) > 1.5e-6) <= 2, name
+        else:
+            assert len(other) == len(data), name
+    # truncated data section
+    bad = str(in_tmp_cwd / "predictors" / "TRAIN" / "par" / "bad.prd")
+    raw = open(files[1], "rb").read()
+    open(bad, "wb").write(raw[: len(raw) - 100])
+    monkeypatch.delenv("ECOZ2_VQ_LOAD_SERIAL")
+    assert vq.vq_learn(36, 0.05, "par", [files[0], bad, files[2]]) == 2
+
+
 def test_vq_quantize_seq_bytes_match_reference(built_lib, in_tmp_cwd):
     from ecoz2rs_b200 import formats, vq
     q = np.load(os.path.join(GOLD, "quantize_P36.npz"))
