@@ -77,6 +77,31 @@ bool files_from_csv(const std::string &csv, const std::string &tt, const std::st
     }
     return !out.empty();
 }
+// Order of Rust's PathBuf (what `list.sort()` of src/utl/mod.rs:222,244 uses): component by
+// component, not byte by byte -- "a/x.prd" sorts before "a-b/x.prd" although '-' < '/'.
+// Components as std::path::Path::components(): repeated separators and inner "." dropped; kinds order
+// RootDir < CurDir < ParentDir < Normal, normal components compare as bytes.
+struct PathKey {
+    std::vector<std::pair<int, std::string>> comps;
+    explicit PathKey(const std::string &p) {
+        size_t i = 0;
+        if (!p.empty() && p[0] == '/') comps.emplace_back(0, "");
+        bool first = true;
+        while (i <= p.size()) {
+            const size_t j = p.find('/', i);
+            const std::string c = p.substr(i, j == std::string::npos ? std::string::npos : j - i);
+            if (c == ".") { if (first && comps.empty()) comps.emplace_back(1, ""); }
+            else if (c == "..") comps.emplace_back(2, "");
+            else if (!c.empty()) comps.emplace_back(3, c);
+            if (!c.empty()) first = false;
+            if (j == std::string::npos) break;
+            i = j + 1;
+        }
+    }
+    bool operator<(const PathKey &o) const { return comps < o.comps; }
+};
+bool path_less(const std::string &a, const std::string &b) { return PathKey(a) < PathKey(b); }
+
 // src/utl/mod.rs:66-83,201-243
 bool resolve(const std::vector<std::string> &given, const std::string &tt, const std::string &cls,
              const std::string &subdir, const std::string &ext, const std::string *templ,
@@ -87,7 +112,7 @@ bool resolve(const std::vector<std::string> &given, const std::string &tt, const
         if (is_dir(g)) walk(g, ext, out);
         else if (is_file(g) && ends_with(g, ext)) out.push_back(g);
     }
-    std::sort(out.begin(), out.end());
+    std::sort(out.begin(), out.end(), path_less);
     return !out.empty();
 }
 
@@ -183,6 +208,13 @@ int main(int argc, char **argv) {
     }
     (void) have_templ;
     std::vector<std::string> files;
+    if (cmd == "files") {   // (no counterpart: prints the resolved predictor list, one per line, in run order)
+        if (!resolve(predictors, tt.empty() ? "TRAIN" : tt, have_class ? class_name : "", "predictors", ".prd",
+                     nullptr, files))
+            return 1;
+        for (const std::string &f : files) printf("%s\n", f.c_str());
+        return 0;
+    }
     if (cmd == "learn") {
         if (!base_cb.empty() && P >= 0) {
             printf("Only one of base codebook or prediction order expected\n");
@@ -224,7 +256,7 @@ int main(int argc, char **argv) {
             if (is_dir(g)) walk(g, ".cbook", cbs);
             else if (is_file(g) && ends_with(g, ".cbook")) cbs.push_back(g);
         }
-        std::sort(cbs.begin(), cbs.end());
+        std::sort(cbs.begin(), cbs.end(), path_less);
         if (cbs.empty() || !resolve(predictors, tt, "", "predictors", ".prd", nullptr, files)) {
             printf("No codebooks or predictors given\n");
             return 1;

@@ -15,6 +15,7 @@
 
 #include "../../include/ecoz2_lpc_b200.h"
 #include "lpc_front.h"
+#include "vq_engine.h"
 #include "vq_io.h"
 
 namespace {
@@ -53,6 +54,7 @@ const char *ecoz2b200_lpc_last_error(void) { return g_lpc_err.c_str(); }
 
 double ecoz2b200_dfma_peak_tflops(int device, double millis) {
     if (!have_device()) return 0.0;
+    vqb200::DeviceGuard device_guard_;
     return lpcb200::dfma_peak_tflops(device, millis);
 }
 

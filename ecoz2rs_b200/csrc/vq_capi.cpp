@@ -286,6 +286,7 @@ extern "C" {
 static int learn_entry(int prediction_order, double epsilon, const char *codebook_class_name,
                        const char *predictor_filenames[], int num_predictors, void *callback_target,
                        vq_learn_callback_t callback) {
+    vqb200::DeviceGuard device_guard_;
     // vq_learn.c:17-19
     printf("\nCodebook generation:\n\n");
     printf("prediction_order=%d class='%s'  epsilon=%g\n\n", prediction_order, codebook_class_name,
@@ -303,6 +304,7 @@ int ecoz2_vq_learn(int prediction_order, double epsilon, const char *codebook_cl
 
 static int learn_base_entry(char *base_codebook, double epsilon, const char *predictor_filenames[],
                             int num_predictors, void *callback_target, vq_learn_callback_t callback) {
+    vqb200::DeviceGuard device_guard_;
     // vq_learn.c:44-60
     int P = 0, M = 0;
     char cls[vqb200::kMaxClassNameLen];
@@ -331,6 +333,7 @@ int ecoz2_vq_learn_using_base_codebook(char *base_codebook, double epsilon,
 
 static int quantize_entry(const char *nom_raas, const char *predictor_filenames[], int num_predictors,
                           int show_filenames) {
+    vqb200::DeviceGuard device_guard_;
     // vq_quantize.c:13-111
     int P = 0, M = 0;
     char cb_class[vqb200::kMaxClassNameLen];
@@ -460,6 +463,7 @@ int ecoz2b200_device_count(void) {
 }
 
 ecoz2b200_engine *ecoz2b200_create(const int *devices, int num_devices, int P, int max_M) {
+    vqb200::DeviceGuard device_guard_;
     ecoz2b200_engine *e = new ecoz2b200_engine(devices, num_devices, P, max_M);
     if (!e->impl.ok()) {
         delete e;
@@ -467,10 +471,14 @@ ecoz2b200_engine *ecoz2b200_create(const int *devices, int num_devices, int P, i
     }
     return e;
 }
-void ecoz2b200_destroy(ecoz2b200_engine *e) { delete e; }
+void ecoz2b200_destroy(ecoz2b200_engine *e) {
+    vqb200::DeviceGuard device_guard_;
+    delete e;
+}
 
 #define ENG(e)                                  \
     if (!(e)) return ECOZ2B200_ERR_ARG;         \
+    vqb200::DeviceGuard device_guard_;          \
     Engine &eng = (e)->impl
 
 int ecoz2b200_set_mode(ecoz2b200_engine *e, int mode) { ENG(e); return eng.set_mode(mode); }
@@ -648,6 +656,7 @@ int ecoz2b200_counters_get(ecoz2b200_engine *e, ecoz2b200_counters *out) {
 }
 
 double ecoz2b200_ffma_peak_tflops(int device, double millis) {
+    vqb200::DeviceGuard device_guard_;
     if (cudaSetDevice(device) != cudaSuccess) return 0.0;
     cudaDeviceProp prop;
     if (cudaGetDeviceProperties(&prop, device) != cudaSuccess) return 0.0;

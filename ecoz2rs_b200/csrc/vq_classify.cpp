@@ -140,6 +140,7 @@ void sort_dists(const std::vector<double> &dists, std::vector<int> &ordp) {
 // to each other through the dynamic symbol table (see learn_entry in vq_capi.cpp)
 int ecoz2b200_classify_entry(char **cb_filenames, int num_codebooks, char **prd_filenames,
                                  int num_predictors, int show_ranked) {
+    vqb200::DeviceGuard device_guard_;
     // the reference asserts num_codebooks < MAX_CB_MODELS (256) but its tables have 127 class rows
     // (vq_classify.c:16-37): more models than that corrupt its memory; here they are refused
     if (!(0 < num_codebooks && num_codebooks <= kTotal && num_codebooks < kMaxModels) || num_predictors <= 0) {

@@ -8,6 +8,7 @@
 
 #include <cfloat>
 #include <chrono>
+#include <mutex>
 #include <cmath>
 #include <cstdio>
 #include <cstdlib>
@@ -23,6 +24,37 @@ void set_last_error(const std::string &msg) {
     fprintf(stderr, "ecoz2_vq_b200: %s\n", msg.c_str());
 }
 const char *get_last_error() { return g_last_error.c_str(); }
+
+namespace {
+typedef int (*CtxGetFn)(void **);
+typedef int (*CtxSetFn)(void *);
+CtxGetFn g_ctx_get = nullptr;
+CtxSetFn g_ctx_set = nullptr;
+std::once_flag g_ctx_once;
+void ctx_fns_init() {
+    void *g = nullptr, *s = nullptr;
+    cudaDriverEntryPointQueryResult q1, q2;
+    if (cudaGetDriverEntryPoint("cuCtxGetCurrent", &g, cudaEnableDefault, &q1) == cudaSuccess &&
+        cudaGetDriverEntryPoint("cuCtxSetCurrent", &s, cudaEnableDefault, &q2) == cudaSuccess &&
+        q1 == cudaDriverEntryPointSuccess && q2 == cudaDriverEntryPointSuccess && g && s) {
+        g_ctx_get = reinterpret_cast<CtxGetFn>(g);
+        g_ctx_set = reinterpret_cast<CtxSetFn>(s);
+    } else {
+        cudaGetLastError();
+    }
+}
+}  // namespace
+
+DeviceGuard::DeviceGuard() {
+    std::call_once(g_ctx_once, ctx_fns_init);
+    if (g_ctx_get && g_ctx_get(&ctx_) == 0) have_ = true;
+}
+DeviceGuard::~DeviceGuard() {
+    if (!have_ || !g_ctx_set) return;
+    void *now = nullptr;
+    if (g_ctx_get(&now) == 0 && now == ctx_) return;
+    g_ctx_set(ctx_);
+}
 
 #define CUDA_TRY(expr)                                                                     \
     do {                                                                                   \

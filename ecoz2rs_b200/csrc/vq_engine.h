@@ -15,6 +15,23 @@
 namespace vqb200 {
 
 void set_last_error(const std::string &msg);
+
+// Every extern "C" entry point leaves the calling thread's current CUDA context as it found it
+// (the engine switches devices with cudaSetDevice).  Saved and restored through the driver's
+// cuCtxGetCurrent / cuCtxSetCurrent (looked up with cudaGetDriverEntryPoint, so libcuda is not a
+// link dependency): unlike cudaSetDevice(previous) this does not create a context on a device the
+// caller had only selected implicitly.
+class DeviceGuard {
+  public:
+    DeviceGuard();
+    ~DeviceGuard();
+    DeviceGuard(const DeviceGuard &) = delete;
+    DeviceGuard &operator=(const DeviceGuard &) = delete;
+
+  private:
+    void *ctx_ = nullptr;
+    bool have_ = false;
+};
 const char *get_last_error();
 
 struct NcclApi;  // dlopen'ed libnccl (vq_nccl.cpp)

@@ -289,7 +289,10 @@ char *format_f6(char *p, double x) {
     memcpy(&bits, &x, sizeof bits);
     const int ef = (int) ((bits >> 52) & 0x7ff);
     uint64_t m = bits & ((1ull << 52) - 1);
-    if (ef == 0x7ff || ef >= 1023 + 62) return p + sprintf(p, "%f", x);   // inf / nan / huge
+    if (ef == 0x7ff || ef >= 1023 + 62) {   // inf / nan / huge: at most kMaxF6Chars (DBL_MAX has 309 digits)
+        const int w = snprintf(p, kMaxF6Chars + 1, "%f", x);
+        return p + (w < 0 ? 0 : (w > kMaxF6Chars ? kMaxF6Chars : w));
+    }
     if (bits >> 63) *p++ = '-';
     int e;
     if (ef == 0) e = -1074;            // subnormal (or zero)
@@ -337,6 +340,12 @@ bool write_min_dists_csv(const char *name, const int32_t *codeword, const double
             if (b.size() < (size_t) kLines * 64) b.resize((size_t) kLines * 64);
             char *p = b.data();
             for (long v = lo; v < hi; v++) {
+                // usual lines are < 64 chars; a huge distortion ("%f" of 1e300) needs up to kMaxF6Chars
+                if ((size_t) (p - b.data()) + 16 + kMaxF6Chars > b.size()) {
+                    const size_t at = (size_t) (p - b.data());
+                    b.resize(b.size() * 2);
+                    p = b.data() + at;
+                }
                 p = format_i32(p, codeword[v]);
                 *p++ = ',';
                 p = format_f6(p, min_dist[v]);

@@ -36,7 +36,8 @@ int seq_save(const char *path, const char *class_name, const uint16_t *seq, int 
 
 // reference ecoz2/src/utl/fileutil.c:14-119
 // "%f" of x appended at p (exact integer arithmetic, identical to printf); returns the end
-char *format_f6(char *p, double x);
+constexpr int kMaxF6Chars = 320;   // "%f" of -DBL_MAX: sign + 309 digits + "." + 6 digits
+char *format_f6(char *p, double x);   // writes at most kMaxF6Chars chars, no terminator
 // "<cbook>.min_dists.csv" (report.c:109-123), formatted by all host threads
 bool write_min_dists_csv(const char *name, const int32_t *codeword, const double *min_dist, long n);
 

@@ -50,26 +50,27 @@ def test_vq_learn_files_match_reference(built_lib, in_tmp_cwd, monkeypatch, tag,
     assert [(r[0], r[1]) for r in rows] == [(int(r[0]), int(r[1])) for r in ref_rows]
     assert [c[0] for c in calls] == [r[0] for r in rows]
     for r, rr, c in zip(rows, ref_rows, calls):
-        assert abs(r[2] - rr[2]) <= 1e-4 * rr[2] + 2e-6
-        assert abs(r[3] - rr[3]) <= 1e-4 * abs(rr[3]) + 2e-6
-        assert abs(r[4] - rr[4]) <= 1e-4 * abs(rr[4]) + 2e-6
-        assert abs(c[1] - rr[2]) <= 1e-4 * rr[2] + 2e-6      # callback carries the same values
+        # the report prints 6 decimals: equal to the last printed digit (the path's stated tolerance
+        # is 1e-4; what it achieves is the print resolution)
+        for col in (2, 3, 4):
+            assert abs(r[col] - rr[col]) <= 1e-7 * abs(rr[col]) + 1.01e-6, (r, rr)
+        assert abs(c[1] - rr[2]) <= 1e-7 * rr[2] + 1.01e-6   # callback carries the same values
         M = r[0]
         cls, refl = formats.read_cbook(str(cdir / f"eps_0.05_M_{M:04d}.cbook"))
         assert cls == "gold"
         ref_refl = g[f"refl_{M}"]
         scale = np.abs(ref_refl).max(axis=1, keepdims=True)
-        assert np.all(np.abs(refl - ref_refl) <= 1e-4 * scale)
+        assert np.all(np.abs(refl - ref_refl) <= 1e-7 * scale)   # stated tolerance 1e-4
         assert np.all(refl[:, 0] == 0)                        # reflections[.][0] stays 0
         cards = np.genfromtxt(cdir / f"eps_0.05_M_{M:04d}.cbook.cards_dists.csv", delimiter=",",
                               skip_header=1).reshape(-1, 3)
-        assert np.abs(cards[:, 1] - g[f"cards_{M}"][:, 1]).sum() <= 2
+        assert np.array_equal(cards[:, 1], g[f"cards_{M}"][:, 1])            # cardinalities: exact
+        assert np.allclose(cards[:, 2], g[f"cards_{M}"][:, 2], rtol=1e-7, atol=1.01e-6)
     md = np.genfromtxt(cdir / f"eps_0.05_M_{rows[-1][0]:04d}.cbook.min_dists.csv", delimiter=",",
                        skip_header=1)
     ref_md = g["last_min_dists"]
-    assert (md[:, 0] != ref_md[:, 0]).mean() <= 1e-3
-    same = md[:, 0] == ref_md[:, 0]
-    assert np.allclose(md[same, 1], ref_md[same, 1], rtol=0, atol=2e-6)
+    assert np.array_equal(md[:, 0], ref_md[:, 0])             # every frame's codeword
+    assert np.allclose(md[:, 1], ref_md[:, 1], rtol=0, atol=1.01e-6)   # "%f": 6 decimals
     # header lines of the report files are the reference's
     head = open(cdir / "eps_0.05.rpt.csv", encoding="utf-8").read().splitlines()[:2]
     ref_head = g["rpt_csv_text"].tobytes().decode("utf-8").splitlines()[:2]

@@ -36,3 +36,41 @@ def test_engines_on_several_devices_agree(built_lib):
         v = torch.empty((T, 37), dtype=torch.float64, device="cuda")
         assert lpc.lpa_on_signal_device(d.data_ptr(), len(sig), 32000., 36, 45, 15, v.data_ptr(), T) == T
         assert np.array_equal(v.cpu().numpy(), want)
+
+
+def test_entry_points_leave_the_current_device_alone(built_lib, tmp_path, monkeypatch):
+    """Every extern "C" entry point restores the caller's current CUDA context (DeviceGuard): a host
+    that works on device 0 and runs an engine on device 1 still finds device 0 current afterwards."""
+    from ecoz2rs_b200 import formats, vq
+    from ecoz2rs_b200.synth import ar_mix
+    if vq.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    import torch
+    torch.cuda.set_device(0)
+    torch.zeros(1, device="cuda")
+
+    def current():
+        return torch.cuda.current_device()
+
+    x = ar_mix(50_000, 36, seed=5)
+    assert current() == 0
+    with vq.VqEngine(36, max_M=64, devices=(1,)) as eng:
+        assert current() == 0
+        eng.set_frames(x)
+        assert current() == 0
+        eng.codebook_initial()
+        eng.learn(eps=0.05, stop_M=64)
+        assert current() == 0
+        eng.quantize(x[:1000])
+        assert current() == 0
+        eng.counters()
+    assert current() == 0
+    # the file-level entry point on devices (1, 0)
+    f = str(tmp_path / "predictors" / "TRAIN" / "g" / "a.prd")
+    formats.write_prd(f, x, "g")
+    monkeypatch.chdir(tmp_path)
+    monkeypatch.setenv("ECOZ2_VQ_GPUS", "1,0")
+    monkeypatch.setenv("ECOZ2_VQ_MAX_M", "16")
+    assert vq.vq_learn(36, 0.05, "g", [f]) == 0
+    assert current() == 0
+    assert vq.ffma_peak_tflops(1, 5.0) > 0 and current() == 0

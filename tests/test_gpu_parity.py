@@ -115,6 +115,34 @@ def test_kmeans_pass_teacher_forced(built_lib, frames36, oracle_run36, stage_i):
     assert _coef_close(nrefl, ref["refl"]) and _coef_close(nraas, ref["raas"])
 
 
+@pytest.mark.parametrize("t", [1e-6, 1e-9], ids=["t1e-6", "t1e-9"])
+def test_cell_distortion_from_sums_when_distortions_are_tiny(built_lib, frames36, t):
+    """The per-cell distortion is taken from the cell sums (cellsum . w - count, vq_cells.cu) instead of
+    summing per-frame values as add_to_cell does (vq_learn.i:99-106): a cancellation when every frame
+    sits almost on its codeword.  Frames = (1 - t) centre + t other with the codebook = the centres' own
+    predictors (distortion of a centre to its codeword is 0): per-frame distortions of 1e-6 .. 1e-10 at
+    hundreds of frames per cell must still come out within the tolerance of the path (1e-4).  (The
+    identity loses digits as eps_f64 * sum|x_k w_k| / mean distortion ~ 6e-15 / mean distortion: 1e-4
+    would be reached at a mean distortion of 6e-11; codebooks of real data sit at 1e-2 .. 1.)"""
+    from oracle import oracle as O
+    K, per = 32, 400
+    centres = frames36[:K]
+    refl = np.stack([O.lpca_r(c)[1] for c in centres])            # reflections of each centre's own predictor
+    raas = O.refl_to_raas(refl)
+    rng = np.random.default_rng(3)
+    other = frames36[rng.integers(K, len(frames36), size=K * per)]
+    x = (1.0 - t) * np.repeat(centres, per, axis=0) + t * other
+    ref = O.kmeans_pass(x, refl, raas)
+    assert (ref["cardd"] >= per // 2).all() and 0 < ref["DD"] < 40.0 * t * K * per
+    with _engine(36, max_M=K) as eng:
+        eng.set_frames(x)
+        eng.set_reflections(refl)
+        out = eng.kmeans_pass()
+    if np.array_equal(out["cardd"], ref["cardd"]):
+        assert np.allclose(out["discel"], ref["discel"], rtol=REL_COEF, atol=1e-13 * per)
+    assert abs(out["DD"] - ref["DD"]) <= REL_COEF * abs(ref["DD"])
+
+
 def test_empty_cells_keep_codeword(built_lib, frames36):
     """A cell that attracts no frame keeps its reflections / raas and an all-zero
     cell row (vq_learn.i:133)."""

@@ -136,6 +136,8 @@ def test_min_dists_csv_writer_matches_printf(built_lib, tmp_path):
         -rng.random(2000),
         np.array([0.0, -0.0, 5e-324, 1e-310, 0.5e-6, 1.5e-6, 2.5e-6, 0.9999995, 0.99999949999,
                   1e15, 123456789012345.678, 9.2e18, 1e19, 1e300, np.inf, -np.inf, np.nan]),
+        # 317-character lines, more of them than a formatter thread's line buffer was sized for
+        np.full(40_000, -1.7976931348623157e308), rng.random(30_000) * 1e300,
     ])
     cw = rng.integers(0, 65536, size=md.shape[0]).astype(np.int32)
     cw[:3] = [0, -1, 2 ** 31 - 1]
@@ -146,3 +148,24 @@ def test_min_dists_csv_writer_matches_printf(built_lib, tmp_path):
     want = ["%d,%f" % (int(c), float(x)) for c, x in zip(cw, md)]
     bad = [i for i, (a, b) in enumerate(zip(got[1:-1], want)) if a != b]
     assert not bad, f"{len(bad)} lines differ, first: {got[1 + bad[0]]!r} vs {want[bad[0]]!r} ({md[bad[0]]!r})"
+
+
+def test_cli_orders_files_like_rust_pathbuf(tmp_path):
+    """`list.sort()` on Vec<PathBuf> (src/utl/mod.rs:222,244) compares path COMPONENTS: "a/x.prd" comes
+    before "a-b/x.prd" although '-' < '/' as bytes.  The order is the frame order of `vq learn`."""
+    import subprocess
+    import __graft_entry__ as g
+    g.build()
+    exe = os.path.join(ROOT, "ecoz2rs_b200", "csrc", "ecoz2")
+    names = ["a/x.prd", "a-b/x.prd", "a/b/y.prd", "a.b/x.prd", "a/x-1.prd", "a/x.1.prd", "B/z.prd", "a+/q.prd"]
+    for n in names:
+        p = tmp_path / "predictors" / n
+        p.parent.mkdir(parents=True, exist_ok=True)
+        p.write_bytes(b"")
+    r = subprocess.run([exe, "vq", "files", "--predictors", "predictors"], cwd=tmp_path, capture_output=True,
+                       text=True, timeout=60)
+    assert r.returncode == 0, r.stderr
+    got = [ln[len("predictors/"):] for ln in r.stdout.split()]
+    want = sorted(names, key=lambda s: [c.encode() for c in s.split("/")])
+    assert got == want
+    assert got.index("a/x.prd") < got.index("a-b/x.prd") and sorted(names) != want

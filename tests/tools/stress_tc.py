@@ -10,6 +10,7 @@ from ecoz2rs_b200.synth import ar_mix
 from oracle import oracle as O
 
 reps = int(sys.argv[1]) if len(sys.argv) > 1 else 30
+total_bad = 0
 for P, K, N in [(12, 64, (1 << 20) + 12345), (36, 64, 300_000), (36, 512, 200_000), (12, 256, 500_000)]:
     x = ar_mix(N, P, seed=5)
     stages, _ = O.learn(x[:20000], eps=0.05, max_M=K)
@@ -29,3 +30,6 @@ for P, K, N in [(12, 64, (1 << 20) + 12345), (36, 64, 300_000), (36, 512, 200_00
                 print(f"P={P} K={K} rep {rep}: {nb} mismatches, first {b[:5]}, last {b[-3:]}, "
                       f"chunks {np.bincount(b >> 20)}", flush=True)
     print(f"P={P} K={K} N={N}: {bad_runs} bad runs of {reps}", flush=True)
+    total_bad += bad_runs
+print("STRESS", "OK" if total_bad == 0 else f"FAILED ({total_bad})")
+sys.exit(1 if total_bad else 0)
