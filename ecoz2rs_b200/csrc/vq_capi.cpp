@@ -635,6 +635,13 @@ int ecoz2b200_quantize_resident(ecoz2b200_engine *e, uint16_t *seq, double *avg)
     return eng.quantize_resident(seq, avg);
 }
 
+int ecoz2b200_quantize_models(ecoz2b200_engine *e, const double *reflections, int R, int K,
+                              const long *seg_offsets, int num_segments, uint16_t *seq_out, double *dists_out,
+                              int *one_sweep) {
+    ENG(e);
+    return eng.quantize_models(reflections, R, K, seg_offsets, num_segments, seq_out, dists_out, one_sweep);
+}
+
 int ecoz2b200_counters_reset(ecoz2b200_engine *e) { ENG(e); eng.counters_reset(); return 0; }
 int ecoz2b200_counters_get(ecoz2b200_engine *e, ecoz2b200_counters *out) {
     ENG(e);

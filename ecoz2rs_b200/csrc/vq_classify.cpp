@@ -13,6 +13,7 @@
 // the reference's accumulation (quantize.c:27, 32).
 #include "../../include/ecoz2_vq_b200.h"
 #include "vq_engine.h"
+#include "vq_hostio.h"
 #include "vq_io.h"
 
 #include <cstdio>
@@ -208,33 +209,41 @@ int ecoz2b200_classify_entry(char **cb_filenames, int num_codebooks, char **prd_
         if (!eng.ok()) return ECOZ2B200_ERR_CUDA;
         ecoz2b200_apply_mode_env(eng);
         if (eng.frames_reserve(n_total)) return ECOZ2B200_ERR_CUDA;
-        std::vector<double> buf;
-        for (Instance &it : inst) {
-            if (it.classId < 0) continue;
-            const size_t vals = (size_t) it.T * (P + 1);
-            if (buf.size() < vals) buf.resize(vals);
-            if (vqb200::prd_read(prd_filenames[it.file], buf.data(), (long) vals)) {
-                it.classId = -2;   // cannot happen after prd_info succeeded, short of a truncated file
-                memset(buf.data(), 0, vals * sizeof(double));
+        // the classifiable files, in order: loaded by the reader threads of vq_hostio.cpp
+        std::vector<const char *> lf;
+        std::vector<int> lT;
+        std::vector<size_t> lk;
+        for (size_t k = 0; k < inst.size(); k++)
+            if (inst[k].classId >= 0) {
+                lf.push_back(prd_filenames[inst[k].file]);
+                lT.push_back((int) inst[k].T);
+                lk.push_back(k);
             }
-            // pageable source: the copy has left `buf` when the call returns, so it can be reused
-            if (eng.frames_append_host(buf.data(), it.T)) return ECOZ2B200_ERR_CUDA;
+        const size_t total_bytes = (size_t) n_total * (size_t) (P + 1) * sizeof(double);
+        const int small_threads = (int) (total_bytes >> 25) + 1;
+        vqb200::IoLanes lanes(eng.devices(), small_threads < 8 ? small_threads : 0);
+        if (!lanes.ready()) return ECOZ2B200_ERR_CUDA;
+        const int lr = vqb200::load_prd_frames(eng, lanes, lf.data(), lT.data(), (int) lf.size(), P);
+        if (lr < 0) return ECOZ2B200_ERR_CUDA;
+        if (lr > 0) {   // a file shorter than its header says (prd_info had succeeded)
+            fprintf(stderr, "%s: error loading predictor.\n", lf[(size_t) lr - 1]);
+            return 1;
         }
         if (eng.frames_commit()) return ECOZ2B200_ERR_CUDA;
 
-        // ---- one search pass per model over all frames; per-file averages on the host
-        std::vector<double> md((size_t) n_total);
+        // ---- all models against all frames (one sweep when the codebook size allows it,
+        // Engine::quantize_models), per-file average distortions from the device
+        std::vector<double> refl_all;
+        for (int r = 0; r < num_models; r++) refl_all.insert(refl_all.end(), models[r].refl.begin(), models[r].refl.end());
+        std::vector<long> seg(lk.size() + 1, 0);
+        for (size_t j = 0; j < lk.size(); j++) seg[j + 1] = seg[j] + inst[lk[j]].T;
+        std::vector<double> dd((size_t) num_models * lk.size());
+        if (eng.quantize_models(refl_all.data(), num_models, num_vecs, seg.data(), (int) lk.size(), nullptr, dd.data(),
+                                nullptr))
+            return ECOZ2B200_ERR_CUDA;
         for (int r = 0; r < num_models; r++) {
-            if (eng.codebook_set_reflections(models[r].refl.data(), num_vecs)) return ECOZ2B200_ERR_CUDA;
-            if (eng.assign(nullptr, md.data(), nullptr, /*raw=*/false)) return ECOZ2B200_ERR_CUDA;
             dists[r].assign(inst.size(), 0.0);
-            for (size_t k = 0; k < inst.size(); k++) {
-                const Instance &it = inst[k];
-                if (it.classId < 0) continue;
-                double ddprm = 0;
-                for (long t = 0; t < it.T; t++) ddprm += md[(size_t) (it.first + t)];   // = ddmin - 1
-                dists[r][k] = ddprm / (double) it.T;
-            }
+            for (size_t j = 0; j < lk.size(); j++) dists[r][lk[j]] = dd[(size_t) r * lk.size() + j];
         }
     }
 

@@ -166,6 +166,12 @@ Engine::~Engine() {
             cudaFree(tb.d);
             if (tb.ready) cudaEventDestroy(tb.ready);
         }
+        if (i < mbuf_.size()) {
+            MBuf &m = mbuf_[i];
+            cudaFree(m.refl); cudaFree(m.raas); cudaFree(m.w64); cudaFree(m.w32); cudaFree(m.w1); cudaFree(m.w1max);
+            cudaFree(m.wtc); cudaFree(m.idx); cudaFree(m.seq); cudaFree(m.chunks); cudaFree(m.seg_first);
+            cudaFree(m.partial); cudaFree(m.sums);
+        }
         for (int b = 0; b < 2; b++) {
             QBuf &q = qbuf_[2 * i + b];
             cudaFree(q.x64); cudaFree(q.x32); cudaFree(q.idx); cudaFree(q.sc_mem); cudaFree(q.seq);
@@ -1367,6 +1373,242 @@ int Engine::quantize_resident(uint16_t *seq_out, double *avg) {
     CUDA_TRY(cudaGetLastError());
     harvest_times(false);
     if (avg) *avg = n_global_ > 0 ? tail[0] / (double) n_global_ : 0.0;
+    return ECOZ2B200_OK;
+}
+
+// ---------------------------------------------------------------------------------
+// R codebooks at once (cbook_quantize for a SeqProvider / vq_classify): see vq_engine.h, vq_models.cu
+int Engine::quantize_models(const double *reflections, int R, int K, const long *seg_offsets, int num_segments,
+                            uint16_t *seq_out, double *dists_out, int *one_sweep) {
+    if (one_sweep) *one_sweep = 0;
+    if (!committed_ || multi_process_ || !reflections || R < 1 || K < 1 || K > 65536 || num_segments < 0 ||
+        (num_segments > 0 && !seg_offsets)) {
+        set_last_error("quantize_models: frames not committed, one process per GPU, or bad argument");
+        return ECOZ2B200_ERR_ARG;
+    }
+    if (num_segments > 0 && (seg_offsets[0] != 0 || seg_offsets[num_segments] != n_total_)) {
+        set_last_error("quantize_models: segments must cover the resident frames");
+        return ECOZ2B200_ERR_ARG;
+    }
+    for (int f = 0; f < num_segments; f++)
+        if (seg_offsets[f + 1] < seg_offsets[f]) {
+            set_last_error("quantize_models: segment offsets must not decrease");
+            return ECOZ2B200_ERR_ARG;
+        }
+    static const bool timing = getenv("ECOZ2_VQ_TIMING") != nullptr;
+    auto now = [] { return std::chrono::duration<double>(std::chrono::steady_clock::now().time_since_epoch()).count(); };
+    double t_mark = now();
+    auto mark = [&](const char *what) {
+        if (!timing) return;
+        sync_all();
+        const double t = now();
+        fprintf(stderr, "[timing]   quantize_models: %s %.2f ms\n", what, (t - t_mark) * 1e3);
+        t_mark = t;
+    };
+    if (mbuf_.size() != shards_.size()) mbuf_.resize(shards_.size());
+    // one sweep: the concatenation padded to whole 256-column tiles with copies of the first model
+    long r_pad = R;
+    while (((long) r_pad * K) % 256 != 0) r_pad++;
+    const long cols = r_pad * K;
+    const bool fused = mode_ == ECOZ2B200_MODE_TENSOR && assign_tc_models_supported(K, D_, cols) &&
+                       cols <= (1L << 20) && !getenv("ECOZ2_VQ_MODELS_SERIAL");
+    if (!fused && K > max_M_) {
+        set_last_error("quantize_models: codebook larger than the engine's max_M");
+        return ECOZ2B200_ERR_ARG;
+    }
+    const float err_tc = (float) (kappa_tc_ * ldexp(1.0, -24));
+    const size_t cb_vals = (size_t) K * D_;
+    const long kChunkFrames = 1024;
+    std::vector<std::vector<long>> h_chunks(shards_.size());
+    std::vector<std::vector<int>> h_first(shards_.size());
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        MBuf &b = mbuf_[i];
+        if (s.n <= 0) continue;
+        CUDA_TRY(cudaSetDevice(s.device));
+        // ---- buffers
+        const size_t idx_items = (size_t) r_pad * (size_t) s.n;
+        if (b.idx_items < idx_items) {
+            CUDA_TRY(cudaStreamSynchronize(s.stream));
+            cudaFree(b.idx); b.idx = nullptr; b.idx_items = 0;
+            CUDA_TRY(cudaMalloc(&b.idx, sizeof(int32_t) * idx_items));
+            b.idx_items = idx_items;
+        }
+        if (b.cols < cols) {
+            CUDA_TRY(cudaStreamSynchronize(s.stream));
+            cudaFree(b.refl); cudaFree(b.raas); cudaFree(b.w64); cudaFree(b.w32); cudaFree(b.w1); cudaFree(b.w1max);
+            cudaFree(b.wtc);
+            b = MBuf{.idx = b.idx, .idx_items = b.idx_items, .seq = b.seq, .seq_items = b.seq_items,
+                     .chunks = b.chunks, .seg_first = b.seg_first, .partial = b.partial, .sums = b.sums,
+                     .chunk_cap = b.chunk_cap, .seg_cap = b.seg_cap, .partial_cap = b.partial_cap,
+                     .sums_cap = b.sums_cap};
+            CUDA_TRY(cudaMalloc(&b.refl, sizeof(double) * (size_t) cols * D_));
+            CUDA_TRY(cudaMalloc(&b.raas, sizeof(double) * (size_t) cols * D_));
+            CUDA_TRY(cudaMalloc(&b.w64, sizeof(double) * (size_t) ((cols + 63) / 64) * 64 * D_));
+            CUDA_TRY(cudaMalloc(&b.w32, sizeof(float) * (size_t) ((cols + 127) / 128) * 128 * D_));
+            CUDA_TRY(cudaMalloc(&b.w1, sizeof(float) * (size_t) ((cols + 127) / 128) * 128));
+            CUDA_TRY(cudaMalloc(&b.w1max, sizeof(float) * 4));
+            if (assign_tc_supported((int) cols, D_))
+                CUDA_TRY(cudaMalloc(&b.wtc, sizeof(float) * tc_codebook_floats((int) cols, D_)));
+            b.cols = cols;
+        }
+        // ---- codebooks: reflections -> raas for all models (padding = copies of model 0)
+        CUDA_TRY(cudaMemcpyAsync(b.refl, reflections, sizeof(double) * cb_vals * R, cudaMemcpyHostToDevice, s.stream));
+        for (long m = R; m < r_pad; m++)
+            CUDA_TRY(cudaMemcpyAsync(b.refl + cb_vals * m, b.refl, sizeof(double) * cb_vals, cudaMemcpyDeviceToDevice,
+                                     s.stream));
+        launch_refl_to_raas(b.refl, b.raas, (int) cols, D_, s.stream);
+        ctr_.kernel_launches++;
+    }
+    // ---- chunk table per shard for the per-(model, file) sums (chunks never cross a segment)
+    std::vector<double> sums((size_t) num_segments * R, 0.0);
+    std::vector<size_t> n_chunks_of(shards_.size(), 0);
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        MBuf &b = mbuf_[i];
+        if (s.n <= 0 || num_segments == 0 || !dists_out) continue;
+        CUDA_TRY(cudaSetDevice(s.device));
+        std::vector<long> &ch = h_chunks[i];
+        std::vector<int> &first = h_first[i];
+        const long lo = s.frame_offset, hi = s.frame_offset + s.n;
+        for (int f = 0; f < num_segments; f++) {
+            first.push_back((int) (ch.size() / 2));
+            const long a = seg_offsets[f] > lo ? seg_offsets[f] : lo;
+            const long e = seg_offsets[f + 1] < hi ? seg_offsets[f + 1] : hi;
+            for (long c = a; c < e; c += kChunkFrames) {
+                ch.push_back(c - lo);
+                ch.push_back(e - c < kChunkFrames ? e - c : kChunkFrames);
+            }
+        }
+        first.push_back((int) (ch.size() / 2));
+        const size_t n_chunks = ch.size() / 2;
+        n_chunks_of[i] = n_chunks;
+        if (n_chunks == 0) continue;
+        if (b.chunk_cap < n_chunks || b.seg_cap < (size_t) num_segments + 1 || b.partial_cap < n_chunks * R ||
+            b.sums_cap < (size_t) num_segments * R) {
+            CUDA_TRY(cudaStreamSynchronize(s.stream));
+            cudaFree(b.chunks); cudaFree(b.seg_first); cudaFree(b.partial); cudaFree(b.sums);
+            b.chunks = nullptr; b.seg_first = nullptr; b.partial = nullptr; b.sums = nullptr;
+            CUDA_TRY(cudaMalloc(&b.chunks, sizeof(long) * 2 * n_chunks));
+            CUDA_TRY(cudaMalloc(&b.seg_first, sizeof(int) * ((size_t) num_segments + 1)));
+            CUDA_TRY(cudaMalloc(&b.partial, sizeof(double) * n_chunks * R));
+            CUDA_TRY(cudaMalloc(&b.sums, sizeof(double) * (size_t) num_segments * R));
+            b.chunk_cap = n_chunks; b.seg_cap = (size_t) num_segments + 1; b.partial_cap = n_chunks * R;
+            b.sums_cap = (size_t) num_segments * R;
+        }
+        CUDA_TRY(cudaMemcpyAsync(b.chunks, ch.data(), sizeof(long) * ch.size(), cudaMemcpyHostToDevice, s.stream));
+        CUDA_TRY(cudaMemcpyAsync(b.seg_first, first.data(), sizeof(int) * first.size(), cudaMemcpyHostToDevice, s.stream));
+    }
+    mark("buffers + codebooks");
+    if (fused) {
+        for (size_t i = 0; i < shards_.size(); i++) {
+            Shard &s = shards_[i];
+            MBuf &b = mbuf_[i];
+            if (s.n <= 0) continue;
+            CUDA_TRY(cudaSetDevice(s.device));
+            launch_prepare_codebook(b.raas, (int) cols, D_, b.w32, b.w64, b.w1, b.w1max, s.stream);
+            launch_prepare_codebook_tc(b.raas, (int) cols, D_, b.wtc, b.w1max, err_tc, s.stream);
+            CUDA_TRY(cudaMemsetAsync(s.sc.counters, 0, 4 * sizeof(int32_t), s.stream));
+            debug_poison(s);
+            const long seg_cap = s.sc.cap < (1L << 30) ? s.sc.cap : (1L << 30);
+            launch_assign_tc_models(s.x32, s.n, D_, b.wtc, K, cols, s.sc, err_tc, b.idx, s.n, s.sc.min_key,
+                                    (int) seg_cap, s.num_sms, s.stream);
+            mark("search");
+            launch_models_recheck(s.x64, D_, b.raas, K, s.sc.min_key, s.sc.counters, (int) seg_cap, b.idx, s.n,
+                                  s.num_sms, s.stream);
+            vq_stat_add<<<1, 32, 0, s.stream>>>(s.sc.counters, s.dstat + 3);
+            ctr_.kernel_launches += 5;
+            ctr_.evals += (double) s.n * (double) R * (double) K;
+        }
+        // more pairs inside the bound than the key list holds: cannot happen short of degenerate
+        // codebooks (every frame of every model); then the serial route is the answer
+        for (size_t i = 0; i < shards_.size(); i++) {
+            Shard &s = shards_[i];
+            if (s.n <= 0) continue;
+            CUDA_TRY(cudaSetDevice(s.device));
+            int32_t fc = 0;
+            CUDA_TRY(cudaMemcpyAsync(&fc, s.sc.counters, sizeof(int32_t), cudaMemcpyDeviceToHost, s.stream));
+            CUDA_TRY(cudaStreamSynchronize(s.stream));
+            if ((long) fc > s.sc.cap) {
+                set_last_error("quantize_models: too many ambiguous (model, frame) pairs for one sweep");
+                return ECOZ2B200_ERR_ARG;
+            }
+        }
+        if (one_sweep) *one_sweep = 1;
+    } else {
+        for (int m = 0; m < R; m++) {
+            int rc = codebook_set_reflections(reflections + cb_vals * m, K);
+            if (rc) return rc;
+            const PackedLayout L{K_, D_};
+            for (size_t i = 0; i < shards_.size(); i++) {
+                Shard &s = shards_[i];
+                if (s.n <= 0) continue;
+                CUDA_TRY(cudaSetDevice(s.device));
+                CUDA_TRY(cudaMemsetAsync(s.packed + L.dd(), 0, 2 * sizeof(double), s.stream));
+                pass_kernels(s, s.x64, s.x32, s.n, mbuf_[i].idx + (size_t) m * s.n, s.sc, s.mindist, nullptr, false);
+                // the pass has left ddmin - 1 of every frame in s.mindist: per-chunk sums for this model
+                if (n_chunks_of[i] > 0) {
+                    launch_chunk_sums(s.mindist, mbuf_[i].chunks, (int) n_chunks_of[i], R, m, mbuf_[i].partial, s.stream);
+                    ctr_.kernel_launches++;
+                }
+            }
+        }
+    }
+    mark("search + re-evaluation");
+    // ---- distortions per (model, segment)
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        MBuf &b = mbuf_[i];
+        if (n_chunks_of[i] == 0) continue;
+        CUDA_TRY(cudaSetDevice(s.device));
+        if (fused) {
+            launch_models_distortion(s.x64, D_, b.raas, K, R, b.idx, s.n, b.chunks, (int) n_chunks_of[i], b.partial,
+                                     s.num_sms, s.stream);
+            ctr_.kernel_launches++;
+        }
+        launch_models_segments(b.partial, b.seg_first, num_segments, R, b.sums, s.stream);
+        ctr_.kernel_launches++;
+    }
+    mark("distortions");
+    // ---- results to the host
+    std::vector<std::vector<double>> h_sums(shards_.size());
+    for (size_t i = 0; i < shards_.size(); i++) {
+        Shard &s = shards_[i];
+        MBuf &b = mbuf_[i];
+        if (s.n <= 0) continue;
+        CUDA_TRY(cudaSetDevice(s.device));
+        if (dists_out && num_segments > 0 && !h_chunks[i].empty()) {
+            h_sums[i].resize((size_t) num_segments * R);
+            CUDA_TRY(cudaMemcpyAsync(h_sums[i].data(), b.sums, sizeof(double) * h_sums[i].size(), cudaMemcpyDeviceToHost,
+                                     s.stream));
+        }
+        if (seq_out) {
+            const size_t items = (size_t) R * (size_t) s.n;
+            if (b.seq_items < items) {
+                CUDA_TRY(cudaStreamSynchronize(s.stream));
+                cudaFree(b.seq); b.seq = nullptr; b.seq_items = 0;
+                CUDA_TRY(cudaMalloc(&b.seq, sizeof(uint16_t) * items));
+                b.seq_items = items;
+            }
+            launch_idx_to_u16(b.idx, b.seq, items, s.stream);
+            ctr_.kernel_launches++;
+            for (int m = 0; m < R; m++)
+                CUDA_TRY(cudaMemcpyAsync(seq_out + (size_t) m * n_total_ + s.frame_offset, b.seq + (size_t) m * s.n,
+                                         sizeof(uint16_t) * (size_t) s.n, cudaMemcpyDeviceToHost, s.stream));
+        }
+    }
+    int rc = sync_all();
+    if (rc) return rc;
+    CUDA_TRY(cudaGetLastError());
+    if (dists_out) {
+        for (size_t i = 0; i < shards_.size(); i++)
+            for (size_t k = 0; k < h_sums[i].size(); k++) sums[k] += h_sums[i][k];
+        for (int m = 0; m < R; m++)
+            for (int f = 0; f < num_segments; f++) {
+                const long T = seg_offsets[f + 1] - seg_offsets[f];
+                dists_out[(size_t) m * num_segments + f] = T > 0 ? sums[(size_t) f * R + m] / (double) T : 0.0;
+            }
+    }
     return ECOZ2B200_OK;
 }
 

@@ -181,6 +181,15 @@ class Engine {
     int learn(double eps, int stop_M, ecoz2b200_stage_cb on_stage, ecoz2b200_pass_cb on_pass,
               void *ctx);
     int quantize_host(const double *x, long T, uint16_t *seq_out, double *avg);
+    // cbook_quantize (vq/vq.c:154-157) of ALL resident frames against R codebooks of K codewords
+    // (reflections [R][K][D]) -- the work of a SeqProvider (vq/vq.c:285-315) / of vq_classify.c:265-280
+    // for every predictor file at once.  Segment f = frames [seg_offsets[f], seg_offsets[f + 1]) of the
+    // append order (a predictor file).  seq_out [R][n] symbols (optional), dists_out [R][num_segments]
+    // average distortion (the `dist` of cbook_quantize) (optional).  The engine's own codebook is
+    // left alone on the one-sweep route (tensor mode, K = 32, 64, 128 or 256) and is
+    // overwritten by the last model otherwise.  *one_sweep (optional) says which route ran.
+    int quantize_models(const double *reflections, int R, int K, const long *seg_offsets, int num_segments,
+                        uint16_t *seq_out, double *dists_out, int *one_sweep);
     int quantize_resident(uint16_t *seq_out, double *avg);
 
     void counters_reset();
@@ -245,6 +254,16 @@ class Engine {
     struct QBuf { double *x64 = nullptr; float *x32 = nullptr; int32_t *idx = nullptr;
                   void *sc_mem = nullptr; SearchScratch sc; uint16_t *seq = nullptr; long cap = 0; };
     std::vector<QBuf> qbuf_;
+    // scratch of quantize_models (per shard, lazily allocated, grows)
+    struct MBuf {
+        double *refl = nullptr, *raas = nullptr, *w64 = nullptr; float *w32 = nullptr, *w1 = nullptr, *w1max = nullptr, *wtc = nullptr;
+        long cols = 0;                       // codewords the operand buffers are sized for
+        int32_t *idx = nullptr; size_t idx_items = 0;
+        uint16_t *seq = nullptr; size_t seq_items = 0;
+        long *chunks = nullptr; int *seg_first = nullptr; double *partial = nullptr, *sums = nullptr;
+        size_t chunk_cap = 0, seg_cap = 0, partial_cap = 0, sums_cap = 0;
+    };
+    std::vector<MBuf> mbuf_;
     int append_block(const double *x, long n, bool device_src);
     int rank_ = 0, world_ = 1;
     bool multi_process_ = false;

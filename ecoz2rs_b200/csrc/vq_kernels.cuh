@@ -106,6 +106,24 @@ void launch_prepare_codebook_tc(const double *raas, int K, int D, float *wtc, co
 // counts (FP64 reductions issued by otherwise idle warps while the tensor core works); the flagged
 // frames follow through launch_cell_fixup after launch_recheck, then launch_cell_finish.
 bool assign_tc_fuses_cells(int K, int D);
+// R codebooks of K codewords in ONE sweep (wtc = launch_prepare_codebook_tc of the R * K concatenated
+// raas rows, total_cols = R * K padded to a multiple of 256 with copies of real codewords):
+// idx_out[model][idx_stride] model-local argmins; (model << 40 | frame) keys of the pairs inside the
+// error bound in seg_key (count in sc.counters[0], may exceed seg_cap: then keys were dropped).
+bool assign_tc_models_supported(int K, int D, long total_cols);
+void launch_assign_tc_models(const float *x32, long n, int D, const float *wtc, int K, long total_cols,
+                             const SearchScratch &sc, float err_scale, int32_t *idx_out, long idx_stride,
+                             unsigned long long *seg_key, int seg_cap, int num_sms, cudaStream_t s);
+// all-FP64 argmin (strict <, first index wins: quantize.c:14-30) of every (model, frame) key over the
+// model's K codewords; raas_all [R * K][D].  One warp per key.
+void launch_models_recheck(const double *x64, int D, const double *raas_all, int K, const unsigned long long *keys,
+                           const int32_t *count, int cap, int32_t *idx_out, long idx_stride, int num_sms,
+                           cudaStream_t s);
+// FP64 distortion - 1 of every frame's winner in every model, summed per chunk of frames:
+// chunks[c] = {first frame, frames} (never across a segment boundary), partial[c][R].  Deterministic.
+void launch_models_distortion(const double *x64, int D, const double *raas_all, int K, int R, const int32_t *idx_all,
+                              long idx_stride, const long *chunks, int num_chunks, double *partial, int num_sms,
+                              cudaStream_t s);
 void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
                       const int32_t *list, const int32_t *list_count, const SearchScratch &sc,
                       bool flag, const float *w1, const float *w1max, float err_scale, int32_t *idx,
@@ -182,6 +200,12 @@ void launch_pass_small(const double *x64, long n, int D, const double *raas, int
 // ---- (c) centroid update / split ----------------------------------------------
 // calculate_reflections (vq_learn.i:125-155): for every cell with count > 0,
 // Levinson-Durbin on the raw cell sum -> refl, raas; cell sum /= errPred.
+void launch_chunk_sums(const double *md, const long *chunks, int num_chunks, int R, int m, double *partial,
+                       cudaStream_t s);
+void launch_models_segments(const double *partial, const int *seg_first_chunk, int num_segments, int R, double *sums,
+                            cudaStream_t s);
+// idx (model-local, < 65536) -> u16 symbols
+void launch_idx_to_u16(const int32_t *idx, uint16_t *seq, size_t n, cudaStream_t s);
 void launch_centroids(double *packed, int K, int D, double *refl, double *raas,
                       cudaStream_t s);
 // grow_codebook (vq_learn.i:47-72): refl K -> 2K rows (x 0.99f / x 1.01f), then

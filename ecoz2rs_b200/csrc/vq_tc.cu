@@ -78,6 +78,14 @@ struct TcParams {
     const double *x64;
     double *cells;              // packed cell sums [K][D]
     int32_t *hist;              // frames per cell
+    // several codebooks in one sweep (SEG instance; cbook_quantize of R models, vq/vq.c:154-157,
+    // 285-315): the K columns are R codebooks of seg_cols codewords each (seg_cols = 32 .. BN dividing
+    // BN, or a multiple of BN); the argmin restarts at every boundary, idx_out is [R][idx_stride] with
+    // model-local indices, frames inside the bound are reported as keys (model << 40 | frame)
+    int seg_cols;
+    long idx_stride;
+    unsigned long long *seg_key;
+    int seg_cap;
     unsigned long long *prof;   // dev (exp bit 256): per CTA {SM clocks, ns} of the kernel
     int exp;                    // dev experiments (ECOZ2_VQ_TC_EXP): bit mask 1 no record path, 2 trivial reduction, 4 no tcgen05.ld, 8 no MMA, 16 no tcgen05.st, 32 no B copy
 };
@@ -495,7 +503,7 @@ struct Tc2Smem {
 };
 }  // namespace
 
-template <int KS, bool FILTER, bool DBG, bool H16, bool CELLS>
+template <int KS, bool FILTER, bool DBG, bool H16, bool CELLS, bool SEG = false>
 __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) {
     const int exp = DBG ? p.exp : 0;
     unsigned long long prof_c0 = 0, prof_t0 = 0;
@@ -849,6 +857,25 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             FilterState fst;
             fst.init();
             if (FILTER && row >= 0) thr = p.flag_ub[base + r];
+            // SEG: a codebook of the concatenation is complete -> its argmin, bound test, restart
+            auto seg_done = [&](int col0) {
+                const float sbest = est.best;
+                float ssecond;
+                int sidx;
+                epi_finish(est, ssecond, sidx);
+                if (row >= 0) {
+                    const int model = col0 / p.seg_cols;
+                    p.idx_out[(long) model * p.idx_stride + row] = sidx - col0;
+                    const float x0 = s_x0[((it & 3) * 2 + h) * kBM + r];
+                    const float ub = fmaf(e2 * x0, p.w1[sidx], sbest);
+                    if (!(ssecond > ub)) {
+                        const int pos = atomicAdd(p.flag_count, 1);
+                        if (pos < p.seg_cap)
+                            p.seg_key[pos] = ((unsigned long long) model << 40) | (unsigned long long) row;
+                    }
+                }
+                est.init();
+            };
             for (int t = 0; t < n_wtiles; t++, u++) {
                 const uint32_t buf = wide ? 0u : (u & 1), acc_ph = wide ? (u & 1) : ((u >> 1) & 1);
                 const long long pc0 = DBG ? clock64() : 0;
@@ -858,7 +885,18 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 const int nv = K - t * BN < BN ? K - t * BN : BN;
                 const uint32_t taddr = lane_addr + (wide ? (uint32_t) h * 256u : (2 * buf + h) * 128u);
                 const bool fast = !FILTER && (!DBG || (!(exp & 7) && p.dump == nullptr));
-                if (fast && nv == 256) {
+                if (SEG) {   // whole tiles only (the host pads the concatenation)
+                    if (p.seg_cols < BN) {
+                        if (BN == 256) epi_tile_seg<256>(taddr, t * BN, p.seg_cols, est, &sm->acc_empty[2 * buf + h], seg_done);
+                        else if (BN == 128) epi_tile_seg<128>(taddr, t * BN, p.seg_cols, est, &sm->acc_empty[2 * buf + h], seg_done);
+                        else epi_tile_seg<64>(taddr, t * BN, p.seg_cols, est, &sm->acc_empty[2 * buf + h], seg_done);
+                    } else {
+                        if (BN == 256) epi_tile_full<256>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
+                        else if (BN == 128) epi_tile_full<128>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
+                        else epi_tile_full<64>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
+                        if (((t + 1) * BN) % p.seg_cols == 0) seg_done((t + 1) * BN - p.seg_cols);
+                    }
+                } else if (fast && nv == 256) {
                     epi_tile_full<256>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
                 } else if (fast && nv == 128) {
                     epi_tile_full<128>(taddr, t * BN, est, &sm->acc_empty[2 * buf + h]);
@@ -877,6 +915,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 epi_filter_flush(fst, (int) (base + r), row, p);
                 continue;
             }
+            if (SEG) continue;
             float best = est.best, second;
             int bidx;
             epi_finish(est, second, bidx);
@@ -1193,16 +1232,17 @@ static int tc2_raw_bufs(int D, int BN) {
     return n;
 }
 
-template <int KS, bool FILTER, bool DBG, bool H16, bool CELLS>
+template <int KS, bool FILTER, bool DBG, bool H16, bool CELLS, bool SEG = false>
 static void launch_tc2_inst2(const TcParams &p, long grid, cudaStream_t s) {
     // per device (function attributes belong to the context): set on every launch, ~1 us
-    cudaFuncSetAttribute(vq_assign_tc2<KS, FILTER, DBG, H16, CELLS>,
+    cudaFuncSetAttribute(vq_assign_tc2<KS, FILTER, DBG, H16, CELLS, SEG>,
                          cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024);
-    vq_assign_tc2<KS, FILTER, DBG, H16, CELLS><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN, p.raw_bufs), s>>>(p);
+    vq_assign_tc2<KS, FILTER, DBG, H16, CELLS, SEG><<<(unsigned) grid, k2Threads, tc2_smem_bytes(p.D, p.BN, p.raw_bufs), s>>>(p);
 }
 template <int KS, bool H16>
 static void launch_tc2_inst(const TcParams &p, long grid, cudaStream_t s) {
-    if (p.cand != nullptr) launch_tc2_inst2<KS, true, false, H16, false>(p, grid, s);
+    if (H16 && p.seg_cols != 0) launch_tc2_inst2<KS, false, false, H16, false, H16>(p, grid, s);
+    else if (p.cand != nullptr) launch_tc2_inst2<KS, true, false, H16, false>(p, grid, s);
     else if (p.exp != 0 || p.dump != nullptr) launch_tc2_inst2<KS, false, true, H16, false>(p, grid, s);
     else if (H16 && p.cells != nullptr) launch_tc2_inst2<KS, false, false, H16, H16>(p, grid, s);
     else launch_tc2_inst2<KS, false, false, H16, false>(p, grid, s);
@@ -1323,6 +1363,32 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
     vq_assign_tc<<<(unsigned) grid, kThreads, smem, s>>>(p);
 }
 
+
+// R codebooks of K codewords each, concatenated (wtc built from the R * K raas rows, padded by the
+// caller to whole tiles): one sweep over the frames, idx_out[R][idx_stride] model-local argmins,
+// (model, frame) pairs inside the error bound as keys in seg_key (count in sc.counters[0]; pairs
+// beyond seg_cap are dropped -- the caller checks the count).
+bool assign_tc_models_supported(int K, int D, long total_cols) {
+    if (!(tc_variant() == 2 && tc_f16() && assign_tc_supported((int) total_cols, D))) return false;
+    if (total_cols < 256 || total_cols % 256 != 0) return false;
+    // (larger codebooks: the search is compute-bound anyway and the FP64 scan of the ambiguous pairs,
+    // K evaluations each, would cost more than the R - 1 frame sweeps saved)
+    return K == 32 || K == 64 || K == 128 || K == 256;
+}
+void launch_assign_tc_models(const float *x32, long n, int D, const float *wtc, int K, long total_cols,
+                             const SearchScratch &sc, float err_scale, int32_t *idx_out, long idx_stride,
+                             unsigned long long *seg_key, int seg_cap, int num_sms, cudaStream_t s) {
+    if (n <= 0) return;
+    TcParams p{};
+    p.x = x32; p.n_frames = n; p.D = D; p.ksteps = tc_ksteps(D);
+    p.wtc = wtc; p.K = (int) total_cols; p.BN = tc_tile_cols((int) total_cols, D);
+    p.err_scale = err_scale; p.idx_out = idx_out;
+    p.flag_count = sc.counters + 0;
+    p.seg_cols = K; p.idx_stride = idx_stride; p.seg_key = seg_key; p.seg_cap = seg_cap;
+    long tiles = (n + 2 * kBM - 1) / (2 * kBM);
+    long grid = tiles < num_sms ? tiles : num_sms;
+    launch_tc2(p, grid, s);
+}
 
 bool filter_tc_supported() { return tc_variant() == 2; }
 

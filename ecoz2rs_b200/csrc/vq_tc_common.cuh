@@ -351,6 +351,42 @@ __device__ __forceinline__ void epi_tile_full(uint32_t taddr, int tcol0, EpiStat
         }
     }
 }
+
+// Same sweep over a tile that holds SEVERAL codebooks of seg_cols columns each (seg_cols a multiple
+// of 32 that divides NCOLS): seg_done(first global column of the finished codebook) is called after
+// the last 32 columns of each one (it finishes the argmin state and resets it).
+template <int NCOLS, class F>
+__device__ __forceinline__ void epi_tile_seg(uint32_t taddr, int tcol0, int seg_cols, EpiState &est,
+                                             uint64_t *release_bar, F &&seg_done) {
+    constexpr int NS = NCOLS / 32;
+    uint32_t ra[32], rb[32];
+    tmem_ld32(taddr, ra);
+#pragma unroll
+    for (int s = 0; s < NS; s += 2) {
+        tmem_ld_wait();
+        if (s + 1 < NS) {
+            tmem_ld32(taddr + 32 * (s + 1), rb);
+        } else {
+            tc_fence_before();
+            __syncwarp();
+            if ((threadIdx.x & 31) == 0) mbar_arrive(release_bar);
+        }
+        epi_step32(ra, tcol0 + 32 * s, 32, est, 0);
+        if ((32 * (s + 1)) % seg_cols == 0) seg_done(tcol0 + 32 * (s + 1) - seg_cols);
+        if (s + 1 < NS) {
+            tmem_ld_wait();
+            if (s + 2 < NS) {
+                tmem_ld32(taddr + 32 * (s + 2), ra);
+            } else {
+                tc_fence_before();
+                __syncwarp();
+                if ((threadIdx.x & 31) == 0) mbar_arrive(release_bar);
+            }
+            epi_step32(rb, tcol0 + 32 * (s + 1), 32, est, 0);
+            if ((32 * (s + 2)) % seg_cols == 0) seg_done(tcol0 + 32 * (s + 2) - seg_cols);
+        }
+    }
+}
 }  // namespace
 
 }  // namespace vqb200

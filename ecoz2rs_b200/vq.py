@@ -70,7 +70,7 @@ EXPORTED_SYMBOLS = (
     "ecoz2b200_assign", "ecoz2b200_kmeans_pass", "ecoz2b200_kmeans_pass_host", "ecoz2b200_sigma",
     "ecoz2b200_inertia",
     "ecoz2b200_last_assignment", "ecoz2b200_learn",
-    "ecoz2b200_quantize_host", "ecoz2b200_quantize_resident",
+    "ecoz2b200_quantize_host", "ecoz2b200_quantize_resident", "ecoz2b200_quantize_models",
     "ecoz2b200_counters_reset", "ecoz2b200_counters_get", "ecoz2b200_ffma_peak_tflops",
     "ecoz2b200_prd_info", "ecoz2b200_prd_read", "ecoz2b200_cbook_save", "ecoz2b200_cbook_info",
     "ecoz2b200_cbook_read", "ecoz2b200_seq_save",
@@ -135,6 +135,7 @@ def lib():
             "ecoz2b200_learn": (i, [vp, d, i, _STAGE_CB, _PASS_CB, vp]),
             "ecoz2b200_quantize_host": (i, [vp, vp, l, vp, _dp]),
             "ecoz2b200_quantize_resident": (i, [vp, vp, _dp]),
+            "ecoz2b200_quantize_models": (i, [vp, vp, i, i, vp, i, vp, vp, C.POINTER(C.c_int)]),
             "ecoz2b200_counters_reset": (i, [vp]),
             "ecoz2b200_counters_get": (i, [vp, C.POINTER(Counters)]),
             "ecoz2b200_ffma_peak_tflops": (d, [i, d]),
@@ -426,6 +427,24 @@ class VqEngine:
         _check(lib().ecoz2b200_quantize_resident(self._h, seq.ctypes.data if want_seq else None,
                                                  C.byref(avg)), "quantize_resident")
         return seq, avg.value
+
+    def quantize_models(self, reflections: np.ndarray, seg_offsets=None, want_seq: bool = True):
+        """cbook_quantize of all resident frames against R codebooks at once (reflections [R, K, 1+P]);
+        seg_offsets = frame offsets of the predictor files (default: one segment).
+        -> (seq [R, n] u16 or None, dists [R, num_segments], one_sweep)."""
+        r = np.ascontiguousarray(reflections, dtype=np.float64)
+        assert r.ndim == 3 and r.shape[2] == self.D
+        R, K = r.shape[0], r.shape[1]
+        n = self.num_frames
+        so = np.ascontiguousarray([0, n] if seg_offsets is None else seg_offsets, dtype=np.int64)
+        nseg = len(so) - 1
+        seq = np.empty((R, n), np.uint16) if want_seq else None
+        dists = np.empty((R, nseg), np.float64)
+        one = C.c_int(0)
+        _check(lib().ecoz2b200_quantize_models(self._h, r.ctypes.data, R, K, so.ctypes.data, nseg,
+                                               seq.ctypes.data if want_seq else None, dists.ctypes.data,
+                                               C.byref(one)), "quantize_models")
+        return seq, dists, bool(one.value)
 
     def quantize_resident_ptr(self, seq_ptr: int) -> float:
         """Resident frames -> u16 symbols at host address seq_ptr (pinned memory for full speed)."""

@@ -310,6 +310,21 @@ int ecoz2b200_quantize_host(ecoz2b200_engine *e, const double *x, long T,
 int ecoz2b200_quantize_resident(ecoz2b200_engine *e, uint16_t *seq_out,
                                 double *avg_distortion);
 
+/* cbook_quantize (ecoz2/src/vq/vq.c:154-157) of ALL resident frames against R codebooks of K codewords
+ * at once: the work a SeqProvider does per predictor file for `hmm classify` (vq/vq.c:285-315:
+ * next_seq.sequences[r], next_seq.dists[r]) and vq_classify.c:265-280 per (model, file), here for every
+ * file in one call.  reflections [R][K][1+P] (what the R `.cbook` files hold); segment f = frames
+ * [seg_offsets[f], seg_offsets[f+1]) of the append order = predictor file f (seg_offsets[0] = 0,
+ * seg_offsets[num_segments] = frames_count()).  seq_out [R][frames_count()] symbols (or NULL),
+ * dists_out [R][num_segments] = the `dist` cbook_quantize returns for (model r, file f) (or NULL).
+ * In tensor mode with K = 32, 64, 128 or 256 all R searches are ONE sweep over the
+ * frames (the codebooks concatenated, the argmin restarted at every codebook; *one_sweep = 1) and
+ * the engine's own codebook is untouched; otherwise R sweeps, and the engine's codebook ends as
+ * model R-1.  Not available with one process per GPU (comm_init).                              */
+int ecoz2b200_quantize_models(ecoz2b200_engine *e, const double *reflections, int R, int K,
+                              const long *seg_offsets, int num_segments, uint16_t *seq_out,
+                              double *dists_out, int *one_sweep);
+
 /* ---- timing / counters (CUDA events on the engine's own streams) ------------ */
 typedef struct {
     double assign_ms;      /* search kernels (incl. FP64 re-evaluation) */

@@ -75,3 +75,45 @@ def test_classify_errors(built_lib, tmp_path, monkeypatch):
     assert rc == 1 and "error loading model" in err
     rc, _, err = _capture_fds(lambda: vq.vq_classify(["a.cbook", "b.cbook"], ["x.prd"]))
     assert rc == 1 and "conformity error" in err
+
+
+@pytest.mark.parametrize("P,K,R", [(36, 64, 5), (36, 128, 3), (36, 256, 7), (12, 32, 9), (36, 512, 2), (36, 16, 3),
+                                   (36, 64, 40)],
+                         ids=["K64xR5", "K128xR3", "K256xR7", "P12-K32xR9", "K512xR2-serial", "K16xR3-serial", "K64xR40"])
+def test_quantize_models_matches_one_model_at_a_time(built_lib, P, K, R):
+    """ecoz2b200_quantize_models (cbook_quantize of every file against R codebooks, vq/vq.c:154-157,
+    285-315): the one-sweep search over the concatenated codebooks gives, for every model, the symbols
+    and per-file distortions of quantizing with that model alone -- which is the oracle's quantize
+    (quantize.c:8-34) on the frames of each file."""
+    from ecoz2rs_b200 import vq
+    from ecoz2rs_b200.synth import ar_mix
+    from oracle import oracle as O
+    from conftest import allowed_index_mismatches
+    rng = np.random.default_rng(K + R)
+    x = ar_mix(30_011, P, seed=K * 7 + R)
+    # R different codebooks: learnt on different slices of other data
+    models = []
+    for r in range(R):
+        y = ar_mix(4000, P, seed=1000 + 13 * r + K)
+        st, _ = O.learn(y, eps=0.05, max_M=K)
+        refl = st[-1]["refl"]
+        assert refl.shape[0] == K
+        models.append(refl)
+    refl_all = np.stack(models)
+    cuts = np.array([0, 1, 700, 700, 12_345, 30_011])                       # one-frame and empty files
+    with vq.VqEngine(P, max_M=max(K, 2)) as eng:
+        eng.set_frames(x)
+        seq, dists, one = eng.quantize_models(refl_all, cuts)
+        assert one == (K in (32, 64, 128, 256))
+        c = eng.counters()
+    assert seq.shape == (R, len(x)) and dists.shape == (R, len(cuts) - 1)
+    for r in range(0, R, max(1, R // 6)):
+        raas = O.refl_to_raas(models[r])
+        ref_idx, ref_dd, ref_second = O.assign(x, raas)
+        assert allowed_index_mismatches(seq[r].astype(np.int64), ref_idx, ref_dd, ref_second).size == 0
+        for f in range(len(cuts) - 1):
+            a, b = cuts[f], cuts[f + 1]
+            want = (ref_dd[a:b] - 1.0).sum() / (b - a) if b > a else 0.0
+            assert abs(dists[r, f] - want) <= 1e-9 * max(1.0, abs(want)), (r, f)
+    if one:
+        assert c["rechecked"] > 0                                           # the FP64 scan of ambiguous pairs ran
