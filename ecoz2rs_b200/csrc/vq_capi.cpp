@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -447,6 +448,56 @@ int ecoz2_vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenam
 int vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenames, int num_predictors,
                 int show_ranked) {
     return ecoz2b200_classify_entry(cb_filenames, num_codebooks, prd_filenames, num_predictors, show_ranked);
+}
+
+// quantize.c:8-34 behind the reference's own cbook_quantize / SeqProvider (vq/vq.c:154-157, 285-315)
+double quantize(double *raas, int num_raas, ecoz2_ref_predictor *prd, uint16_t *seq) {
+    static std::mutex mu;
+    static ecoz2b200_engine *cached = nullptr;   // kept for the life of the process (never torn down at exit)
+    static int cached_P = -1, cached_max = 0;
+    static std::vector<double> cached_raas;       // the codebook currently staged on the device
+    static std::vector<double> rows;
+    if (!raas || !prd || num_raas < 1 || prd->P < 0) {
+        fprintf(stderr, "quantize: bad argument\n");
+        exit(1);
+    }
+    const int P = prd->P, T = prd->T, D = P + 1;
+    if (T <= 0) return 0.0 / 0.0;                  // the reference divides by T
+    std::lock_guard<std::mutex> lock(mu);
+    vqb200::DeviceGuard device_guard_;
+    if (!cached || cached_P != P || cached_max < num_raas) {
+        delete cached;
+        cached = nullptr;
+        cached_raas.clear();
+        std::vector<int> devs = devices_from_env();
+        int cap = 2;
+        while (cap < num_raas) cap *= 2;
+        cached = new ecoz2b200_engine(devs.data(), (int) devs.size(), P, cap);
+        if (!cached->impl.ok()) {
+            fprintf(stderr, "quantize: %s\n", vqb200::get_last_error());
+            exit(1);
+        }
+        apply_mode_env(cached->impl);
+        cached_P = P;
+        cached_max = cap;
+    }
+    Engine &eng = cached->impl;
+    const size_t vals = (size_t) num_raas * D;
+    if (cached_raas.size() != vals || memcmp(cached_raas.data(), raas, vals * sizeof(double)) != 0) {
+        if (eng.codebook_set_raas(raas, num_raas)) {
+            fprintf(stderr, "quantize: %s\n", vqb200::get_last_error());
+            exit(1);
+        }
+        cached_raas.assign(raas, raas + vals);
+    }
+    if (rows.size() < (size_t) T * D) rows.resize((size_t) T * D);
+    for (int t = 0; t < T; t++) memcpy(rows.data() + (size_t) t * D, prd->vectors[t], sizeof(double) * D);
+    double ddprm = 0;
+    if (eng.quantize_host(rows.data(), T, seq, &ddprm)) {
+        fprintf(stderr, "quantize: %s\n", vqb200::get_last_error());
+        exit(1);
+    }
+    return ddprm;
 }
 
 // ============================================================================ PART 2

@@ -56,7 +56,7 @@ _PASS_CB = C.CFUNCTYPE(None, C.c_void_p, C.c_int, C.c_int, C.c_double, C.c_doubl
 # every symbol include/ecoz2_vq_b200.h declares (tests check the library exports them all)
 EXPORTED_SYMBOLS = (
     "ecoz2_vq_learn", "ecoz2_vq_learn_using_base_codebook", "ecoz2_vq_quantize", "ecoz2_vq_classify",
-    "vq_learn", "vq_learn_using_base_codebook", "vq_quantize", "vq_classify",
+    "vq_learn", "vq_learn_using_base_codebook", "vq_quantize", "vq_classify", "quantize",
     "ecoz2b200_version", "ecoz2b200_last_error", "ecoz2b200_device_count",
     "ecoz2b200_create", "ecoz2b200_destroy", "ecoz2b200_set_mode", "ecoz2b200_set_recheck_kappa",
     "ecoz2b200_set_recheck_kappa_tc", "ecoz2b200_set_audit", "ecoz2b200_debug_tc_distortions",

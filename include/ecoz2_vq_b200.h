@@ -87,6 +87,22 @@ int vq_quantize(const char *nom_raas, const char *predictor_filenames[], int num
                 int show_filenames);
 int vq_classify(char **cb_filenames, int num_codebooks, char **prd_filenames, int num_predictors,
                 int show_ranked);
+/* quantize (ecoz2/src/include/vq.h:74-78, ecoz2/src/vq/quantize.c:8-34): the in-memory quantizer that the
+ * reference's cbook_quantize (vq/vq.c:154-157) and through it its SeqProvider (vq/vq.c:285-315, used by
+ * hmm_classify.c:396) call.  `prd` is the reference's Predictor (include/lpc.h:29-34: className[96],
+ * sample_t **vectors, int T, int P), declared here as ecoz2_ref_predictor with the same layout; seq
+ * receives T symbols (may be NULL); returns the average distortion sum(ddmin - 1) / T.  With this
+ * exported, quantize.c leaves the reference's build and vq.c links unmodified.  The engine behind it
+ * is created on first use and kept for the process (devices: ECOZ2_VQ_GPUS); the codebook is uploaded
+ * again only when raas changes.  On a CUDA failure the process exits with status 1, as the
+ * reference does on its own fatal errors (the signature has no error channel).                  */
+typedef struct {
+    char className[96];
+    double **vectors;
+    int T;
+    int P;
+} ecoz2_ref_predictor;
+double quantize(double *raas, int num_raas, ecoz2_ref_predictor *prd, uint16_t *seq);
 
 /* ===================================================================== PART 2
  * In-memory API.                                                            */

@@ -123,3 +123,45 @@ def test_patched_crate_library_runs_on_the_gpu(built_lib, tmp_path):
     seq = np.frombuffer((tmp_path / "data" / "sequences" / "TRAIN" / "M32" / "c" / "a.seq").read_bytes(), "<u2", offset=120)
     oseq, _ = O.quantize(O.refl_to_raas(refl), x)
     assert (seq != oseq).mean() < 1e-4
+
+
+def test_reference_seq_provider_over_the_library_quantize(built_lib, tmp_path):
+    """The reference's SeqProvider (vq/vq.c:162-334, compiled unmodified) quantizes every predictor with
+    every codebook through cbook_quantize -> quantize (vq/vq.c:154-157).  Linked against the library,
+    `quantize` IS the B200 path (quantize.c leaves the build): same symbols (hash of every sequence) and
+    distortions as the all-reference build, for codebooks of different content, files of 1 .. 30k frames."""
+    import subprocess
+    from ecoz2rs_b200 import formats
+    from ecoz2rs_b200.synth import ar_mix
+    from oracle import oracle as O
+    from oracle import refbuild
+    d = refbuild.arch_dir()
+    exes = [os.path.join(d, "ref.seqprov"), os.path.join(d, "dropin.seqprov")]
+    if not all(os.path.exists(e) for e in exes):
+        pytest.skip("oracle/_ref seqprov executables not built")
+    K, R = 128, 3
+    cbs = []
+    for r in range(R):
+        st, _ = O.learn(ar_mix(6000, P, seed=300 + r), eps=0.05, max_M=K)
+        f = tmp_path / f"m{r}.cbook"
+        formats.write_cbook(str(f), st[-1]["refl"], f"class{r}")
+        cbs.append(str(f))
+    prds = []
+    for k, T in enumerate((1, 7, 2500, 30_001, 1023)):
+        f = tmp_path / "predictors" / "TEST" / f"class{k % R}" / f"f{k}.prd"
+        formats.write_prd(str(f), ar_mix(T, P, seed=900 + k), f"class{k % R}")
+        prds.append(str(f))
+    outs = []
+    for exe in exes:
+        pr = subprocess.run([exe, str(R)] + cbs + prds, cwd=tmp_path, capture_output=True, text=True, timeout=300)
+        if exe.endswith("ref.seqprov") and pr.returncode != 0:
+            pytest.skip("reference seqprov failed on this host: " + pr.stderr[-300:])
+        assert pr.returncode == 0, pr.stdout[-500:] + pr.stderr[-500:]
+        rows = [ln.split() for ln in pr.stdout.splitlines() if ln and ln[0].isdigit()]
+        outs.append(rows)
+    ref, got = outs
+    assert len(ref) == len(got) == R * len(prds)
+    for a, b in zip(ref, got):
+        assert a[:3] == b[:3]                                                # file, model, T
+        assert abs(float(a[3]) - float(b[3])) <= 1e-9 * max(1.0, abs(float(a[3]))), (a, b)
+        assert a[4:] == b[4:], (a, b)                                        # hash of the symbols, first symbols
