@@ -516,6 +516,20 @@ def _dropin_cfg2(dev, n_frames, stop_M):
             wall = time.perf_counter() - t0
             os.chdir(cwd)
             sizes = sum(os.path.getsize(os.path.join(dp, fn)) for dp, _, fns in os.walk(wd) for fn in fns)
+            if rep == 4:
+                # `ecoz2_vq_quantize` of the same shards with the codebook just learnt (parallel loader,
+                # one sweep over the resident frames, `.seq` files written): second of two calls
+                cbk = os.path.join(wd, "data", "codebooks", "cfg2", f"eps_{EPS:g}_M_{stop_M:04d}.cbook")
+                if os.path.exists(cbk):
+                    os.chdir(wd)
+                    qw = []
+                    for _ in range(2):
+                        t0 = time.perf_counter()
+                        qrc = vq.vq_quantize(cbk, files)
+                        qw.append(time.perf_counter() - t0)
+                    os.chdir(cwd)
+                    out["vq_quantize_files"] = {"wall_s": qw[-1], "walls_s": qw, "rc": qrc, "K": stop_M,
+                                                "evals_per_s": n_frames * stop_M / qw[-1]}
             shutil.rmtree(wd, ignore_errors=True)
             if label == "first_call":
                 out["first_call_without_min_dists_s"] = wall

@@ -356,26 +356,70 @@ static int quantize_entry(const char *nom_raas, const char *predictor_filenames[
     if (eng.codebook_set_reflections(refl.data(), M)) return ECOZ2B200_ERR_CUDA;
     printf("%s: %d symbols\n", nom_raas, M);
 
+    // Headers first.  The reference works file by file and stops at the first one it cannot load
+    // (vq_quantize.c:49-53), after having written the sequences of the files before it: same here.
+    std::vector<int> Ts;
+    int first_bad = -1;
+    for (int i = 0; i < num_predictors; i++) {
+        int p = 0, T = 0;
+        if (vqb200::prd_info(predictor_filenames[i], &p, &T, nullptr) || p != P) {
+            first_bad = i;
+            break;
+        }
+        Ts.push_back(T);
+    }
+    int num_ok = (int) Ts.size();   // files [0, num_ok) are processed; shrinks if a file turns out truncated
+    // All frames of a batch of files are resident at once: loaded by the reader threads of
+    // vq_hostio.cpp, quantized in one sweep, the per-file distortions summed on the device
+    // (Engine::quantize_models with one model).  A batch is bounded by the free device memory.
+    size_t free_b = 0, total_b = 0;
+    {
+        cudaSetDevice(devs[0]);
+        if (cudaMemGetInfo(&free_b, &total_b) != cudaSuccess) free_b = (size_t) 8 << 30;
+    }
+    const size_t per_frame = (size_t) (P + 1) * 12 + 64;            // f64 + f32 rows, per-frame outputs
+    long budget = (long) (free_b / 2 / per_frame) * (long) devs.size();
+    if (budget < (1L << 20)) budget = 1L << 20;
+    std::unique_ptr<vqb200::IoLanes> lanes;
+
     int num_seqs = 0;
     double ddprm_total = 0;
-    std::vector<double> buf;
-    std::vector<uint16_t> seq;
-    for (int i = 0; i < num_predictors; i++) {
+    std::vector<uint16_t> seq_all;
+    std::vector<double> dd;
+    std::vector<long> seg;
+    int done = 0;
+    while (done < num_ok) {
+        int hi = done;
+        long frames = 0;
+        while (hi < num_ok && (hi == done || frames + Ts[hi] <= budget)) frames += Ts[hi++];
+        if (frames > 0) {
+            if (!lanes) {
+                const size_t bytes = (size_t) frames * (size_t) (P + 1) * sizeof(double);
+                const int small_threads = (int) (bytes >> 25) + 1;
+                lanes.reset(new vqb200::IoLanes(eng.devices(), small_threads < 8 ? small_threads : 0));
+                if (!lanes->ready()) return ECOZ2B200_ERR_CUDA;
+            }
+            if (eng.frames_clear() || eng.frames_reserve(frames)) return ECOZ2B200_ERR_CUDA;
+            const int lr = vqb200::load_prd_frames(eng, *lanes, predictor_filenames + done, Ts.data() + done, hi - done, P);
+            if (lr < 0) return ECOZ2B200_ERR_CUDA;
+            if (lr > 0) {   // shorter than its header says: everything before it is still written
+                first_bad = done + lr - 1;
+                num_ok = first_bad;   // re-run the batch up to that file
+                continue;
+            }
+            if (eng.frames_commit()) return ECOZ2B200_ERR_CUDA;
+            seg.assign((size_t) (hi - done) + 1, 0);
+            for (int i = done; i < hi; i++) seg[(size_t) (i - done) + 1] = seg[(size_t) (i - done)] + Ts[i];
+            seq_all.resize((size_t) frames);
+            dd.assign((size_t) (hi - done), 0.0);
+            if (eng.quantize_models(refl.data(), 1, M, seg.data(), hi - done, seq_all.data(), dd.data(), nullptr))
+                return ECOZ2B200_ERR_CUDA;
+        }
+        for (int i = done; i < hi; i++) {
         const char *prd_filename = predictor_filenames[i];
-        int p = 0, T = 0;
-        if (vqb200::prd_info(prd_filename, &p, &T, nullptr) || p != P) {
-            fprintf(stderr, "%s: error loading predictor.\n", prd_filename);
-            return 2;
-        }
-        const size_t vals = (size_t) T * (P + 1);
-        if (buf.size() < vals) buf.resize(vals);
-        if (vqb200::prd_read(prd_filename, buf.data(), (long) vals)) {
-            fprintf(stderr, "%s: error loading predictor.\n", prd_filename);
-            return 2;
-        }
-        if (seq.size() < (size_t) T) seq.resize((size_t) T);
-        double ddprm = 0;
-        if (eng.quantize_host(buf.data(), T, seq.data(), &ddprm)) return ECOZ2B200_ERR_CUDA;
+        const int T = Ts[i];
+        const uint16_t *seq = seq_all.data() + (frames > 0 ? seg[(size_t) (i - done)] : 0);
+        const double ddprm = frames > 0 ? dd[(size_t) (i - done)] : 0.0;
         ddprm_total += ddprm;
         num_seqs++;
 
@@ -386,7 +430,7 @@ static int quantize_entry(const char *nom_raas, const char *predictor_filenames[
         const std::string base_dir_with_m = std::string(base_dir) + "/M" + std::to_string(M);
         const std::string seq_filename =
             vqb200::get_output_filename(prd_filename, base_dir_with_m, ".seq");
-        if (vqb200::seq_save(seq_filename.c_str(), className.c_str(), seq.data(), T, M))
+        if (vqb200::seq_save(seq_filename.c_str(), className.c_str(), seq, T, M))
             printf("error saving sequence\n");
         if (show_filenames)
             printf("\n%s className='%s' (%1.4g) = ", seq_filename.c_str(), className.c_str(), ddprm);
@@ -405,6 +449,12 @@ static int quantize_entry(const char *nom_raas, const char *predictor_filenames[
             }
             printf(">\n");
         }
+        }
+        done = hi;
+    }
+    if (first_bad >= 0) {
+        fprintf(stderr, "%s: error loading predictor.\n", predictor_filenames[first_bad]);
+        return 2;
     }
     if (num_seqs > 0)
         printf("\ntotal: %d sequences; total  average distortion = %f\n", num_seqs,

@@ -166,6 +166,50 @@ def test_vq_quantize_seq_bytes_match_reference(built_lib, in_tmp_cwd):
     assert out.read_bytes() == q["seq_file_bytes"].tobytes()
 
 
+def test_vq_quantize_batches_of_files(built_lib, in_tmp_cwd, capfd):
+    """ecoz2_vq_quantize keeps a whole batch of files resident (parallel loader, one sweep, per-file
+    distortions from the device): every `.seq` equals the oracle's quantize of that file alone
+    (quantize.c:8-34), the per-file distortions printed with -s and the total line are the
+    reference's; a file that cannot be loaded ends the run with code 2 AFTER the files before it were
+    written (vq_quantize.c:49-53)."""
+    from ecoz2rs_b200 import formats, vq
+    from ecoz2rs_b200.synth import ar_mix
+    from oracle import oracle as O
+    q = np.load(os.path.join(GOLD, "quantize_P36.npz"))
+    refl = q["refl"]
+    M = refl.shape[0]
+    raas = O.refl_to_raas(refl)
+    cb = str(in_tmp_cwd / "cb.cbook")
+    formats.write_cbook(cb, refl, "gold")
+    sizes = [1, 50, 4097, 20_000, 3, 1024]
+    files, xs = [], []
+    for k, T in enumerate(sizes):
+        x = ar_mix(T, 36, seed=40 + k)
+        f = str(in_tmp_cwd / "predictors" / "TEST" / f"c{k % 2}" / f"f{k}.prd")
+        formats.write_prd(f, x, f"c{k % 2}")
+        files.append(f)
+        xs.append(x)
+    assert vq.vq_quantize(cb, files, show_filenames=True) == 0
+    out = capfd.readouterr().out
+    total = 0.0
+    for k, (f, x) in enumerate(zip(files, xs)):
+        seq_ref, dist_ref = O.quantize(raas, x)
+        cls, m, seq = formats.read_seq(str(in_tmp_cwd / "data" / "sequences" / "TEST" / f"M{M}" / f"c{k % 2}" / f"f{k}.seq"))
+        assert (cls, m) == (f"c{k % 2}", M) and np.array_equal(seq, seq_ref), k
+        assert f"f{k}.seq className='c{k % 2}' ({dist_ref:1.4g})" in out, (k, dist_ref)
+        total += dist_ref
+    assert f"total: {len(files)} sequences; total  average distortion = {total / len(files):f}" in out
+    # a truncated file in the middle
+    raw = open(files[3], "rb").read()
+    bad = str(in_tmp_cwd / "predictors" / "TEST" / "c0" / "bad.prd")
+    open(bad, "wb").write(raw[:-64])
+    import shutil
+    shutil.rmtree(in_tmp_cwd / "data")
+    assert vq.vq_quantize(cb, [files[0], files[2], bad, files[4]]) == 2
+    seqs = sorted(p_.name for p_ in (in_tmp_cwd / "data").rglob("*.seq"))
+    assert seqs == ["f0.seq", "f2.seq"]
+
+
 def test_cli_learn_and_quantize(built_lib, in_tmp_cwd):
     """`ecoz2 vq learn` / `ecoz2 vq quantize` with the reference's option names."""
     from ecoz2rs_b200 import formats
