@@ -347,6 +347,14 @@ static int quantize_entry(const char *nom_raas, const char *predictor_filenames[
         printf("error loading codebook (%d).\n", vqb200::cb_errnum_last);
         return 1;
     }
+    static const bool timing = getenv("ECOZ2_VQ_TIMING") != nullptr;
+    double t_mark = wall_s();
+    auto mark = [&](const char *what) {
+        if (!timing) return;
+        const double t = wall_s();
+        fprintf(stderr, "[timing] vq_quantize: %s %.1f ms\n", what, (t - t_mark) * 1e3);
+        t_mark = t;
+    };
     std::vector<int> devs = devices_from_env();
     std::unique_ptr<ecoz2b200_engine> h(
         new ecoz2b200_engine(devs.data(), (int) devs.size(), P, M < 2 ? 2 : M));
@@ -355,6 +363,7 @@ static int quantize_entry(const char *nom_raas, const char *predictor_filenames[
     apply_mode_env(eng);
     if (eng.codebook_set_reflections(refl.data(), M)) return ECOZ2B200_ERR_CUDA;
     printf("%s: %d symbols\n", nom_raas, M);
+    mark("engine + codebook");
 
     // Headers first.  The reference works file by file and stops at the first one it cannot load
     // (vq_quantize.c:49-53), after having written the sequences of the files before it: same here.
@@ -408,12 +417,14 @@ static int quantize_entry(const char *nom_raas, const char *predictor_filenames[
                 continue;
             }
             if (eng.frames_commit()) return ECOZ2B200_ERR_CUDA;
+            mark("frames loaded");
             seg.assign((size_t) (hi - done) + 1, 0);
             for (int i = done; i < hi; i++) seg[(size_t) (i - done) + 1] = seg[(size_t) (i - done)] + Ts[i];
             seq_all.resize((size_t) frames);
             dd.assign((size_t) (hi - done), 0.0);
             if (eng.quantize_models(refl.data(), 1, M, seg.data(), hi - done, seq_all.data(), dd.data(), nullptr))
                 return ECOZ2B200_ERR_CUDA;
+            mark("quantized, symbols on the host");
         }
         for (int i = done; i < hi; i++) {
         const char *prd_filename = predictor_filenames[i];
@@ -451,6 +462,7 @@ static int quantize_entry(const char *nom_raas, const char *predictor_filenames[
         }
         }
         done = hi;
+        mark(".seq files written");
     }
     if (first_bad >= 0) {
         fprintf(stderr, "%s: error loading predictor.\n", predictor_filenames[first_bad]);
