@@ -183,6 +183,66 @@ vq_cell_sums(const double *__restrict__ x64, const int32_t *__restrict__ perm,
     }
 }
 
+// The same sums from a PADDED copy of the frames (rows of ld doubles, ld a multiple of 8 = whole
+// 64-byte DRAM atoms, pad columns zero): a gathered 296-byte row of the dense array straddles
+// atoms (ncu: 789 MB read for 608 MB of rows, 1.30x), a 320-byte row of the copy does not.  Lane l
+// < ld / 2 loads components (2 l, 2 l + 1) as one 16-byte access: one load instruction per row.
+__global__ void __launch_bounds__(256)
+vq_cell_sums_padded(const double *__restrict__ xp, int ld, const int32_t *__restrict__ perm,
+                    const int32_t *__restrict__ offsets, const int32_t *__restrict__ item_start, int K,
+                    int D, PackedLayout L, double *__restrict__ packed) {
+    const int lane = threadIdx.x & 31;
+    const int warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int n_warps = (gridDim.x * blockDim.x) >> 5;
+    const int n_items = item_start[K];
+    const bool active = 2 * lane < ld;
+    for (int item = warp; item < n_items; item += n_warps) {
+        int lo = 0, hi = K;
+        while (hi - lo > 1) {
+            const int mid = (lo + hi) >> 1;
+            if (item_start[mid] <= item) lo = mid; else hi = mid;
+        }
+        const int c = lo;
+        const int first = offsets[c] + (item - item_start[c]) * kCellChunk;
+        const int last = min(first + kCellChunk, offsets[c + 1]);
+        double s0 = 0.0, s1 = 0.0;
+        for (int g = first; g < last; g += 32) {
+            const int mine = g + lane < last ? perm[g + lane] : -1;
+            const int cnt = min(32, last - g);
+            int u = 0;
+            for (; u + 8 <= cnt; u += 8) {
+                double2 xv[8];
+#pragma unroll
+                for (int k = 0; k < 8; k++) {
+                    const long row = __shfl_sync(0xffffffffu, mine, u + k);
+                    xv[k] = active ? reinterpret_cast<const double2 *>(xp + row * ld)[lane] : make_double2(0.0, 0.0);
+                }
+#pragma unroll
+                for (int k = 0; k < 8; k++) { s0 += xv[k].x; s1 += xv[k].y; }
+            }
+            for (; u < cnt; u++) {
+                const long row = __shfl_sync(0xffffffffu, mine, u);
+                if (active) {
+                    const double2 v = reinterpret_cast<const double2 *>(xp + row * ld)[lane];
+                    s0 += v.x; s1 += v.y;
+                }
+            }
+        }
+        if (2 * lane < D) atomicAdd(packed + L.cells() + (long) c * D + 2 * lane, s0);
+        if (2 * lane + 1 < D) atomicAdd(packed + L.cells() + (long) c * D + 2 * lane + 1, s1);
+    }
+}
+
+// dense rows [n][D] -> padded rows [n][ld] (pad columns zero)
+__global__ void vq_pad_rows(const double *__restrict__ x, double *__restrict__ xp, long n, int D, int ld) {
+    const long total = n * ld;
+    for (long i = (long) blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (long) gridDim.x * blockDim.x) {
+        const long row = i / ld;
+        const int k = (int) (i - row * ld);
+        xp[i] = k < D ? x[row * D + k] : 0.0;
+    }
+}
+
 // D <= 16 (P <= 15): a row is at most 128 bytes, so one load instruction of the kernel above
 // would keep 16+ lanes idle.  Here a warp load covers TWO rows (lanes 0-15: row u, lanes 16-31:
 // row u + 1), 8 such loads in flight; the two half-warp sums meet in one shuffle at the end.
@@ -360,9 +420,25 @@ static bool cell_stream_enabled() {
     return v == 1;
 }
 
+int cell_pad_ld(int D) {
+    static int on = -1;
+    // OFF by default: measured on B200 (10M frames, K = 16 .. 2048) the sums take 0.79-0.82 ms from the
+    // padded copy and 0.78-0.84 ms from the dense rows -- the gather is bound by DRAM random-access
+    // efficiency (63-67 % of peak at 320-byte granularity), not by the 1.3x over-fetch, and the copy
+    // costs 3.2 GB of HBM per 10M frames.  ECOZ2_VQ_CELL_PAD=1 switches it on for A/B runs.
+    if (on < 0) { const char *e = getenv("ECOZ2_VQ_CELL_PAD"); on = (e && e[0] == '1') ? 1 : 0; }
+    const int ld = (D + 7) / 8 * 8;
+    // (short rows take the streaming kernel; rows that are whole atoms already need no copy)
+    return (on && D > 20 && ld != D && ld <= 64) ? ld : 0;
+}
+void launch_pad_rows(const double *x64, double *xp, long n, int D, int ld, int num_sms, cudaStream_t s) {
+    if (n <= 0) return;
+    vq_pad_rows<<<num_sms * 16, 256, 0, s>>>(x64, xp, n, D, ld);
+}
+
 void launch_cell_sums(const double *x64, const int32_t *idx, long n, int D, const double *raas,
                       int K, double *packed, uint16_t *seq, const CellScratch &cs, int num_sms,
-                      cudaStream_t s) {
+                      cudaStream_t s, const double *x64_padded, int ld) {
     const PackedLayout L{K, D};
     cudaMemsetAsync(cs.hist, 0, sizeof(int32_t) * (size_t) (K + 1), s);
     constexpr size_t kStreamSmemMax = 200 * 1024;
@@ -396,7 +472,9 @@ void launch_cell_sums(const double *x64, const int32_t *idx, long n, int D, cons
         if (blocks > (long) num_sms * 4) blocks = (long) num_sms * 4;
         vq_cell_scatter<<<(unsigned) blocks, 256, smem, s>>>(idx, n, K, cs.cursor, cs.perm);
         const int grid = num_sms * 8;
-        if (D <= 16) {
+        if (x64_padded != nullptr && ld > 0) {
+            vq_cell_sums_padded<<<grid, 256, 0, s>>>(x64_padded, ld, cs.perm, cs.offsets, cs.item_start, K, D, L, packed);
+        } else if (D <= 16) {
             vq_cell_sums_pair<<<grid, 256, 0, s>>>(x64, cs.perm, cs.offsets, cs.item_start, K, D, L, packed);
         } else switch ((D + 31) / 32) {
             case 1: vq_cell_sums<1><<<grid, 256, 0, s>>>(x64, cs.perm, cs.offsets, cs.item_start, K, D, L, packed); break;

@@ -161,7 +161,7 @@ Engine::~Engine() {
         cudaFree(s.refl); cudaFree(s.raas); cudaFree(s.w32); cudaFree(s.w64); cudaFree(s.w1max); cudaFree(s.w1);
         cudaFree(s.wtc); cudaFree(s.cs_mem); cudaFree(s.packed_scratch); cudaFree(s.raas_prev);
         cudaFree(s.packed); cudaFree(s.scalars); cudaFree(s.dstat);
-        cudaFree(s.fmt_scratch); cudaFree(s.fmt_text);
+        cudaFree(s.fmt_scratch); cudaFree(s.fmt_text); cudaFree(s.x64p);
         for (auto &tb : s.text_pool) {
             cudaFree(tb.d);
             if (tb.ready) cudaEventDestroy(tb.ready);
@@ -306,7 +306,7 @@ int Engine::ensure_capacity(Shard &s, long n) {
 }
 
 int Engine::frames_clear() {
-    for (Shard &s : shards_) s.n = 0;
+    for (Shard &s : shards_) { s.n = 0; s.x64p_valid = false; }
     n_total_ = n_global_ = 0;
     reserved_ = per_shard_ = appended_ = 0;
     committed_ = false;
@@ -432,6 +432,7 @@ int Engine::frames_commit() {
     n_total_ = 0;
     long off = 0;
     for (Shard &s : shards_) {
+        s.x64p_valid = false;
         if (reserved_ == 0) s.frame_offset = off;
         off += s.n;
         n_total_ += s.n;
@@ -709,7 +710,23 @@ void Engine::pass_kernels(Shard &s, const double *x64, const float *x32, long n,
         // codebook this assignment was made against
         cudaMemcpyAsync(s.raas_prev, s.raas, sizeof(double) * (size_t) K_ * D_, cudaMemcpyDeviceToDevice,
                         s.stream);
-        launch_cell_sums(x64, idx, n, D_, s.raas, K_, s.packed, seq, s.cs, s.num_sms, s.stream);
+        const int ld = cell_pad_ld(D_);
+        if (ld > 0 && !s.x64p_valid && n == s.n) {
+            if (s.x64p_cap < s.cap) {
+                cudaFree(s.x64p);
+                s.x64p = nullptr; s.x64p_cap = 0;
+                if (cudaMalloc(&s.x64p, sizeof(double) * (size_t) s.cap * ld) == cudaSuccess) s.x64p_cap = s.cap;
+                else cudaGetLastError();   // no room for the copy: the dense rows serve
+            }
+            if (s.x64p) {
+                launch_pad_rows(s.x64, s.x64p, s.n, D_, ld, s.num_sms, s.stream);
+                ctr_.kernel_launches++;
+                s.x64p_valid = true;
+            }
+        }
+        const bool padded = ld > 0 && s.x64p_valid && n == s.n;
+        launch_cell_sums(x64, idx, n, D_, s.raas, K_, s.packed, seq, s.cs, s.num_sms, s.stream,
+                         padded ? s.x64p : nullptr, padded ? ld : 0);
         K_prev_ = K_;
         mindist_valid_ = false;
         ctr_.kernel_launches += n > 0 ? 5 : 2;
@@ -873,6 +890,7 @@ int Engine::kmeans_pass_host(const double *x, long n, double *cells_out, int32_t
         int rc = ensure_capacity(s, mine > 0 ? mine : 1);
         if (rc) return rc;
         s.n = mine;
+        s.x64p_valid = false;   // new frames: the padded copy is rebuilt by the next resident pass
         CUDA_TRY(cudaSetDevice(s.device));
         if (!s.copy_stream) {
             CUDA_TRY(cudaStreamCreateWithFlags(&s.copy_stream, cudaStreamNonBlocking));

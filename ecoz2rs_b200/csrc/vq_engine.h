@@ -75,6 +75,11 @@ struct Shard {
     void *cs_mem = nullptr;   // scratch of the sorted cell accumulation
     CellScratch cs;
     long cap = 0;             // capacity (frames) of the per-frame buffers
+    // padded copy of x64 for the gather of the sorted cell sums (rows of whole 64-byte atoms,
+    // vq_cells.cu); made lazily by the first pass after the frame set changed
+    double *x64p = nullptr;
+    long x64p_cap = 0;
+    bool x64p_valid = false;
 
     // codebook replica
     double *refl = nullptr;   // [max_M][D]

@@ -165,9 +165,13 @@ struct CellScratch {
 bool cell_sort_supported(int K);
 size_t cell_scratch_bytes(long cap, int max_K);
 void cell_scratch_carve(void *base, long cap, int max_K, CellScratch *out);
+// A padded copy of the frames for the gather of the sorted path: rows of cell_pad_ld(D) doubles (whole
+// 64-byte atoms; 0 = not worth it for this D), made once per frame set by launch_pad_rows.
+int cell_pad_ld(int D);
+void launch_pad_rows(const double *x64, double *xp, long n, int D, int ld, int num_sms, cudaStream_t s);
 void launch_cell_sums(const double *x64, const int32_t *idx, long n, int D, const double *raas,
                       int K, double *packed, uint16_t *seq, const CellScratch &cs, int num_sms,
-                      cudaStream_t s);
+                      cudaStream_t s, const double *x64_padded = nullptr, int ld = 0);
 
 // ---- (a+b) fused pass for codebooks of ONE tensor-core tile (vq_mid.cu), 8 < K <= 128 ------------
 // One sweep over the FP64 frames: tensor-core search (same operands, same error bound and flag
