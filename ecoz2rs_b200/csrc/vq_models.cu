@@ -64,7 +64,7 @@ vq_models_recheck(const double *__restrict__ x64, int D, const double *__restric
             const int oi = __shfl_xor_sync(0xffffffffu, bidx, off);
             if (ob < best || (ob == best && oi < bidx)) { best = ob; bidx = oi; }
         }
-        if (lane == 0) idx_out[(long) model * idx_stride + row] = bidx;
+        if (lane == 0) idx_out[(long) model * idx_stride + row] = bidx < K ? bidx : 0;   // all NaN: codeword 0
     }
 }
 

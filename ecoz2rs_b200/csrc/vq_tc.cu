@@ -865,9 +865,11 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 epi_finish(est, ssecond, sidx);
                 if (row >= 0) {
                     const int model = col0 / p.seg_cols;
-                    p.idx_out[(long) model * p.idx_stride + row] = sidx - col0;
+                    // (a frame of NaNs never records a minimum: keep the index inside the model)
+                    const int local = sidx - col0;
+                    p.idx_out[(long) model * p.idx_stride + row] = (unsigned) local < (unsigned) p.seg_cols ? local : 0;
                     const float x0 = s_x0[((it & 3) * 2 + h) * kBM + r];
-                    const float ub = fmaf(e2 * x0, p.w1[sidx], sbest);
+                    const float ub = fmaf(e2 * x0, p.w1[(unsigned) sidx < (unsigned) K ? sidx : 0], sbest);
                     if (!(ssecond > ub)) {
                         const int pos = atomicAdd(p.flag_count, 1);
                         if (pos < p.seg_cap)
