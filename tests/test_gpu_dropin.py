@@ -134,9 +134,9 @@ def test_parallel_prd_loader_equals_serial(built_lib, in_tmp_cwd, monkeypatch):
     for name, data in outs["serial"].items():
         other = outs["parallel"][name]
         if name.endswith(".cbook"):
-            ra = np.frombuffer(data[128:], dtype="<f8")
-            rb = np.frombuffer(other[128:], dtype="<f8")
-            assert data[:128] == other[:128] and np.allclose(ra, rb, rtol=0, atol=1e-11), name
+            ra = np.frombuffer(data[120:], dtype="<f8")        # ident 16 + class 96 + P, M
+            rb = np.frombuffer(other[120:], dtype="<f8")
+            assert data[:120] == other[:120] and np.allclose(ra, rb, rtol=0, atol=1e-11), name
         elif name.endswith(".min_dists.csv"):
             ta = np.loadtxt(io.BytesIO(data), delimiter=",", skiprows=1)
             tb = np.loadtxt(io.BytesIO(other), delimiter=",", skiprows=1)
