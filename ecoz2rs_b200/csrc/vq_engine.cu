@@ -161,7 +161,7 @@ Engine::~Engine() {
         cudaFree(s.refl); cudaFree(s.raas); cudaFree(s.w32); cudaFree(s.w64); cudaFree(s.w1max); cudaFree(s.w1);
         cudaFree(s.wtc); cudaFree(s.cs_mem); cudaFree(s.packed_scratch); cudaFree(s.raas_prev);
         cudaFree(s.packed); cudaFree(s.scalars); cudaFree(s.dstat);
-        cudaFree(s.fmt_scratch); cudaFree(s.fmt_text); cudaFree(s.x64p);
+        cudaFree(s.fmt_scratch); cudaFree(s.fmt_text); cudaFree(s.x64p); cudaFree(s.xop);
         for (auto &tb : s.text_pool) {
             cudaFree(tb.d);
             if (tb.ready) cudaEventDestroy(tb.ready);
@@ -306,7 +306,7 @@ int Engine::ensure_capacity(Shard &s, long n) {
 }
 
 int Engine::frames_clear() {
-    for (Shard &s : shards_) { s.n = 0; s.x64p_valid = false; }
+    for (Shard &s : shards_) { s.n = 0; s.x64p_valid = false; s.xop_valid = false; }
     n_total_ = n_global_ = 0;
     reserved_ = per_shard_ = appended_ = 0;
     committed_ = false;
@@ -432,7 +432,7 @@ int Engine::frames_commit() {
     n_total_ = 0;
     long off = 0;
     for (Shard &s : shards_) {
-        s.x64p_valid = false;
+        s.x64p_valid = false; s.xop_valid = false;
         if (reserved_ == 0) s.frame_offset = off;
         off += s.n;
         n_total_ += s.n;
@@ -591,6 +591,28 @@ const Counters &Engine::counters() {
 // ---------------------------------------------------------------------------------
 // (a) the search on one shard: FP32 main pass + FP64 re-evaluation of the frames
 // inside the FP32 ambiguity bound, or the all-FP64 verification mode.
+const void *Engine::frame_operands(Shard &s, float err_tc) {
+    const size_t bytes = tc_frames_bytes(s.n, D_);
+    if (bytes == 0 || !tc_operands_f16()) return nullptr;
+    if (s.xop_valid && s.xop_err == err_tc) return s.xop;
+    if (s.xop_cap < bytes) {
+        cudaFree(s.xop);
+        s.xop = nullptr; s.xop_cap = 0;
+        const size_t want = tc_frames_bytes(s.cap > s.n ? s.cap : s.n, D_);
+        if (cudaMalloc(&s.xop, want) != cudaSuccess) {   // no room: the loaders convert per search
+            cudaGetLastError();
+            s.xop = nullptr;
+            return nullptr;
+        }
+        s.xop_cap = want;
+    }
+    launch_prepare_frames_tc(s.x32, s.n, D_, err_tc, s.xop, s.stream);
+    ctr_.kernel_launches++;
+    s.xop_valid = true;
+    s.xop_err = err_tc;
+    return s.xop;
+}
+
 void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32_t *idx,
                     const SearchScratch &sc, bool fuse_cells) {
     if (n <= 0) return;
@@ -605,9 +627,10 @@ void Engine::search(Shard &s, const double *x64, const float *x32, long n, int32
         const float err_tc = (float) (kappa_tc_ * ldexp(1.0, -24));
         const float err_scale = (float) (kappa_ * ldexp(1.0, -24));
         cudaMemsetAsync(sc.counters, 0, 4 * sizeof(int32_t), s.stream);
+        const void *xop = (x32 == s.x32 && n == s.n) ? frame_operands(s, err_tc) : nullptr;
         launch_assign_tc(x32, n, D_, s.wtc, K_, nullptr, nullptr, sc, true, s.w1, s.w1max, err_tc, idx,
                          nullptr, 0, s.num_sms, s.stream, x64, fuse_cells ? s.packed : nullptr,
-                         fuse_cells ? s.cs.hist : nullptr);
+                         fuse_cells ? s.cs.hist : nullptr, xop);
         cudaEventRecord(s.ev[7], s.stream);
         launch_recheck(x32, x64, n, D_, s.w32, s.w64, s.w1, s.w1max, s.raas, K_, 2.f * err_scale, sc,
                        idx, s.num_sms, s.stream, s.wtc, err_tc);
@@ -890,7 +913,7 @@ int Engine::kmeans_pass_host(const double *x, long n, double *cells_out, int32_t
         int rc = ensure_capacity(s, mine > 0 ? mine : 1);
         if (rc) return rc;
         s.n = mine;
-        s.x64p_valid = false;   // new frames: the padded copy is rebuilt by the next resident pass
+        s.x64p_valid = false; s.xop_valid = false;   // new frames: the padded copy is rebuilt by the next resident pass
         CUDA_TRY(cudaSetDevice(s.device));
         if (!s.copy_stream) {
             CUDA_TRY(cudaStreamCreateWithFlags(&s.copy_stream, cudaStreamNonBlocking));
@@ -1530,7 +1553,7 @@ int Engine::quantize_models(const double *reflections, int R, int K, const long 
             debug_poison(s);
             const long seg_cap = s.sc.cap < (1L << 30) ? s.sc.cap : (1L << 30);
             launch_assign_tc_models(s.x32, s.n, D_, b.wtc, K, cols, s.sc, err_tc, b.idx, s.n, s.sc.min_key,
-                                    (int) seg_cap, s.num_sms, s.stream);
+                                    (int) seg_cap, s.num_sms, s.stream, frame_operands(s, err_tc));
             mark("search");
             launch_models_recheck(s.x64, D_, b.raas, K, s.sc.min_key, s.sc.counters, (int) seg_cap, b.idx, s.n,
                                   s.num_sms, s.stream);

@@ -80,6 +80,12 @@ struct Shard {
     double *x64p = nullptr;
     long x64p_cap = 0;
     bool x64p_valid = false;
+    // the frames as ready-made operands of the tensor-core search (launch_prepare_frames_tc): built by
+    // the first search after the frame set (or the bound constant) changed
+    void *xop = nullptr;
+    size_t xop_cap = 0;
+    bool xop_valid = false;
+    float xop_err = 0.f;
 
     // codebook replica
     double *refl = nullptr;   // [max_M][D]
@@ -182,6 +188,7 @@ class Engine {
     int min_dists_text_device(std::vector<TextSegment> &segs);
     int min_dists_text_device_impl(std::vector<TextSegment> &segs);
     int ensure_fmt_scratch(Shard &s);
+    const void *frame_operands(Shard &s, float err_tc);   // pre-staged operands of s.x32, or nullptr
     void release_text(const TextSegment &seg);
     int learn(double eps, int stop_M, ecoz2b200_stage_cb on_stage, ecoz2b200_pass_cb on_pass,
               void *ctx);

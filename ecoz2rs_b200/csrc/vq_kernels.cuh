@@ -113,7 +113,14 @@ bool assign_tc_fuses_cells(int K, int D);
 bool assign_tc_models_supported(int K, int D, long total_cols);
 void launch_assign_tc_models(const float *x32, long n, int D, const float *wtc, int K, long total_cols,
                              const SearchScratch &sc, float err_scale, int32_t *idx_out, long idx_stride,
-                             unsigned long long *seg_key, int seg_cap, int num_sms, cudaStream_t s);
+                             unsigned long long *seg_key, int seg_cap, int num_sms, cudaStream_t s,
+                             const void *xop = nullptr);
+// The frames as ready-made operands of the tensor-core search (FP16 format; built once per frame set
+// from the FP32 copy with the operations of the search's own loaders): tc_frames_bytes(n, D) bytes
+// (0 = not available); pass the buffer as `xop` to launch_assign_tc / launch_assign_tc_models when
+// the search runs over ALL n frames in order (no gather list).
+size_t tc_frames_bytes(long n, int D);
+void launch_prepare_frames_tc(const float *x32, long n, int D, float err_scale, void *xop, cudaStream_t s);
 // all-FP64 argmin (strict <, first index wins: quantize.c:14-30) of every (model, frame) key over the
 // model's K codewords; raas_all [R * K][D].  One warp per key.
 void launch_models_recheck(const double *x64, int D, const double *raas_all, int K, const unsigned long long *keys,
@@ -128,7 +135,7 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
                       const int32_t *list, const int32_t *list_count, const SearchScratch &sc,
                       bool flag, const float *w1, const float *w1max, float err_scale, int32_t *idx,
                       float *dump, int dump_ld, int num_sms, cudaStream_t s, const double *x64 = nullptr,
-                      double *cells = nullptr, int32_t *hist = nullptr);
+                      double *cells = nullptr, int32_t *hist = nullptr, const void *xop = nullptr);
 
 // ---- (b) cell accumulation ----------------------------------------------------
 // For every frame: dd = FP64 distortion against its codeword raas[idx];

@@ -72,6 +72,11 @@ struct TcParams {
     int32_t *exact_count;
     int mc;                     // 1: launched as clusters of 2 CTAs that share the codeword stream
     int raw_bufs;               // variant 2: staging buffers for raw frame halves (1 .. 8)
+    // variant 2, FP16 format: the frames ALREADY as tensor-core operands (launch_prepare_frames_tc:
+    // per 128-frame half-tile the scaled (hi, lo) parts in canonical K-major order + the 128 norms),
+    // built once per frame set.  A half-tile is then two bulk copies straight into the operand
+    // buffer: no conversion work per search at all (the loader warps idle).
+    const unsigned char *xop;
     // fused cell sums (CELLS instance): the FP64 row of every frame OUTSIDE the error bound is added
     // to its cell with FP64 reductions (RED) by the loader warps while the tensor core is busy with
     // later tiles; flagged frames are added after their re-evaluation (vq_cell_fixup)
@@ -518,6 +523,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
     const int BN = p.BN;
     const bool wide = BN == 256;                  // UMMA N = 256: see tc_tile_cols
     const uint32_t n_bstages = wide ? 2 : kB2Stages;
+    const bool pre = H16 && !DBG && !FILTER && p.xop != nullptr;   // pre-staged frame operands
+    // norms of the frame tiles in flight: [slot][half][128]; 8 slots when the producer can run far
+    // ahead of the epilogue's once-per-tile finish (pre-staged operands), else 4
+    const uint32_t x0_mask = pre ? 7u : 3u;
     // KS = MMAs per product term (TF32 format, 8 elements each) or 8-element chunks per split
     // part (FP16 format); either way a part of a row is KC 16-byte chunks
     constexpr int KC = H16 ? KS : 2 * KS;
@@ -560,7 +569,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             mbar_init(&sm->raw_empty[i], 4);
         }
         for (int i = 0; i < 4; i++) {
-            mbar_init(&sm->a_full[i], 4);
+            mbar_init(&sm->a_full[i], pre ? 1 : 4);
             mbar_init(&sm->a_free[i], 1);
         }
         for (int i = 0; i < 4; i++) {
@@ -602,7 +611,25 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         }
     } else if (warp == 14) {
         // ===== raw frame producer (full, contiguous halves only) =====
-        if (lane == 0 && p.list == nullptr && !(exp & 64)) {
+        if (pre) {
+            // pre-staged operands: the half-tile record [hi | lo parts, a_half_bytes][128 norms] goes
+            // straight into the operand buffer and the norm slot
+            if (lane == 0) {
+                const size_t rec = (size_t) a_half_bytes + kBM * sizeof(float);
+                uint32_t it = 0;
+                for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+                    for (int h = 0; h < 2; h++) {
+                        const uint32_t ab = it & 1, aph = (it >> 1) & 1;
+                        mbar_wait(&sm->a_free[2 * ab + h], aph ^ 1);
+                        const unsigned char *src = p.xop + (size_t) (2 * ft + h) * rec;
+                        mbar_expect_tx(&sm->a_full[2 * ab + h], (uint32_t) rec);
+                        bulk_g2s(a_base + (size_t) (2 * ab + h) * a_half_bytes, src, a_half_bytes, &sm->a_full[2 * ab + h]);
+                        bulk_g2s(s_x0 + ((it & x0_mask) * 2 + h) * kBM, src + a_half_bytes, kBM * sizeof(float),
+                                 &sm->a_full[2 * ab + h]);
+                    }
+                }
+            }
+        } else if (lane == 0 && p.list == nullptr && !(exp & 64)) {
             uint32_t rs = 0;   // staged halves so far
             for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x) {
                 for (int h = 0; h < 2; h++) {
@@ -744,6 +771,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
         };
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
             if (CELLS && it >= 2) accumulate_tile(it - 2);
+            if (pre) continue;   // the operands come ready-made from the producer warp
             for (int h = 0; h < 2; h++) {
                 const long base = ft * (2 * kBM) + h * kBM;
                 const bool staged = p.list == nullptr && base + kBM <= total && !(exp & 64);
@@ -827,7 +855,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                         *reinterpret_cast<float4 *>(lo + ((size_t) c * kBM + r) * 16) = lv;
                     }
                 }
-                s_x0[((it & 3) * 2 + h) * kBM + r] = x0;
+                s_x0[((it & x0_mask) * 2 + h) * kBM + r] = x0;
                 fence_proxy_async();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&sm->a_full[2 * ab + h]);
@@ -868,7 +896,8 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                     // (a frame of NaNs never records a minimum: keep the index inside the model)
                     const int local = sidx - col0;
                     p.idx_out[(long) model * p.idx_stride + row] = (unsigned) local < (unsigned) p.seg_cols ? local : 0;
-                    const float x0 = s_x0[((it & 3) * 2 + h) * kBM + r];
+                    const float x0 = s_x0[((it & x0_mask) * 2 + h) * kBM + r];
+                    if (pre) fence_proxy_async();   // generic read before a later bulk copy reuses the slot
                     const float ub = fmaf(e2 * x0, p.w1[(unsigned) sidx < (unsigned) K ? sidx : 0], sbest);
                     if (!(ssecond > ub)) {
                         const int pos = atomicAdd(p.flag_count, 1);
@@ -930,7 +959,8 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                     // accumulator = lower bound L_ij = d~_ij - e |x0| W1_j of the true distortion;
                     // bidx is certainly the true argmin when every other lower bound exceeds its
                     // upper bound L + 2 e |x0| W1.  NaN-safe.
-                    const float x0 = s_x0[((it & 3) * 2 + h) * kBM + r];
+                    const float x0 = s_x0[((it & x0_mask) * 2 + h) * kBM + r];
+                    if (pre) fence_proxy_async();   // generic read before a later bulk copy reuses the slot
                     const float ub = fmaf(e2 * x0, p.w1[bidx], best);
                     if (!(second > ub)) {
                         const int pos = atomicAdd(p.flag_count, 1);
@@ -1162,6 +1192,56 @@ static bool tc_wide() {
 
 bool tc_operands_f16() { return tc_f16(); }
 
+// Frames -> pre-staged operands of vq_assign_tc2 (FP16 format): per half-tile of 128 frames one
+// record [hi part: KS chunks x 128 rows x 8 halves][lo part: same][128 norms f32], i.e. exactly what
+// the loader warps write into shared memory (same operations in the same order: bit-identical
+// operands), built ONCE per frame set.  Rows beyond n are zero.  thread = frame row.
+template <int KS>
+__global__ void __launch_bounds__(kBM)
+vq_prepare_frames_tc2h(const float *__restrict__ x, long n, int D, float err_scale,
+                       unsigned char *__restrict__ xop) {
+    constexpr int NE = KS * 8;
+    constexpr size_t part_bytes = (size_t) KS * kBM * 16;
+    constexpr size_t rec = 2 * part_bytes + kBM * sizeof(float);
+    const int r = threadIdx.x;
+    const long g = blockIdx.x;                 // half-tile
+    const long row = g * kBM + r;
+    float v[NE];
+    const float *src = x + row * D;
+#pragma unroll
+    for (int k = 0; k < NE; k++) v[k] = (row < n && k < D) ? __ldg(src + k) : 0.f;
+    float xm = 0.f;
+#pragma unroll
+    for (int k = 0; k < NE; k++) xm = fmaxf(xm, fabsf(v[k]));
+    uint32_t ef = (__float_as_uint(xm) >> 23) & 0xffu;
+    ef = ef < 16u ? 16u : ef;
+    const float scale = __uint_as_float((268u - ef) << 23);   // 2^(14 - floor(log2 xm))
+#pragma unroll
+    for (int k = 0; k < NE; k++) v[k] *= scale;
+    const float x0 = xm * scale;
+#pragma unroll
+    for (int k = 0; k < NE; k++)
+        if (k == D) v[k] = -1.001f * err_scale * x0;
+    unsigned char *hi = xop + (size_t) g * rec;
+    unsigned char *lo = hi + part_bytes;
+#pragma unroll
+    for (int c = 0; c < KS; c++) {
+        uint32_t hw[4], lw[4];
+#pragma unroll
+        for (int e = 0; e < 4; e++) {
+            const float a = v[8 * c + 2 * e], b2 = v[8 * c + 2 * e + 1];
+            const __half2 hh = __floats2half2_rn(a, b2);
+            const float2 hf = __half22float2(hh);
+            const __half2 ll = __floats2half2_rn(a - hf.x, b2 - hf.y);
+            hw[e] = *reinterpret_cast<const uint32_t *>(&hh);
+            lw[e] = *reinterpret_cast<const uint32_t *>(&ll);
+        }
+        *reinterpret_cast<uint4 *>(hi + ((size_t) c * kBM + r) * 16) = make_uint4(hw[0], hw[1], hw[2], hw[3]);
+        *reinterpret_cast<uint4 *>(lo + ((size_t) c * kBM + r) * 16) = make_uint4(lw[0], lw[1], lw[2], lw[3]);
+    }
+    reinterpret_cast<float *>(hi + 2 * part_bytes)[r] = x0;
+}
+
 int tc_tile_cols(int K, int D) {
     // (wide tiles need 2 x 13 chunks x 4 KB for D + 1 > 40: no room next to the frame tiles)
     if (tc_variant() == 2)
@@ -1276,6 +1356,31 @@ static void launch_tc2(TcParams &p, long grid, cudaStream_t s) {
     }
 }
 
+// pre-staged frame operands (see vq_prepare_frames_tc2h): bytes for n frames, 0 = not available
+static bool tc_pre_enabled() {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("ECOZ2_VQ_TC_PRE"); on = (e && e[0] == '0') ? 0 : 1; }
+    return on == 1;
+}
+size_t tc_frames_bytes(long n, int D) {
+    if (!(tc_pre_enabled() && tc_variant() == 2 && tc_f16() && n > 0 && tc_ksteps(D) <= 6)) return 0;
+    const size_t halves = 2 * (size_t) ((n + 2 * kBM - 1) / (2 * kBM));
+    return halves * ((size_t) 2 * tc_ksteps(D) * kBM * 16 + kBM * sizeof(float));
+}
+void launch_prepare_frames_tc(const float *x32, long n, int D, float err_scale, void *xop, cudaStream_t s) {
+    if (tc_frames_bytes(n, D) == 0) return;
+    const unsigned halves = (unsigned) (2 * ((n + 2 * kBM - 1) / (2 * kBM)));
+    unsigned char *o = static_cast<unsigned char *>(xop);
+    switch (tc_ksteps(D)) {
+        case 1: vq_prepare_frames_tc2h<1><<<halves, kBM, 0, s>>>(x32, n, D, err_scale, o); break;
+        case 2: vq_prepare_frames_tc2h<2><<<halves, kBM, 0, s>>>(x32, n, D, err_scale, o); break;
+        case 3: vq_prepare_frames_tc2h<3><<<halves, kBM, 0, s>>>(x32, n, D, err_scale, o); break;
+        case 4: vq_prepare_frames_tc2h<4><<<halves, kBM, 0, s>>>(x32, n, D, err_scale, o); break;
+        case 5: vq_prepare_frames_tc2h<5><<<halves, kBM, 0, s>>>(x32, n, D, err_scale, o); break;
+        default: vq_prepare_frames_tc2h<6><<<halves, kBM, 0, s>>>(x32, n, D, err_scale, o); break;
+    }
+}
+
 bool assign_tc_fuses_cells(int K, int D) {
     static int on = -1;
     if (on < 0) { const char *e = getenv("ECOZ2_VQ_TC_CELLS"); on = (e && e[0] == '0') ? 0 : 1; }
@@ -1286,9 +1391,10 @@ void launch_assign_tc(const float *x32, long n, int D, const float *wtc, int K,
                       const int32_t *list, const int32_t *list_count, const SearchScratch &sc,
                       bool flag, const float *w1, const float *w1max, float err_scale, int32_t *idx,
                       float *dump, int dump_ld, int num_sms, cudaStream_t s, const double *x64,
-                      double *cells, int32_t *hist) {
+                      double *cells, int32_t *hist, const void *xop) {
     if (n <= 0) return;
     TcParams p{};
+    if (xop != nullptr && list == nullptr && dump == nullptr) p.xop = static_cast<const unsigned char *>(xop);
     if (cells != nullptr && list == nullptr && dump == nullptr && flag && assign_tc_fuses_cells(K, D)) {
         p.x64 = x64; p.cells = cells; p.hist = hist;
     }
@@ -1379,9 +1485,11 @@ bool assign_tc_models_supported(int K, int D, long total_cols) {
 }
 void launch_assign_tc_models(const float *x32, long n, int D, const float *wtc, int K, long total_cols,
                              const SearchScratch &sc, float err_scale, int32_t *idx_out, long idx_stride,
-                             unsigned long long *seg_key, int seg_cap, int num_sms, cudaStream_t s) {
+                             unsigned long long *seg_key, int seg_cap, int num_sms, cudaStream_t s,
+                             const void *xop) {
     if (n <= 0) return;
     TcParams p{};
+    p.xop = static_cast<const unsigned char *>(xop);
     p.x = x32; p.n_frames = n; p.D = D; p.ksteps = tc_ksteps(D);
     p.wtc = wtc; p.K = (int) total_cols; p.BN = tc_tile_cols((int) total_cols, D);
     p.err_scale = err_scale; p.idx_out = idx_out;
