@@ -440,6 +440,10 @@ int Engine::frames_commit() {
             CUDA_TRY(cudaSetDevice(s.device));
             launch_convert_frames(s.x64, s.x32, s.n, D_, s.stream);
             ctr_.kernel_launches++;
+            // tensor mode: the frames as ready-made search operands, once per frame set (rebuilt by
+            // the search itself if the bound constant changes later)
+            if (mode_ == ECOZ2B200_MODE_TENSOR && assign_tc_supported(max_M_ < 2 ? 2 : max_M_, D_))
+                frame_operands(s, (float) (kappa_tc_ * ldexp(1.0, -24)));
         }
     }
     n_global_ = n_total_;

@@ -500,6 +500,7 @@ constexpr int kB2Stages = 3;
 
 struct Tc2Smem {
     uint64_t cell_full[8];                // [2 * (tile & 3) + half]: the half's cell indices are in s_cell
+    uint64_t cell_free[4];                // [tile & 3]: the loader warps have added that tile's rows (pre-staged operands)
     uint64_t b_full[kB2Stages], b_empty[kB2Stages];
     uint64_t raw_full[8], raw_empty[8];   // raw-frame staging buffers (TcParams::raw_bufs of them)
     uint64_t a_full[4], a_free[4];        // [2 * frame-tile buffer + half]
@@ -577,6 +578,7 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
             mbar_init(&sm->acc_empty[i], 4);
         }
         for (int i = 0; i < 8; i++) mbar_init(&sm->cell_full[i], 4);
+        for (int i = 0; i < 4; i++) mbar_init(&sm->cell_free[i], 4);
         fence_barrier_init();
     }
     if (warp == 13) tmem_alloc(&sm->tmem_slot, 512);
@@ -618,6 +620,10 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 const size_t rec = (size_t) a_half_bytes + kBM * sizeof(float);
                 uint32_t it = 0;
                 for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
+                    // fused cell sums: the loader warps no longer pace the pipeline (they only add
+                    // rows), so the ring of four cell-index slots needs its own back-pressure -- tile
+                    // `it` may start only when the rows of tile it - 4 have been added
+                    if (CELLS && it >= 4) mbar_wait(&sm->cell_free[it & 3], ((it >> 2) + 1) & 1);
                     for (int h = 0; h < 2; h++) {
                         const uint32_t ab = it & 1, aph = (it >> 1) & 1;
                         mbar_wait(&sm->a_free[2 * ab + h], aph ^ 1);
@@ -768,6 +774,8 @@ __global__ void __launch_bounds__(k2Threads, 1) vq_assign_tc2(const TcParams p) 
                 }
                 if (cmine >= 0) atomicAdd(p.hist + cmine, 1);
             }
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&sm->cell_free[t & 3]);
         };
         for (long ft = blockIdx.x; ft < n_ftiles; ft += gridDim.x, it++) {
             if (CELLS && it >= 2) accumulate_tile(it - 2);

@@ -38,6 +38,13 @@ def test_repeated_tensor_core_search_equals_fp64(built_lib):
     _run([sys.executable, "tests/tools/stress_tc.py", "8"])
 
 
+def test_repeated_passes_with_prestaged_operands_and_host_chunks(built_lib):
+    """The search fed by bulk copies of pre-staged operands (no loader warps pacing the pipeline) and the
+    chunked host pass, alternating, 3 x 24 repetitions: identical counts every time."""
+    out = _run([sys.executable, "tests/tools/stress_pre.py", "24"])
+    assert "STRESS OK" in out
+
+
 def test_search_parity_with_poisoned_shared_memory(built_lib):
     out = _run([sys.executable, "-m", "pytest", "-q", "-m", "gpu", "-x", "-p", "no:cacheprovider",
                 "tests/test_gpu_tc.py", "tests/test_gpu_parity.py", "-k",
