@@ -1334,6 +1334,8 @@ int Engine::learn(double eps, int stop_M, ecoz2b200_stage_cb on_stage, ecoz2b200
     std::vector<int32_t> h_cardd;
     double DDprv = DBL_MAX;
     int pass = 0;
+    static const bool timing = getenv("ECOZ2_VQ_TIMING") != nullptr;
+    double tm_pass = 0;
     double t_stage = now_s();
     Counters at_stage_start = ctr_;
     for (;;) {
@@ -1343,6 +1345,7 @@ int Engine::learn(double eps, int stop_M, ecoz2b200_stage_cb on_stage, ecoz2b200
         h_discel.resize(K_);
         int rc = kmeans_pass(nullptr, h_cardd.data(), h_discel.data(), &DD);
         if (rc) return rc;
+        tm_pass += now_s() - t_pass;
         const double avg = DD / (double) n_global_;
         if (on_pass) {
             int empty = 0;
@@ -1351,15 +1354,19 @@ int Engine::learn(double eps, int stop_M, ecoz2b200_stage_cb on_stage, ecoz2b200
         }
 
         if (pass > 0 && ((DDprv - DD) / DD) < eps) {
+            const double tq0 = now_s();
             h_refl.resize((size_t) K_ * D_);
             h_raas.resize((size_t) K_ * D_);
             rc = codebook_get(h_refl.data(), h_raas.data());
             if (rc) return rc;
+            const double tq1 = now_s();
             double sig = 0, inert = 0;
             rc = sigma(avg, &sig);
             if (rc) return rc;
+            const double tq2 = now_s();
             rc = inertia(&inert);
             if (rc) return rc;
+            const double tq3 = now_s();
             ecoz2b200_stage_info info;
             info.M = K_;
             info.passes = pass + 1;
@@ -1374,6 +1381,12 @@ int Engine::learn(double eps, int stop_M, ecoz2b200_stage_cb on_stage, ecoz2b200
             info.assign_ms = ctr_.assign_ms - at_stage_start.assign_ms;
             info.evals = (ctr_.evals - at_stage_start.evals);
             if (on_stage) on_stage(ctx, &info);
+            const double tq4 = now_s();
+            if (timing)
+                fprintf(stderr, "[timing] learn M=%d: %d passes %.2f ms | codebook read %.2f, sigma %.2f, inertia %.2f, "
+                                "stage callback %.2f ms\n", K_, pass + 1, tm_pass * 1e3, (tq1 - tq0) * 1e3,
+                        (tq2 - tq1) * 1e3, (tq3 - tq2) * 1e3, (tq4 - tq3) * 1e3);
+            tm_pass = 0;
             if (K_ >= stop_M) break;
             pass = 0;
             rc = codebook_grow();
