@@ -132,9 +132,13 @@ Engine::Engine(const int *devices, int num_devices, int P, int max_M)
         if (!chk(cudaMalloc(&s.raas_prev, cb), "cudaMalloc raas_prev")) return;
         if (!chk(cudaMalloc(&s.scalars, sizeof(double) * 8), "cudaMalloc scalars")) return;
         if (!chk(cudaMalloc(&s.dstat, sizeof(unsigned long long) * 8), "cudaMalloc dstat")) return;
-        cudaMemset(s.dstat, 0, sizeof(unsigned long long) * 8);
-        cudaMemset(s.refl, 0, cb);
-        cudaMemset(s.raas, 0, cb);
+        // on s.stream, NOT cudaMemset: that one runs on the legacy default stream, returns before the
+        // fill has run and is not ordered against the non-blocking s.stream -- a codebook uploaded
+        // right after the constructor could be zeroed again (seen as a rare wrong pass on cold boxes)
+        if (!chk(cudaMemsetAsync(s.dstat, 0, sizeof(unsigned long long) * 8, s.stream), "cudaMemsetAsync")) return;
+        if (!chk(cudaMemsetAsync(s.refl, 0, cb, s.stream), "cudaMemsetAsync")) return;
+        if (!chk(cudaMemsetAsync(s.raas, 0, cb, s.stream), "cudaMemsetAsync")) return;
+        if (!chk(cudaStreamSynchronize(s.stream), "cudaStreamSynchronize")) return;
     }
     const char *fs = getenv("ECOZ2_VQ_FUSED_SMALL");
     if (fs && fs[0] == '0') use_small_ = false;
@@ -285,8 +289,11 @@ int Engine::ensure_capacity(Shard &s, long n) {
     CUDA_TRY(cudaStreamSynchronize(s.stream));
     double *nx64 = nullptr;
     CUDA_TRY(cudaMalloc(&nx64, sizeof(double) * (size_t) n * D_));
-    if (s.x64 && s.n > 0)
-        CUDA_TRY(cudaMemcpy(nx64, s.x64, sizeof(double) * (size_t) s.n * D_, cudaMemcpyDeviceToDevice));
+    if (s.x64 && s.n > 0) {   // (a device-to-device cudaMemcpy would run on the legacy stream and return early)
+        CUDA_TRY(cudaMemcpyAsync(nx64, s.x64, sizeof(double) * (size_t) s.n * D_, cudaMemcpyDeviceToDevice,
+                                 s.stream));
+        CUDA_TRY(cudaStreamSynchronize(s.stream));
+    }
     cudaFree(s.x64); s.x64 = nx64;
     cudaFree(s.x32); cudaFree(s.idx); cudaFree(s.idx_tmp); cudaFree(s.seq); cudaFree(s.mindist);
     cudaFree(s.sc_mem); cudaFree(s.cs_mem);

@@ -45,6 +45,13 @@ def test_repeated_passes_with_prestaged_operands_and_host_chunks(built_lib):
     assert "STRESS OK" in out
 
 
+def test_codebook_uploaded_right_after_create_survives_a_busy_default_stream(built_lib):
+    """Nothing the constructor queues may land after the caller's first upload (it used cudaMemset on the
+    legacy default stream once; see tests/tools/create_upload_order.py)."""
+    out = _run([sys.executable, "tests/tools/create_upload_order.py", "20"])
+    assert "STRESS OK" in out
+
+
 def test_search_parity_with_poisoned_shared_memory(built_lib):
     out = _run([sys.executable, "-m", "pytest", "-q", "-m", "gpu", "-x", "-p", "no:cacheprovider",
                 "tests/test_gpu_tc.py", "tests/test_gpu_parity.py", "-k",
