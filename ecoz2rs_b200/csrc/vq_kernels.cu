@@ -829,10 +829,149 @@ void launch_audit(const double *x64, long n, int D, const double *raas, int K, c
     vq_audit<<<num_sms * 4, 256, 0, s>>>(x64, n, D, raas, K, idx, every, out);
 }
 
+// --------------------------------------------------------------------------------
+// (b') the same without cell sums (vq quantize, inertia, min_dists): FP64 distortion of every
+// frame against its chosen codeword, symbols, DD and inertia.  vq_accumulate spends ~80 warp
+// instructions per frame (a 5-level 64-bit shuffle tree per frame) and is issue-bound at
+// 2.7 TB/s; here a warp takes 8 consecutive frames = 8 D consecutive doubles with fully
+// coalesced loads (lane = element, not component), multiplies each element with its codeword
+// weight, parks the products in shared memory and lets 4 lanes per frame add them up:
+// ~15 instructions per frame.  Sum order per frame: four strided partial sums (components
+// q, q + 4, ...), then (q0 + q1) + (q2 + q3).
+// reference: quantize.c:14-30 (distortion of the winner), inertia.c:15-28
+// --------------------------------------------------------------------------------
+constexpr int kWdFrames = 8;
+constexpr int kWdMaxD = 40;
+template <int NL>
+__global__ void __launch_bounds__(256, 4)
+vq_winner_distortion(const double *__restrict__ x64, const int32_t *__restrict__ idx, long n, int D,
+                     const double *__restrict__ raas, PackedLayout L, double *__restrict__ packed,
+                     double *__restrict__ mindist, uint16_t *__restrict__ seq,
+                     int32_t *__restrict__ neg_list, int32_t *__restrict__ neg_count) {
+    constexpr int RS = 4 * NL + 1;   // row stride of the product rows (odd: spreads the banks)
+    __shared__ double s_p[8][kWdFrames * RS];
+    __shared__ int s_ci[8][kWdFrames];
+    // element e of a block -> (frame in the block) << 8 | component (a table: registers are short)
+    __shared__ int s_efm[32 * NL];
+    const int lane = threadIdx.x & 31;
+    const int w = threadIdx.x >> 5;
+    const long warp = ((long) blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long n_warps = ((long) gridDim.x * blockDim.x) >> 5;
+    double *sp = s_p[w];
+    int *sci = s_ci[w];
+    // columns D .. 4 NL - 1 of every row are never written: zero once, the sums below run over 4 NL
+    for (int k = lane; k < kWdFrames * RS; k += 32) sp[k] = 0.0;
+    for (int e = threadIdx.x; e < 32 * NL; e += blockDim.x) s_efm[e] = ((e / D) << 8) | (e % D);
+    __syncthreads();
+    const int *efm = s_efm + lane;
+    const bool last_ok = lane + 32 * (NL - 1) < kWdFrames * D;
+    const int rf = lane >> 2, rq = lane & 3;
+    const double *srow = sp + rf * RS + rq;
+    double dd_sum = 0.0, in_sum = 0.0;
+
+    // sums of the 8 product rows and the outputs of nf <= 8 frames.  The factor 2 of the components
+    // m >= 1 (distortion.c:6-13) is applied to their SUM: scaling by 2 is exact, so this equals the
+    // sum of the doubled terms bit for bit.
+    auto finish = [&](long v0, int nf) {
+        __syncwarp();
+        double part = 0.0;
+#pragma unroll
+        for (int j = 1; j < NL; j++) part += srow[4 * j];
+        const double first = srow[0];          // component rq: the undoubled one in lane rq == 0
+        if (rq != 0) part += first;
+        part += __shfl_xor_sync(0xffffffffu, part, 1);
+        part += __shfl_xor_sync(0xffffffffu, part, 2);
+        __syncwarp();
+        if (rq == 0 && rf < nf) {
+            const double dd = first + 2.0 * part;
+            const double md = dd - 1.0;
+            dd_sum += md;
+            // (inertia.c:21-25: min_i (dd_i^2); a negative minimum goes to the exact scan, see vq_accumulate)
+            if (neg_list != nullptr && dd < 0.0) neg_list[atomicAdd(neg_count, 1)] = (int32_t) (v0 + rf);
+            else in_sum += dd * dd;
+            if (mindist) mindist[v0 + rf] = md;
+            if (seq) seq[v0 + rf] = (uint16_t) sci[rf];
+        }
+    };
+
+    const long n_full = n / kWdFrames;
+    long b = warp;
+    int ci_next = (b < n_full && lane < kWdFrames) ? idx[b * kWdFrames + lane] : 0;
+    for (; b < n_full; b += n_warps) {
+        const long v0 = b * kWdFrames;
+        const double *xb = x64 + v0 * D;
+        double xv[NL];
+#pragma unroll
+        for (int r = 0; r < NL; r++) xv[r] = (r < NL - 1 || last_ok) ? xb[lane + 32 * r] : 0.0;
+        if (lane < kWdFrames) sci[lane] = ci_next;
+        __syncwarp();
+        if (b + n_warps < n_full && lane < kWdFrames) ci_next = idx[(b + n_warps) * kWdFrames + lane];
+#pragma unroll
+        for (int r = 0; r < NL; r++) {
+            if (r < NL - 1 || last_ok) {
+                const int fm = efm[32 * r];
+                const int f = fm >> 8, m = fm & 255;
+                const double wv = raas[sci[f] * D + m];
+                sp[f * RS + m] = xv[r] * wv;
+            }
+        }
+        finish(v0, kWdFrames);
+    }
+    if (n_full * kWdFrames < n && warp == n_full % n_warps) {   // the partial block at the end
+        const long v0 = n_full * kWdFrames;
+        const int nf = (int) (n - v0);
+        if (lane < nf) sci[lane] = idx[v0 + lane];
+        __syncwarp();
+        for (int e = lane; e < kWdFrames * D; e += 32) {
+            const int f = e / D, m = e - f * D;
+            sp[f * RS + m] = f < nf ? x64[v0 * D + e] * raas[sci[f] * D + m] : 0.0;
+        }
+        finish(v0, nf);
+    }
+    dd_sum = warp_sum(dd_sum);
+    in_sum = warp_sum(in_sum);
+    __shared__ double s_dd[8], s_in[8];
+    if (lane == 0) { s_dd[w] = dd_sum; s_in[w] = in_sum; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, b2 = 0.0;
+        for (int i = 0; i < (int) (blockDim.x >> 5); i++) { a += s_dd[i]; b2 += s_in[i]; }
+        atomicAdd(packed + L.dd(), a);
+        atomicAdd(packed + L.inertia(), b2);
+    }
+}
+
+template <int NL>
+static void launch_winner_distortion_nl(const double *x64, const int32_t *idx, long n, int D, const double *raas,
+                                        int K, double *packed, double *mindist, uint16_t *seq, int num_sms,
+                                        cudaStream_t s, int32_t *neg_list, int32_t *neg_count) {
+    PackedLayout L{K, D};
+    const long n_blocks = (n + kWdFrames - 1) / kWdFrames;
+    long blocks = (n_blocks + 7) / 8;
+    const long cap = (long) num_sms * 8;
+    if (blocks > cap) blocks = cap;
+    vq_winner_distortion<NL><<<(unsigned) blocks, 256, 0, s>>>(x64, idx, n, D, raas, L, packed, mindist, seq,
+                                                               neg_list, neg_count);
+}
+
+static bool winner_distortion_enabled() {
+    static int on = -1;
+    if (on < 0) { const char *e = getenv("ECOZ2_VQ_WINNER_KERNEL"); on = (e && e[0] == '0') ? 0 : 1; }
+    return on == 1;
+}
+
 void launch_accumulate(const double *x64, const int32_t *idx, long n, int D, const double *raas,
                        int K, double *packed, double *mindist, uint16_t *seq, bool with_cells,
                        int num_sms, cudaStream_t s, int32_t *neg_list, int32_t *neg_count) {
     if (n <= 0) return;
+    if (!with_cells && D <= kWdMaxD && winner_distortion_enabled()) {
+#define WD_CASE(NLV) case NLV: launch_winner_distortion_nl<NLV>(x64, idx, n, D, raas, K, packed, mindist, seq, num_sms, s, neg_list, neg_count); return;
+        switch ((kWdFrames * D + 31) / 32) {
+            WD_CASE(1) WD_CASE(2) WD_CASE(3) WD_CASE(4) WD_CASE(5) WD_CASE(6) WD_CASE(7) WD_CASE(8) WD_CASE(9) WD_CASE(10)
+            default: break;
+        }
+#undef WD_CASE
+    }
     const int nr = (D + 31) / 32;
     switch (nr) {
         case 1: launch_accumulate_nr<1>(x64, idx, n, D, raas, K, packed, mindist, seq, with_cells, num_sms, s, neg_list, neg_count); break;

@@ -206,6 +206,42 @@ def test_sigma_and_inertia(built_lib, frames36, oracle_run36):
     assert abs(inert - in_ref) <= 1e-7 * abs(in_ref)
 
 
+@pytest.mark.parametrize("P", [12, 20, 36])
+def test_winner_distortion_kernel_edges(built_lib, P):
+    """vq_winner_distortion (FP64 distortion of every frame against its chosen codeword, 8 frames per warp
+    step): frame counts below, at and around the block of 8, K above the fused small-codebook sizes so
+    that the kernel is the one that runs; min distances, symbols, average distortion and inertia against
+    the oracle (quantize.c:14-30, inertia.c:15-28), including frames that are not gain-normalised
+    (negative distortions: min_i dd_i^2 is then not (min_i dd_i)^2)."""
+    from ecoz2rs_b200.synth import ar_mix
+    from oracle import oracle as O
+    K = 24
+    rng = np.random.default_rng(100 + P)
+    refl = np.zeros((K, P + 1))
+    refl[:, 1:] = np.clip(rng.normal(size=(K, P)) * 0.25, -0.9, 0.9)
+    raas = O.refl_to_raas(refl)
+    for n in (1, 7, 8, 9, 15, 16, 17, 1003):
+        x = ar_mix(n + 5, P, seed=n)[:n].copy()
+        if n >= 9:                       # a few frames that are not autocorrelations of anything
+            x[3, 1:] *= -3.0
+            x[n - 1, 1:] = rng.normal(size=P) * 4.0
+        idx_ref, dd_ref, d2_ref = O.assign(x, raas)
+        with _engine(P, max_M=K) as eng:
+            eng.set_frames(x)
+            eng.set_reflections(refl)
+            seq, avg = eng.quantize_resident()
+            inert = eng.inertia()
+            eng.kmeans_pass()                                 # last_assignment: the pass's codewords and
+            codeword, min_dist = eng.last_assignment()        # distances against the codebook it started from
+        assert allowed_index_mismatches(seq.astype(np.int32), idx_ref, dd_ref, d2_ref).size == 0
+        own = np.array([O.distortion(x[t], raas[seq[t]]) for t in range(n)]) - 1.0
+        assert np.array_equal(codeword, seq.astype(np.int32))
+        assert np.allclose(min_dist, own, rtol=1e-12, atol=1e-12)
+        assert abs(avg - own.sum() / n) <= 1e-12 * max(1.0, abs(own).sum() / n)
+        in_ref = O.inertia(x, raas)
+        assert abs(inert - in_ref) <= 1e-9 * abs(in_ref)
+
+
 @pytest.mark.parametrize("P,fix", [(36, "oracle_run36"), (12, "oracle_run12")])
 def test_learn_end_to_end(built_lib, request, P, fix, frames36, frames12):
     """Whole LBG run: same number of passes per stage, per-pass DD, codebooks, sigma,
