@@ -833,24 +833,25 @@ void launch_audit(const double *x64, long n, int D, const double *raas, int K, c
 // (b') the same without cell sums (vq quantize, inertia, min_dists): FP64 distortion of every
 // frame against its chosen codeword, symbols, DD and inertia.  vq_accumulate spends ~80 warp
 // instructions per frame (a 5-level 64-bit shuffle tree per frame) and is issue-bound at
-// 2.7 TB/s; here a warp takes 8 consecutive frames = 8 D consecutive doubles with fully
-// coalesced loads (lane = element, not component), multiplies each element with its codeword
-// weight, parks the products in shared memory and lets 4 lanes per frame add them up:
-// ~15 instructions per frame.  Sum order per frame: four strided partial sums (components
-// q, q + 4, ...), then (q0 + q1) + (q2 + q3).
+// 2.7 TB/s; here a warp takes 8 consecutive frames (16 for rows of D <= 20) = 8 D consecutive
+// doubles with fully coalesced loads (lane = element, not component), multiplies each element
+// with its codeword weight, parks the products in shared memory and lets 4 (2) lanes per frame
+// add them up.  Sum order per frame: strided partial sums (components q, q + 4, ... without
+// component 0), then (q0 + q1) + (q2 + q3), times 2, plus component 0.
 // reference: quantize.c:14-30 (distortion of the winner), inertia.c:15-28
 // --------------------------------------------------------------------------------
-constexpr int kWdFrames = 8;
 constexpr int kWdMaxD = 40;
-template <int NL>
+// FB frames per warp step: 8 (4 lanes add up a frame), or 16 (2 lanes) for the short rows D <= 20
+template <int NL, int FB>
 __global__ void __launch_bounds__(256, 4)
 vq_winner_distortion(const double *__restrict__ x64, const int32_t *__restrict__ idx, long n, int D,
                      const double *__restrict__ raas, PackedLayout L, double *__restrict__ packed,
                      double *__restrict__ mindist, uint16_t *__restrict__ seq,
                      int32_t *__restrict__ neg_list, int32_t *__restrict__ neg_count) {
-    constexpr int RS = 4 * NL + 1;   // row stride of the product rows (odd: spreads the banks)
-    __shared__ double s_p[8][kWdFrames * RS];
-    __shared__ int s_ci[8][kWdFrames];
+    constexpr int LPF = 32 / FB;       // lanes per frame in the sums
+    constexpr int RS = LPF * NL + 1;   // row stride of the product rows (odd: spreads the banks)
+    __shared__ double s_p[8][FB * RS];
+    __shared__ int s_ci[8][FB];
     // element e of a block -> (frame in the block) << 8 | component (a table: registers are short)
     __shared__ int s_efm[32 * NL];
     const int lane = threadIdx.x & 31;
@@ -859,28 +860,28 @@ vq_winner_distortion(const double *__restrict__ x64, const int32_t *__restrict__
     const long n_warps = ((long) gridDim.x * blockDim.x) >> 5;
     double *sp = s_p[w];
     int *sci = s_ci[w];
-    // columns D .. 4 NL - 1 of every row are never written: zero once, the sums below run over 4 NL
-    for (int k = lane; k < kWdFrames * RS; k += 32) sp[k] = 0.0;
+    // columns D .. LPF NL - 1 of every row are never written: zero once, the sums below run over LPF NL
+    for (int k = lane; k < FB * RS; k += 32) sp[k] = 0.0;
     for (int e = threadIdx.x; e < 32 * NL; e += blockDim.x) s_efm[e] = ((e / D) << 8) | (e % D);
     __syncthreads();
     const int *efm = s_efm + lane;
-    const bool last_ok = lane + 32 * (NL - 1) < kWdFrames * D;
-    const int rf = lane >> 2, rq = lane & 3;
+    const bool last_ok = lane + 32 * (NL - 1) < FB * D;
+    const int rf = lane / LPF, rq = lane % LPF;
     const double *srow = sp + rf * RS + rq;
     double dd_sum = 0.0, in_sum = 0.0;
 
-    // sums of the 8 product rows and the outputs of nf <= 8 frames.  The factor 2 of the components
+    // sums of the FB product rows and the outputs of nf <= FB frames.  The factor 2 of the components
     // m >= 1 (distortion.c:6-13) is applied to their SUM: scaling by 2 is exact, so this equals the
     // sum of the doubled terms bit for bit.
     auto finish = [&](long v0, int nf) {
         __syncwarp();
         double part = 0.0;
 #pragma unroll
-        for (int j = 1; j < NL; j++) part += srow[4 * j];
+        for (int j = 1; j < NL; j++) part += srow[LPF * j];
         const double first = srow[0];          // component rq: the undoubled one in lane rq == 0
         if (rq != 0) part += first;
         part += __shfl_xor_sync(0xffffffffu, part, 1);
-        part += __shfl_xor_sync(0xffffffffu, part, 2);
+        if (LPF == 4) part += __shfl_xor_sync(0xffffffffu, part, 2);
         __syncwarp();
         if (rq == 0 && rf < nf) {
             const double dd = first + 2.0 * part;
@@ -894,18 +895,18 @@ vq_winner_distortion(const double *__restrict__ x64, const int32_t *__restrict__
         }
     };
 
-    const long n_full = n / kWdFrames;
+    const long n_full = n / FB;
     long b = warp;
-    int ci_next = (b < n_full && lane < kWdFrames) ? idx[b * kWdFrames + lane] : 0;
+    int ci_next = (b < n_full && lane < FB) ? idx[b * FB + lane] : 0;
     for (; b < n_full; b += n_warps) {
-        const long v0 = b * kWdFrames;
+        const long v0 = b * FB;
         const double *xb = x64 + v0 * D;
         double xv[NL];
 #pragma unroll
         for (int r = 0; r < NL; r++) xv[r] = (r < NL - 1 || last_ok) ? xb[lane + 32 * r] : 0.0;
-        if (lane < kWdFrames) sci[lane] = ci_next;
+        if (lane < FB) sci[lane] = ci_next;
         __syncwarp();
-        if (b + n_warps < n_full && lane < kWdFrames) ci_next = idx[(b + n_warps) * kWdFrames + lane];
+        if (b + n_warps < n_full && lane < FB) ci_next = idx[(b + n_warps) * FB + lane];
 #pragma unroll
         for (int r = 0; r < NL; r++) {
             if (r < NL - 1 || last_ok) {
@@ -915,14 +916,14 @@ vq_winner_distortion(const double *__restrict__ x64, const int32_t *__restrict__
                 sp[f * RS + m] = xv[r] * wv;
             }
         }
-        finish(v0, kWdFrames);
+        finish(v0, FB);
     }
-    if (n_full * kWdFrames < n && warp == n_full % n_warps) {   // the partial block at the end
-        const long v0 = n_full * kWdFrames;
+    if (n_full * FB < n && warp == n_full % n_warps) {   // the partial block at the end
+        const long v0 = n_full * FB;
         const int nf = (int) (n - v0);
         if (lane < nf) sci[lane] = idx[v0 + lane];
         __syncwarp();
-        for (int e = lane; e < kWdFrames * D; e += 32) {
+        for (int e = lane; e < FB * D; e += 32) {
             const int f = e / D, m = e - f * D;
             sp[f * RS + m] = f < nf ? x64[v0 * D + e] * raas[sci[f] * D + m] : 0.0;
         }
@@ -941,16 +942,16 @@ vq_winner_distortion(const double *__restrict__ x64, const int32_t *__restrict__
     }
 }
 
-template <int NL>
+template <int NL, int FB>
 static void launch_winner_distortion_nl(const double *x64, const int32_t *idx, long n, int D, const double *raas,
                                         int K, double *packed, double *mindist, uint16_t *seq, int num_sms,
                                         cudaStream_t s, int32_t *neg_list, int32_t *neg_count) {
     PackedLayout L{K, D};
-    const long n_blocks = (n + kWdFrames - 1) / kWdFrames;
+    const long n_blocks = (n + FB - 1) / FB;
     long blocks = (n_blocks + 7) / 8;
     const long cap = (long) num_sms * 8;
     if (blocks > cap) blocks = cap;
-    vq_winner_distortion<NL><<<(unsigned) blocks, 256, 0, s>>>(x64, idx, n, D, raas, L, packed, mindist, seq,
+    vq_winner_distortion<NL, FB><<<(unsigned) blocks, 256, 0, s>>>(x64, idx, n, D, raas, L, packed, mindist, seq,
                                                                neg_list, neg_count);
 }
 
@@ -965,8 +966,9 @@ void launch_accumulate(const double *x64, const int32_t *idx, long n, int D, con
                        int num_sms, cudaStream_t s, int32_t *neg_list, int32_t *neg_count) {
     if (n <= 0) return;
     if (!with_cells && D <= kWdMaxD && winner_distortion_enabled()) {
-#define WD_CASE(NLV) case NLV: launch_winner_distortion_nl<NLV>(x64, idx, n, D, raas, K, packed, mindist, seq, num_sms, s, neg_list, neg_count); return;
-        switch ((kWdFrames * D + 31) / 32) {
+#define WD_CASE(NLV) case NLV: if (D <= 20) launch_winner_distortion_nl<NLV, 16>(x64, idx, n, D, raas, K, packed, mindist, seq, num_sms, s, neg_list, neg_count); \
+                               else launch_winner_distortion_nl<NLV, 8>(x64, idx, n, D, raas, K, packed, mindist, seq, num_sms, s, neg_list, neg_count); return;
+        switch (((D <= 20 ? 16 : 8) * D + 31) / 32) {
             WD_CASE(1) WD_CASE(2) WD_CASE(3) WD_CASE(4) WD_CASE(5) WD_CASE(6) WD_CASE(7) WD_CASE(8) WD_CASE(9) WD_CASE(10)
             default: break;
         }
