@@ -16,7 +16,9 @@
 // are produced on demand (stage reports, ecoz2b200_last_assignment) by vq_accumulate's
 // distortion-only instance.
 #include "vq_kernels.cuh"
+#include "vq_tc_common.cuh"
 
+#include <cstdint>
 #include <cstdlib>
 
 namespace vqb200 {
@@ -353,6 +355,153 @@ vq_cell_sums_stream(const double *__restrict__ x64, const int32_t *__restrict__ 
         if (cnt[i]) atomicAdd(hist + i, cnt[i]);
 }
 
+// ---- streaming variant without atomics: one PRIVATE table per warp --------------------------------
+// For tables small enough that every consumer warp of the CTA holds its own copy ([K][D + 1] doubles,
+// column D counts the frames; K <= 32 with 16 warps, K <= 64 with 8 at P = 36).  The frames are read
+// ONCE, in natural order: a producer warp streams tiles of 64 consecutive frames and their cell
+// indices (two cp.async.bulk per tile, S stages in flight) into a shared-memory ring; each of the W
+// consumer warps takes 64 / W rows of a tile and adds them into ITS table with plain shared-memory
+// read-modify-writes -- element (c, m) of a warp's table is only ever touched by lane m (mod 32) of
+// that warp, so program order is all the ordering needed.  One flush per CTA at the end: K D FP64
+// atomics.  A last partial tile is read from global memory.
+// Measured on B200, 10M frames at P = 36: 0.63 ms (K = 16, 32) and 0.70 ms (K = 64) against 0.79 ms of
+// the sorted gather; what bounds it is the shared-memory pipe (row in by bulk copy, row out, table
+// row out and back in: ~1.2 KB per frame at 128 B/clk).  Rows of 13 doubles (two frames per
+// instruction were tried) gain nothing over vq_cell_sums_stream and keep that kernel.
+constexpr int kPrivTile = 64;
+
+template <int NR, int W>
+__global__ void __launch_bounds__(32 * (W + 1), 1)
+vq_cell_sums_private(const double *__restrict__ x64, const int32_t *__restrict__ idx, long n, int K, int D,
+                     int S, PackedLayout L, double *__restrict__ packed, int32_t *__restrict__ hist,
+                     uint16_t *__restrict__ seq) {
+    constexpr int TF = kPrivTile, FPW = TF / W;
+    static_assert(FPW % 4 == 0, "rows per warp: whole batches of 4");
+    extern __shared__ __align__(128) unsigned char cp_smem[];
+    const int RS = D + 1;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    double *tab_all = reinterpret_cast<double *>(cp_smem);
+    const size_t tab_bytes = (sizeof(double) * (size_t) W * K * RS + 127) & ~(size_t) 127;
+    unsigned char *ring = cp_smem + tab_bytes;
+    // a stage = the tile's rows (a multiple of 16 bytes: TF is even) + its TF cell indices
+    const uint32_t stage_bytes = (uint32_t) (TF * D * sizeof(double));
+    const uint32_t idx_off = (stage_bytes + 127u) & ~127u;
+    const uint32_t stage_stride = idx_off + TF * (uint32_t) sizeof(int32_t);
+    uint64_t *full = reinterpret_cast<uint64_t *>(ring + (size_t) S * stage_stride);
+    uint64_t *empty = full + S;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < S; i++) { mbar_init(&full[i], 1); mbar_init(&empty[i], W); }
+        fence_barrier_init();
+    }
+    for (int e = threadIdx.x; e < W * K * RS; e += blockDim.x) tab_all[e] = 0.0;
+    __syncthreads();
+
+    const long n_full = n / TF;
+    if (warp == W) {
+        // producer: two bulk copies per tile
+        if (lane == 0) {
+            long i = 0;
+            for (long t = blockIdx.x; t < n_full; t += gridDim.x, i++) {
+                const int st = (int) (i % S);
+                if (i >= S) mbar_wait(&empty[st], (uint32_t) (((i / S) & 1) ^ 1));   // (one lane spinning)
+                mbar_expect_tx(&full[st], stage_bytes + TF * (uint32_t) sizeof(int32_t));
+                bulk_g2s(ring + (size_t) st * stage_stride, x64 + t * TF * D, stage_bytes, &full[st]);
+                bulk_g2s(ring + (size_t) st * stage_stride + idx_off, idx + t * TF, TF * (uint32_t) sizeof(int32_t),
+                         &full[st]);
+            }
+        }
+    } else {
+        double *tab = tab_all + (size_t) warp * K * RS;
+        // rows[0 .. cnt) of this warp, cc = cell of row `lane` (-1: none)
+        auto process = [&](const double *rows, int cc, int cnt) {
+            double xv[FPW][NR];
+#pragma unroll
+            for (int k = 0; k < FPW; k++)
+#pragma unroll
+                for (int r = 0; r < NR; r++) {
+                    const int m = lane + 32 * r;
+                    double v = 0.0;
+                    if (k < cnt) { if (m < D) v = rows[k * D + m]; else if (m == D) v = 1.0; }
+                    xv[k][r] = v;
+                }
+            // Batches of 4 frames.  The read-modify-writes of one frame after the other are a chain of
+            // dependent LDS -> DADD -> STS (~100 clocks each); when the 4 cells of a batch differ
+            // (warp-uniform test: one match + one ballot per call) the 4 chains are independent and
+            // are issued together.
+            const unsigned peers = __match_any_sync(0xffffffffu, cc);
+            const unsigned batch = 0xFu << (lane & ~3);
+            const unsigned uniq = __ballot_sync(0xffffffffu, cc >= 0 && (peers & batch) == (1u << lane));
+#pragma unroll
+            for (int b = 0; b < FPW / 4; b++) {
+                if (((uniq >> (4 * b)) & 0xFu) == 0xFu) {
+                    int cs[4];
+                    double t[4][NR];
+#pragma unroll
+                    for (int j = 0; j < 4; j++) cs[j] = __shfl_sync(0xffffffffu, cc, 4 * b + j);
+#pragma unroll
+                    for (int j = 0; j < 4; j++)
+#pragma unroll
+                        for (int r = 0; r < NR; r++) {
+                            const int m = lane + 32 * r;
+                            t[j][r] = m <= D ? tab[cs[j] * RS + m] : 0.0;
+                        }
+#pragma unroll
+                    for (int j = 0; j < 4; j++)
+#pragma unroll
+                        for (int r = 0; r < NR; r++) {
+                            const int m = lane + 32 * r;
+                            if (m <= D) tab[cs[j] * RS + m] = t[j][r] + xv[4 * b + j][r];
+                        }
+                    continue;
+                }
+#pragma unroll
+                for (int k = 4 * b; k < 4 * b + 4; k++) {
+                    const int c = __shfl_sync(0xffffffffu, cc, k);
+                    if (c >= 0) {                              // warp-uniform
+#pragma unroll
+                        for (int r = 0; r < NR; r++) {
+                            const int m = lane + 32 * r;
+                            if (m <= D) tab[c * RS + m] += xv[k][r];
+                        }
+                    }
+                }
+            }
+        };
+        long i = 0;
+        for (long t = blockIdx.x; t < n_full; t += gridDim.x, i++) {
+            const int st = (int) (i % S);
+            const long v0 = t * TF + warp * FPW;
+            const unsigned char *stage = ring + (size_t) st * stage_stride;
+            mbar_wait(&full[st], (uint32_t) ((i / S) & 1));
+            const int cc = lane < FPW ? reinterpret_cast<const int32_t *>(stage + idx_off)[warp * FPW + lane] : -1;
+            if (seq != nullptr && lane < FPW) seq[v0 + lane] = (uint16_t) cc;
+            process(reinterpret_cast<const double *>(stage) + warp * FPW * D, cc, FPW);
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&empty[st]);
+        }
+        if (n_full * TF < n && (long) blockIdx.x == n_full % gridDim.x) {
+            const long v0 = n_full * TF + warp * FPW;
+            long mine = n - v0;
+            if (mine > FPW) mine = FPW;
+            if (mine > 0) {
+                const int cc = lane < mine ? idx[v0 + lane] : -1;
+                if (seq != nullptr && lane < mine) seq[v0 + lane] = (uint16_t) cc;
+                process(x64 + v0 * D, cc, (int) mine);
+            }
+        }
+    }
+    __syncthreads();
+    for (int e = threadIdx.x; e < K * RS; e += blockDim.x) {
+        double sum = tab_all[e];
+        for (int i = 1; i < W; i++) sum += tab_all[(size_t) i * K * RS + e];
+        if (sum != 0.0) {
+            const int c = e / RS, m = e - c * RS;
+            if (m < D) atomicAdd(packed + L.cells() + (long) c * D + m, sum);
+            else atomicAdd(hist + c, (int32_t) (sum + 0.5));
+        }
+    }
+}
+
 // counts, per-cell distortion  cellsum . w - count,  DD = sum of them; one warp per cell
 __global__ void __launch_bounds__(256)
 vq_cell_finish(const double *__restrict__ raas, const int32_t *__restrict__ hist, int K, int D,
@@ -420,6 +569,12 @@ static bool cell_stream_enabled() {
     return v == 1;
 }
 
+// ECOZ2_VQ_CELL_PRIV=0 switches the private-table variant off
+static bool cell_private_enabled() {
+    static int v = -1;
+    if (v < 0) { const char *e = getenv("ECOZ2_VQ_CELL_PRIV"); v = (e && e[0] == '0') ? 0 : 1; }
+    return v == 1;
+}
 int cell_pad_ld(int D) {
     static int on = -1;
     // OFF by default: measured on B200 (10M frames, K = 16 .. 2048) the sums take 0.79-0.82 ms from the
@@ -442,6 +597,41 @@ void launch_cell_sums(const double *x64, const int32_t *idx, long n, int D, cons
     const PackedLayout L{K, D};
     cudaMemsetAsync(cs.hist, 0, sizeof(int32_t) * (size_t) (K + 1), s);
     constexpr size_t kStreamSmemMax = 200 * 1024;
+    // private tables (no atomics): rows of 16 .. 62 doubles, when 16 or 8 copies of the [K][D + 1] table
+    // and a ring of at least 3 tiles fit into the shared memory of an SM
+    if (n > 0 && cell_private_enabled() && D > 15 && D <= 62 && x64_padded == nullptr &&
+        ((reinterpret_cast<uintptr_t>(x64) | reinterpret_cast<uintptr_t>(idx)) & 15) == 0) {
+        constexpr size_t kPrivSmemMax = 224 * 1024;
+        const size_t tab1 = sizeof(double) * (size_t) K * (D + 1);
+        const size_t stage = ((sizeof(double) * (size_t) kPrivTile * D + 127) & ~(size_t) 127) +
+                             sizeof(int32_t) * (size_t) kPrivTile;      // rows + cell indices of a tile
+        int W = 0, S = 0;
+        for (int w : {16, 8}) {
+            const size_t tabs = (tab1 * w + 127) & ~(size_t) 127;
+            if (tabs + 3 * (stage + 16) > kPrivSmemMax) continue;
+            W = w;
+            S = (int) ((kPrivSmemMax - tabs) / (stage + 16));
+            if (S > 8) S = 8;
+            break;
+        }
+        if (W > 0) {
+            const size_t smem = ((tab1 * W + 127) & ~(size_t) 127) + (size_t) S * (stage + 16);
+            const long tiles = (n + kPrivTile - 1) / kPrivTile;
+            const long grid = tiles < num_sms ? tiles : num_sms;
+#define PRIV_LAUNCH(NRV, WV)                                                                               \
+    do {                                                                                                   \
+        cudaFuncSetAttribute(vq_cell_sums_private<NRV, WV>, cudaFuncAttributeMaxDynamicSharedMemorySize,   \
+                             (int) kPrivSmemMax);                                                          \
+        vq_cell_sums_private<NRV, WV><<<(unsigned) grid, 32 * (WV + 1), smem, s>>>(                        \
+            x64, idx, n, K, D, S, L, packed, cs.hist, seq);                                                \
+    } while (0)
+            if (D <= 31) { if (W == 16) PRIV_LAUNCH(1, 16); else PRIV_LAUNCH(1, 8); }
+            else { if (W == 16) PRIV_LAUNCH(2, 16); else PRIV_LAUNCH(2, 8); }
+#undef PRIV_LAUNCH
+            vq_cell_finish<<<(K + 7) / 8, 256, 0, s>>>(raas, cs.hist, K, D, L, packed);
+            return;
+        }
+    }
     const long stream_grid = n > 0 ? ((n + 4095) / 4096 < num_sms ? (n + 4095) / 4096 : num_sms) : 1;
     const long per_cta = (n + stream_grid - 1) / stream_grid;
     // measured on B200 (10M x P=36: 0.75 ms either way -- the CAS atomics cost what the gather

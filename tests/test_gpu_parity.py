@@ -436,6 +436,39 @@ def test_fused_small_codebook_pass_edges(built_lib, P):
                     assert np.allclose(out2["cells"], ref2["cells"], rtol=REL_TIGHT, atol=1e-9)
 
 
+@pytest.mark.parametrize("P", [12, 20, 36])
+def test_private_table_cell_sums_edges(built_lib, P):
+    """The streaming cell sums -- vq_cell_sums_private (rows of 16 .. 62 doubles: one table per warp, no
+    atomics, batches of 4 frames with independent chains when their cells differ) and
+    vq_cell_sums_stream (P = 12): tiles that end in the middle (N not a multiple of 64), a single
+    frame, runs of identical frames (batches that are NOT distinct), more CTAs than one, K that is not
+    a power of two and the largest tables that still take the variant -- cell sums, counts, cell
+    distortions and DD of add_to_cell (vq_learn.i:84-106) against the oracle."""
+    from ecoz2rs_b200.synth import ar_mix
+    from oracle import oracle as O
+    rng = np.random.default_rng(5 + P)
+    xall = ar_mix(40000, P, seed=91 + P)
+    xall[100:140] = xall[100]            # 40 identical frames in a row
+    xall[1001] = xall[1000]
+    for K, N in [(9, 1), (16, 7), (16, 17), (24, 1000), (32, 4099), (64, 40000), (256 if P == 12 else 100, 39993)]:
+        refl = np.zeros((K, P + 1))
+        refl[:, 1:] = np.clip(rng.normal(size=(K, P)) * 0.3, -0.9, 0.9)
+        raas = O.refl_to_raas(refl)
+        x = np.ascontiguousarray(xall[:N])
+        ref = O.kmeans_pass(x, refl, raas)
+        with _engine(P, max_M=256) as eng:
+            eng.set_frames(x)
+            eng.set_reflections(refl)
+            out = eng.kmeans_pass()
+            idx, _ = eng.last_assignment()
+        assert allowed_index_mismatches(idx, ref["idx"], ref["ddmin"], ref["second"]).size == 0, (K, N)
+        if np.array_equal(idx, ref["idx"]):
+            assert np.array_equal(out["cardd"], ref["cardd"]), (K, N)
+            assert np.allclose(out["cells"], ref["cells"], rtol=REL_TIGHT, atol=1e-9), (K, N)
+            assert np.allclose(out["discel"], ref["discel"], rtol=1e-7, atol=1e-9), (K, N)
+            assert abs(out["DD"] - ref["DD"]) <= REL_TIGHT * max(1.0, abs(ref["DD"])), (K, N)
+
+
 @pytest.mark.parametrize("K", [4, 16, 200], ids=["K4", "K16", "K200"])
 def test_inertia_as_written_with_negative_distortions(built_lib, K):
     """inertia.c:21-25 takes min_i (dd_i^2), which is NOT (min_i dd_i)^2 when a frame has negative
