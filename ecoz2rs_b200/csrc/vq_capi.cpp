@@ -825,4 +825,19 @@ int ecoz2b200_seq_save(const char *path, const char *cls, const uint16_t *seq, i
     return vqb200::seq_save(path, cls, seq, T, M) ? ECOZ2B200_ERR_IO : ECOZ2B200_OK;
 }
 
+int ecoz2b200_class_name_of(const char *path, char class_name[96]) {
+    if (!path || !class_name) return ECOZ2B200_ERR_ARG;
+    const std::string cls = vqb200::get_class_name(path);
+    memset(class_name, 0, 96);
+    memcpy(class_name, cls.data(), cls.size() < 95 ? cls.size() : 95);
+    return ECOZ2B200_OK;
+}
+int ecoz2b200_output_filename(const char *from, const char *base_dir, const char *ext, char *out, long capacity) {
+    if (!from || !base_dir || !ext || !out || capacity < 1) return ECOZ2B200_ERR_ARG;
+    const std::string name = vqb200::get_output_filename(from, base_dir, ext);
+    if ((long) name.size() + 1 > capacity) return ECOZ2B200_ERR_ARG;
+    memcpy(out, name.c_str(), name.size() + 1);
+    return ECOZ2B200_OK;
+}
+
 }  // extern "C"

@@ -73,7 +73,7 @@ EXPORTED_SYMBOLS = (
     "ecoz2b200_quantize_host", "ecoz2b200_quantize_resident", "ecoz2b200_quantize_models",
     "ecoz2b200_counters_reset", "ecoz2b200_counters_get", "ecoz2b200_ffma_peak_tflops",
     "ecoz2b200_prd_info", "ecoz2b200_prd_read", "ecoz2b200_cbook_save", "ecoz2b200_cbook_info",
-    "ecoz2b200_cbook_read", "ecoz2b200_seq_save",
+    "ecoz2b200_cbook_read", "ecoz2b200_seq_save", "ecoz2b200_class_name_of", "ecoz2b200_output_filename",
 )
 
 _lib = None
@@ -145,6 +145,8 @@ def lib():
             "ecoz2b200_cbook_info": (i, [C.c_char_p, C.POINTER(i), C.POINTER(i), C.c_char_p]),
             "ecoz2b200_cbook_read": (i, [C.c_char_p, _dp, l]),
             "ecoz2b200_seq_save": (i, [C.c_char_p, C.c_char_p, _up, i, i]),
+            "ecoz2b200_class_name_of": (i, [C.c_char_p, C.c_char_p]),
+            "ecoz2b200_output_filename": (i, [C.c_char_p, C.c_char_p, C.c_char_p, C.c_char_p, l]),
         }
         for name, (res, args) in sig.items():
             fn = getattr(L, name)

@@ -383,6 +383,16 @@ int ecoz2b200_cbook_read(const char *path, double *refl_out,
 int ecoz2b200_seq_save(const char *path, const char *class_name,
                        const uint16_t *seq, int T, int M);
 
+/* ---- path helpers (host only; what decides where `.cbook` / `.seq` files land) ------------- */
+/* class of a file = name of its parent directory, "" without one; reference get_class_name,
+ * ecoz2/src/utl/fileutil.c:14-30 (truncated to 95 characters like the 96-byte header field) */
+int ecoz2b200_class_name_of(const char *path, char class_name[96]);
+/* `data/<base_dir>/<class or "_">/<stem><ext>`, directories created under the current working
+ * directory; reference get_output_filename + camext, ecoz2/src/utl/fileutil.c:32-63, 97-119.
+ * Returns ECOZ2B200_ERR_ARG when `out` (capacity bytes) is too small. */
+int ecoz2b200_output_filename(const char *from, const char *base_dir, const char *ext,
+                              char *out, long capacity);
+
 #ifdef __cplusplus
 }
 #endif

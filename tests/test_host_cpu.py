@@ -121,6 +121,30 @@ def test_class_name_header_padding(tmp_path):
     assert len(raw) == 120 + 3 * 8
 
 
+def test_path_helpers_match_reference_fileutil(built_lib, tmp_path, monkeypatch):
+    """get_class_name / get_output_filename / camext (ecoz2/src/utl/fileutil.c:14-63, 97-119) decide
+    where every `.cbook` and `.seq` lands.  Golden outputs of the reference's own functions
+    (tests/golden/make_golden_paths.py through oracle/_ref): no parent directory, dots in directory
+    names (camext takes the LAST dot of the whole path), extensions shorter than two characters,
+    empty / dot-only new extensions, doubled slashes, class names longer than the 96-byte field --
+    and the directories the call creates."""
+    import json
+    L = built_lib
+    gold = json.load(open(os.path.join(os.path.dirname(__file__), "golden", "path_helpers.json")))
+    monkeypatch.chdir(tmp_path)
+    for path, want in gold["class_name"]:
+        buf = C.create_string_buffer(b"\xff" * 95, 96)
+        assert L.ecoz2b200_class_name_of(path.encode(), buf) == 0
+        assert buf.value.decode() == want, path
+    for path, base, ext, want, made in gold["output_filename"]:
+        out = C.create_string_buffer(4096)
+        assert L.ecoz2b200_output_filename(path.encode(), base.encode(), ext.encode(), out, 4096) == 0
+        assert out.value.decode() == want, (path, base, ext)
+        assert os.path.isdir(os.path.dirname(want)) == made, want
+    small = C.create_string_buffer(8)
+    assert L.ecoz2b200_output_filename(b"a/b/c.prd", b"sequences", b".seq", small, 8) != 0
+
+
 def test_min_dists_csv_writer_matches_printf(built_lib, tmp_path):
     """The parallel "<cbook>.min_dists.csv" writer reproduces fprintf("%d,%f\\n")
     of reference report.c:118-120 byte for byte: random magnitudes, exact ties of the 6th decimal
