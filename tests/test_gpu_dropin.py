@@ -75,7 +75,30 @@ def test_vq_learn_files_match_reference(built_lib, in_tmp_cwd, monkeypatch, tag,
     head = open(cdir / "eps_0.05.rpt.csv", encoding="utf-8").read().splitlines()[:2]
     ref_head = g["rpt_csv_text"].tobytes().decode("utf-8").splitlines()[:2]
     assert head == ref_head
-    assert (cdir / "eps_0.05.rpt").exists()
+    # the text report (report.c:14-75): the reference's own file for the same frames, token by token --
+    # words, paths, pass counts and cardinalities exact, "%f" values to the last printed digit,
+    # "%8.3g" cell distortions to their three digits; "(n empty cells)" / "_" would have to agree too
+    ours = open(cdir / "eps_0.05.rpt", encoding="utf-8").read().split("\n")
+    theirs = open(os.path.join(GOLD, f"learn_{tag}.rpt.txt"), encoding="utf-8").read().split("\n")
+    assert len(ours) == len(theirs)
+    for lo, lt in zip(ours, theirs):
+        to, tt = lo.split(), lt.split()
+        assert len(to) == len(tt), (lo, lt)
+        g3 = not lt.startswith("###") and "." in lt       # the line of %8.3g values
+        for a, b in zip(to, tt):
+            if a == b:
+                continue
+            fa, fb = float(a), float(b)                   # (a word that differs fails here)
+            if g3:
+                # (a cell of one frame sitting on its own codeword: rounding noise around 0 on both
+                # sides, 2.84e-14 against -2.84e-14 in this fixture)
+                assert abs(fa - fb) <= 1.01e-2 * abs(fb) + 1e-9, (lo, lt)
+            else:
+                assert "." in b and abs(fa - fb) <= 1e-7 * abs(fb) + 1.01e-6, (lo, lt)
+        assert lo.startswith("###") == lt.startswith("###")
+    # column layout of the "%8d " fields
+    card = lambda ls: [len(l) for l in ls if l.startswith(" ") and "." not in l]
+    assert card(ours) == card(theirs)
 
 
 def test_vq_learn_from_base_codebook_and_errors(built_lib, in_tmp_cwd, monkeypatch):
