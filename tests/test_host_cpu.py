@@ -121,6 +121,27 @@ def test_class_name_header_padding(tmp_path):
     assert len(raw) == 120 + 3 * 8
 
 
+def test_search_kernels_are_tcgen05_code(built_lib):
+    """The shipped library holds sm_100a machine code whose search kernels issue tcgen05 MMAs
+    (UTCHMMA), read their accumulators from tensor memory (LDTM), stage operands with bulk copies
+    (UBLKCP) and hand over through tensor-core barriers (UTCBAR) -- the mnemonics
+    /opt/skills/guides/B200_PROFILING.md names as the proof.  No GPU needed: cuobjdump reads the
+    .so the tests load."""
+    import shutil
+    import subprocess
+    from ecoz2rs_b200 import vq
+    exe = shutil.which("cuobjdump") or "/usr/local/cuda/bin/cuobjdump"
+    if not os.path.exists(exe):
+        pytest.skip("cuobjdump not installed")
+    elf = subprocess.run([exe, "-lelf", vq.LIB_PATH], capture_output=True, text=True, check=True).stdout
+    assert "sm_100a" in elf
+    sass = subprocess.run([exe, "-sass", "-fun", "vq_assign_tc2", vq.LIB_PATH], capture_output=True, text=True)
+    if sass.returncode != 0 or "UTCHMMA" not in sass.stdout:      # (-fun wants mangled names on some versions)
+        sass = subprocess.run([exe, "-sass", vq.LIB_PATH], capture_output=True, text=True, check=True)
+    for op in ("UTCHMMA", "LDTM", "UBLKCP", "UTCBAR"):
+        assert sass.stdout.count(op) > 0, op
+
+
 def test_path_helpers_match_reference_fileutil(built_lib, tmp_path, monkeypatch):
     """get_class_name / get_output_filename / camext (ecoz2/src/utl/fileutil.c:14-63, 97-119) decide
     where every `.cbook` and `.seq` lands.  Golden outputs of the reference's own functions
